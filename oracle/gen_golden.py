@@ -1,0 +1,300 @@
+"""Generate tests/golden/*.npz by RUNNING THE REFERENCE ITSELF (TEST INFRASTRUCTURE ONLY).
+
+Run in the build container only (needs /root/reference):  ``python -m oracle.gen_golden``
+
+What is produced
+----------------
+``mpn_<case>.npz``   The unmodified ``/root/reference/models/mpn.py`` ``MOTMPNet`` (random init, fixed
+                     seed) run on small ragged cross-camera graphs: weights (state_dict), inputs,
+                     every classified step's logits; for training cases also the loss of
+                     ``train.py:80-97`` (sum of BCE-with-logits over the classified steps) and every
+                     parameter gradient, and the BatchNorm buffers after the step.
+``graph_<case>.npz`` The reference's own graph-construction loop, i.e. the body of
+                     ``inference.validate_GNN_cross_camera_association`` (``inference.py:172-283``),
+                     executed UNMODIFIED on CPU: ``torch.Tensor.cuda`` is made the identity, a stub CNN
+                     returns prescribed embeddings, and a capturing stand-in for the MPN records the
+                     ``Batch`` it is handed (x, edge_index, edge_attr, edge_labels, y, ptr) and stops
+                     the loop.  Inputs are real ground-truth frames of EPFL-Terrace / EPFL-Laboratory
+                     (parsed by the rules of ``libs/datasets.py:89-134``) and synthetic frames.
+
+The vectors pin ``oracle/mpn_oracle.py`` and ``oracle/graph_oracle.py`` (tests/test_oracle_golden.py);
+the CUDA path is then compared with those oracles and with the vectors directly.
+"""
+from __future__ import annotations
+
+import copy
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import yaml
+
+from . import graph_oracle, ref_shim
+
+GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+REF = ref_shim.REFERENCE_ROOT
+
+
+# ----------------------------------------------------------------------------------------------
+# small ragged cross-camera graphs
+# ----------------------------------------------------------------------------------------------
+def ragged_frames(rng: np.random.Generator, n_frames: int, n_cams: int, max_ids: int, p_keep: float = 0.6):
+    """Frames with >= 2 cameras, camera-major row order like the reference's DataFrames."""
+    frames = []
+    while len(frames) < n_frames:
+        cam, ids, xw, yw = [], [], [], []
+        centers = rng.uniform([0, 0], [360, 288], size=(max_ids, 2))
+        for c in range(n_cams):
+            for i in range(max_ids):
+                if rng.random() < p_keep:
+                    cam.append(c); ids.append(i)
+                    p = centers[i] + rng.normal(0, 5, size=2)
+                    xw.append(p[0]); yw.append(p[1])
+        if len(set(cam)) < 2:
+            continue
+        frames.append(dict(id=np.asarray(ids, np.int64), id_cam=np.asarray(cam, np.int64),
+                           xw=np.asarray(xw, np.float64), yw=np.asarray(yw, np.float64),
+                           frame=np.full(len(ids), len(frames), np.int64)))
+    return frames
+
+
+def batch_edge_index(frames):
+    parts, first = [], 0
+    for fr in frames:
+        n = len(fr["id"])
+        parts.append(graph_oracle.enumerate_edges(fr["id_cam"], np.arange(first, first + n)))
+        first += n
+    return torch.cat(parts, dim=1), first
+
+
+# ----------------------------------------------------------------------------------------------
+# MPN cases
+# ----------------------------------------------------------------------------------------------
+def load_params(which: str) -> dict:
+    with open(os.path.join(REF, "config", which)) as f:
+        return yaml.safe_load(f)["GRAPH_NET_PARAMS"]
+
+
+def run_mpn_case(name, params, arch, seed, frames_kw, train=False, shuffle_edges=False, isolated=False,
+                 randomize_bn=False, edge_in_dim=None):
+    mpn = ref_shim.import_reference("models.mpn")
+    params = copy.deepcopy(params)
+    if edge_in_dim is not None:
+        params["encoder_feats_dict"]["edges"]["edge_in_dim"] = edge_in_dim
+    ctor_params = copy.deepcopy(params)
+    torch.manual_seed(seed)
+    model = mpn.MOTMPNet(copy.deepcopy(params), None, arch)
+    rng = np.random.default_rng(seed + 100)
+    frames = ragged_frames(rng, **frames_kw)
+    edge_index, n_nodes = batch_edge_index(frames)
+    if isolated:  # one extra node that is nobody's source and nobody's target
+        n_nodes += 1
+    if shuffle_edges:
+        perm = torch.from_numpy(rng.permutation(edge_index.size(1)))
+        edge_index = edge_index[:, perm].contiguous()
+    f_x = params["encoder_feats_dict"]["nodes"][arch]["node_in_dim"]
+    f_a = params["encoder_feats_dict"]["edges"]["edge_in_dim"]
+    g = torch.Generator().manual_seed(seed + 200)
+    x = torch.relu(torch.randn(n_nodes, f_x, generator=g))
+    x = x / x.norm(dim=0).clamp_min(1e-12)
+    edge_attr = torch.rand(edge_index.size(1), f_a, generator=g)
+    labels = (torch.rand(edge_index.size(1), generator=g) < 0.2).float()
+    if randomize_bn:
+        for m in model.modules():
+            if isinstance(m, torch.nn.BatchNorm1d):
+                m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.3)
+                m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.weight.data.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.bias.data.copy_(torch.randn(m.num_features, generator=g) * 0.2)
+    sd0 = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    data = graph_oracle.Data(x=x, edge_index=edge_index, edge_attr=edge_attr)
+    out = dict(config=json.dumps(ctor_params), arch=arch, train=int(train),
+               x=x.numpy(), edge_index=edge_index.numpy(), edge_attr=edge_attr.numpy(), labels=labels.numpy())
+    for k, v in sd0.items():
+        out["sd/" + k] = v.numpy()
+    if train:
+        model.train()
+        res = model(data)["classified_edges"]
+        crit = torch.nn.BCEWithLogitsLoss()
+        loss = sum(crit(r.view(-1), labels) for r in res)  # train.py:80-97
+        loss.backward()
+        out["loss"] = np.asarray(loss.item(), np.float64)
+        for k, p in model.named_parameters():
+            out["grad/" + k] = p.grad.numpy()
+        for k, v in model.state_dict().items():
+            if "running_" in k or "num_batches" in k:
+                out["sd_after/" + k] = v.detach().numpy()
+    else:
+        model.eval()
+        with torch.no_grad():
+            res = model(data)["classified_edges"]
+    for i, r in enumerate(res):
+        out["logits/%d" % i] = r.detach().numpy()
+    out["n_steps"] = np.asarray(len(res))
+    np.savez_compressed(os.path.join(GOLDEN, "mpn_%s.npz" % name), **out)
+    print("mpn_%s: N=%d E=%d steps=%d" % (name, n_nodes, edge_index.size(1), len(res)))
+
+
+def gen_mpn():
+    tr = load_params("config_training.yaml")      # no BN anywhere
+    inf = load_params("config_inference.yaml")    # classifier with BatchNorm
+    small = dict(n_frames=3, n_cams=4, max_ids=5)
+    run_mpn_case("shipped_resnet50_eval", tr, "resnet50", 0, dict(n_frames=2, n_cams=4, max_ids=6))
+    run_mpn_case("shipped_bdnet_train", tr, "bdnet_market", 1, small, train=True)
+    run_mpn_case("bncls_eval", inf, "bdnet_market", 2, small, randomize_bn=True)
+    run_mpn_case("bncls_train", inf, "bdnet_market", 3, small, train=True, randomize_bn=True)
+    p = copy.deepcopy(tr); p["node_agg_fn"] = "mean"
+    run_mpn_case("mean_isolated_eval", p, "osnet_market", 4, small, isolated=True)
+    run_mpn_case("mean_train", p, "osnet_market", 14, small, train=True)
+    p = copy.deepcopy(tr); p["node_agg_fn"] = "max"
+    run_mpn_case("max_isolated_eval", p, "osnet_market", 5, small, isolated=True)
+    run_mpn_case("max_train", p, "osnet_market", 15, small, train=True)
+    p = copy.deepcopy(tr); p["reattach_initial_nodes"] = True; p["reattach_initial_edges"] = True
+    run_mpn_case("reattach_eval", p, "bdnet_cuhk", 6, small)
+    run_mpn_case("reattach_train", p, "bdnet_cuhk", 16, small, train=True)
+    run_mpn_case("shuffled_eval", tr, "bdnet_market", 7, small, shuffle_edges=True, isolated=True)
+    run_mpn_case("shuffled_train", tr, "bdnet_market", 17, small, shuffle_edges=True, train=True)
+    run_mpn_case("onlydist_eval", tr, "bdnet_market", 8, small, edge_in_dim=2)  # main_training.py:153-158
+    p = copy.deepcopy(tr); p["num_enc_steps"] = 2; p["num_class_steps"] = 2
+    run_mpn_case("l2k2_eval", p, "bdnet_market", 9, small)
+    p = copy.deepcopy(tr); p["num_enc_steps"] = 0; p["num_class_steps"] = 0
+    run_mpn_case("l0_eval", p, "bdnet_market", 10, small)
+
+
+# ----------------------------------------------------------------------------------------------
+# graph-construction cases: drive the reference's own loop
+# ----------------------------------------------------------------------------------------------
+COLS = ("id", "xmin", "ymin", "xmax", "ymax", "frame", "lost", "occluded", "generated", "label")  # datasets.py:21
+
+
+def parse_gt(dataset: str):
+    """libs/datasets.py:53-134 restated (the class itself cannot run on current pandas/numpy)."""
+    import pandas as pd
+    root = os.path.join(REF, "datasets", dataset)
+    cams = sorted(c for c in os.listdir(root) if c[0] != ".")
+    parts = []
+    for c in cams:
+        df = pd.read_csv(os.path.join(root, c, "gt", "gt.txt"), header=None, sep=" ")
+        df = df[df.columns[:len(COLS)]]
+        df.columns = COLS
+        df = df[df["lost"] == 0].copy()
+        df["xmin"] = df["xmin"].values + 1
+        df["width"] = (df["xmax"] - df["xmin"]).values
+        df["height"] = (df["ymax"] - df["ymin"]).values
+        df["id_cam"] = int(c[-1:])
+        H = np.asarray(pd.read_csv(os.path.join(root, c, "Homography.txt"), header=None, sep="\t"))
+        bx = df["xmin"].values + np.round(df["width"].values / 2)
+        by = df["ymax"].values
+        xw, yw = graph_oracle.homography_image_to_world(bx, by, H)
+        df["xw"], df["yw"] = xw, yw
+        parts.append(df)
+    det = pd.concat(parts)  # == repeated DataFrame.append (datasets.py:122): camera-major row order
+    det["frame"] = det["frame"].values.astype(int)
+    return det
+
+
+def valid_frame(det, f) -> bool:  # datasets.py:126-134
+    sel = det[det["frame"].values == f]
+    if len(np.unique(sel["id_cam"].values)) > 1:
+        return bool(np.max(np.bincount(sel["id"].values)) > 1)
+    return False
+
+
+class _Captured(Exception):
+    pass
+
+
+def run_reference_loop(frames_df, max_dist, reid, node, mode):
+    """Execute inference.py:172-283 unmodified; return the Batch handed to the MPN."""
+    inference = ref_shim.import_reference("inference")
+    captured = {}
+
+    class CNN(torch.nn.Module):
+        def forward(self, _):
+            return node.clone(), reid.clone()
+
+    class Capture(torch.nn.Module):
+        def forward(self, batch):
+            captured["batch"] = batch
+            raise _Captured()
+
+    n_total = sum(len(d) for d in frames_df)
+    bboxes = [torch.zeros(len(d), 1) for d in frames_df]
+    loader = [[bboxes, [d.copy() for d in frames_df], list(max_dist)]]
+    cfg = {"CNN_MODEL": {"arch": "resnet50"},
+           "TRAINING": {"ONLY_APPEARANCE": mode == "only_appearance", "ONLY_DIST": mode == "only_dist"}}
+    assert n_total == reid.size(0)
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self  # the loop hard-codes .cuda(); identity on this CPU box
+    try:
+        inference.validate_GNN_cross_camera_association(cfg, loader, CNN(), Capture())
+    except _Captured:
+        pass
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    return captured["batch"]
+
+
+def save_graph_case(name, frames_df, max_dist, seed, mode="full", reid_dim=256, node_dim=64):
+    g = torch.Generator().manual_seed(seed)
+    n_total = sum(len(d) for d in frames_df)
+    reid = torch.relu(torch.randn(n_total, reid_dim, generator=g))
+    node = torch.relu(torch.randn(n_total, node_dim, generator=g))
+    b = run_reference_loop(frames_df, max_dist, reid, node, mode)
+    out = dict(mode=mode, max_dist=np.asarray(max_dist, np.float64), reid=reid.numpy(), node=node.numpy(),
+               graph_ptr=np.cumsum([0] + [len(d) for d in frames_df]).astype(np.int64),
+               id=np.concatenate([d["id"].values for d in frames_df]).astype(np.int64),
+               id_cam=np.concatenate([d["id_cam"].values for d in frames_df]).astype(np.int64),
+               xw=np.concatenate([d["xw"].values for d in frames_df]).astype(np.float64),
+               yw=np.concatenate([d["yw"].values for d in frames_df]).astype(np.float64),
+               out_x=b.x.numpy(), out_edge_index=b.edge_index.numpy(), out_edge_attr=b.edge_attr.numpy(),
+               out_edge_labels=b.edge_labels.numpy(), out_y=b.y.numpy(), out_ptr=b.ptr.numpy(),
+               out_batch=b.batch.numpy())
+    assert out["out_edge_index"].dtype == np.int64 and out["out_edge_attr"].dtype == np.float32
+    np.savez_compressed(os.path.join(GOLDEN, "graph_%s.npz" % name), **out)
+    print("graph_%s: B=%d N=%d E=%d mode=%s" % (name, len(frames_df), n_total, b.edge_index.size(1), mode))
+
+
+def gen_graph():
+    import pandas as pd
+    for dataset, md, picks in (("EPFL-Terrace", 50.83, None), ("EPFL-Laboratory", 44.23, None)):
+        det = parse_gt(dataset)
+        fmin, fmax = int(det["frame"].min()), int(det["frame"].max())
+        valid = [f for f in range(fmin, fmax + 1, 97) if valid_frame(det, f)]
+        # a spread of sizes: smallest, largest and a few in between
+        sizes = sorted(valid, key=lambda f: int((det["frame"].values == f).sum()))
+        chosen = sorted(set([sizes[0], sizes[len(sizes) // 4], sizes[len(sizes) // 2], sizes[-2], sizes[-1]]))
+        frames_df = [det[det["frame"] == f][["id", "id_cam", "xw", "yw", "frame"]] for f in chosen]
+        tag = dataset.split("-")[1].lower()
+        save_graph_case("%s_real" % tag, frames_df, [md] * len(frames_df), seed=11)
+        # also keep the raw table so the "next" row (GT parse + homography) can be pinned later
+        print("   frames", chosen, "sizes", [len(d) for d in frames_df])
+    rng = np.random.default_rng(5)
+    syn = ragged_frames(rng, n_frames=4, n_cams=4, max_ids=6)
+    to_df = lambda fr: pd.DataFrame({k: fr[k] for k in ("id", "id_cam", "xw", "yw", "frame")})
+    save_graph_case("synthetic_full", [to_df(f) for f in syn], [153.54] * 4, seed=12)
+    save_graph_case("synthetic_only_appearance", [to_df(f) for f in syn], [153.54] * 4, seed=13, mode="only_appearance")
+    save_graph_case("synthetic_only_dist", [to_df(f) for f in syn], [153.54] * 4, seed=14, mode="only_dist")
+    # camera ids not in row order (cameras interleaved): the enumeration is then camera-major, not row-major
+    mixed = []
+    for fr in ragged_frames(rng, n_frames=3, n_cams=3, max_ids=5):
+        perm = rng.permutation(len(fr["id"]))
+        mixed.append(to_df({k: fr[k][perm] for k in ("id", "id_cam", "xw", "yw", "frame")}))
+    save_graph_case("synthetic_interleaved_cams", mixed, [50.83] * 3, seed=15)
+    # full-occupancy Terrace-shaped frames (4 cams x 9), the BASELINE.json cfg-1 shape
+    full = ragged_frames(rng, n_frames=2, n_cams=4, max_ids=9, p_keep=1.1)
+    save_graph_case("synthetic_terrace_full", [to_df(f) for f in full], [50.83] * 2, seed=16)
+
+
+def main():
+    if not ref_shim.reference_available():
+        sys.exit("needs /root/reference (build container only)")
+    os.makedirs(GOLDEN, exist_ok=True)
+    gen_mpn()
+    gen_graph()
+
+
+if __name__ == "__main__":
+    main()
