@@ -1,0 +1,99 @@
+"""Cross-camera graph + edge-attribute construction on the device.
+
+The reference has no function for this: the code sits inline in its epoch loops (train.py:257-259,
+286-361,450; repeated at train.py:582-692 and inference.py:189-279).  ``build_graph_batch`` produces what
+those lines hand to the MPN -- a PyG-``Batch``-like object with ``x``, ``edge_index`` (int64, bit-exact),
+``edge_attr``, ``edge_labels``, ``y``, ``batch``, ``ptr`` -- from flat per-detection device tensors.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .plan import _stream
+
+
+class Batch:
+    """The attributes of ``torch_geometric.data.Batch`` that the reference reads
+    (train.py:454-458, inference.py:283-299)."""
+
+    def __init__(self, **kw):
+        for k, v in kw.items():
+            setattr(self, k, v)
+
+    @property
+    def num_nodes(self) -> int:
+        return int(self.x.size(0))
+
+    @property
+    def num_edges(self) -> int:
+        return int(self.edge_index.size(1))
+
+    def to(self, device):
+        return Batch(**{k: (v.to(device) if torch.is_tensor(v) else v) for k, v in self.__dict__.items()})
+
+
+def column_normalize(emb: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``F.normalize(emb, p=2, dim=0)`` (train.py:257-259): each feature COLUMN is divided by its L2 norm over
+    all detections of the batch (clamped at 1e-12)."""
+    lib = _lib.load()
+    if not emb.is_cuda or emb.dtype != torch.float32 or emb.dim() != 2:
+        raise ValueError("column_normalize expects a 2-D float32 CUDA tensor")
+    emb = emb.contiguous()
+    out = torch.empty_like(emb) if out is None else out
+    rows, cols = emb.shape
+    scratch = torch.empty(int(lib.gnncca_colnorm_scratch_bytes(rows, cols)) // 4 + 1, dtype=torch.float32, device=emb.device)
+    _lib.check(lib.gnncca_colnorm(_lib.ptr(emb), _lib.ptr(out), rows, cols, _lib.ptr(scratch), _stream()), "colnorm")
+    return out
+
+
+def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.Tensor, xw: torch.Tensor, yw: torch.Tensor,
+                      max_dist: torch.Tensor, reid_embeds: torch.Tensor, node_embeds: torch.Tensor, mode: str = "full",
+                      l2norm: bool = True) -> Batch:
+    """graph_ptr [B+1] int64 (detections of frame g are rows graph_ptr[g]:graph_ptr[g+1], in the row order of
+    the frame's table), id_cam [N] int, ids [N] int, xw/yw [N] float64 ground-plane coordinates, max_dist [B]
+    float64 (CONV_TO_M of the frame's dataset), reid_embeds [N,R] / node_embeds [N,F] float32 CNN outputs.
+    ``mode``: 'full' | 'only_appearance' | 'only_dist' (train.py:335-344); ``l2norm`` = CNN_MODEL.L2norm."""
+    lib = _lib.load()
+    dev = node_embeds.device
+    if dev.type != "cuda":
+        raise RuntimeError("gnn-cca_b200 builds graphs on CUDA tensors only (no CPU path)")
+    attr_mode = _lib.ATTR_MODES[mode]
+    graph_ptr = graph_ptr.to(device=dev, dtype=torch.int64).contiguous()
+    B, N = int(graph_ptr.numel()) - 1, int(node_embeds.size(0))
+    id_cam32 = id_cam.to(device=dev, dtype=torch.int32).contiguous()
+    ids64 = ids.to(device=dev, dtype=torch.int64).contiguous()
+    xw = xw.to(device=dev, dtype=torch.float64).contiguous()
+    yw = yw.to(device=dev, dtype=torch.float64).contiguous()
+    max_dist = max_dist.to(device=dev, dtype=torch.float64).contiguous()
+    if l2norm:
+        reid = column_normalize(reid_embeds)
+        x = column_normalize(node_embeds)
+    else:
+        reid, x = reid_embeds.contiguous(), node_embeds.contiguous()
+
+    nbytes = int(lib.gnncca_graph_prepare_scratch_bytes(B, N))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    edge_ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
+    _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
+                                            _lib.ptr(scratch), nbytes, _stream()), "graph_edge_counts")
+    # the output size is data dependent: one 16-byte read back (the reference syncs several times per FRAME)
+    tile_total_addr = lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N)
+    off = (tile_total_addr - scratch.data_ptr()) // 8
+    totals = torch.stack([edge_ptr[B], scratch.view(torch.int64)[off]]).cpu()
+    E, n_tiles = int(totals[0]), int(totals[1])
+
+    width = 4 if mode == "full" else 2
+    edge_index = torch.empty((2, E), dtype=torch.int64, device=dev)
+    edge_attr = torch.empty((E, width), dtype=torch.float32, device=dev)
+    edge_labels = torch.empty(E, dtype=torch.float32, device=dev)
+    _lib.check(lib.gnncca_build_graphs(_lib.ptr(graph_ptr), _lib.ptr(edge_ptr), B, N, E, n_tiles, _lib.ptr(id_cam32),
+                                       _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
+                                       int(reid.size(1)), attr_mode, _lib.ptr(scratch), _lib.ptr(edge_index),
+                                       _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
+    counts = graph_ptr[1:] - graph_ptr[:-1]
+    batch_vec = torch.repeat_interleave(torch.arange(B, device=dev), counts, output_size=N)
+    return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64, batch=batch_vec,
+                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B)

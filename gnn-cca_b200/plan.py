@@ -1,0 +1,77 @@
+"""Source-sorted int32 CSR of a batched graph, built on the device once per forward
+(replaces the implicit ``x[row]`` / ``x[col]`` / ``scatter(..., row)`` index handling of models/mpn.py:44-99)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class GraphPlan:
+    """rowptr[N+1], src[E], dst[E] (int32, source-sorted) and, when the caller's edge order is not
+    source-major, ``perm`` (sorted position -> original edge id)."""
+
+    def __init__(self, edge_index: torch.Tensor, num_nodes: int):
+        if edge_index.dim() != 2 or edge_index.size(0) != 2 or edge_index.dtype != torch.int64:
+            raise ValueError("edge_index must be an int64 tensor of shape [2, E]")
+        if not edge_index.is_cuda:
+            raise RuntimeError("gnn-cca_b200 runs on CUDA tensors only (no CPU path)")
+        self.lib = _lib.load()
+        self.edge_index = edge_index.contiguous()
+        self.N, self.E = int(num_nodes), int(edge_index.size(1))
+        dev = edge_index.device
+        self.src = torch.empty(self.E, dtype=torch.int32, device=dev)
+        self.dst = torch.empty(self.E, dtype=torch.int32, device=dev)
+        self.rowptr = torch.empty(self.N + 1, dtype=torch.int32, device=dev)
+        self.flags = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, device=dev)
+        self.perm: Optional[torch.Tensor] = None
+        self._flags_host = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, pin_memory=True)
+        self._event = torch.cuda.Event()
+        self._resolved = False
+        _lib.check(self.lib.gnncca_csr_from_edge_index(_lib.ptr(self.edge_index), self.N, self.E, _lib.ptr(self.src),
+                                                       _lib.ptr(self.dst), _lib.ptr(self.rowptr), _lib.ptr(self.flags),
+                                                       _stream()), "csr_from_edge_index")
+        self._flags_host.copy_(self.flags, non_blocking=True)
+        self._event.record()
+
+    def resolve(self) -> "GraphPlan":
+        """Wait for the order / range flags (a 16-byte read that overlaps the node encoder) and run the
+        stable sort when the edges are not source-major."""
+        if self._resolved:
+            return self
+        self._event.synchronize()
+        unsorted, bad = int(self._flags_host[0]), int(self._flags_host[1])
+        if bad:
+            raise IndexError("edge_index has entries outside [0, num_nodes=%d)" % self.N)
+        if unsorted:
+            dev = self.src.device
+            self.perm = torch.empty(self.E, dtype=torch.int32, device=dev)
+            nbytes = int(self.lib.gnncca_csr_sort_workspace_bytes(self.N, self.E))
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            _lib.check(self.lib.gnncca_csr_sort(self.N, self.E, _lib.ptr(self.src), _lib.ptr(self.dst), _lib.ptr(self.perm),
+                                                _lib.ptr(self.rowptr), _lib.ptr(ws), nbytes, _stream()), "csr_sort")
+        self._resolved = True
+        return self
+
+    # edge-row permutations between the caller's order and the sorted order
+    def to_sorted(self, rows: torch.Tensor) -> torch.Tensor:
+        if self.perm is None:
+            return rows
+        out = torch.empty_like(rows)
+        _lib.check(self.lib.gnncca_permute_rows(_lib.ptr(rows), _lib.ptr(out), _lib.ptr(self.perm), rows.size(0),
+                                                rows.size(1), 0, _stream()), "permute_rows")
+        return out
+
+    def to_caller(self, rows: torch.Tensor) -> torch.Tensor:
+        if self.perm is None:
+            return rows
+        out = torch.empty_like(rows)
+        _lib.check(self.lib.gnncca_permute_rows(_lib.ptr(rows), _lib.ptr(out), _lib.ptr(self.perm), rows.size(0),
+                                                rows.size(1), 1, _stream()), "permute_rows")
+        return out

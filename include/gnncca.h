@@ -1,0 +1,189 @@
+/*
+ * gnncca.h -- C ABI of libgnncca.so: the sm_100a kernels behind the GNN-CCA message-passing hot path.
+ *
+ * The reference (vpulab/GNN-CCA @ 98cbbae4) is pure Python and has no FFI layer; the boundary this
+ * library sits behind is the nn.Module API of models/mpn.py:MOTMPNet.  Every
+ * entry point below replaces the eager PyTorch / torch_scatter / PyG call sequence cited beside it.
+ * The Python mirror of the reference module (gnn-cca_b200/mpn.py) binds these with ctypes; the stub a
+ * reference maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; tensors are dense row-major;
+ *   - float = IEEE fp32, indices as stated (int64 at the module boundary like torch, int32 inside);
+ *   - `stream` is a cudaStream_t passed as void*; entries never synchronise, never allocate, never
+ *     free and keep no pointer after returning (the caller owns all memory, SURVEY 8b "ownership");
+ *   - every entry returns 0 on success or a negative gnncca_status; gnncca_status_string() names it;
+ *   - entries are reentrant and CUDA-graph capturable (no host reads of device memory).
+ *   - weights use torch.nn.Linear layout: W[out][in] row-major, bias[out].
+ */
+#ifndef GNNCCA_H_
+#define GNNCCA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNNCCA_ABI_VERSION 1
+#pragma GCC visibility push(default)
+
+typedef enum {
+  GNNCCA_OK = 0,
+  GNNCCA_ERR_BAD_ARG = -1,       /* null pointer, negative size, misaligned buffer               */
+  GNNCCA_ERR_UNSUPPORTED = -2,   /* a configuration this build has no kernel for (never a fallback) */
+  GNNCCA_ERR_LAUNCH = -3,        /* cudaGetLastError() != cudaSuccess after a launch                */
+  GNNCCA_ERR_WORKSPACE = -4      /* workspace too small                                             */
+} gnncca_status;
+
+enum { GNNCCA_AGG_SUM = 0, GNNCCA_AGG_MEAN = 1, GNNCCA_AGG_MAX = 2 };   /* models/mpn.py:192-202 */
+enum { GNNCCA_MATH_FP32 = 0, GNNCCA_MATH_TF32 = 1 };                      /* FFMA vs tcgen05 kind::tf32 */
+enum { GNNCCA_ATTR_FULL = 0, GNNCCA_ATTR_ONLY_APPEARANCE = 1, GNNCCA_ATTR_ONLY_DIST = 2 }; /* train.py:335-344 */
+
+int gnncca_abi_version(void);
+const char* gnncca_status_string(int status);
+/* Text of the last CUDA error seen by this thread inside the library ("" if none). */
+const char* gnncca_last_cuda_error(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * CSR / index work (bit-exact).  Replaces the implicit indexing of x[row], x[col] and the
+ * torch_scatter index handling (models/mpn.py:44,48,97-99).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* flags[] written by gnncca_csr_from_edge_index (int32 x 4, device; the entry zeroes them first):
+ *   [0] 1 if edge_index[0] is NOT non-decreasing (0 = source-major, what train.py:292-299 produces
+ *         for camera-major frames);  [1] 1 if any index is outside [0, n_nodes);  [2],[3] reserved. */
+#define GNNCCA_CSR_NFLAGS 4
+
+/* Narrow edge_index [2,E] int64 to src[E], dst[E] int32, detect ordering / range, and -- when the
+ * rows are non-decreasing -- fill rowptr[n_nodes+1] by boundary detection.  When flags[0]==1 the
+ * caller must run gnncca_csr_sort next (rowptr is then unspecified). */
+int gnncca_csr_from_edge_index(const int64_t* edge_index, int64_t n_nodes, int64_t n_edges,
+                               int32_t* src, int32_t* dst, int32_t* rowptr, int32_t* flags, void* stream);
+
+/* Bytes of scratch gnncca_csr_sort needs. */
+int64_t gnncca_csr_sort_workspace_bytes(int64_t n_nodes, int64_t n_edges);
+
+/* Stable sort of the edges by source: perm[E] (sorted position -> original edge id), src/dst rewritten
+ * in sorted order, rowptr filled.  Deterministic (stable LSD radix sort). */
+int gnncca_csr_sort(int64_t n_nodes, int64_t n_edges, int32_t* src, int32_t* dst, int32_t* perm,
+                    int32_t* rowptr, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* out[i, :] = in[perm[i], :]  (gather) or out[perm[i], :] = in[i, :] (scatter), rows of `width` floats. */
+int gnncca_permute_rows(const float* in, float* out, const int32_t* perm, int64_t n_rows, int32_t width,
+                        int32_t scatter, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Dense layers of models/mlp.py:12-23 (Linear [+BatchNorm1d eval] [+ReLU]) on row blocks.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* y[rows,out] = act( x[rows,in] @ W^T + b ), act = ReLU iff relu != 0.  BatchNorm1d in eval mode is
+ * folded when bn_weight != NULL: y = act( (z - mean) / sqrt(var + eps) * gamma + beta ).
+ * math: GNNCCA_MATH_FP32 (FFMA) or GNNCCA_MATH_TF32 (tcgen05, needs in % 32 == 0, out % 16 == 0,
+ * out <= 256; `tmap_workspace` must then point to 256 bytes of 64B-aligned device scratch or be NULL
+ * to let the library encode descriptors on the host side). */
+int gnncca_linear(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
+                  int32_t out_dim, int32_t relu, const float* bn_weight, const float* bn_bias,
+                  const float* bn_mean, const float* bn_var, float bn_eps, int32_t math, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * One message-passing step, models/mpn.py:32-54 (MetaLayer) = EdgeModel :67-69 + NodeModel :97-101
+ * + the classifier of mpn.py:290-293, fused.
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct {
+  int32_t f_node;          /* latent node width  (encoder node_out_dim, 32)                      */
+  int32_t f_edge;          /* latent edge width  (encoder edge_out_dim, 6)                        */
+  int32_t cls_hidden;      /* classifier hidden width (classifier edge_fc_dims[0], 4); 0 = none  */
+  int32_t agg;             /* GNNCCA_AGG_*                                                        */
+  int32_t reattach_nodes;  /* mpn.py:284-285                                                      */
+  int32_t reattach_edges;  /* mpn.py:282-283                                                      */
+  int32_t math;            /* GNNCCA_MATH_*: how the 6->32 message product is computed            */
+  int32_t reserved;
+} gnncca_mp_cfg;
+
+/* Weights of one step, all device pointers into the caller's parameters (read at every call, so
+ * in-place optimiser updates are seen).  Shapes for reattach off / on:
+ *   w_edge  [f_edge][2*nf*f_node + ef*f_edge]   MPNet.edge_model.edge_mlp.fc_layers.0.weight
+ *   b_edge  [f_edge]
+ *   w_node  [f_node][nf*f_node + f_edge]        MPNet.node_model.node_mlp.fc_layers.0.weight
+ *   b_node  [f_node]
+ *   classifier (NULL when the step is not classified): w_c1 [cls_hidden][f_edge], b_c1, optional
+ *   BatchNorm1d eval parameters (bn_* NULL when absent), w_c2 [1][cls_hidden], b_c2 [1].          */
+typedef struct {
+  const float* w_edge; const float* b_edge;
+  const float* w_node; const float* b_node;
+  const float* w_c1; const float* b_c1;
+  const float* bn_weight; const float* bn_bias; const float* bn_mean; const float* bn_var;
+  const float* w_c2; const float* b_c2;
+  float bn_eps; int32_t pad_;
+} gnncca_mp_weights;
+
+/* Per-node projections that make the step HBM-bound (SURVEY 7.3 "weight splitting"):
+ *   P[v] = W_edge[:, src block] h[v] + b_edge   (padded to 8 floats per node)
+ *   Q[v] = W_edge[:, dst block] h[v]            (padded to 8 floats per node)
+ *   R[v] = W_node[:, node block] h[v] + b_node  (f_node floats per node)
+ * h0 is the encoder output (only read when reattach_nodes), h the current node latent. */
+int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* h0, const float* h,
+                        int64_t n_nodes, float* P, float* Q, float* R, void* stream);
+
+int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes, int64_t n_edges);
+
+/* e_out[i]   = ReLU( P[src[i]] + Q[dst[i]] + W_edge[:, edge block] [e0[i],] e_in[i] )   (mpn.py:48,68-69)
+ * h_out[v]   = agg_{i : src[i]==v} ReLU( R[v] + W_node[:, edge block] e_out[i] )        (mpn.py:97-99)
+ * logits[i]  = classifier(e_out[i])  if logits != NULL                                  (mpn.py:290-293)
+ * Edges must be source-sorted (rowptr consistent with src).  Deterministic: no floating-point atomics;
+ * segments that span tiles are combined in tile order by the last tile to arrive.
+ * e_out may alias e_in.  h_out may be NULL (last step: the node update is dead, mpn.py:288-299).
+ * cls_stats (training-mode classifier BatchNorm): when non-NULL, logits are NOT written; instead
+ * per-tile partial sums of the classifier's hidden pre-activation are written for
+ * gnncca_cls_bn_finalize. */
+int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
+                       const int32_t* rowptr, const int32_t* src, const int32_t* dst,
+                       int64_t n_nodes, int64_t n_edges,
+                       const float* P, const float* Q, const float* R,
+                       const float* e0, const float* e_in, float* e_out, float* h_out, float* logits,
+                       void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Independent per-edge MLP chain (MLPGraphIndependent edge branch, mpn.py:128-142): encoder edge MLP
+ * (4 -> 6 + ReLU) and, stand-alone, the classifier.  Up to 4 layers, widths <= 32.
+ * dims[0..n_layers] are the layer widths, W[l]/b[l] the torch weights, relu[l] per layer. */
+int gnncca_edge_mlp(const float* x, float* y, int64_t n_rows, int32_t n_layers, const int32_t* host_dims,
+                    const float* const* host_W, const float* const* host_b, const int32_t* host_relu, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Graph + edge-attribute construction, train.py:257-259,286-361,450.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* F.normalize(emb, p=2, dim=0): every COLUMN divided by max(||column||_2, 1e-12)  (train.py:257-259).
+ * Deterministic two-pass reduction; scratch of gnncca_colnorm_scratch_bytes(). In place allowed. */
+int64_t gnncca_colnorm_scratch_bytes(int64_t rows, int32_t cols);
+int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, float* scratch, void* stream);
+
+/* Step 1 of graph construction.  graph_ptr[B+1] int64 node offsets of the frames, id_cam[N] int32 camera id
+ * per detection (row order of the frame's table).  Writes edge_ptr[B+1] (int64 exclusive scan of the
+ * per-frame directed edge counts n_g^2 - sum_c n_{g,c}^2) and fills `scratch`
+ * (gnncca_graph_prepare_scratch_bytes) with the per-detection enumeration tables step 2 needs.
+ * The caller reads edge_ptr[B] (= E) and *gnncca_graph_tile_total_ptr() (= n_tiles) to size step 2. */
+int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes);
+int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t* id_cam, int64_t n_graphs, int64_t n_nodes,
+                             int64_t* edge_ptr, void* scratch, int64_t scratch_bytes, void* stream);
+const int64_t* gnncca_graph_tile_total_ptr(const void* scratch, int64_t n_graphs, int64_t n_nodes);
+
+/* Step 2: fill edge_index [2,E] int64 (frame-rebased ids + running node offset, i.e. exactly what
+ * train.py:356 + Batch.from_data_list :450 yield), edge_attr [E, 4 or 2] fp32 in the reference's
+ * column order (L2/max_dist, L1/max_dist computed in float64 then cast; ||a-b+1e-6||_2; cosine), and
+ * edge_labels [E] fp32 (train.py:348-351).  Enumeration order = train.py:292-299: cameras ascending,
+ * sources of the camera in row order, targets (all other cameras) in row order.  reid [N,reid_dim] is
+ * the (already column-normalised) appearance embedding; ids int64, xw/yw/max_dist float64. */
+int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64_t n_graphs, int64_t n_nodes,
+                        int64_t n_edges, int64_t n_tiles, const int32_t* id_cam, const int64_t* ids, const double* xw,
+                        const double* yw, const double* max_dist, const float* reid, int32_t reid_dim,
+                        int32_t attr_mode, const void* scratch, int64_t* edge_index, float* edge_attr,
+                        float* edge_labels, void* stream);
+
+#pragma GCC visibility pop
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNNCCA_H_ */

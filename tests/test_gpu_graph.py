@@ -1,0 +1,77 @@
+"""GPU parity of graph construction + CSR against vectors produced by the reference's own loop."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_cases, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", golden_cases("graph_"))
+def test_build_graph_batch_matches_reference_loop(case, cuda_device):
+    import gnncca
+    z = load_golden("graph_" + case)
+    t = lambda k, dt=None: torch.from_numpy(z[k]).to(cuda_device) if dt is None else torch.from_numpy(z[k]).to(cuda_device, dt)
+    b = gnncca.build_graph_batch(t("graph_ptr"), t("id_cam"), t("id"), t("xw"), t("yw"), t("max_dist"), t("reid"), t("node"),
+                                 mode=str(z["mode"]), l2norm=True)
+    assert b.edge_index.dtype == torch.int64
+    assert np.array_equal(b.edge_index.cpu().numpy(), z["out_edge_index"])       # bit-exact
+    assert np.array_equal(b.edge_labels.cpu().numpy(), z["out_edge_labels"])     # bit-exact
+    assert np.array_equal(b.y.cpu().numpy(), z["out_y"])
+    assert np.array_equal(b.ptr.cpu().numpy(), z["out_ptr"])
+    assert np.array_equal(b.batch.cpu().numpy(), z["out_batch"])
+    # floats: column-normalised embeddings and the four attributes, fp32 tolerance
+    np.testing.assert_allclose(b.x.cpu().numpy(), z["out_x"], rtol=2e-6, atol=1e-9)
+    np.testing.assert_allclose(b.edge_attr.cpu().numpy(), z["out_edge_attr"], rtol=1e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("sorted_rows", [True, False])
+def test_csr_is_bit_exact(sorted_rows, cuda_device):
+    import gnncca
+    rng = np.random.default_rng(7)
+    N, E = 1000, 20000
+    row = rng.integers(0, N, E)
+    row[row == 17] = 18            # node 17 has no out-edge
+    if sorted_rows:
+        row = np.sort(row)
+    col = rng.integers(0, N, E)
+    ei = torch.from_numpy(np.stack([row, col])).to(cuda_device)
+    plan = gnncca.GraphPlan(ei, N).resolve()
+    order = np.argsort(row, kind="stable")
+    assert (plan.perm is None) == sorted_rows
+    if not sorted_rows:
+        assert np.array_equal(plan.perm.cpu().numpy(), order)
+    assert np.array_equal(plan.src.cpu().numpy(), row[order])
+    assert np.array_equal(plan.dst.cpu().numpy(), col[order])
+    rp = np.concatenate([[0], np.cumsum(np.bincount(row, minlength=N))])
+    assert np.array_equal(plan.rowptr.cpu().numpy(), rp)
+
+
+def test_csr_rejects_out_of_range(cuda_device):
+    import gnncca
+    ei = torch.tensor([[0, 1, 2], [1, 2, 5]], device=cuda_device)
+    with pytest.raises(IndexError):
+        gnncca.GraphPlan(ei, 3).resolve()
+
+
+def test_full_size_properties_cfg2(cuda_device):
+    """BASELINE cfg 2 (4 cams x 6, 1024 frames) at full size through size-independent properties:
+    edge count closed form, source-major order, both directions present, labels symmetric."""
+    import gnncca
+    from importlib import import_module
+    syn = import_module("gnn-cca_b200.synthetic")
+    det = syn.make_detections(4, 6, 1024, seed=1236, device=cuda_device, node_dim=64, max_dist=44.23)
+    b = gnncca.build_graph_batch(**det)
+    E = 1024 * syn.edges_per_graph(4, 6)
+    assert b.num_edges == E == 442368
+    src, dst = b.edge_index[0], b.edge_index[1]
+    assert bool((src[1:] >= src[:-1]).all())
+    assert bool((det["id_cam"][src] != det["id_cam"][dst]).all())
+    key = src * b.num_nodes + dst
+    rkey = dst * b.num_nodes + src
+    assert torch.equal(torch.sort(key).values, torch.sort(rkey).values)        # every edge has its reverse
+    lab = b.edge_labels
+    assert torch.equal(lab, (det["ids"][src] == det["ids"][dst]).float())
+    assert abs(float(lab.mean()) - 3 / 18) < 1e-6                              # C-1 positives per node
+    assert bool((b.edge_attr[:, :3] >= 0).all()) and bool((b.edge_attr[:, 3].abs() <= 1 + 1e-5).all())

@@ -1,0 +1,132 @@
+"""GPU parity of the CUDA MPN against vectors produced by the reference and against the CPU oracle."""
+import copy
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_cases, load_golden
+from oracle import mpn_oracle
+
+pytestmark = pytest.mark.gpu
+
+FP32_RTOL = 1e-4   # |got - ref| <= 1e-4 * (1 + |ref|)  (SURVEY 8c, FP32-FMA kernels)
+
+
+def close(got, ref, tol=FP32_RTOL):
+    got, ref = got.detach().cpu().double(), ref.detach().cpu().double()
+    err = (got - ref).abs() / (1 + ref.abs())
+    return float(err.max()) if err.numel() else 0.0
+
+
+def build_model(z, device, math="fp32"):
+    import gnncca
+    params = json.loads(str(z["config"]))
+    m = gnncca.MOTMPNet(copy.deepcopy(params), None, str(z["arch"]), math=math)
+    sd = {k[3:]: torch.from_numpy(v) for k, v in z.items() if k.startswith("sd/")}
+    m.load_state_dict(sd, strict=True)
+    return m.to(device)
+
+
+class D:
+    def __init__(self, x, ei, ea):
+        self.x, self.edge_index, self.edge_attr = x, ei, ea
+
+
+@pytest.mark.parametrize("case", [c for c in golden_cases("mpn_") if c.endswith("_eval")])
+def test_forward_matches_reference_vectors(case, cuda_device):
+    z = load_golden("mpn_" + case)
+    model = build_model(z, cuda_device).eval()
+    data = D(torch.from_numpy(z["x"]).to(cuda_device), torch.from_numpy(z["edge_index"]).to(cuda_device),
+             torch.from_numpy(z["edge_attr"]).to(cuda_device))
+    with torch.no_grad():
+        out = model(data)["classified_edges"]
+    assert len(out) == int(z["n_steps"])
+    for i, o in enumerate(out):
+        ref = torch.from_numpy(z["logits/%d" % i])
+        assert o.shape == ref.shape and o.dtype == torch.float32 and o.is_cuda
+        assert close(o, ref) <= FP32_RTOL, (case, i, close(o, ref))
+
+
+def synthetic_graph(n_cams, n_dets, n_graphs, seed, f_x=512, ragged=0.0):
+    rng = np.random.default_rng(seed)
+    parts, first = [], 0
+    for _ in range(n_graphs):
+        cam = np.repeat(np.arange(n_cams), n_dets)
+        if ragged > 0:
+            keep = rng.random(cam.size) > ragged
+            if len(set(cam[keep])) < 2:
+                keep[:] = True
+            cam = cam[keep]
+        i, j = np.nonzero(cam[:, None] != cam[None, :])
+        parts.append(np.stack([i + first, j + first]))
+        first += cam.size
+    ei = torch.from_numpy(np.concatenate(parts, axis=1)).long()
+    g = torch.Generator().manual_seed(seed)
+    x = torch.relu(torch.randn(first, f_x, generator=g))
+    x = x / x.norm(dim=0).clamp_min(1e-12)
+    ea = torch.rand(ei.size(1), 4, generator=g)
+    return x, ei, ea
+
+
+@pytest.mark.parametrize("shape", [(4, 9, 64, 0.0), (4, 6, 200, 0.47), (8, 64, 2, 0.0), (3, 300, 1, 0.0), (2, 1, 5, 0.0)])
+@pytest.mark.parametrize("agg", ["sum", "mean", "max"])
+def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, cuda_device):
+    """cfg-1 shape, ragged EPFL-like frames, the cfg-4 per-graph shape (degree 448: segments span tiles and
+    warps), a degree-600 graph (segments span 3 tiles) and degenerate 2-node frames."""
+    import gnncca
+    from importlib import import_module
+    cfgmod = import_module("gnn-cca_b200.config")
+    if agg != "sum" and shape[2] > 100:
+        pytest.skip("covered by the sum variant")
+    params = cfgmod.graph_net_params()
+    params["node_agg_fn"] = agg
+    torch.manual_seed(0)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    spec = mpn_oracle.MPNSpec(params, "bdnet_market")
+    x, ei, ea = synthetic_graph(*shape[:3], seed=42, ragged=shape[3])
+    with torch.no_grad():
+        ref, ref_lat = mpn_oracle.motmpnet_forward(spec, model.state_dict(), x, ei, ea, return_latents=True)
+    model = model.to(cuda_device)
+    from importlib import import_module
+    engine = import_module("gnn-cca_b200.engine")
+    with torch.no_grad():
+        outs, lat, _ = engine.forward_inference(model, x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device), return_latents=True)
+    for step, ((h, e), (rh, re)) in enumerate(zip(lat, ref_lat)):
+        assert close(e, re) <= FP32_RTOL, ("edge latent", step, close(e, re))
+        assert close(h, rh) <= FP32_RTOL, ("node latent", step, close(h, rh))
+    for o, r in zip(outs, ref["classified_edges"]):
+        assert close(o, r) <= FP32_RTOL
+    # decisions agree wherever the reference is not within tolerance of the threshold
+    last, rlast = outs[-1].cpu().view(-1), ref["classified_edges"][-1].view(-1)
+    sure = rlast.abs() > 1e-3
+    assert torch.equal((last[sure] >= 0), (rlast[sure] >= 0))
+
+
+def test_forward_is_bit_reproducible(cuda_device):
+    """The segmented reduction has no floating-point atomics: 20 runs give identical bits."""
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(1)
+    model = gnncca.MOTMPNet(params, None, "bdnet_market").to(cuda_device).eval()
+    x, ei, ea = synthetic_graph(8, 40, 3, seed=3)
+    data = D(x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device))
+    with torch.no_grad():
+        first = [o.clone() for o in model(data)["classified_edges"]]
+        for _ in range(20):
+            again = model(data)["classified_edges"]
+            for a, b in zip(first, again):
+                assert torch.equal(a, b)
+
+
+def test_cpu_tensors_fail_loudly():
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    model = gnncca.MOTMPNet(params, None, "bdnet_market").eval()
+    x, ei, ea = synthetic_graph(2, 2, 1, seed=0)
+    with pytest.raises(RuntimeError):
+        with torch.no_grad():
+            model(D(x, ei, ea))
