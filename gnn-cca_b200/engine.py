@@ -107,7 +107,7 @@ def check_supported(model) -> None:
         raise NotImplementedError("fused step: BatchNorm inside the edge/node update MLPs is not implemented")
     if not em.layer_specs[0].relu or not nm.layer_specs[0].relu:
         raise NotImplementedError("fused step: width-1 update MLPs (no ReLU) are not implemented")
-    cs = cls.layer_specs
+    cs = cls.edge_mlp.layer_specs
     if len(cs) != 2 or cs[0].in_dim != f_edge or cs[1].out_dim != 1:
         raise NotImplementedError("fused step: classifier must be edge_in_dim=f_edge, one hidden layer, edge_out_dim=1")
     if (f_node, f_edge, cs[0].out_dim) != (32, 6, 4):

@@ -75,14 +75,15 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
         reid, x = reid_embeds.contiguous(), node_embeds.contiguous()
 
     nbytes = int(lib.gnncca_graph_prepare_scratch_bytes(B, N))
-    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    scratch = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
+    nbytes = scratch.numel() * 8
     edge_ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
     _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
                                             _lib.ptr(scratch), nbytes, _stream()), "graph_edge_counts")
     # the output size is data dependent: one 16-byte read back (the reference syncs several times per FRAME)
     tile_total_addr = lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N)
     off = (tile_total_addr - scratch.data_ptr()) // 8
-    totals = torch.stack([edge_ptr[B], scratch.view(torch.int64)[off]]).cpu()
+    totals = torch.stack([edge_ptr[B], scratch[off]]).cpu()
     E, n_tiles = int(totals[0]), int(totals[1])
 
     width = 4 if mode == "full" else 2
