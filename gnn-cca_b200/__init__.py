@@ -8,5 +8,6 @@ from .mpn import MOTMPNet, MetaLayer, EdgeModel, NodeModel, MLPGraphIndependent
 from .plan import GraphPlan
 from .graph import Batch, build_graph_batch, column_normalize
 from . import _lib
+from .engine import forward_host, StageTimer
 
-__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize"]
+__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer"]

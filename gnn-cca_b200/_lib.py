@@ -35,6 +35,7 @@ SIGNATURES = {
     "gnncca_abi_version": (C.c_int, []),
     "gnncca_status_string": (C.c_char_p, [C.c_int]),
     "gnncca_last_cuda_error": (C.c_char_p, []),
+    "gnncca_launch_count": (i64, []),
     "gnncca_csr_from_edge_index": (C.c_int, [vp, i64, i64, vp, vp, vp, vp, vp]),
     "gnncca_csr_sort_workspace_bytes": (i64, [i64, i64]),
     "gnncca_csr_sort": (C.c_int, [i64, i64, vp, vp, vp, vp, vp, i64, vp]),
@@ -43,7 +44,7 @@ SIGNATURES = {
     "gnncca_node_project": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp]),
     "gnncca_mp_step_workspace_bytes": (i64, [C.POINTER(MpCfg), i64, i64]),
     "gnncca_mp_step_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, i64, i64, vp, vp, vp, vp, vp,
-                                     vp, vp, vp, vp, i64, vp]),
+                                     vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_edge_mlp": (C.c_int, [vp, vp, i64, i32, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32), vp]),
     "gnncca_colnorm_scratch_bytes": (i64, [i64, i32]),
     "gnncca_colnorm": (C.c_int, [vp, vp, i64, i32, vp, vp]),

@@ -1,5 +1,6 @@
 // Version / status plumbing of the C ABI (include/gnncca.h).
 #include <string.h>
+#include <atomic>
 #include "common.cuh"
 
 namespace gnncca {
@@ -8,7 +9,11 @@ void set_cuda_error(cudaError_t e) {
   strncpy(g_last_error, cudaGetErrorString(e), sizeof(g_last_error) - 1);
   g_last_error[sizeof(g_last_error) - 1] = 0;
 }
+static std::atomic<long long> g_launches{0};
+void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 }  // namespace gnncca
+
+extern "C" int64_t gnncca_launch_count(void) { return (int64_t)gnncca::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int gnncca_abi_version(void) { return GNNCCA_ABI_VERSION; }
 

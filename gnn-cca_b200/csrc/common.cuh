@@ -7,10 +7,12 @@
 namespace gnncca {
 
 void set_cuda_error(cudaError_t e);   // thread-local last CUDA error text (abi.cu)
+void count_launches(int n);           // process-wide count of kernels this library launched (abi.cu)
 
-inline int check_launch() {
+inline int check_launch(int n_kernels = 1) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_cuda_error(e); return GNNCCA_ERR_LAUNCH; }
+  count_launches(n_kernels);
   return GNNCCA_OK;
 }
 inline int check_cuda(cudaError_t e) {

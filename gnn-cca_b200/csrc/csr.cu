@@ -17,9 +17,9 @@ __global__ void __launch_bounds__(256) csr_narrow_kernel(const int64_t* __restri
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_edges; i += stride) {
     const int64_t r = ei[i], c = ei[n_edges + i];
     const int64_t prev = (i == 0) ? -1 : ei[i - 1];
-    src[i] = (int32_t)r;
-    dst[i] = (int32_t)c;
     const bool ok = (r >= 0) & (r < n_nodes) & (c >= 0) & (c < n_nodes);
+    src[i] = ok ? (int32_t)r : 0;   // out-of-range entries are reported through flags[1]; never let them index memory
+    dst[i] = ok ? (int32_t)c : 0;
     bad |= !ok;
     unsorted |= (r < prev);
     if (ok && prev < r && prev >= -1) {
@@ -132,7 +132,7 @@ extern "C" int gnncca_csr_sort(int64_t n_nodes, int64_t n_edges, int32_t* src, i
   rc = check_cuda(cudaMemcpyAsync(dst, tmp, sizeof(int32_t) * n_edges, cudaMemcpyDeviceToDevice, st));
   if (rc) return rc;
   rowptr_from_sorted_kernel<<<g, 256, 0, st>>>(src, n_nodes, n_edges, rowptr);
-  return check_launch();
+  return check_launch(3);
 }
 
 extern "C" int gnncca_permute_rows(const float* in, float* out, const int32_t* perm, int64_t n_rows, int32_t width,

@@ -231,7 +231,7 @@ extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_
   colnorm_partial_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
   colnorm_final_kernel<<<(unsigned)ceil_div(cols, 256), 256, 0, st>>>(scratch, chunks, cols, norm);
   colnorm_apply_kernel<<<grid_for(rows * cols, 256), 256, 0, st>>>(emb, out, rows, cols, norm);
-  return check_launch();
+  return check_launch(3);
 }
 
 extern "C" int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes) {
@@ -267,7 +267,7 @@ extern "C" int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t*
                                                            L.graph_edges, L.graph_tiles, GT);
   scan_i64_kernel<<<1, 1024, 0, st>>>(L.graph_edges, n_graphs, edge_ptr);
   scan_i64_kernel<<<1, 1024, 0, st>>>(L.graph_tiles, n_graphs, L.tile_ptr);
-  return check_launch();
+  return check_launch(3);
 }
 
 extern "C" int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64_t n_graphs, int64_t n_nodes,

@@ -38,6 +38,7 @@ struct StepParams {
   int num_tiles;
   float* tile_part;      // [num_tiles][2][FN]  slot 0: continuation piece (started in an earlier tile), slot 1: open tail
   int32_t* counters;     // [num_tiles] arrival counters, zeroed by the host entry before the launch
+  const int32_t* guard;  // optional CSR flags (gnncca_csr_from_edge_index): the kernel is a no-op when any is set
 };
 
 __device__ __forceinline__ float agg_init(int agg) { return agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f; }
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(TILE, 3) mp_step_fwd_kernel(const StepParams p
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = p.nf * FN;
+  if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;   // CSR not valid (unsorted / out of range): uniform exit
   {  // stage weights (read from the live parameters at every launch)
     const int edge_row = 2 * K + EIN, node_row = K + FE;
     for (int idx = tid; idx < FE * EIN; idx += TILE) s_wee[idx / EIN][idx % EIN] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
@@ -230,7 +232,7 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
 extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
                                   const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
                                   const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
-                                  float* h_out, float* logits, void* workspace, int64_t workspace_bytes, void* stream) {
+                                  float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream) {
   if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   if (h_out && n_nodes > 0) {  // nodes without out-edges aggregate to 0 (torch_scatter semantics)
@@ -250,6 +252,7 @@ extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weig
   StepParams sp{};
   sp.rowptr = rowptr; sp.src = src; sp.dst = dst; sp.n_nodes = n_nodes; sp.n_edges = n_edges;
   sp.P = P; sp.Q = Q; sp.R = R; sp.e0 = e0; sp.e_in = e_in; sp.e_out = e_out; sp.h_out = h_out; sp.logits = logits;
+  sp.guard = guard_flags;
   sp.w = *w; sp.agg = cfg->agg; sp.nf = cfg->reattach_nodes ? 2 : 1;
   sp.num_tiles = (int)ceil_div(n_edges, TILE);
   char* ws = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);

@@ -21,12 +21,13 @@ def _require_cuda(t: torch.Tensor, name: str) -> None:
 
 
 def linear(x: torch.Tensor, lin: torch.nn.Linear, relu: bool, bn: Optional[torch.nn.BatchNorm1d] = None,
-           math: int = _lib.MATH_FP32) -> torch.Tensor:
+           math: int = _lib.MATH_FP32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """models/mlp.py:14-19 for one fc_dims entry: Linear [+ BatchNorm1d(eval)] [+ ReLU]."""
     lib = _lib.load()
     x = x.contiguous()
     rows, in_dim = x.shape
-    y = torch.empty((rows, lin.out_features), dtype=torch.float32, device=x.device)
+    y = torch.empty((rows, lin.out_features), dtype=torch.float32, device=x.device) if out is None else out
+    assert y.is_contiguous() and y.shape == (rows, lin.out_features)
     bnw = bnb = bnm = bnv = None
     eps = 0.0
     if bn is not None:
@@ -120,25 +121,61 @@ def check_supported(model) -> None:
             raise NotImplementedError("classifier dropout_p > 0 in training mode is not implemented")
 
 
+class StageTimer:
+    """CUDA-event marks on the current stream between the stages of a forward (bench.py uses it to time the
+    dominant kernel live; costs one event record per stage)."""
+
+    def __init__(self):
+        self.marks = []
+
+    def mark(self, name: str) -> None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        self.marks.append((name, ev))
+
+    def stages(self):
+        """[(stage name, milliseconds)] for every interval between consecutive marks (call after a sync)."""
+        return [(self.marks[i][0], self.marks[i - 1][1].elapsed_time(self.marks[i][1])) for i in range(1, len(self.marks))]
+
+
 def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
-                      plan: Optional[GraphPlan] = None, return_latents: bool = False):
+                      plan: Optional[GraphPlan] = None, return_latents: bool = False, prof: Optional[StageTimer] = None,
+                      h_encoded: Optional[torch.Tensor] = None):
     """``MOTMPNet.forward`` (models/mpn.py:250-299), no autograd graph.  Returns the list of per-step logits
-    [E,1] in the caller's edge order."""
+    [E,1] in the caller's edge order.
+
+    The whole forward is enqueued optimistically on the assumption that ``edge_index`` is source-major (what the
+    reference's construction yields, train.py:292-299); the step kernels are no-ops when the CSR flags say
+    otherwise.  The 16-byte flag read-back happens after the last launch, so the device never waits for the host;
+    a batch that turns out not to be source-major is then sorted (stable) and run again.
+    ``h_encoded``: node latents already produced by the node encoder (used by ``forward_host``)."""
     lib = _lib.load()
-    _require_cuda(x, "data.x")
     _require_cuda(edge_attr, "data.edge_attr")
     check_supported(model)
     math = MATH_MODES[model.math]
-    N, E = int(x.size(0)), int(edge_index.size(1))
+    N, E = (int(x.size(0)) if h_encoded is None else int(h_encoded.size(0))), int(edge_index.size(1))
     if edge_attr.size(0) != E:
         raise ValueError("edge_attr has %d rows but edge_index has %d edges" % (edge_attr.size(0), E))
+    if prof is not None:
+        prof.mark("begin")
     if plan is None:
         plan = GraphPlan(edge_index, N)          # async: narrow + order check + rowptr
-    dev = x.device
-    # encoder (MLPGraphIndependent.forward, mpn.py:128-142); the CSR flags are read while it runs
-    h = mlp_forward_nograd(model.encoder.node_mlp, x, math)
-    plan.resolve()
+    optimistic = not plan.resolved
+    guard = _lib.ptr(plan.flags) if optimistic else 0
+    if prof is not None:
+        prof.mark("csr")
+    dev = edge_attr.device
+    # encoder (MLPGraphIndependent.forward, mpn.py:128-142)
+    if h_encoded is None:
+        _require_cuda(x, "data.x")
+        h = mlp_forward_nograd(model.encoder.node_mlp, x, math)
+    else:
+        h = h_encoded
+    if prof is not None:
+        prof.mark("encoder_node")
     e = small_mlp_rows(model.encoder.edge_mlp, plan.to_sorted(edge_attr.contiguous()))
+    if prof is not None:
+        prof.mark("encoder_edge")
     h0, e0 = h, e
     sb = StepBinding(model, math)
     L, k = model.num_enc_steps, model.num_class_steps
@@ -163,24 +200,93 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
             _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
                                               _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
                                               _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e), _lib.ptr(e_out),
-                                              _lib.ptr(h_out), _lib.ptr(logits), _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+                                              _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()),
+                       "mp_step_fwd")
             e = e_out
             if h_out is not None:
                 h = h_out
             latents.append((h, e))
             if classify:
                 outs.append(plan.to_caller(logits))
+            if prof is not None:
+                prof.mark("step%d" % step)
     else:
         outs.append(plan.to_caller(small_mlp_rows_cls(model, e)))            # mpn.py:295-297
+    if optimistic and not plan.source_major():
+        plan.resolve()   # stable sort by source; outputs go back to the caller's edge order
+        return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h0)
+    plan._resolved = True
     return (outs, latents, plan) if return_latents else outs
 
 
-def mlp_forward_nograd(mlp, inp, math):
-    out = inp
+def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor, out: Optional[List[torch.Tensor]] = None,
+                 device: Optional[torch.device] = None, n_chunks: int = 8) -> List[torch.Tensor]:
+    """The same forward for HOST buffers (pinned memory recommended): the inputs are copied to the device on a
+    side stream in row chunks, the node encoder of chunk i runs while chunk i+1 is in flight, and the per-step
+    logits are copied back into ``out`` (host tensors [E,1]; allocated pinned when None).  Returns ``out``
+    after the copies have completed."""
+    if x.is_cuda or edge_index.is_cuda or edge_attr.is_cuda:
+        raise ValueError("forward_host takes host tensors; call the module itself for device tensors")
+    check_supported(model)
+    dev = device if device is not None else next(model.parameters()).device
+    if dev.type != "cuda":
+        raise RuntimeError("gnn-cca_b200: the model must live on a CUDA device (no CPU path)")
+    math = MATH_MODES[model.math]
+    N, E = int(x.size(0)), int(edge_index.size(1))
+    cur = torch.cuda.current_stream(dev)
+    side = _side_stream(dev)
+    side.wait_stream(cur)
+    x_d = torch.empty((N, x.size(1)), dtype=torch.float32, device=dev)
+    ei_d = torch.empty((2, E), dtype=torch.int64, device=dev)
+    ea_d = torch.empty((E, edge_attr.size(1)), dtype=torch.float32, device=dev)
+    bounds = [N * i // n_chunks for i in range(n_chunks + 1)]
+    events = []
+    with torch.cuda.stream(side):
+        ei_d.copy_(edge_index, non_blocking=True)
+        ea_d.copy_(edge_attr, non_blocking=True)
+        ev0 = torch.cuda.Event(); ev0.record(side)
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            if b > a:
+                x_d[a:b].copy_(x[a:b], non_blocking=True)
+            ev = torch.cuda.Event(); ev.record(side)
+            events.append(ev)
+    for t in (x_d, ei_d, ea_d):
+        t.record_stream(side)
+    cur.wait_event(ev0)
+    plan = GraphPlan(ei_d, N)
+    enc = model.encoder.node_mlp
+    h = torch.empty((N, enc.layer_specs[-1].out_dim), dtype=torch.float32, device=dev)
+    for (a, b), ev in zip(zip(bounds[:-1], bounds[1:]), events):
+        cur.wait_event(ev)
+        if b > a:
+            mlp_forward_nograd(enc, x_d[a:b], math, out=h[a:b])
+    outs = forward_inference(model, x_d, ei_d, ea_d, plan, h_encoded=h)
+    if out is None:
+        out = [torch.empty((E, 1), dtype=torch.float32, pin_memory=True) for _ in outs]
+    for o, d in zip(out, outs):
+        o.copy_(d, non_blocking=True)
+    cur.synchronize()
+    return out
+
+
+_SIDE_STREAMS = {}
+
+
+def _side_stream(dev) -> "torch.cuda.Stream":
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _SIDE_STREAMS[key]
+
+
+def mlp_forward_nograd(mlp, inp, math, out=None):
+    cur = inp
+    n = len(mlp.layer_specs)
     for i, sp in enumerate(mlp.layer_specs):
         ok_tc = sp.in_dim % 32 == 0 and sp.out_dim % 16 == 0 and sp.out_dim <= 256 and sp.bn is None
-        out = linear(out, mlp.linear(i), sp.relu, mlp.batchnorm(i), math if ok_tc else _lib.MATH_FP32)
-    return out
+        cur = linear(cur, mlp.linear(i), sp.relu, mlp.batchnorm(i), math if ok_tc else _lib.MATH_FP32,
+                     out=out if i == n - 1 else None)
+    return cur
 
 
 def small_mlp_rows_cls(model, e):

@@ -145,5 +145,11 @@ class MOTMPNet(nn.Module):
             outs = engine.forward_inference(self, x, edge_index, edge_attr, plan)
         return {'classified_edges': outs}
 
+    def forward_host(self, x, edge_index, edge_attr, out=None):
+        """The same forward for HOST tensors (pinned memory recommended): chunked host->device copies overlap the
+        node encoder, per-step logits are copied back into ``out`` (list of host tensors [E,1])."""
+        from . import engine
+        return engine.forward_host(self, x, edge_index, edge_attr, out=out)
+
     def _has_batchnorm(self) -> bool:
         return any(isinstance(m, nn.BatchNorm1d) for m in self.modules())

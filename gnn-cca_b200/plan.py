@@ -40,15 +40,23 @@ class GraphPlan:
         self._flags_host.copy_(self.flags, non_blocking=True)
         self._event.record()
 
+    @property
+    def resolved(self) -> bool:
+        return self._resolved
+
+    def source_major(self) -> bool:
+        """Wait for the order / range flags (a 16-byte read back) and report whether the caller's edge order is
+        already source-major (what train.py:292-299 produces).  Raises on out-of-range indices."""
+        self._event.synchronize()
+        if int(self._flags_host[1]):
+            raise IndexError("edge_index has entries outside [0, num_nodes=%d)" % self.N)
+        return not int(self._flags_host[0])
+
     def resolve(self) -> "GraphPlan":
-        """Wait for the order / range flags (a 16-byte read that overlaps the node encoder) and run the
-        stable sort when the edges are not source-major."""
+        """Make the CSR valid: read the flags and run the stable sort when the edges are not source-major."""
         if self._resolved:
             return self
-        self._event.synchronize()
-        unsorted, bad = int(self._flags_host[0]), int(self._flags_host[1])
-        if bad:
-            raise IndexError("edge_index has entries outside [0, num_nodes=%d)" % self.N)
+        unsorted = not self.source_major()
         if unsorted:
             dev = self.src.device
             self.perm = torch.empty(self.E, dtype=torch.int32, device=dev)
@@ -56,6 +64,7 @@ class GraphPlan:
             ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
             _lib.check(self.lib.gnncca_csr_sort(self.N, self.E, _lib.ptr(self.src), _lib.ptr(self.dst), _lib.ptr(self.perm),
                                                 _lib.ptr(self.rowptr), _lib.ptr(ws), nbytes, _stream()), "csr_sort")
+            self.flags.zero_()        # the CSR is valid now: lift the guard the step kernels look at
         self._resolved = True
         return self
 

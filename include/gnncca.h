@@ -44,6 +44,9 @@ int gnncca_abi_version(void);
 const char* gnncca_status_string(int status);
 /* Text of the last CUDA error seen by this thread inside the library ("" if none). */
 const char* gnncca_last_cuda_error(void);
+/* Number of kernels this library has launched in this process so far (monotonic; bench.py reports the
+ * difference over its timed region as "gpu_launches"). */
+int64_t gnncca_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
  * CSR / index work (bit-exact).  Replaces the implicit indexing of x[row], x[col] and the
@@ -137,13 +140,15 @@ int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes
  * e_out may alias e_in.  h_out may be NULL (last step: the node update is dead, mpn.py:288-299).
  * cls_stats (training-mode classifier BatchNorm): when non-NULL, logits are NOT written; instead
  * per-tile partial sums of the classifier's hidden pre-activation are written for
- * gnncca_cls_bn_finalize. */
+ * gnncca_cls_bn_finalize.
+ * guard_flags (optional): the flags[] of gnncca_csr_from_edge_index; when any is set the launch is a
+ * no-op, so a caller may enqueue the whole forward before reading the flags back. */
 int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                        const int32_t* rowptr, const int32_t* src, const int32_t* dst,
                        int64_t n_nodes, int64_t n_edges,
                        const float* P, const float* Q, const float* R,
                        const float* e0, const float* e_in, float* e_out, float* h_out, float* logits,
-                       void* workspace, int64_t workspace_bytes, void* stream);
+                       const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Independent per-edge MLP chain (MLPGraphIndependent edge branch, mpn.py:128-142): encoder edge MLP
  * (4 -> 6 + ReLU) and, stand-alone, the classifier.  Up to 4 layers, widths <= 32.

@@ -151,6 +151,35 @@ class MPNSpec:
         self.num_class_steps = model_params["num_class_steps"]
 
 
+def init_state_dict(spec: MPNSpec, seed: int = 0) -> Dict[str, Tensor]:
+    """Random-init weights in the order ``MOTMPNet.__init__`` creates its modules (mpn.py:173-174 encoder then
+    classifier, each node MLP before edge MLP, mpn.py:116-126; then edge_mlp, node_mlp and the dead
+    ``node_mlp_old`` Linear of mpn.py:217-242), with torch's default ``nn.Linear`` / ``nn.BatchNorm1d`` init."""
+    torch.manual_seed(seed)
+    sd: Dict[str, Tensor] = {}
+
+    def build(prefix, layout):
+        if layout is None:
+            return
+        for idx, kind, a, b in layout:
+            key = "{}.fc_layers.{}".format(prefix, idx)
+            if kind == "linear":
+                lin = torch.nn.Linear(a, b)
+                sd[key + ".weight"], sd[key + ".bias"] = lin.weight.detach(), lin.bias.detach()
+            elif kind == "bn":
+                bn = torch.nn.BatchNorm1d(a)
+                for name, t in bn.state_dict().items():
+                    sd[key + "." + name] = t.detach()
+
+    build("encoder.node_mlp", spec.enc_node)
+    build("encoder.edge_mlp", spec.enc_edge)
+    build("classifier.node_mlp", spec.cls_node)
+    build("classifier.edge_mlp", spec.cls_edge)
+    build("MPNet.edge_model.edge_mlp", spec.edge_model)
+    build("MPNet.node_model.node_mlp", spec.node_model)
+    return sd
+
+
 def motmpnet_forward(spec: MPNSpec, sd: Dict[str, Tensor], x: Tensor, edge_index: Tensor, edge_attr: Tensor,
                      training: bool = False, return_latents: bool = False):
     """``MOTMPNet.forward`` (mpn.py:250-299) on CPU tensors; returns {'classified_edges': [...]}.
