@@ -193,8 +193,8 @@ __global__ void __launch_bounds__(256) edge_mlp_kernel(const float* __restrict__
 
 using namespace gnncca;
 
-int gnncca_linear_tf32(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
-                       int32_t out_dim, int32_t relu, void* stream);   // encoder_tc.cu
+int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+                             int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream);   // encoder_tc.cu
 
 extern "C" int gnncca_linear(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
                              int32_t out_dim, int32_t relu, const float* bn_weight, const float* bn_bias,
@@ -203,15 +203,21 @@ extern "C" int gnncca_linear(const float* x, const float* W, const float* b, flo
   if (rows == 0) return GNNCCA_OK;
   if (!x || !W || !y) return GNNCCA_ERR_BAD_ARG;
   if (bn_weight && (!bn_bias || !bn_mean || !bn_var)) return GNNCCA_ERR_BAD_ARG;
-  if (math == GNNCCA_MATH_TF32) {
-    if (bn_weight) return GNNCCA_ERR_UNSUPPORTED;
-    return gnncca_linear_tf32(x, W, b, y, rows, in_dim, out_dim, relu, stream);
-  }
+  if (math == GNNCCA_MATH_TF32) return GNNCCA_ERR_UNSUPPORTED;   // the tensor-core path is gnncca_node_encoder (fused two layers)
   if (math != GNNCCA_MATH_FP32) return GNNCCA_ERR_BAD_ARG;
   LinearEpilogue ep{b, bn_weight, bn_bias, bn_mean, bn_var, bn_eps, relu};
   dim3 grid((unsigned)ceil_div(rows, BM), (unsigned)ceil_div(out_dim, BN));
   linear_fp32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, W, y, rows, in_dim, out_dim, ep);
   return check_launch();
+}
+
+extern "C" int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+                                   int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, int32_t math, void* stream) {
+  if (rows < 0 || in_dim <= 0 || hidden <= 0 || out_dim <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!x || !W1 || !b1 || !W2 || !b2 || !h) return GNNCCA_ERR_BAD_ARG;
+  if (math != GNNCCA_MATH_TF32) return GNNCCA_ERR_UNSUPPORTED;   // FP32: two gnncca_linear calls
+  return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, h, rows, in_dim, hidden, out_dim, stream);
 }
 
 extern "C" int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* h0, const float* h,

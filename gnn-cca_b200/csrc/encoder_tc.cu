@@ -1,9 +1,327 @@
-// tcgen05 (kind::tf32) path of the wide node-encoder layer.  Placeholder until the TMA/TMEM kernel lands:
-// reports "unsupported" (never falls back silently).
+// Node encoder of MOTMPNet (reference models/mpn.py:128-142 MLPGraphIndependent.forward, node branch;
+// models/mlp.py:12-23 for node_fc_dims=[H]): h = ReLU(W2 ReLU(W1 x + b1) + b2), x [N, K] fp32 -> h [N, 32].
+//
+// This is the one true dense contraction of the path (N x K x H, K = 2048, H = 128) and, at EPFL sizes, the
+// largest HBM stream of the whole forward (8 KB per node).  One persistent, warp-specialised kernel:
+//   warp 0      TMA producer : cp.async.bulk.tensor 128-row x 32-float boxes of x (evict-first) and H x 32 boxes
+//                              of W1 (evict-last, L2 resident) into a ring of 128B-swizzled shared-memory stages
+//   warp 1      MMA issuer   : tcgen05.mma kind::tf32, M=128, N=H, K=8 per instruction, accumulators in TMEM
+//                              (double buffered: 2 x H columns) -- fp32 bits are consumed as TF32 in place, so
+//                              x is never converted or re-written
+//   warps 2..5  epilogue     : tcgen05.ld the accumulator row of "their" node, + b1, ReLU, then the 128 -> 32
+//                              layer in exact FP32 FFMA against W2 held in shared memory, + b2, ReLU, one 128 B
+//                              store per node.  The hidden activations never touch HBM.
+// Roofline: HBM.  Algorithmic bytes per launch = N * (4 K + 128) + weights.
+#include <cuda.h>
 #include "common.cuh"
 
-int gnncca_linear_tf32(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
-                       int32_t out_dim, int32_t relu, void* stream) {
-  (void)x; (void)W; (void)b; (void)y; (void)rows; (void)in_dim; (void)out_dim; (void)relu; (void)stream;
-  return GNNCCA_ERR_UNSUPPORTED;
+namespace gnncca {
+namespace enc {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 32;            // floats per k-block = 128 bytes = one swizzle row
+constexpr int UMMA_K = 8;              // tf32: 32 bytes per instruction along K
+constexpr int F_OUT = 32;              // node latent width
+constexpr int NUM_THREADS = 192;
+constexpr int MAX_STAGES = 8;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);        // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                              // leading byte offset (unused for swizzled K-major), bits [16,30)
+  d |= (uint64_t)(1024 >> 4) << 32;                    // stride byte offset = 8 rows x 128 B, bits [32,46)
+  d |= (uint64_t)1 << 46;                              // descriptor version 1 (sm_100)
+  d |= (uint64_t)2 << 61;                              // layout type SWIZZLE_128B
+  return d;
+}
+// cute::UMMA::InstrDescriptor for kind::tf32, fp32 accumulate, both operands K-major
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+struct Params {
+  const float* b1; const float* W2; const float* b2;
+  float* h_out;
+  int64_t rows;
+  int K, H, num_tiles, stages;
+};
+
+template <int H>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, const Params p) {
+  constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;       // 16 KB
+  constexpr uint32_t B_BYTES = H * BLOCK_K * 4;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = (2 * H <= 32) ? 32 : (2 * H <= 64) ? 64 : (2 * H <= 128) ? 128 : (2 * H <= 256) ? 256 : 512;
+  constexpr uint32_t IDESC = make_idesc(BLOCK_M, H);
+  constexpr uint64_t HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // 128B swizzle atoms need 1024 B alignment
+  const int NS = p.stages;
+  uint8_t* tiles = smem;
+  float* w2t = (float*)(tiles + (size_t)NS * STAGE_BYTES);     // [H][32]: W2 transposed, row j = the 32 output weights of hidden j
+  float* b1s = w2t + H * F_OUT;
+  float* b2s = b1s + H;
+  uint64_t* full = (uint64_t*)(b2s + F_OUT);
+  uint64_t* empty = full + MAX_STAGES;
+  uint64_t* tmem_full = empty + MAX_STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
+    for (int s = 0; s < NS; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {   // TMEM: 2 accumulators of H columns (this warp also frees them)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= 2) {   // epilogue warps stage the small second layer
+    const int t = threadIdx.x - 64;
+    for (int idx = t; idx < H * F_OUT; idx += 128) { const int j = idx / F_OUT, o = idx % F_OUT; w2t[idx] = p.W2[o * H + j]; }
+    for (int idx = t; idx < H; idx += 128) b1s[idx] = p.b1[idx];
+    if (t < F_OUT) b2s[t] = p.b2[t];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int KB = p.K / BLOCK_K;
+
+  if (warp == 0) {
+    if (lane == 0) {   // ------------------------------------------------ TMA producer
+      int s = 0; uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(empty + s, ph ^ 1);
+          uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
+          mbar_expect_tx(full + s, STAGE_BYTES);
+          tma_load_2d(a, &tmap_x, full + s, kb * BLOCK_K, tile * BLOCK_M, HINT_EVICT_FIRST);
+          tma_load_2d(a + A_BYTES, &tmap_w, full + s, kb * BLOCK_K, 0, HINT_EVICT_LAST);
+          if (++s == NS) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {   // ------------------------------------------------ MMA issuer
+      int s = 0; uint32_t ph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(tmem_empty + as, aph ^ 1);     // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * H);
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(full + s, ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
+          const uint64_t adesc = make_smem_desc(a_addr), bdesc = make_smem_desc(a_addr + A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)   // +32 bytes along K inside the swizzle atom = +2 in the (>>4) address field
+            umma_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (uint32_t)((kb | k) != 0));
+          umma_commit(empty + s);                  // stage reusable once these MMAs have read it
+          if (kb == KB - 1) umma_commit(tmem_full + as);
+          if (++s == NS) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else {             // ---------------------------------------------------- epilogue: one node row per thread
+    const int q = warp & 3;                         // TMEM lane quarter this warp may access
+    const int row_in_tile = q * 32 + lane;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(tmem_full + as, aph);
+      tc_fence_after();
+      float out[F_OUT];
+#pragma unroll
+      for (int o = 0; o < F_OUT; ++o) out[o] = b2s[o];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * H);
+#pragma unroll 1
+      for (int c = 0; c < H / 32; ++c) {
+        float v[32];
+        tmem_ld32(taddr + c * 32, v);
+        if (c == H / 32 - 1) {                      // accumulator fully read: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tmem_empty + as);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float hj = fmaxf(v[j] + b1s[c * 32 + j], 0.f);            // Linear + ReLU (mlp.py:14,18)
+          const float4* wr = reinterpret_cast<const float4*>(w2t + (c * 32 + j) * F_OUT);
+#pragma unroll
+          for (int o4 = 0; o4 < F_OUT / 4; ++o4) {
+            const float4 w = wr[o4];                                        // same address in every lane: broadcast
+            out[4 * o4 + 0] = fmaf(hj, w.x, out[4 * o4 + 0]);
+            out[4 * o4 + 1] = fmaf(hj, w.y, out[4 * o4 + 1]);
+            out[4 * o4 + 2] = fmaf(hj, w.z, out[4 * o4 + 2]);
+            out[4 * o4 + 3] = fmaf(hj, w.w, out[4 * o4 + 3]);
+          }
+        }
+      }
+      const int64_t row = (int64_t)tile * BLOCK_M + row_in_tile;
+      if (row < p.rows) {
+        float4* dst = reinterpret_cast<float4*>(p.h_out + row * F_OUT);
+#pragma unroll
+        for (int o4 = 0; o4 < F_OUT / 4; ++o4)
+          dst[o4] = make_float4(fmaxf(out[4 * o4], 0.f), fmaxf(out[4 * o4 + 1], 0.f), fmaxf(out[4 * o4 + 2], 0.f), fmaxf(out[4 * o4 + 3], 0.f));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+}  // namespace enc
+}  // namespace gnncca
+
+using namespace gnncca;
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point: libgnncca has no link-time dependency on libcuda
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)sym;
+    (void)cudaGetLastError();
+  }
+  return fn;
+}
+
+// row-major fp32 matrix [rows][cols] -> boxes of box_rows x 32 floats, 128B swizzle, zero fill outside
+bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, int box_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t)enc::BLOCK_K, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int H>
+int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaStream_t st) {
+  enc::Params p = p0;
+  const size_t stage = (size_t)(enc::BLOCK_M + H) * enc::BLOCK_K * 4;
+  const size_t fixed = 1024 /*alignment slack*/ + sizeof(float) * (H * enc::F_OUT + H + enc::F_OUT) + 8 * (2 * enc::MAX_STAGES + 4) + 16;
+  int stages = (int)((227 * 1024 - fixed) / stage);
+  if (stages > enc::MAX_STAGES) stages = enc::MAX_STAGES;
+  if (stages < 2) return GNNCCA_ERR_UNSUPPORTED;
+  p.stages = stages;
+  const size_t smem = fixed + stage * stages;
+  CUtensorMap mx, mw;
+  if (!make_map(&mx, x, p.rows, p.K, enc::BLOCK_M) || !make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
+  auto kern = enc::node_encoder_tf32_kernel<H>;
+  static bool configured = false;
+  if (!configured) {
+    int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (rc) return rc;
+    configured = true;
+  }
+  const int grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
+  kern<<<grid, enc::NUM_THREADS, smem, st>>>(mx, mw, p);
+  return check_launch();
+}
+
+}  // namespace
+
+// Fused two-layer node encoder on the tensor cores (see the header of this file).  Requirements: in_dim % 32 == 0,
+// hidden in {64, 128, 256}, out_dim == 32, x and W1 16-byte aligned.
+int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+                             int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream) {
+  if (out_dim != enc::F_OUT || in_dim % enc::BLOCK_K != 0 || in_dim < enc::BLOCK_K) return GNNCCA_ERR_UNSUPPORTED;
+  if ((((uintptr_t)x | (uintptr_t)W1 | (uintptr_t)h) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows >= ((int64_t)1 << 31) * enc::BLOCK_M) return GNNCCA_ERR_BAD_ARG;
+  enc::Params p{};
+  p.b1 = b1; p.W2 = W2; p.b2 = b2; p.h_out = h; p.rows = rows; p.K = in_dim; p.H = hidden;
+  p.num_tiles = (int)ceil_div(rows, enc::BLOCK_M);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (hidden) {
+    case 64: return launch_encoder<64>(x, W1, p, st);
+    case 128: return launch_encoder<128>(x, W1, p, st);
+    case 256: return launch_encoder<256>(x, W1, p, st);
+    default: return GNNCCA_ERR_UNSUPPORTED;
+  }
 }

@@ -279,7 +279,29 @@ def _side_stream(dev) -> "torch.cuda.Stream":
     return _SIDE_STREAMS[key]
 
 
+FUSED_NODE_ENCODER = True   # bench.py: the node encoder is one kernel in tf32 mode (algorithmic bytes N*(4K+128))
+
+
+def node_encoder_fused_ok(mlp, inp) -> bool:
+    """Shapes the tcgen05 encoder kernel covers: Linear+ReLU, Linear+ReLU, in % 32 == 0, hidden in {64,128,256}, out 32."""
+    sp = mlp.layer_specs
+    return (len(sp) == 2 and all(s.relu and s.bn is None for s in sp) and sp[0].in_dim % 32 == 0 and sp[0].out_dim in (64, 128, 256)
+            and sp[1].out_dim == 32 and inp.data_ptr() % 16 == 0)
+
+
 def mlp_forward_nograd(mlp, inp, math, out=None):
+    if math == _lib.MATH_TF32 and node_encoder_fused_ok(mlp, inp):
+        lib = _lib.load()
+        inp = inp.contiguous()
+        rows = int(inp.size(0))
+        l1, l2 = mlp.linear(0), mlp.linear(1)
+        y = torch.empty((rows, l2.out_features), dtype=torch.float32, device=inp.device) if out is None else out
+        assert y.is_contiguous() and y.shape == (rows, l2.out_features)
+        _lib.check(lib.gnncca_node_encoder(_lib.ptr(inp), _lib.ptr(l1.weight), _lib.ptr(l1.bias), _lib.ptr(l2.weight), _lib.ptr(l2.bias),
+                                           _lib.ptr(y), rows, l1.in_features, l1.out_features, l2.out_features, _lib.MATH_TF32,
+                                           _stream()), "node_encoder")
+        return y
+    math = _lib.MATH_FP32
     cur = inp
     n = len(mlp.layer_specs)
     for i, sp in enumerate(mlp.layer_specs):

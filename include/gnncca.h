@@ -82,12 +82,20 @@ int gnncca_permute_rows(const float* in, float* out, const int32_t* perm, int64_
 
 /* y[rows,out] = act( x[rows,in] @ W^T + b ), act = ReLU iff relu != 0.  BatchNorm1d in eval mode is
  * folded when bn_weight != NULL: y = act( (z - mean) / sqrt(var + eps) * gamma + beta ).
- * math: GNNCCA_MATH_FP32 (FFMA) or GNNCCA_MATH_TF32 (tcgen05, needs in % 32 == 0, out % 16 == 0,
- * out <= 256; `tmap_workspace` must then point to 256 bytes of 64B-aligned device scratch or be NULL
- * to let the library encode descriptors on the host side). */
+ * math: GNNCCA_MATH_FP32 (FFMA).  GNNCCA_MATH_TF32 returns GNNCCA_ERR_UNSUPPORTED here: the tensor-core path is
+ * the fused gnncca_node_encoder below. */
 int gnncca_linear(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
                   int32_t out_dim, int32_t relu, const float* bn_weight, const float* bn_bias,
                   const float* bn_mean, const float* bn_var, float bn_eps, int32_t math, void* stream);
+
+/* Node encoder of MOTMPNet (mpn.py:128-142 node branch with node_fc_dims=[hidden], mlp.py:12-23):
+ *   h[rows,out] = ReLU( ReLU( x[rows,in] @ W1^T + b1 ) @ W2^T + b2 )
+ * as ONE kernel: TMA-fed tcgen05 kind::tf32 MMA for the wide first layer (x is consumed as TF32 in place),
+ * exact-FP32 second layer in the epilogue; the hidden activations never reach HBM.
+ * math must be GNNCCA_MATH_TF32; needs in % 32 == 0, hidden in {64,128,256}, out == 32, 16-byte aligned
+ * x / W1 / h.  Anything else returns GNNCCA_ERR_UNSUPPORTED (the caller then uses two gnncca_linear calls). */
+int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+                        int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, int32_t math, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * One message-passing step, models/mpn.py:32-54 (MetaLayer) = EdgeModel :67-69 + NodeModel :97-101
