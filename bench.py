@@ -131,6 +131,8 @@ def stage_bytes(stage: str, N: int, E: int, f_x: int, hidden: int = 128, fused_e
         return E * (16 + 24)
     if stage == "csr":
         return E * (16 + 8) + 4 * (N + 1)
+    if stage == "mp_fused":      # all steps on chip: edge_attr + int32 src/dst + k logits per edge; encoded node + CSR row per node
+        return E * (16 + 8 + 12) + N * (128 + 4)
     if stage.startswith("step"):
         k = int(stage[4:])
         return E * 64 + N * 256 + (4 * E if k >= 2 else 0)
@@ -251,7 +253,7 @@ def main():
 
     def step(i, prof=None):
         b = batches[i & 1]
-        return engine.forward_inference(model, b.x, b.edge_index, b.edge_attr, prof=prof)
+        return engine.forward_inference(model, b.x, b.edge_index, b.edge_attr, prof=prof, graph_ptr=b.ptr, caps=b.gnncca_caps)
 
     def barrier():
         if world > 1:
@@ -309,14 +311,15 @@ def main():
         hosts = []
         for b in batches:
             hosts.append((b.x.cpu().pin_memory(), b.edge_index.cpu().pin_memory(), b.edge_attr.cpu().pin_memory()))
+        ptrs = [b.ptr.cpu().pin_memory() for b in batches]
         outs_host = [torch.empty((E, 1), dtype=torch.float32).pin_memory() for _ in range(model.num_class_steps)]
         e2e_steps = max(3, min(args.steps, 20))
         for i in range(2):
-            model.forward_host(*hosts[i & 1], out=outs_host)
+            model.forward_host(*hosts[i & 1], out=outs_host, graph_ptr=ptrs[i & 1], caps=batches[i & 1].gnncca_caps)
         barrier()
         t0 = time.perf_counter()
         for i in range(e2e_steps):
-            model.forward_host(*hosts[i & 1], out=outs_host)     # returns after the D2H copy of the logits
+            model.forward_host(*hosts[i & 1], out=outs_host, graph_ptr=ptrs[i & 1], caps=batches[i & 1].gnncca_caps)     # returns after the D2H copy of the logits
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -375,7 +378,7 @@ def main():
                        "l2": "two input batches used alternately (2 x %.0f MB > 126 MB L2)" % (in_bytes / 1e6),
                        "graphs_per_s": world * wl["frames"] * args.steps / (ms_max * 1e-3)},
             "clocks": sampler.result(), "gpu_launches": launches,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": d2h_bytes,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes + 8 * (wl["frames"] + 1), "d2h_bytes_per_step": d2h_bytes,
                     "steps": e2e_steps, "api": "MOTMPNet.forward_host (pinned host x/edge_index/edge_attr -> pinned host logits)"},
             "roofline": roofline}
     if cpu is not None:

@@ -1,0 +1,329 @@
+// All message-passing steps of MOTMPNet.forward (reference models/mpn.py:270-299) for batches of SMALL graphs,
+// as ONE kernel: a CTA takes one frame graph at a time, keeps its node and edge latents in shared memory across
+// the L steps (edge encoder mlp.py / mpn.py:128-142, EdgeModel :59-69, NodeModel :71-101 with the aggregation of
+// :192-202, classifier :290-293) and touches HBM only for the inputs (encoded nodes, edge_attr, CSR) and the
+// per-step logits.  EPFL frames are 2..40 detections / <= 1200 directed edges (~30 KB of state), so nothing
+// of size E is ever written between steps: compulsory traffic is 44 B/edge instead of 268 B/edge.
+//
+// Arithmetic is the same split form as mp_step.cu (P/Q/R per node, 6x6 + 6x32 FMAs per edge), FP32 FFMA, with
+// the same fixed summation order (a warp owns a node's whole out-edge segment), so results are bit-identical
+// run to run and equal to the per-step kernels' up to nothing at all (same operation order).
+//
+// Validity is checked on the device (frame fits the capacity class, every target lies inside the frame); a
+// violation raises flags[2] and the host re-runs the batch through the general per-step kernels.
+#include "common.cuh"
+
+namespace gnncca {
+namespace fused {
+
+constexpr int FN = 32, FE = 6, HC = 4, EP = 8;   // node width, edge width, classifier hidden, padded edge row
+constexpr int MAX_FA = 8;                         // widest raw edge attribute row supported
+
+struct Params {
+  const int64_t* graph_ptr; int64_t n_graphs; int64_t n_nodes; int64_t n_edges;
+  const int32_t* rowptr; const int32_t* src; const int32_t* dst;
+  const float* h_enc;                    // [N][FN] node encoder output
+  const float* edge_attr; int fa;        // [E][fa], source-sorted order
+  const float* w_enc; const float* b_enc;   // edge encoder Linear(fa, FE)
+  gnncca_mp_weights w;
+  int L, first_cls, agg, reatt_n, reatt_e, has_cls;
+  int cap_n, cap_e;
+  float* logits;                         // [(L - first_cls + 1)][E], classified steps in order
+  float* h_dump; float* e_dump;          // optional per-step latents [L+1][N][FN], [L+1][E][FE] (tests / saved for backward)
+  int32_t* flags;                        // [0],[1]: CSR invalid -> no-op; [2]: raised here when a frame does not fit
+};
+
+__device__ __forceinline__ float agg_init(int agg) { return agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f; }
+__device__ __forceinline__ float agg_comb(int agg, float a, float b) { return agg == GNNCCA_AGG_MAX ? fmaxf(a, b) : a + b; }
+
+struct Smem {
+  float* wproj;   // [K][44]   transposed projection weights: outputs 0..5 P, 6..11 Q, 12..43 R
+  float* bproj;   // [44]
+  float* wee;     // [FE][EIN]
+  float* wne;     // [FE][FN]
+  float* wenc;    // [FE][MAX_FA] , benc [FE]
+  float* benc;
+  float* c1;      // [HC][FE] (BatchNorm eval folded), b1 [HC], c2 [HC], b2 [1]
+  float* b1; float* c2; float* b2;
+  float* h;       // [cap_n][FN]
+  float* h0;      // [cap_n][FN] (reattach_nodes)
+  float* pqr;     // [cap_n][44]  per node: P (6, edge-update source part + bias) | Q (6, target part) | R (32, node-update part + bias)
+  float* e;       // [cap_e][EP]
+  float* e0;      // [cap_e][EP] (reattach_edges)
+  int* rp;        // [cap_n + 1]
+  uint16_t* sl; uint16_t* dl;   // [cap_e] local source / target
+};
+
+__host__ __device__ inline size_t carve(Smem& s, float* base, int K, int EIN, int cap_n, int cap_e, bool rn, bool re) {
+  float* p = base;
+  s.wproj = p; p += K * 44;
+  s.bproj = p; p += 44;
+  s.wee = p; p += FE * EIN;
+  s.wne = p; p += FE * FN;
+  s.wenc = p; p += FE * MAX_FA;
+  s.benc = p; p += 8;
+  s.c1 = p; p += HC * FE;
+  s.b1 = p; p += HC; s.c2 = p; p += HC; s.b2 = p; p += 4;
+  p = (float*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  s.h = p; p += cap_n * FN;
+  s.h0 = p; if (rn) p += cap_n * FN;
+  s.pqr = p; p += cap_n * 44;
+  s.e = p; p += (size_t)cap_e * EP;
+  s.e0 = p; if (re) p += (size_t)cap_e * EP;
+  s.rp = (int*)p; p += ((cap_n + 1 + 3) & ~3);
+  s.sl = (uint16_t*)p; p += (cap_e + 1) / 2;
+  p = (float*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
+  s.dl = (uint16_t*)p; p += (cap_e + 1) / 2;
+  return (size_t)((char*)p - (char*)base) + 16;
+}
+
+template <bool REATT_E>
+__global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
+  constexpr int EIN = REATT_E ? 2 * FE : FE;
+  extern __shared__ __align__(16) float smem_f[];
+  if ((p.flags[0] | p.flags[1]) != 0) return;      // CSR not valid (unsorted / out-of-range edge_index): uniform exit
+  const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = NT >> 5;
+  const int K = p.reatt_n ? 2 * FN : FN;
+  Smem s;
+  carve(s, smem_f, K, EIN, p.cap_n, p.cap_e, p.reatt_n != 0, REATT_E);
+
+  // ---- weights, once per CTA (read from the live parameters at every launch)
+  {
+    const int edge_row = 2 * K + EIN, node_row = K + FE;
+    for (int idx = tid; idx < K * 44; idx += NT) {
+      const int k = idx / 44, o = idx - k * 44;
+      float v;
+      if (o < FE) v = p.w.w_edge[o * edge_row + k];                        // source block of the edge update
+      else if (o < 2 * FE) v = p.w.w_edge[(o - FE) * edge_row + K + k];    // target block
+      else v = p.w.w_node[(o - 2 * FE) * node_row + k];                    // node block of the node update
+      s.wproj[idx] = v;
+    }
+    for (int o = tid; o < 44; o += NT) s.bproj[o] = o < FE ? p.w.b_edge[o] : (o < 2 * FE ? 0.f : p.w.b_node[o - 2 * FE]);
+    for (int idx = tid; idx < FE * EIN; idx += NT) s.wee[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
+    for (int idx = tid; idx < FE * FN; idx += NT) s.wne[idx] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
+    for (int idx = tid; idx < FE * MAX_FA; idx += NT) { const int o = idx / MAX_FA, k = idx % MAX_FA; s.wenc[idx] = k < p.fa ? p.w_enc[o * p.fa + k] : 0.f; }
+    for (int o = tid; o < FE; o += NT) s.benc[o] = p.b_enc[o];
+    if (p.has_cls) {
+      for (int c = tid; c < HC; c += NT) {
+        float scale = 1.f, shift = 0.f;
+        if (p.w.bn_weight) {   // BatchNorm1d (eval) folded into the hidden layer
+          scale = p.w.bn_weight[c] / sqrtf(p.w.bn_var[c] + p.w.bn_eps);
+          shift = p.w.bn_bias[c] - p.w.bn_mean[c] * scale;
+        }
+        for (int k = 0; k < FE; ++k) s.c1[c * FE + k] = p.w.w_c1[c * FE + k] * scale;
+        s.b1[c] = p.w.b_c1[c] * scale + shift;
+        s.c2[c] = p.w.w_c2[c];
+      }
+      if (tid == 0) s.b2[0] = p.w.b_c2[0];
+    }
+  }
+  __syncthreads();
+  float wne[FE];
+#pragma unroll
+  for (int k = 0; k < FE; ++k) wne[k] = s.wne[k * FN + lane];
+
+  for (int64_t g = blockIdx.x; g < p.n_graphs; g += gridDim.x) {
+    const int64_t a = p.graph_ptr[g], b = p.graph_ptr[g + 1];
+    if (a < 0 || b < a || b > p.n_nodes) { if (tid == 0) atomicOr(p.flags + 2, 1); continue; }
+    const int n = (int)min(b - a, (int64_t)INT32_MAX);
+    const int64_t eb = p.rowptr[a];
+    const int ne = p.rowptr[b] - (int)eb;
+    if (n > p.cap_n || ne > p.cap_e || ne < 0) { if (tid == 0) atomicOr(p.flags + 2, 1); continue; }   // CTA-uniform
+    // ---- load the frame: encoded nodes, local CSR, edge encoder
+    for (int idx = tid; idx < n * (FN / 4); idx += NT) {
+      const float4 v = *reinterpret_cast<const float4*>(p.h_enc + a * FN + (int64_t)idx * 4);
+      *reinterpret_cast<float4*>(s.h + idx * 4) = v;
+      if (p.reatt_n) *reinterpret_cast<float4*>(s.h0 + idx * 4) = v;
+    }
+    for (int v = tid; v <= n; v += NT) s.rp[v] = p.rowptr[a + v] - (int)eb;
+    bool bad = false;
+    for (int j = tid; j < ne; j += NT) {
+      const int sg = ld_stream_i32(p.src + eb + j) - (int)a, dg = ld_stream_i32(p.dst + eb + j) - (int)a;
+      const bool ok = (sg >= 0) & (sg < n) & (dg >= 0) & (dg < n);
+      bad |= !ok;
+      s.sl[j] = (uint16_t)(ok ? sg : 0);
+      s.dl[j] = (uint16_t)(ok ? dg : 0);
+      float ea[MAX_FA];
+      if (p.fa == 4) {   // the shipped 4-attribute row: one 16-byte streaming load
+        const float4 v4 = ld_stream_f4(p.edge_attr + (eb + j) * 4);
+        ea[0] = v4.x; ea[1] = v4.y; ea[2] = v4.z; ea[3] = v4.w;
+#pragma unroll
+        for (int k = 4; k < MAX_FA; ++k) ea[k] = 0.f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < MAX_FA; ++k) ea[k] = k < p.fa ? p.edge_attr[(eb + j) * p.fa + k] : 0.f;
+      }
+      float en[EP];
+#pragma unroll
+      for (int o = 0; o < FE; ++o) {
+        float acc = s.benc[o];
+#pragma unroll
+        for (int k = 0; k < MAX_FA; ++k) acc = fmaf(ea[k], s.wenc[o * MAX_FA + k], acc);
+        en[o] = fmaxf(acc, 0.f);                     // Linear + ReLU (edge_out_dim != 1), mlp.py:14,18
+      }
+      en[6] = 0.f; en[7] = 0.f;
+      *reinterpret_cast<float4*>(s.e + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+      *reinterpret_cast<float4*>(s.e + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
+      if (REATT_E) {
+        *reinterpret_cast<float4*>(s.e0 + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+        *reinterpret_cast<float4*>(s.e0 + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
+      }
+      if (p.e_dump) {
+#pragma unroll
+        for (int o = 0; o < FE; ++o) p.e_dump[(eb + j) * FE + o] = en[o];
+      }
+    }
+    if (bad) atomicOr(p.flags + 2, 1);               // a target outside the frame: not a disjoint union of frames
+    if (p.h_dump) for (int idx = tid; idx < n * FN; idx += NT) p.h_dump[a * FN + idx] = p.h_enc[a * FN + idx];
+    __syncthreads();
+
+    for (int step = 1; step <= p.L; ++step) {
+      // ---- per-node projections P | Q | R  (Linear over a concatenation = sum of per-block products)
+      for (int item = tid; item < n * 11; item += NT) {
+        const int v = item / 11, q = item - v * 11;
+        float4 acc = *reinterpret_cast<const float4*>(s.bproj + 4 * q);
+        const float* wq = s.wproj + 4 * q;
+        if (p.reatt_n) {
+          const float* hv0 = s.h0 + v * FN;         // cat(initial, current), mpn.py:285
+#pragma unroll 8
+          for (int k = 0; k < FN; ++k) {
+            const float x = hv0[k];
+            const float4 w = *reinterpret_cast<const float4*>(wq + k * 44);
+            acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y); acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
+          }
+          wq += FN * 44;
+        }
+        const float* hv = s.h + v * FN;
+#pragma unroll 8
+        for (int k = 0; k < FN; ++k) {
+          const float x = hv[k];
+          const float4 w = *reinterpret_cast<const float4*>(wq + k * 44);
+          acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y); acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
+        }
+        *reinterpret_cast<float4*>(s.pqr + v * 44 + 4 * q) = acc;
+      }
+      __syncthreads();
+      // ---- phase A: thread per edge -- edge update (+ classifier)
+      const bool classify = p.has_cls && step >= p.first_cls;
+      float* logit_out = classify ? p.logits + (int64_t)(step - p.first_cls) * p.n_edges + eb : nullptr;
+      for (int j = tid; j < ne; j += NT) {
+        const float* Ps = s.pqr + (int)s.sl[j] * 44;
+        const float* Qd = s.pqr + (int)s.dl[j] * 44 + FE;
+        const float4 p0 = *reinterpret_cast<const float4*>(Ps);
+        const float2 p1 = *reinterpret_cast<const float2*>(Ps + 4);
+        const float2 q0 = *reinterpret_cast<const float2*>(Qd), q1 = *reinterpret_cast<const float2*>(Qd + 2), q2 = *reinterpret_cast<const float2*>(Qd + 4);
+        const float pq[FE] = {p0.x + q0.x, p0.y + q0.y, p0.z + q1.x, p0.w + q1.y, p1.x + q2.x, p1.y + q2.y};
+        float ein[EIN];
+        if (REATT_E) {   // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
+          const float4 u0 = *reinterpret_cast<const float4*>(s.e0 + j * EP), u1 = *reinterpret_cast<const float4*>(s.e0 + j * EP + 4);
+          ein[0] = u0.x; ein[1] = u0.y; ein[2] = u0.z; ein[3] = u0.w; ein[4] = u1.x; ein[5] = u1.y;
+        }
+        constexpr int OFF = REATT_E ? FE : 0;
+        {
+          const float4 u0 = *reinterpret_cast<const float4*>(s.e + j * EP), u1 = *reinterpret_cast<const float4*>(s.e + j * EP + 4);
+          ein[OFF] = u0.x; ein[OFF + 1] = u0.y; ein[OFF + 2] = u0.z; ein[OFF + 3] = u0.w; ein[OFF + 4] = u1.x; ein[OFF + 5] = u1.y;
+        }
+        float en[FE];
+#pragma unroll
+        for (int o = 0; o < FE; ++o) {
+          float acc = pq[o];
+#pragma unroll
+          for (int k = 0; k < EIN; ++k) acc = fmaf(ein[k], s.wee[o * EIN + k], acc);
+          en[o] = fmaxf(acc, 0.f);
+        }
+        *reinterpret_cast<float4*>(s.e + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+        *reinterpret_cast<float2*>(s.e + j * EP + 4) = make_float2(en[4], en[5]);
+        if (p.e_dump) {
+#pragma unroll
+          for (int o = 0; o < FE; ++o) p.e_dump[((int64_t)step * p.n_edges + eb + j) * FE + o] = en[o];
+        }
+        if (classify) {
+          float logit = s.b2[0];
+#pragma unroll
+          for (int c = 0; c < HC; ++c) {
+            float hcv = s.b1[c];
+#pragma unroll
+            for (int k = 0; k < FE; ++k) hcv = fmaf(en[k], s.c1[c * FE + k], hcv);
+            logit = fmaf(fmaxf(hcv, 0.f), s.c2[c], logit);
+          }
+          st_stream_f1(logit_out + j, logit);
+        }
+      }
+      if (step == p.L && !p.h_dump) break;           // the last node update is dead (mpn.py:288-299)
+      __syncthreads();
+      // ---- phase B: a warp owns a node's whole out-edge segment, lane = feature; fixed summation order
+      for (int v = warp; v < n; v += nwarps) {
+        const float r = s.pqr[v * 44 + 2 * FE + lane];
+        const int j0 = s.rp[v], j1 = s.rp[v + 1];
+        float acc = agg_init(p.agg);
+        for (int j = j0; j < j1; ++j) {
+          const float4 u0 = *reinterpret_cast<const float4*>(s.e + j * EP);
+          const float2 u1 = *reinterpret_cast<const float2*>(s.e + j * EP + 4);
+          float m = r;
+          m = fmaf(u0.x, wne[0], m); m = fmaf(u0.y, wne[1], m); m = fmaf(u0.z, wne[2], m);
+          m = fmaf(u0.w, wne[3], m); m = fmaf(u1.x, wne[4], m); m = fmaf(u1.y, wne[5], m);
+          acc = agg_comb(p.agg, acc, fmaxf(m, 0.f));
+        }
+        if (j1 == j0) acc = 0.f;                                        // no out-edge: torch_scatter leaves 0
+        else if (p.agg == GNNCCA_AGG_MEAN) acc = acc / (float)(j1 - j0);
+        s.h[v * FN + lane] = acc;
+        if (p.h_dump) p.h_dump[((int64_t)step * p.n_nodes + a + v) * FN + lane] = acc;
+      }
+      __syncthreads();
+    }
+    __syncthreads();   // the next frame overwrites every buffer
+  }
+}
+
+}  // namespace fused
+}  // namespace gnncca
+
+using namespace gnncca;
+
+extern "C" int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* w_enc_edge,
+                                   const float* b_enc_edge, int32_t edge_in_dim, const int64_t* graph_ptr, int64_t n_graphs,
+                                   const int32_t* rowptr, const int32_t* src, const int32_t* dst, int64_t n_nodes,
+                                   int64_t n_edges, const float* h_enc, const float* edge_attr, int32_t num_steps,
+                                   int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges, float* logits,
+                                   float* h_dump, float* e_dump, int32_t* flags, void* stream) {
+  if (!cfg || !w || n_graphs < 0 || n_nodes < 0 || n_edges < 0 || num_steps < 1 || !flags) return GNNCCA_ERR_BAD_ARG;
+  if (n_graphs == 0 || n_nodes == 0) return GNNCCA_OK;
+  if (!graph_ptr || !rowptr || !h_enc || !w->w_edge || !w->b_edge || !w->w_node || !w->b_node || !w_enc_edge || !b_enc_edge)
+    return GNNCCA_ERR_BAD_ARG;
+  if (n_edges > 0 && (!src || !dst || !edge_attr)) return GNNCCA_ERR_BAD_ARG;
+  if (cfg->f_node != fused::FN || cfg->f_edge != fused::FE) return GNNCCA_ERR_UNSUPPORTED;
+  if (edge_in_dim < 1 || edge_in_dim > fused::MAX_FA) return GNNCCA_ERR_UNSUPPORTED;
+  if (cfg->agg < GNNCCA_AGG_SUM || cfg->agg > GNNCCA_AGG_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (cap_nodes < 1 || cap_nodes > 65535 || cap_edges < 1) return GNNCCA_ERR_BAD_ARG;
+  const bool has_cls = first_class_step <= num_steps;
+  if (has_cls && (cfg->cls_hidden != fused::HC || !w->w_c1 || !w->b_c1 || !w->w_c2 || !w->b_c2 || !logits || first_class_step < 1))
+    return cfg->cls_hidden != fused::HC ? GNNCCA_ERR_UNSUPPORTED : GNNCCA_ERR_BAD_ARG;
+  if ((((uintptr_t)h_enc | (uintptr_t)edge_attr) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
+
+  fused::Params p{};
+  p.graph_ptr = graph_ptr; p.n_graphs = n_graphs; p.n_nodes = n_nodes; p.n_edges = n_edges;
+  p.rowptr = rowptr; p.src = src; p.dst = dst; p.h_enc = h_enc; p.edge_attr = edge_attr; p.fa = edge_in_dim;
+  p.w_enc = w_enc_edge; p.b_enc = b_enc_edge; p.w = *w;
+  p.L = num_steps; p.first_cls = first_class_step; p.agg = cfg->agg;
+  p.reatt_n = cfg->reattach_nodes ? 1 : 0; p.reatt_e = cfg->reattach_edges ? 1 : 0; p.has_cls = has_cls ? 1 : 0;
+  p.cap_n = cap_nodes; p.cap_e = cap_edges; p.logits = logits; p.h_dump = h_dump; p.e_dump = e_dump; p.flags = flags;
+
+  fused::Smem lay;
+  const int K = p.reatt_n ? 64 : 32, EIN = p.reatt_e ? 12 : 6;
+  const size_t smem = fused::carve(lay, (float*)4096, K, EIN, cap_nodes, cap_edges, p.reatt_n != 0, p.reatt_e != 0);
+  if (smem > 227 * 1024) return GNNCCA_ERR_UNSUPPORTED;   // frame class too large for one CTA: use the per-step kernels
+  const int threads = cap_edges <= 512 ? 128 : 256;
+  int occ = (int)((227 * 1024) / (smem + 1024));
+  if (occ > 2048 / threads) occ = 2048 / threads;
+  if (occ < 1) occ = 1;
+  const int64_t want = (int64_t)kNumSMs * occ;
+  const int grid = (int)(n_graphs < want ? n_graphs : want);
+  cudaStream_t st = (cudaStream_t)stream;
+  auto kern = p.reatt_e ? fused::mp_fused_fwd_kernel<true> : fused::mp_fused_fwd_kernel<false>;
+  if (smem > 48 * 1024) {
+    int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    if (rc) return rc;
+  }
+  kern<<<grid, threads, smem, st>>>(p);
+  return check_launch();
+}

@@ -138,16 +138,57 @@ class StageTimer:
         return [(self.marks[i][0], self.marks[i - 1][1].elapsed_time(self.marks[i][1])) for i in range(1, len(self.marks))]
 
 
+CAP_NODE_CLASSES = (32, 64, 128, 256)
+CAP_EDGE_CLASSES = (512, 1024, 2048, 4096)
+
+
+def frame_capacity(model, N: int, E: int, B: int, hint=None):
+    """Capacity class (nodes, edges per frame) the fused all-steps kernel is launched for, or None when the frames
+    are too large for one CTA.  ``hint`` = exact (max nodes, max edges) when known (our batch builder records them);
+    otherwise 1.25 x the batch average, but never below the largest frame this model has met so far (a launch that
+    reports an overflow makes the host measure the true maxima, see ``forward_inference``)."""
+    if B <= 0:
+        return None
+    if hint is not None:
+        need_n, need_e = int(hint[0]), int(hint[1])
+    else:
+        seen = getattr(model, "_gnncca_caps_seen", (0, 0))
+        need_n = max(int(1.25 * N / B) + 1, seen[0])
+        need_e = max(int(1.25 * E / B) + 1, seen[1])
+    cn = next((c for c in CAP_NODE_CLASSES if c >= need_n), None)
+    ce = next((c for c in CAP_EDGE_CLASSES if c >= need_e), None)
+    if cn is None or ce is None:
+        return None
+    if model.reattach_initial_edges and ce > 2048:
+        return None
+    return cn, ce
+
+
+def measure_frames(graph_ptr: torch.Tensor, rowptr: torch.Tensor):
+    """(max nodes, max edges) over the frames; one small synchronising read back (slow path only)."""
+    gp = graph_ptr.long()
+    if gp.numel() < 2:
+        return 0, 0
+    ok = bool(((gp >= 0) & (gp < rowptr.numel())).all()) and bool((gp[1:] >= gp[:-1]).all())
+    if not ok:
+        raise ValueError("data.ptr is not a non-decreasing vector of node offsets in [0, num_nodes]")
+    ep = rowptr.long()[gp]
+    m = torch.stack([(gp[1:] - gp[:-1]).max(), (ep[1:] - ep[:-1]).max()]).cpu()
+    return int(m[0]), int(m[1])
+
+
 def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
                       plan: Optional[GraphPlan] = None, return_latents: bool = False, prof: Optional[StageTimer] = None,
-                      h_encoded: Optional[torch.Tensor] = None):
+                      h_encoded: Optional[torch.Tensor] = None, graph_ptr: Optional[torch.Tensor] = None, caps=None,
+                      allow_fused: bool = True, return_plan: bool = False):
     """``MOTMPNet.forward`` (models/mpn.py:250-299), no autograd graph.  Returns the list of per-step logits
     [E,1] in the caller's edge order.
 
-    The whole forward is enqueued optimistically on the assumption that ``edge_index`` is source-major (what the
-    reference's construction yields, train.py:292-299); the step kernels are no-ops when the CSR flags say
-    otherwise.  The 16-byte flag read-back happens after the last launch, so the device never waits for the host;
-    a batch that turns out not to be source-major is then sorted (stable) and run again.
+    Two device pipelines: when ``graph_ptr`` (PyG ``Batch.ptr``) is known and the frames are small, ALL steps run
+    in one launch with the latents held in shared memory (gnncca_mp_fused_fwd); otherwise one fused launch per
+    step (gnncca_mp_step_fwd).  Everything is enqueued optimistically -- the kernels are no-ops when the CSR
+    flags say the edges are not source-major -- and the 16-byte flag read-back happens after the last launch,
+    so the device never waits for the host; a batch that fails a check is then re-run on the safe path.
     ``h_encoded``: node latents already produced by the node encoder (used by ``forward_host``)."""
     lib = _lib.load()
     _require_cuda(edge_attr, "data.edge_attr")
@@ -161,11 +202,10 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     if plan is None:
         plan = GraphPlan(edge_index, N)          # async: narrow + order check + rowptr
     optimistic = not plan.resolved
-    guard = _lib.ptr(plan.flags) if optimistic else 0
     if prof is not None:
         prof.mark("csr")
     dev = edge_attr.device
-    # encoder (MLPGraphIndependent.forward, mpn.py:128-142)
+    # node encoder (MLPGraphIndependent.forward, mpn.py:128-142)
     if h_encoded is None:
         _require_cuda(x, "data.x")
         h = mlp_forward_nograd(model.encoder.node_mlp, x, math)
@@ -173,13 +213,58 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         h = h_encoded
     if prof is not None:
         prof.mark("encoder_node")
-    e = small_mlp_rows(model.encoder.edge_mlp, plan.to_sorted(edge_attr.contiguous()))
-    if prof is not None:
-        prof.mark("encoder_edge")
-    h0, e0 = h, e
     sb = StepBinding(model, math)
     L, k = model.num_enc_steps, model.num_class_steps
     first_class_step = L - k + 1                                            # mpn.py:277
+    ea_sorted = plan.to_sorted(edge_attr.contiguous())
+
+    cap = None
+    B = int(graph_ptr.numel()) - 1 if graph_ptr is not None else 0
+    if allow_fused and graph_ptr is not None and L >= 1 and E > 0 and ea_sorted.size(1) <= 8 and first_class_step >= 1:
+        cap = frame_capacity(model, N, E, B, caps)
+    if cap is not None:
+        gp = graph_ptr.to(device=dev, dtype=torch.int64).contiguous()
+        n_cls = max(0, L - first_class_step + 1)
+        logits = torch.empty((max(n_cls, 1), E), dtype=torch.float32, device=dev)
+        h_dump = torch.empty((L + 1, N, sb.f_node), dtype=torch.float32, device=dev) if return_latents else None
+        e_dump = torch.empty((L + 1, E, sb.f_edge), dtype=torch.float32, device=dev) if return_latents else None
+        enc_e = model.encoder.edge_mlp
+        if len(enc_e.layer_specs) != 1 or not enc_e.layer_specs[0].relu or enc_e.layer_specs[0].bn is not None:
+            raise NotImplementedError("fused pipeline: the edge encoder must be a single Linear+ReLU (edge_fc_dims=[])")
+        _lib.check(lib.gnncca_mp_fused_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(enc_e.linear(0).weight), _lib.ptr(enc_e.linear(0).bias),
+                                           int(ea_sorted.size(1)), _lib.ptr(gp), B, _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
+                                           _lib.ptr(plan.dst), N, E, _lib.ptr(h), _lib.ptr(ea_sorted), L, first_class_step, cap[0], cap[1],
+                                           _lib.ptr(logits), _lib.ptr(h_dump), _lib.ptr(e_dump), _lib.ptr(plan.flags), _stream()),
+                   "mp_fused_fwd")
+        if prof is not None:
+            prof.mark("mp_fused")
+        plan.request_flags()
+        ok_order = plan.source_major()
+        if not ok_order or plan.frames_overflowed():
+            if ok_order:        # a frame larger than the class, or an edge leaving its frame
+                plan.clear_overflow()
+                plan._resolved = True
+                true_caps = measure_frames(gp, plan.rowptr)
+                seen = getattr(model, "_gnncca_caps_seen", (0, 0))
+                model._gnncca_caps_seen = (max(seen[0], true_caps[0]), max(seen[1], true_caps[1]))
+                retry = (true_caps[0] > cap[0] or true_caps[1] > cap[1]) and frame_capacity(model, N, E, B, true_caps) is not None
+                return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h, graph_ptr,
+                                         true_caps if retry else None, retry, return_plan)
+            plan.resolve()
+            return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h, graph_ptr, caps, True, return_plan)
+        plan._resolved = True
+        plan.last_path = "fused"
+        outs = [plan.to_caller(logits[i].view(E, 1)) for i in range(n_cls)]
+        if return_latents:
+            return outs, [(h_dump[i], e_dump[i]) for i in range(L + 1)], plan
+        return (outs, plan) if return_plan else outs
+
+    # ------------------------------------------------------------------ general path: one fused launch per step
+    guard = _lib.ptr(plan.flags) if optimistic else 0
+    e = small_mlp_rows(model.encoder.edge_mlp, ea_sorted)
+    if prof is not None:
+        prof.mark("encoder_edge")
+    h0, e0 = h, e
     outs: List[torch.Tensor] = []
     latents = [(h, e)]
     if L > 0:
@@ -212,15 +297,21 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
                 prof.mark("step%d" % step)
     else:
         outs.append(plan.to_caller(small_mlp_rows_cls(model, e)))            # mpn.py:295-297
-    if optimistic and not plan.source_major():
-        plan.resolve()   # stable sort by source; outputs go back to the caller's edge order
-        return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h0)
+    if optimistic:
+        plan.request_flags()
+        if not plan.source_major():
+            plan.resolve()   # stable sort by source; outputs go back to the caller's edge order
+            return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h0, graph_ptr, caps, allow_fused, return_plan)
     plan._resolved = True
-    return (outs, latents, plan) if return_latents else outs
+    plan.last_path = "steps"
+    if return_latents:
+        return outs, latents, plan
+    return (outs, plan) if return_plan else outs
 
 
 def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor, out: Optional[List[torch.Tensor]] = None,
-                 device: Optional[torch.device] = None, n_chunks: int = 8) -> List[torch.Tensor]:
+                 device: Optional[torch.device] = None, n_chunks: int = 8, graph_ptr: Optional[torch.Tensor] = None,
+                 caps=None) -> List[torch.Tensor]:
     """The same forward for HOST buffers (pinned memory recommended): the inputs are copied to the device on a
     side stream in row chunks, the node encoder of chunk i runs while chunk i+1 is in flight, and the per-step
     logits are copied back into ``out`` (host tensors [E,1]; allocated pinned when None).  Returns ``out``
@@ -260,7 +351,9 @@ def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: to
         cur.wait_event(ev)
         if b > a:
             mlp_forward_nograd(enc, x_d[a:b], math, out=h[a:b])
-    outs = forward_inference(model, x_d, ei_d, ea_d, plan, h_encoded=h)
+    if graph_ptr is not None and not graph_ptr.is_cuda:
+        graph_ptr = graph_ptr.to(dev, non_blocking=True)
+    outs = forward_inference(model, x_d, ei_d, ea_d, plan, h_encoded=h, graph_ptr=graph_ptr, caps=caps)
     if out is None:
         out = [torch.empty((E, 1), dtype=torch.float32, pin_memory=True) for _ in outs]
     for o, d in zip(out, outs):

@@ -83,8 +83,12 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     # the output size is data dependent: one 16-byte read back (the reference syncs several times per FRAME)
     tile_total_addr = lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N)
     off = (tile_total_addr - scratch.data_ptr()) // 8
-    totals = torch.stack([edge_ptr[B], scratch[off]]).cpu()
+    counts = graph_ptr[1:] - graph_ptr[:-1]
+    ecounts = edge_ptr[1:] - edge_ptr[:-1]
+    zero = torch.zeros((), dtype=torch.int64, device=dev)
+    totals = torch.stack([edge_ptr[B], scratch[off], counts.max() if B > 0 else zero, ecounts.max() if B > 0 else zero]).cpu()
     E, n_tiles = int(totals[0]), int(totals[1])
+    caps = (int(totals[2]), int(totals[3]))      # exact frame maxima: sizes the fused all-steps kernel without guessing
 
     width = 4 if mode == "full" else 2
     edge_index = torch.empty((2, E), dtype=torch.int64, device=dev)
@@ -94,7 +98,6 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
                                        _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
                                        int(reid.size(1)), attr_mode, _lib.ptr(scratch), _lib.ptr(edge_index),
                                        _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
-    counts = graph_ptr[1:] - graph_ptr[:-1]
     batch_vec = torch.repeat_interleave(torch.arange(B, device=dev), counts, output_size=N)
     return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64, batch=batch_vec,
-                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B)
+                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps)

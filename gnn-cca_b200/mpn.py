@@ -138,18 +138,21 @@ class MOTMPNet(nn.Module):
         from . import autograd_fn, engine
         x, edge_index, edge_attr = data.x, data.edge_index, data.edge_attr
         plan = getattr(data, "gnncca_plan", None)
+        graph_ptr = getattr(data, "ptr", None)             # PyG Batch.ptr / our Batch.ptr: frame boundaries, when known
+        caps = getattr(data, "gnncca_caps", None)
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
         if needs_grad or (self.training and self._has_batchnorm()):
             outs = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan)
         else:
-            outs = engine.forward_inference(self, x, edge_index, edge_attr, plan)
+            outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps, return_plan=True)
+            self.last_plan = plan       # introspection only (which device pipeline ran, the CSR)
         return {'classified_edges': outs}
 
-    def forward_host(self, x, edge_index, edge_attr, out=None):
+    def forward_host(self, x, edge_index, edge_attr, out=None, graph_ptr=None, caps=None):
         """The same forward for HOST tensors (pinned memory recommended): chunked host->device copies overlap the
         node encoder, per-step logits are copied back into ``out`` (list of host tensors [E,1])."""
         from . import engine
-        return engine.forward_host(self, x, edge_index, edge_attr, out=out)
+        return engine.forward_host(self, x, edge_index, edge_attr, out=out, graph_ptr=graph_ptr, caps=caps)
 
     def _has_batchnorm(self) -> bool:
         return any(isinstance(m, nn.BatchNorm1d) for m in self.modules())

@@ -37,17 +37,33 @@ class GraphPlan:
         _lib.check(self.lib.gnncca_csr_from_edge_index(_lib.ptr(self.edge_index), self.N, self.E, _lib.ptr(self.src),
                                                        _lib.ptr(self.dst), _lib.ptr(self.rowptr), _lib.ptr(self.flags),
                                                        _stream()), "csr_from_edge_index")
-        self._flags_host.copy_(self.flags, non_blocking=True)
-        self._event.record()
+        self._requested = False
 
     @property
     def resolved(self) -> bool:
         return self._resolved
 
+    def request_flags(self) -> None:
+        """Enqueue the 16-byte read back of the flags behind everything launched so far (non-blocking)."""
+        self._flags_host.copy_(self.flags, non_blocking=True)
+        self._event.record()
+        self._requested = True
+
+    def frames_overflowed(self) -> bool:
+        """flags[2]: raised by gnncca_mp_fused_fwd when a frame did not fit its capacity class (valid after
+        ``source_major()``)."""
+        return bool(int(self._flags_host[2]))
+
+    def clear_overflow(self) -> None:
+        self.flags[2:3].zero_()
+
     def source_major(self) -> bool:
         """Wait for the order / range flags (a 16-byte read back) and report whether the caller's edge order is
         already source-major (what train.py:292-299 produces).  Raises on out-of-range indices."""
+        if not self._requested:
+            self.request_flags()
         self._event.synchronize()
+        self._requested = False
         if int(self._flags_host[1]):
             raise IndexError("edge_index has entries outside [0, num_nodes=%d)" % self.N)
         return not int(self._flags_host[0])

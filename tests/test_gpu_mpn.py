@@ -36,18 +36,38 @@ def build_model(z, device, math="fp32"):
 
 
 class D:
-    def __init__(self, x, ei, ea):
+    def __init__(self, x, ei, ea, ptr=None):
         self.x, self.edge_index, self.edge_attr = x, ei, ea
+        if ptr is not None:
+            self.ptr = ptr
 
 
+def frame_ptr(ei, n_nodes):
+    """Finest partition of the node range into contiguous blocks that no edge crosses (what PyG's Batch.ptr is
+    for a disjoint union of frames): a cut before node v is allowed iff no edge has min(s,d) < v <= max(s,d)."""
+    ei = ei.cpu().numpy()
+    lo, hi = np.minimum(ei[0], ei[1]), np.maximum(ei[0], ei[1])
+    diff = np.zeros(n_nodes + 2, dtype=np.int64)
+    np.add.at(diff, lo + 1, 1)
+    np.add.at(diff, hi + 1, -1)
+    cover = np.cumsum(diff)[: n_nodes + 1]          # cover[v] = number of edges with lo < v <= hi
+    cuts = [v for v in range(n_nodes + 1) if cover[v] == 0]
+    return torch.tensor(cuts, dtype=torch.int64)
+
+
+@pytest.mark.parametrize("path", ["steps", "fused"])
 @pytest.mark.parametrize("case", [c for c in golden_cases("mpn_") if c.endswith("_eval")])
-def test_forward_matches_reference_vectors(case, cuda_device):
+def test_forward_matches_reference_vectors(case, path, cuda_device):
+    """Both device pipelines (one launch per step / all steps in one launch) against the reference's own outputs."""
     z = load_golden("mpn_" + case)
     model = build_model(z, cuda_device).eval()
-    data = D(torch.from_numpy(z["x"]).to(cuda_device), torch.from_numpy(z["edge_index"]).to(cuda_device),
-             torch.from_numpy(z["edge_attr"]).to(cuda_device))
+    ei = torch.from_numpy(z["edge_index"])
+    ptr = frame_ptr(ei, z["x"].shape[0]).to(cuda_device) if path == "fused" else None
+    data = D(torch.from_numpy(z["x"]).to(cuda_device), ei.to(cuda_device), torch.from_numpy(z["edge_attr"]).to(cuda_device), ptr)
     with torch.no_grad():
         out = model(data)["classified_edges"]
+    if int(z["n_steps"]) and json.loads(str(z["config"]))["num_enc_steps"] > 0:
+        assert model.last_plan.last_path == path
     assert len(out) == int(z["n_steps"])
     for i, o in enumerate(out):
         ref = torch.from_numpy(z["logits/%d" % i])
@@ -76,9 +96,10 @@ def synthetic_graph(n_cams, n_dets, n_graphs, seed, f_x=512, ragged=0.0):
     return x, ei, ea
 
 
+@pytest.mark.parametrize("path", ["steps", "fused"])
 @pytest.mark.parametrize("shape", [(4, 9, 64, 0.0), (4, 6, 200, 0.47), (8, 64, 2, 0.0), (3, 300, 1, 0.0), (2, 1, 5, 0.0)])
 @pytest.mark.parametrize("agg", ["sum", "mean", "max"])
-def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, cuda_device):
+def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, path, cuda_device):
     """cfg-1 shape, ragged EPFL-like frames, the cfg-4 per-graph shape (degree 448: segments span tiles and
     warps), a degree-600 graph (segments span 3 tiles) and degenerate 2-node frames."""
     import gnncca
@@ -86,6 +107,8 @@ def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, cuda_device):
     cfgmod = import_module("gnn-cca_b200.config")
     if agg != "sum" and shape[2] > 100:
         pytest.skip("covered by the sum variant")
+    if path == "fused" and shape[0] * shape[1] > 256:
+        pytest.skip("frames larger than one CTA's shared memory always take the per-step path")
     params = cfgmod.graph_net_params()
     params["node_agg_fn"] = agg
     torch.manual_seed(0)
@@ -98,7 +121,10 @@ def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, cuda_device):
     from importlib import import_module
     engine = import_module("gnn-cca_b200.engine")
     with torch.no_grad():
-        outs, lat, _ = engine.forward_inference(model, x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device), return_latents=True)
+        ptr = frame_ptr(ei, x.size(0)).to(cuda_device) if path == "fused" else None
+        outs, lat, plan = engine.forward_inference(model, x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device), return_latents=True,
+                                                   graph_ptr=ptr)
+    assert plan.last_path == path
     for step, ((h, e), (rh, re)) in enumerate(zip(lat, ref_lat)):
         assert close(e, re) <= FP32_RTOL, ("edge latent", step, close(e, re))
         assert close(h, rh) <= FP32_RTOL, ("node latent", step, close(h, rh))
@@ -136,3 +162,62 @@ def test_cpu_tensors_fail_loudly():
     with pytest.raises(RuntimeError):
         with torch.no_grad():
             model(D(x, ei, ea))
+
+
+def _frames(sizes, seed=5, f_x=512):
+    """Disjoint union of complete 2-camera frames with the given detections per camera."""
+    parts, first = [], 0
+    for d in sizes:
+        cam = np.repeat(np.arange(2), d)
+        i, j = np.nonzero(cam[:, None] != cam[None, :])
+        parts.append(np.stack([i + first, j + first]))
+        first += cam.size
+    ei = torch.from_numpy(np.concatenate(parts, axis=1)).long()
+    g = torch.Generator().manual_seed(seed)
+    x = torch.relu(torch.randn(first, f_x, generator=g))
+    x = x / x.norm(dim=0).clamp_min(1e-12)
+    return x, ei, torch.rand(ei.size(1), 4, generator=g)
+
+
+@pytest.mark.parametrize("sizes,expect", [([1] * 60 + [20], "fused"),        # one frame far above the batch average: re-sized, still fused
+                                           ([1] * 60 + [70], "steps")])       # 9800 edges in one frame: beyond one CTA -> per-step kernels
+def test_fused_pipeline_resizes_or_falls_back_to_step_kernels(sizes, expect, cuda_device):
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(2)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    spec = mpn_oracle.MPNSpec(params, "bdnet_market")
+    x, ei, ea = _frames(sizes)
+    with torch.no_grad():
+        ref = mpn_oracle.motmpnet_forward(spec, model.state_dict(), x, ei, ea)["classified_edges"]
+    model = model.to(cuda_device)
+    data = D(x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device), frame_ptr(ei, x.size(0)).to(cuda_device))
+    with torch.no_grad():
+        out = model(data)["classified_edges"]
+        assert model.last_plan.last_path == expect
+        for o, r in zip(out, ref):
+            assert close(o, r) <= FP32_RTOL
+        again = model(data)["classified_edges"]          # the model remembers the largest frame it has met
+        for a, b in zip(out, again):
+            assert torch.equal(a, b)
+
+
+def test_fused_pipeline_rejects_a_ptr_that_cuts_through_edges(cuda_device):
+    """A wrong data.ptr (an edge leaves its frame) is detected on the device; the result still matches."""
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(2)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    spec = mpn_oracle.MPNSpec(params, "bdnet_market")
+    x, ei, ea = _frames([3, 4, 5])
+    with torch.no_grad():
+        ref = mpn_oracle.motmpnet_forward(spec, model.state_dict(), x, ei, ea)["classified_edges"]
+    model = model.to(cuda_device)
+    bad_ptr = torch.tensor([0, 3, 14, 24], device=cuda_device)     # true boundaries are 0, 6, 14, 24
+    with torch.no_grad():
+        out = model(D(x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device), bad_ptr))["classified_edges"]
+    assert model.last_plan.last_path == "steps"
+    for o, r in zip(out, ref):
+        assert close(o, r) <= FP32_RTOL
