@@ -253,7 +253,8 @@ def main():
 
     def step(i, prof=None):
         b = batches[i & 1]
-        return engine.forward_inference(model, b.x, b.edge_index, b.edge_attr, prof=prof, graph_ptr=b.ptr, caps=b.gnncca_caps)
+        return engine.forward_inference(model, b.x, b.edge_index, b.edge_attr, prof=prof, graph_ptr=b.ptr, caps=b.gnncca_caps,
+                                        trusted=True)   # batches come from build_graph_batch; the CSR is rebuilt every step
 
     def barrier():
         if world > 1:

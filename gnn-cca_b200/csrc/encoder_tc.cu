@@ -100,16 +100,26 @@ struct Params {
   const float* b1; const float* W2; const float* b2;
   float* h_out;
   int64_t rows;
-  int K, H, num_tiles, stages;
+  int K, H, stages;
+  int rows_per_cta;          // multiple of 8: CTA c owns rows [c * rows_per_cta, (c+1) * rows_per_cta)
 };
 
+struct XMaps { CUtensorMap m[5]; };   // x viewed with boxes of 8, 16, 32, 64, 128 rows x 32 floats
+
+// Work decomposition.  A CTA owns ONE contiguous row range sized so that all SMs finish together (rows / grid, a
+// multiple of 8) and walks it in "super tiles" of up to 256 rows = two M=128 MMA tiles that SHARE every W1 stage:
+// per k-block the CTA ingests (rows x 128 B of x) + (H x 128 B of W1), so the L2->SM traffic spent on re-reading
+// W1 is amortised over up to 256 rows instead of 128, and partial tiles load only the rows they own (8-row
+// granular TMA boxes), never a neighbour's.
 template <int H>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, const Params p) {
-  constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;       // 16 KB
+node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_constant__ CUtensorMap tmap_w, const Params p) {
+  constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;       // 16 KB per sub-tile
   constexpr uint32_t B_BYTES = H * BLOCK_K * 4;
-  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr uint32_t TMEM_COLS = (2 * H <= 32) ? 32 : (2 * H <= 64) ? 64 : (2 * H <= 128) ? 128 : (2 * H <= 256) ? 256 : 512;
+  constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + B_BYTES;
+  constexpr int NBUF = (4 * H <= 512) ? 2 : 1;              // accumulator double buffering when TMEM allows
+  constexpr uint32_t TMEM_NEED = 2 * H * NBUF;
+  constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
   constexpr uint32_t IDESC = make_idesc(BLOCK_M, H);
   constexpr uint64_t HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull;
 
@@ -127,16 +137,21 @@ node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row_begin = (int64_t)blockIdx.x * p.rows_per_cta;
+  const int64_t row_end = min(row_begin + p.rows_per_cta, p.rows);
+  const int my_rows = (int)(row_end - row_begin);
+  const int n_super = (my_rows + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
 
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
+#pragma unroll
+    for (int i = 0; i < 5; ++i) asm volatile("prefetch.tensormap [%0];" ::"l"(&xmaps.m[i]) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
     for (int s = 0; s < NS; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 1) {   // TMEM: 2 accumulators of H columns (this warp also frees them)
+  if (warp == 1) {   // TMEM accumulators (this warp also frees them)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -155,13 +170,24 @@ node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   if (warp == 0) {
     if (lane == 0) {   // ------------------------------------------------ TMA producer
       int s = 0; uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int st = 0; st < n_super; ++st) {
+        const int64_t r0 = row_begin + (int64_t)st * 2 * BLOCK_M;
+        const int rem = my_rows - st * 2 * BLOCK_M;
+        const int rows8 = (min(rem, 2 * BLOCK_M) + 7) & ~7;          // rows of x this super tile loads (8-row boxes)
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(empty + s, ph ^ 1);
           uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
-          mbar_expect_tx(full + s, STAGE_BYTES);
-          tma_load_2d(a, &tmap_x, full + s, kb * BLOCK_K, tile * BLOCK_M, HINT_EVICT_FIRST);
-          tma_load_2d(a + A_BYTES, &tmap_w, full + s, kb * BLOCK_K, 0, HINT_EVICT_LAST);
+          mbar_expect_tx(full + s, (uint32_t)rows8 * (BLOCK_K * 4) + B_BYTES);
+          tma_load_2d(a + 2 * A_BYTES, &tmap_w, full + s, kb * BLOCK_K, 0, HINT_EVICT_LAST);
+          int off = 0;                                               // sub-tile 1 continues at row 128 = byte offset A_BYTES
+#pragma unroll
+          for (int b = 4; b >= 0; --b) {
+            const int sz = 8 << b;
+            while (rows8 - off >= sz && (off % BLOCK_M) + sz <= BLOCK_M) {
+              tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[b], full + s, kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST);
+              off += sz;
+            }
+          }
           if (++s == NS) { s = 0; ph ^= 1; }
         }
       }
@@ -169,21 +195,25 @@ node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   } else if (warp == 1) {
     if (lane == 0) {   // ------------------------------------------------ MMA issuer
       int s = 0; uint32_t ph = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aph = (it >> 1) & 1;
-        mbar_wait(tmem_empty + as, aph ^ 1);     // epilogue has drained this accumulator
+      for (int st = 0; st < n_super; ++st) {
+        const int as = NBUF == 2 ? (st & 1) : 0;
+        const uint32_t aph = NBUF == 2 ? ((st >> 1) & 1) : (st & 1);
+        const int rem = my_rows - st * 2 * BLOCK_M;
+        const int nt = rem > BLOCK_M ? 2 : 1;
+        mbar_wait(tmem_empty + as, aph ^ 1);     // epilogue has drained this accumulator pair
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(as * H);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * 2 * H);
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(full + s, ph);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
-          const uint64_t adesc = make_smem_desc(a_addr), bdesc = make_smem_desc(a_addr + A_BYTES);
+          const uint64_t bdesc = make_smem_desc(a_addr + 2 * A_BYTES);
+          for (int t = 0; t < nt; ++t) {
+            const uint64_t adesc = make_smem_desc(a_addr + t * A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)   // +32 bytes along K inside the swizzle atom = +2 in the (>>4) address field
-            umma_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (uint32_t)((kb | k) != 0));
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)   // +32 bytes along K inside the swizzle atom = +2 in the (>>4) address field
+              umma_tf32(d_tmem + (uint32_t)(t * H), adesc + 2 * k, bdesc + 2 * k, IDESC, (uint32_t)((kb | k) != 0));
+          }
           umma_commit(empty + s);                  // stage reusable once these MMAs have read it
           if (kb == KB - 1) umma_commit(tmem_full + as);
           if (++s == NS) { s = 0; ph ^= 1; }
@@ -193,46 +223,50 @@ node_encoder_tf32_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   } else {             // ---------------------------------------------------- epilogue: one node row per thread
     const int q = warp & 3;                         // TMEM lane quarter this warp may access
     const int row_in_tile = q * 32 + lane;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aph = (it >> 1) & 1;
+    for (int st = 0; st < n_super; ++st) {
+      const int as = NBUF == 2 ? (st & 1) : 0;
+      const uint32_t aph = NBUF == 2 ? ((st >> 1) & 1) : (st & 1);
+      const int rem = my_rows - st * 2 * BLOCK_M;
       mbar_wait(tmem_full + as, aph);
       tc_fence_after();
-      float out[F_OUT];
-#pragma unroll
-      for (int o = 0; o < F_OUT; ++o) out[o] = b2s[o];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * H);
 #pragma unroll 1
-      for (int c = 0; c < H / 32; ++c) {
-        float v[32];
-        tmem_ld32(taddr + c * 32, v);
-        if (c == H / 32 - 1) {                      // accumulator fully read: hand it back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(tmem_empty + as);
-        }
+      for (int t = 0; t < 2; ++t) {
+        const int valid = min(rem - t * BLOCK_M, BLOCK_M);             // rows of this sub-tile that exist
+        if (q * 32 < valid) {                                          // warp-uniform: skip quarters with no row at all
+          float out[F_OUT];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float hj = fmaxf(v[j] + b1s[c * 32 + j], 0.f);            // Linear + ReLU (mlp.py:14,18)
-          const float4* wr = reinterpret_cast<const float4*>(w2t + (c * 32 + j) * F_OUT);
+          for (int o = 0; o < F_OUT; ++o) out[o] = b2s[o];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 2 * H + t * H);
+#pragma unroll 1
+          for (int c = 0; c < H / 32; ++c) {
+            float v[32];
+            tmem_ld32(taddr + c * 32, v);
 #pragma unroll
-          for (int o4 = 0; o4 < F_OUT / 4; ++o4) {
-            const float4 w = wr[o4];                                        // same address in every lane: broadcast
-            out[4 * o4 + 0] = fmaf(hj, w.x, out[4 * o4 + 0]);
-            out[4 * o4 + 1] = fmaf(hj, w.y, out[4 * o4 + 1]);
-            out[4 * o4 + 2] = fmaf(hj, w.z, out[4 * o4 + 2]);
-            out[4 * o4 + 3] = fmaf(hj, w.w, out[4 * o4 + 3]);
+            for (int j = 0; j < 32; ++j) {
+              const float hj = fmaxf(v[j] + b1s[c * 32 + j], 0.f);            // Linear + ReLU (mlp.py:14,18)
+              const float4* wr = reinterpret_cast<const float4*>(w2t + (c * 32 + j) * F_OUT);
+#pragma unroll
+              for (int o4 = 0; o4 < F_OUT / 4; ++o4) {
+                const float4 w = wr[o4];                                        // same address in every lane: broadcast
+                out[4 * o4 + 0] = fmaf(hj, w.x, out[4 * o4 + 0]);
+                out[4 * o4 + 1] = fmaf(hj, w.y, out[4 * o4 + 1]);
+                out[4 * o4 + 2] = fmaf(hj, w.z, out[4 * o4 + 2]);
+                out[4 * o4 + 3] = fmaf(hj, w.w, out[4 * o4 + 3]);
+              }
+            }
+          }
+          if (row_in_tile < valid) {
+            const int64_t row = row_begin + (int64_t)st * 2 * BLOCK_M + t * BLOCK_M + row_in_tile;
+            float4* dst = reinterpret_cast<float4*>(p.h_out + row * F_OUT);
+#pragma unroll
+            for (int o4 = 0; o4 < F_OUT / 4; ++o4)
+              dst[o4] = make_float4(fmaxf(out[4 * o4], 0.f), fmaxf(out[4 * o4 + 1], 0.f), fmaxf(out[4 * o4 + 2], 0.f), fmaxf(out[4 * o4 + 3], 0.f));
           }
         }
       }
-      const int64_t row = (int64_t)tile * BLOCK_M + row_in_tile;
-      if (row < p.rows) {
-        float4* dst = reinterpret_cast<float4*>(p.h_out + row * F_OUT);
-#pragma unroll
-        for (int o4 = 0; o4 < F_OUT / 4; ++o4)
-          dst[o4] = make_float4(fmaxf(out[4 * o4], 0.f), fmaxf(out[4 * o4 + 1], 0.f), fmaxf(out[4 * o4 + 2], 0.f), fmaxf(out[4 * o4 + 3], 0.f));
-      }
+      tc_fence_before();                              // both accumulators fully read: hand the pair back to the MMA warp
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty + as);
     }
   }
   tc_fence_before();
@@ -281,27 +315,35 @@ bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, i
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+
 template <int H>
 int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaStream_t st) {
   enc::Params p = p0;
-  const size_t stage = (size_t)(enc::BLOCK_M + H) * enc::BLOCK_K * 4;
+  const size_t stage = (size_t)(2 * enc::BLOCK_M + H) * enc::BLOCK_K * 4;
   const size_t fixed = 1024 /*alignment slack*/ + sizeof(float) * (H * enc::F_OUT + H + enc::F_OUT) + 8 * (2 * enc::MAX_STAGES + 4) + 16;
   int stages = (int)((227 * 1024 - fixed) / stage);
   if (stages > enc::MAX_STAGES) stages = enc::MAX_STAGES;
   if (stages < 2) return GNNCCA_ERR_UNSUPPORTED;
   p.stages = stages;
   const size_t smem = fixed + stage * stages;
-  CUtensorMap mx, mw;
-  if (!make_map(&mx, x, p.rows, p.K, enc::BLOCK_M) || !make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
+  // every SM gets the same number of rows (8-row granules); grids smaller than the machine only for tiny inputs
+  int64_t rpc = (ceil_div(p.rows, kNumSMs) + 7) & ~(int64_t)7;
+  if (rpc < 8) rpc = 8;
+  p.rows_per_cta = (int)rpc;
+  const int grid = (int)ceil_div(p.rows, rpc);
+  enc::XMaps xm;
+  CUtensorMap mw;
+  for (int b = 0; b < 5; ++b)
+    if (!make_map(&xm.m[b], x, p.rows, p.K, 8 << b)) return GNNCCA_ERR_LAUNCH;
+  if (!make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
   auto kern = enc::node_encoder_tf32_kernel<H>;
   static bool configured = false;
   if (!configured) {
-    int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     if (rc) return rc;
     configured = true;
   }
-  const int grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
-  kern<<<grid, enc::NUM_THREADS, smem, st>>>(mx, mw, p);
+  kern<<<grid, enc::NUM_THREADS, smem, st>>>(xm, mw, p);
   return check_launch();
 }
 
@@ -313,10 +355,9 @@ int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, c
                              int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream) {
   if (out_dim != enc::F_OUT || in_dim % enc::BLOCK_K != 0 || in_dim < enc::BLOCK_K) return GNNCCA_ERR_UNSUPPORTED;
   if ((((uintptr_t)x | (uintptr_t)W1 | (uintptr_t)h) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
-  if (rows >= ((int64_t)1 << 31) * enc::BLOCK_M) return GNNCCA_ERR_BAD_ARG;
+  if (rows >= ((int64_t)1 << 31)) return GNNCCA_ERR_BAD_ARG;
   enc::Params p{};
   p.b1 = b1; p.W2 = W2; p.b2 = b2; p.h_out = h; p.rows = rows; p.K = in_dim; p.H = hidden;
-  p.num_tiles = (int)ceil_div(rows, enc::BLOCK_M);
   cudaStream_t st = (cudaStream_t)stream;
   switch (hidden) {
     case 64: return launch_encoder<64>(x, W1, p, st);

@@ -17,6 +17,7 @@ namespace gnncca {
 namespace fused {
 
 constexpr int FN = 32, FE = 6, HC = 4, EP = 8;   // node width, edge width, classifier hidden, padded edge row
+constexpr int HS = 36;                            // shared-memory row stride of the node latents: rows of different nodes start in different banks
 constexpr int MAX_FA = 8;                         // widest raw edge attribute row supported
 
 struct Params {
@@ -36,26 +37,28 @@ struct Params {
 __device__ __forceinline__ float agg_init(int agg) { return agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f; }
 __device__ __forceinline__ float agg_comb(int agg, float a, float b) { return agg == GNNCCA_AGG_MAX ? fmaxf(a, b) : a + b; }
 
+// Offsets (in floats) from the dynamic shared-memory base: integer offsets instead of pointers keep every access
+// provably in the shared address space (LDS/STS, not generic LD/ST with runtime address-space checks).
 struct Smem {
-  float* wproj;   // [K][44]   transposed projection weights: outputs 0..5 P, 6..11 Q, 12..43 R
-  float* bproj;   // [44]
-  float* wee;     // [FE][EIN]
-  float* wne;     // [FE][FN]
-  float* wenc;    // [FE][MAX_FA] , benc [FE]
-  float* benc;
-  float* c1;      // [HC][FE] (BatchNorm eval folded), b1 [HC], c2 [HC], b2 [1]
-  float* b1; float* c2; float* b2;
-  float* h;       // [cap_n][FN]
-  float* h0;      // [cap_n][FN] (reattach_nodes)
-  float* pqr;     // [cap_n][44]  per node: P (6, edge-update source part + bias) | Q (6, target part) | R (32, node-update part + bias)
-  float* e;       // [cap_e][EP]
-  float* e0;      // [cap_e][EP] (reattach_edges)
-  int* rp;        // [cap_n + 1]
-  uint16_t* sl; uint16_t* dl;   // [cap_e] local source / target
+  int wproj;   // [K][44]   transposed projection weights: outputs 0..5 P, 6..11 Q, 12..43 R
+  int bproj;   // [44]
+  int wee;     // [FE][EIN]
+  int wne;     // [FE][FN]
+  int wenc;    // [FE][MAX_FA] , benc [FE]
+  int benc;
+  int c1;      // [HC][FE] (BatchNorm eval folded), b1 [HC], c2 [HC], b2 [1]
+  int b1, c2, b2;
+  int h;       // [cap_n][HS]
+  int h0;      // [cap_n][HS] (reattach_nodes)
+  int pqr;     // [cap_n][44]  per node: P (6, edge-update source part + bias) | Q (6, target part) | R (32, node-update part + bias)
+  int e;       // [cap_e][EP]
+  int e0;      // [cap_e][EP] (reattach_edges)
+  int rp;      // int [cap_n + 1]
+  int sl, dl;  // uint16 [cap_e] local source / target
 };
 
-__host__ __device__ inline size_t carve(Smem& s, float* base, int K, int EIN, int cap_n, int cap_e, bool rn, bool re) {
-  float* p = base;
+__host__ __device__ inline size_t carve(Smem& s, int K, int EIN, int cap_n, int cap_e, bool rn, bool re) {
+  int p = 0;
   s.wproj = p; p += K * 44;
   s.bproj = p; p += 44;
   s.wee = p; p += FE * EIN;
@@ -64,28 +67,29 @@ __host__ __device__ inline size_t carve(Smem& s, float* base, int K, int EIN, in
   s.benc = p; p += 8;
   s.c1 = p; p += HC * FE;
   s.b1 = p; p += HC; s.c2 = p; p += HC; s.b2 = p; p += 4;
-  p = (float*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
-  s.h = p; p += cap_n * FN;
-  s.h0 = p; if (rn) p += cap_n * FN;
+  p = (p + 3) & ~3;
+  s.h = p; p += cap_n * HS;
+  s.h0 = p; if (rn) p += cap_n * HS;
   s.pqr = p; p += cap_n * 44;
-  s.e = p; p += (size_t)cap_e * EP;
-  s.e0 = p; if (re) p += (size_t)cap_e * EP;
-  s.rp = (int*)p; p += ((cap_n + 1 + 3) & ~3);
-  s.sl = (uint16_t*)p; p += (cap_e + 1) / 2;
-  p = (float*)(((uintptr_t)p + 15) & ~(uintptr_t)15);
-  s.dl = (uint16_t*)p; p += (cap_e + 1) / 2;
-  return (size_t)((char*)p - (char*)base) + 16;
+  s.e = p; p += cap_e * EP;
+  s.e0 = p; if (re) p += cap_e * EP;
+  s.rp = p; p += ((cap_n + 1 + 3) & ~3);
+  s.sl = p; p += ((cap_e + 1) / 2 + 3) & ~3;
+  s.dl = p; p += ((cap_e + 1) / 2 + 3) & ~3;
+  return (size_t)p * sizeof(float) + 16;
 }
 
-template <bool REATT_E>
+template <bool REATT_E, int AGG>
 __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   extern __shared__ __align__(16) float smem_f[];
   if ((p.flags[0] | p.flags[1]) != 0) return;      // CSR not valid (unsorted / out-of-range edge_index): uniform exit
   const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = NT >> 5;
   const int K = p.reatt_n ? 2 * FN : FN;
-  Smem s;
-  carve(s, smem_f, K, EIN, p.cap_n, p.cap_e, p.reatt_n != 0, REATT_E);
+  Smem so;
+  carve(so, K, EIN, p.cap_n, p.cap_e, p.reatt_n != 0, REATT_E);
+  int* const smem_i = reinterpret_cast<int*>(smem_f);
+  uint16_t* const smem_h = reinterpret_cast<uint16_t*>(smem_f);
 
   // ---- weights, once per CTA (read from the live parameters at every launch)
   {
@@ -96,13 +100,13 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
       if (o < FE) v = p.w.w_edge[o * edge_row + k];                        // source block of the edge update
       else if (o < 2 * FE) v = p.w.w_edge[(o - FE) * edge_row + K + k];    // target block
       else v = p.w.w_node[(o - 2 * FE) * node_row + k];                    // node block of the node update
-      s.wproj[idx] = v;
+      (smem_f + so.wproj)[idx] = v;
     }
-    for (int o = tid; o < 44; o += NT) s.bproj[o] = o < FE ? p.w.b_edge[o] : (o < 2 * FE ? 0.f : p.w.b_node[o - 2 * FE]);
-    for (int idx = tid; idx < FE * EIN; idx += NT) s.wee[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
-    for (int idx = tid; idx < FE * FN; idx += NT) s.wne[idx] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
-    for (int idx = tid; idx < FE * MAX_FA; idx += NT) { const int o = idx / MAX_FA, k = idx % MAX_FA; s.wenc[idx] = k < p.fa ? p.w_enc[o * p.fa + k] : 0.f; }
-    for (int o = tid; o < FE; o += NT) s.benc[o] = p.b_enc[o];
+    for (int o = tid; o < 44; o += NT) (smem_f + so.bproj)[o] = o < FE ? p.w.b_edge[o] : (o < 2 * FE ? 0.f : p.w.b_node[o - 2 * FE]);
+    for (int idx = tid; idx < FE * EIN; idx += NT) (smem_f + so.wee)[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
+    for (int idx = tid; idx < FE * FN; idx += NT) (smem_f + so.wne)[idx] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
+    for (int idx = tid; idx < FE * MAX_FA; idx += NT) { const int o = idx / MAX_FA, k = idx % MAX_FA; (smem_f + so.wenc)[idx] = k < p.fa ? p.w_enc[o * p.fa + k] : 0.f; }
+    for (int o = tid; o < FE; o += NT) (smem_f + so.benc)[o] = p.b_enc[o];
     if (p.has_cls) {
       for (int c = tid; c < HC; c += NT) {
         float scale = 1.f, shift = 0.f;
@@ -110,17 +114,17 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
           scale = p.w.bn_weight[c] / sqrtf(p.w.bn_var[c] + p.w.bn_eps);
           shift = p.w.bn_bias[c] - p.w.bn_mean[c] * scale;
         }
-        for (int k = 0; k < FE; ++k) s.c1[c * FE + k] = p.w.w_c1[c * FE + k] * scale;
-        s.b1[c] = p.w.b_c1[c] * scale + shift;
-        s.c2[c] = p.w.w_c2[c];
+        for (int k = 0; k < FE; ++k) (smem_f + so.c1)[c * FE + k] = p.w.w_c1[c * FE + k] * scale;
+        (smem_f + so.b1)[c] = p.w.b_c1[c] * scale + shift;
+        (smem_f + so.c2)[c] = p.w.w_c2[c];
       }
-      if (tid == 0) s.b2[0] = p.w.b_c2[0];
+      if (tid == 0) (smem_f + so.b2)[0] = p.w.b_c2[0];
     }
   }
   __syncthreads();
   float wne[FE];
 #pragma unroll
-  for (int k = 0; k < FE; ++k) wne[k] = s.wne[k * FN + lane];
+  for (int k = 0; k < FE; ++k) wne[k] = (smem_f + so.wne)[k * FN + lane];
 
   for (int64_t g = blockIdx.x; g < p.n_graphs; g += gridDim.x) {
     const int64_t a = p.graph_ptr[g], b = p.graph_ptr[g + 1];
@@ -132,17 +136,18 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
     // ---- load the frame: encoded nodes, local CSR, edge encoder
     for (int idx = tid; idx < n * (FN / 4); idx += NT) {
       const float4 v = *reinterpret_cast<const float4*>(p.h_enc + a * FN + (int64_t)idx * 4);
-      *reinterpret_cast<float4*>(s.h + idx * 4) = v;
-      if (p.reatt_n) *reinterpret_cast<float4*>(s.h0 + idx * 4) = v;
+      const int hoff = (idx >> 3) * HS + (idx & 7) * 4;
+      *reinterpret_cast<float4*>((smem_f + so.h) + hoff) = v;
+      if (p.reatt_n) *reinterpret_cast<float4*>((smem_f + so.h0) + hoff) = v;
     }
-    for (int v = tid; v <= n; v += NT) s.rp[v] = p.rowptr[a + v] - (int)eb;
+    for (int v = tid; v <= n; v += NT) (smem_i + so.rp)[v] = p.rowptr[a + v] - (int)eb;
     bool bad = false;
     for (int j = tid; j < ne; j += NT) {
       const int sg = ld_stream_i32(p.src + eb + j) - (int)a, dg = ld_stream_i32(p.dst + eb + j) - (int)a;
       const bool ok = (sg >= 0) & (sg < n) & (dg >= 0) & (dg < n);
       bad |= !ok;
-      s.sl[j] = (uint16_t)(ok ? sg : 0);
-      s.dl[j] = (uint16_t)(ok ? dg : 0);
+      (smem_h + 2 * so.sl)[j] = (uint16_t)(ok ? sg : 0);
+      (smem_h + 2 * so.dl)[j] = (uint16_t)(ok ? dg : 0);
       float ea[MAX_FA];
       if (p.fa == 4) {   // the shipped 4-attribute row: one 16-byte streaming load
         const float4 v4 = ld_stream_f4(p.edge_attr + (eb + j) * 4);
@@ -156,17 +161,17 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
       float en[EP];
 #pragma unroll
       for (int o = 0; o < FE; ++o) {
-        float acc = s.benc[o];
+        float acc = (smem_f + so.benc)[o];
 #pragma unroll
-        for (int k = 0; k < MAX_FA; ++k) acc = fmaf(ea[k], s.wenc[o * MAX_FA + k], acc);
+        for (int k = 0; k < MAX_FA; ++k) acc = fmaf(ea[k], (smem_f + so.wenc)[o * MAX_FA + k], acc);
         en[o] = fmaxf(acc, 0.f);                     // Linear + ReLU (edge_out_dim != 1), mlp.py:14,18
       }
       en[6] = 0.f; en[7] = 0.f;
-      *reinterpret_cast<float4*>(s.e + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-      *reinterpret_cast<float4*>(s.e + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
+      *reinterpret_cast<float4*>((smem_f + so.e) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+      *reinterpret_cast<float4*>((smem_f + so.e) + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
       if (REATT_E) {
-        *reinterpret_cast<float4*>(s.e0 + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-        *reinterpret_cast<float4*>(s.e0 + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
+        *reinterpret_cast<float4*>((smem_f + so.e0) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+        *reinterpret_cast<float4*>((smem_f + so.e0) + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
       }
       if (p.e_dump) {
 #pragma unroll
@@ -181,10 +186,10 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
       // ---- per-node projections P | Q | R  (Linear over a concatenation = sum of per-block products)
       for (int item = tid; item < n * 11; item += NT) {
         const int v = item / 11, q = item - v * 11;
-        float4 acc = *reinterpret_cast<const float4*>(s.bproj + 4 * q);
-        const float* wq = s.wproj + 4 * q;
+        float4 acc = *reinterpret_cast<const float4*>((smem_f + so.bproj) + 4 * q);
+        const float* wq = (smem_f + so.wproj) + 4 * q;
         if (p.reatt_n) {
-          const float* hv0 = s.h0 + v * FN;         // cat(initial, current), mpn.py:285
+          const float* hv0 = (smem_f + so.h0) + v * HS;         // cat(initial, current), mpn.py:285
 #pragma unroll 8
           for (int k = 0; k < FN; ++k) {
             const float x = hv0[k];
@@ -193,34 +198,34 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
           }
           wq += FN * 44;
         }
-        const float* hv = s.h + v * FN;
+        const float* hv = (smem_f + so.h) + v * HS;
 #pragma unroll 8
         for (int k = 0; k < FN; ++k) {
           const float x = hv[k];
           const float4 w = *reinterpret_cast<const float4*>(wq + k * 44);
           acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y); acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
         }
-        *reinterpret_cast<float4*>(s.pqr + v * 44 + 4 * q) = acc;
+        *reinterpret_cast<float4*>((smem_f + so.pqr) + v * 44 + 4 * q) = acc;
       }
       __syncthreads();
       // ---- phase A: thread per edge -- edge update (+ classifier)
       const bool classify = p.has_cls && step >= p.first_cls;
       float* logit_out = classify ? p.logits + (int64_t)(step - p.first_cls) * p.n_edges + eb : nullptr;
       for (int j = tid; j < ne; j += NT) {
-        const float* Ps = s.pqr + (int)s.sl[j] * 44;
-        const float* Qd = s.pqr + (int)s.dl[j] * 44 + FE;
+        const float* Ps = (smem_f + so.pqr) + (int)(smem_h + 2 * so.sl)[j] * 44;
+        const float* Qd = (smem_f + so.pqr) + (int)(smem_h + 2 * so.dl)[j] * 44 + FE;
         const float4 p0 = *reinterpret_cast<const float4*>(Ps);
         const float2 p1 = *reinterpret_cast<const float2*>(Ps + 4);
         const float2 q0 = *reinterpret_cast<const float2*>(Qd), q1 = *reinterpret_cast<const float2*>(Qd + 2), q2 = *reinterpret_cast<const float2*>(Qd + 4);
         const float pq[FE] = {p0.x + q0.x, p0.y + q0.y, p0.z + q1.x, p0.w + q1.y, p1.x + q2.x, p1.y + q2.y};
         float ein[EIN];
         if (REATT_E) {   // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
-          const float4 u0 = *reinterpret_cast<const float4*>(s.e0 + j * EP), u1 = *reinterpret_cast<const float4*>(s.e0 + j * EP + 4);
+          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e0) + j * EP), u1 = *reinterpret_cast<const float4*>((smem_f + so.e0) + j * EP + 4);
           ein[0] = u0.x; ein[1] = u0.y; ein[2] = u0.z; ein[3] = u0.w; ein[4] = u1.x; ein[5] = u1.y;
         }
         constexpr int OFF = REATT_E ? FE : 0;
         {
-          const float4 u0 = *reinterpret_cast<const float4*>(s.e + j * EP), u1 = *reinterpret_cast<const float4*>(s.e + j * EP + 4);
+          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP), u1 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP + 4);
           ein[OFF] = u0.x; ein[OFF + 1] = u0.y; ein[OFF + 2] = u0.z; ein[OFF + 3] = u0.w; ein[OFF + 4] = u1.x; ein[OFF + 5] = u1.y;
         }
         float en[FE];
@@ -228,23 +233,23 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
         for (int o = 0; o < FE; ++o) {
           float acc = pq[o];
 #pragma unroll
-          for (int k = 0; k < EIN; ++k) acc = fmaf(ein[k], s.wee[o * EIN + k], acc);
+          for (int k = 0; k < EIN; ++k) acc = fmaf(ein[k], (smem_f + so.wee)[o * EIN + k], acc);
           en[o] = fmaxf(acc, 0.f);
         }
-        *reinterpret_cast<float4*>(s.e + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-        *reinterpret_cast<float2*>(s.e + j * EP + 4) = make_float2(en[4], en[5]);
+        *reinterpret_cast<float4*>((smem_f + so.e) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
+        *reinterpret_cast<float2*>((smem_f + so.e) + j * EP + 4) = make_float2(en[4], en[5]);
         if (p.e_dump) {
 #pragma unroll
           for (int o = 0; o < FE; ++o) p.e_dump[((int64_t)step * p.n_edges + eb + j) * FE + o] = en[o];
         }
         if (classify) {
-          float logit = s.b2[0];
+          float logit = (smem_f + so.b2)[0];
 #pragma unroll
           for (int c = 0; c < HC; ++c) {
-            float hcv = s.b1[c];
+            float hcv = (smem_f + so.b1)[c];
 #pragma unroll
-            for (int k = 0; k < FE; ++k) hcv = fmaf(en[k], s.c1[c * FE + k], hcv);
-            logit = fmaf(fmaxf(hcv, 0.f), s.c2[c], logit);
+            for (int k = 0; k < FE; ++k) hcv = fmaf(en[k], (smem_f + so.c1)[c * FE + k], hcv);
+            logit = fmaf(fmaxf(hcv, 0.f), (smem_f + so.c2)[c], logit);
           }
           st_stream_f1(logit_out + j, logit);
         }
@@ -253,20 +258,35 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
       __syncthreads();
       // ---- phase B: a warp owns a node's whole out-edge segment, lane = feature; fixed summation order
       for (int v = warp; v < n; v += nwarps) {
-        const float r = s.pqr[v * 44 + 2 * FE + lane];
-        const int j0 = s.rp[v], j1 = s.rp[v + 1];
-        float acc = agg_init(p.agg);
-        for (int j = j0; j < j1; ++j) {
-          const float4 u0 = *reinterpret_cast<const float4*>(s.e + j * EP);
-          const float2 u1 = *reinterpret_cast<const float2*>(s.e + j * EP + 4);
-          float m = r;
-          m = fmaf(u0.x, wne[0], m); m = fmaf(u0.y, wne[1], m); m = fmaf(u0.z, wne[2], m);
-          m = fmaf(u0.w, wne[3], m); m = fmaf(u1.x, wne[4], m); m = fmaf(u1.y, wne[5], m);
-          acc = agg_comb(p.agg, acc, fmaxf(m, 0.f));
+        const float r = (smem_f + so.pqr)[v * 44 + 2 * FE + lane];
+        const int j0 = (smem_i + so.rp)[v], j1 = (smem_i + so.rp)[v + 1];
+        float acc = agg_init(AGG);
+        int j = j0;
+        for (; j + 4 <= j1; j += 4) {      // four independent message evaluations in flight, folded in edge order
+          float m[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + (j + u) * EP);
+            const float2 u1 = *reinterpret_cast<const float2*>((smem_f + so.e) + (j + u) * EP + 4);
+            float t = r;
+            t = fmaf(u0.x, wne[0], t); t = fmaf(u0.y, wne[1], t); t = fmaf(u0.z, wne[2], t);
+            t = fmaf(u0.w, wne[3], t); t = fmaf(u1.x, wne[4], t); t = fmaf(u1.y, wne[5], t);
+            m[u] = fmaxf(t, 0.f);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) acc = agg_comb(AGG, acc, m[u]);
+        }
+        for (; j < j1; ++j) {
+          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP);
+          const float2 u1 = *reinterpret_cast<const float2*>((smem_f + so.e) + j * EP + 4);
+          float t = r;
+          t = fmaf(u0.x, wne[0], t); t = fmaf(u0.y, wne[1], t); t = fmaf(u0.z, wne[2], t);
+          t = fmaf(u0.w, wne[3], t); t = fmaf(u1.x, wne[4], t); t = fmaf(u1.y, wne[5], t);
+          acc = agg_comb(AGG, acc, fmaxf(t, 0.f));
         }
         if (j1 == j0) acc = 0.f;                                        // no out-edge: torch_scatter leaves 0
-        else if (p.agg == GNNCCA_AGG_MEAN) acc = acc / (float)(j1 - j0);
-        s.h[v * FN + lane] = acc;
+        else if (AGG == GNNCCA_AGG_MEAN) acc = acc / (float)(j1 - j0);
+        (smem_f + so.h)[v * HS + lane] = acc;
         if (p.h_dump) p.h_dump[((int64_t)step * p.n_nodes + a + v) * FN + lane] = acc;
       }
       __syncthreads();
@@ -310,20 +330,23 @@ extern "C" int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_wei
 
   fused::Smem lay;
   const int K = p.reatt_n ? 64 : 32, EIN = p.reatt_e ? 12 : 6;
-  const size_t smem = fused::carve(lay, (float*)4096, K, EIN, cap_nodes, cap_edges, p.reatt_n != 0, p.reatt_e != 0);
+  const size_t smem = fused::carve(lay, K, EIN, cap_nodes, cap_edges, p.reatt_n != 0, p.reatt_e != 0);
   if (smem > 227 * 1024) return GNNCCA_ERR_UNSUPPORTED;   // frame class too large for one CTA: use the per-step kernels
   const int threads = cap_edges <= 512 ? 128 : 256;
-  int occ = (int)((227 * 1024) / (smem + 1024));
-  if (occ > 2048 / threads) occ = 2048 / threads;
-  if (occ < 1) occ = 1;
-  const int64_t want = (int64_t)kNumSMs * occ;
-  const int grid = (int)(n_graphs < want ? n_graphs : want);
   cudaStream_t st = (cudaStream_t)stream;
-  auto kern = p.reatt_e ? fused::mp_fused_fwd_kernel<true> : fused::mp_fused_fwd_kernel<false>;
+  void (*kern)(const fused::Params) = nullptr;
+  if (p.reatt_e) kern = p.agg == GNNCCA_AGG_MAX ? fused::mp_fused_fwd_kernel<true, GNNCCA_AGG_MAX>
+                      : p.agg == GNNCCA_AGG_MEAN ? fused::mp_fused_fwd_kernel<true, GNNCCA_AGG_MEAN> : fused::mp_fused_fwd_kernel<true, GNNCCA_AGG_SUM>;
+  else kern = p.agg == GNNCCA_AGG_MAX ? fused::mp_fused_fwd_kernel<false, GNNCCA_AGG_MAX>
+            : p.agg == GNNCCA_AGG_MEAN ? fused::mp_fused_fwd_kernel<false, GNNCCA_AGG_MEAN> : fused::mp_fused_fwd_kernel<false, GNNCCA_AGG_SUM>;
   if (smem > 48 * 1024) {
     int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     if (rc) return rc;
   }
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem) != cudaSuccess || occ < 1) { (void)cudaGetLastError(); occ = 1; }
+  const int64_t want = (int64_t)kNumSMs * occ;        // every frame of the wave resident at once when the batch allows
+  const int grid = (int)(n_graphs < want ? n_graphs : want);
   kern<<<grid, threads, smem, st>>>(p);
   return check_launch();
 }

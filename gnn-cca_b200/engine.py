@@ -149,8 +149,11 @@ def frame_capacity(model, N: int, E: int, B: int, hint=None):
     reports an overflow makes the host measure the true maxima, see ``forward_inference``)."""
     if B <= 0:
         return None
-    if hint is not None:
-        need_n, need_e = int(hint[0]), int(hint[1])
+    if hint is not None:      # exact maxima: size shared memory to the batch (more frames resident per SM)
+        need_n, need_e = max(8, (int(hint[0]) + 7) & ~7), max(32, (int(hint[1]) + 31) & ~31)
+        if need_n > CAP_NODE_CLASSES[-1] or need_e > (2048 if model.reattach_initial_edges else CAP_EDGE_CLASSES[-1]):
+            return None
+        return need_n, need_e
     else:
         seen = getattr(model, "_gnncca_caps_seen", (0, 0))
         need_n = max(int(1.25 * N / B) + 1, seen[0])
@@ -180,7 +183,7 @@ def measure_frames(graph_ptr: torch.Tensor, rowptr: torch.Tensor):
 def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
                       plan: Optional[GraphPlan] = None, return_latents: bool = False, prof: Optional[StageTimer] = None,
                       h_encoded: Optional[torch.Tensor] = None, graph_ptr: Optional[torch.Tensor] = None, caps=None,
-                      allow_fused: bool = True, return_plan: bool = False):
+                      allow_fused: bool = True, return_plan: bool = False, trusted: bool = False):
     """``MOTMPNet.forward`` (models/mpn.py:250-299), no autograd graph.  Returns the list of per-step logits
     [E,1] in the caller's edge order.
 
@@ -189,7 +192,9 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     step (gnncca_mp_step_fwd).  Everything is enqueued optimistically -- the kernels are no-ops when the CSR
     flags say the edges are not source-major -- and the 16-byte flag read-back happens after the last launch,
     so the device never waits for the host; a batch that fails a check is then re-run on the safe path.
-    ``h_encoded``: node latents already produced by the node encoder (used by ``forward_host``)."""
+    ``h_encoded``: node latents already produced by the node encoder (used by ``forward_host``).
+    ``trusted``: the batch comes from ``build_graph_batch`` (source-major, in range, frames closed, exact ``caps``
+    by construction) or was verified by an earlier forward: nothing is read back and the call never synchronises."""
     lib = _lib.load()
     _require_cuda(edge_attr, "data.edge_attr")
     check_supported(model)
@@ -201,7 +206,7 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         prof.mark("begin")
     if plan is None:
         plan = GraphPlan(edge_index, N)          # async: narrow + order check + rowptr
-    optimistic = not plan.resolved
+    optimistic = not plan.resolved and not trusted
     if prof is not None:
         prof.mark("csr")
     dev = edge_attr.device
@@ -238,9 +243,11 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
                    "mp_fused_fwd")
         if prof is not None:
             prof.mark("mp_fused")
-        plan.request_flags()
-        ok_order = plan.source_major()
-        if not ok_order or plan.frames_overflowed():
+        ok_order = True
+        if not trusted:
+            plan.request_flags()
+            ok_order = plan.source_major()
+        if not trusted and (not ok_order or plan.frames_overflowed()):
             if ok_order:        # a frame larger than the class, or an edge leaving its frame
                 plan.clear_overflow()
                 plan._resolved = True
@@ -250,10 +257,12 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
                 retry = (true_caps[0] > cap[0] or true_caps[1] > cap[1]) and frame_capacity(model, N, E, B, true_caps) is not None
                 return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h, graph_ptr,
                                          true_caps if retry else None, retry, return_plan)
+            # not source-major
             plan.resolve()
             return forward_inference(model, x, edge_index, edge_attr, plan, return_latents, None, h, graph_ptr, caps, True, return_plan)
         plan._resolved = True
         plan.last_path = "fused"
+        plan.caps = caps if caps is not None else cap
         outs = [plan.to_caller(logits[i].view(E, 1)) for i in range(n_cls)]
         if return_latents:
             return outs, [(h_dump[i], e_dump[i]) for i in range(L + 1)], plan
@@ -372,6 +381,7 @@ def _side_stream(dev) -> "torch.cuda.Stream":
     return _SIDE_STREAMS[key]
 
 
+CACHE_PLANS = True          # a verified CSR is cached on the Batch object and reused while edge_index is unchanged
 FUSED_NODE_ENCODER = True   # bench.py: the node encoder is one kernel in tf32 mode (algorithmic bytes N*(4K+128))
 
 

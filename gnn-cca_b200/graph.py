@@ -100,4 +100,4 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
                                        _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
     batch_vec = torch.repeat_interleave(torch.arange(B, device=dev), counts, output_size=N)
     return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64, batch=batch_vec,
-                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps)
+                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps, gnncca_trusted=True)

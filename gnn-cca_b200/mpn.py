@@ -137,15 +137,31 @@ class MOTMPNet(nn.Module):
     def forward(self, data):
         from . import autograd_fn, engine
         x, edge_index, edge_attr = data.x, data.edge_index, data.edge_attr
-        plan = getattr(data, "gnncca_plan", None)
         graph_ptr = getattr(data, "ptr", None)             # PyG Batch.ptr / our Batch.ptr: frame boundaries, when known
         caps = getattr(data, "gnncca_caps", None)
+        trusted = bool(getattr(data, "gnncca_trusted", False))
+        plan = getattr(data, "gnncca_plan", None)          # CSR verified by an earlier forward on this very object
+        if plan is not None and (not engine.CACHE_PLANS or plan.key() != (edge_index.data_ptr(), tuple(edge_index.shape),
+                                                                          edge_index._version, int(x.size(0)))):
+            plan = None
+        allow_fused = True
+        if plan is not None and plan.last_path is not None:      # verified before: nothing left to check
+            trusted, allow_fused = True, plan.last_path == "fused"
+            caps = getattr(plan, "caps", caps) if allow_fused else caps
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
         if needs_grad or (self.training and self._has_batchnorm()):
             outs = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan)
         else:
-            outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps, return_plan=True)
+            outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps,
+                                                  return_plan=True, trusted=trusted, allow_fused=allow_fused)
             self.last_plan = plan       # introspection only (which device pipeline ran, the CSR)
+            if engine.CACHE_PLANS and not getattr(data, "gnncca_trusted", False):
+                try:                    # a verified CSR is reused by later forwards on the same, unmodified Batch
+                    data.gnncca_plan = plan
+                    if caps is None and getattr(plan, "caps", None) is not None and plan.last_path == "fused":
+                        data.gnncca_caps = plan.caps
+                except AttributeError:
+                    pass
         return {'classified_edges': outs}
 
     def forward_host(self, x, edge_index, edge_attr, out=None, graph_ptr=None, caps=None):

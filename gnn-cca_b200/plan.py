@@ -10,7 +10,8 @@ from . import _lib
 
 
 def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+    """Raw handle of torch's current CUDA stream (the fast path: no Stream object is built)."""
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
 
 
 class GraphPlan:
@@ -31,9 +32,10 @@ class GraphPlan:
         self.rowptr = torch.empty(self.N + 1, dtype=torch.int32, device=dev)
         self.flags = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, device=dev)
         self.perm: Optional[torch.Tensor] = None
-        self._flags_host = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, pin_memory=True)
-        self._event = torch.cuda.Event()
+        self._flags_host = None     # pinned read-back buffer + event, created on first use only
+        self._event = None
         self._resolved = False
+        self.last_path = None
         _lib.check(self.lib.gnncca_csr_from_edge_index(_lib.ptr(self.edge_index), self.N, self.E, _lib.ptr(self.src),
                                                        _lib.ptr(self.dst), _lib.ptr(self.rowptr), _lib.ptr(self.flags),
                                                        _stream()), "csr_from_edge_index")
@@ -45,6 +47,9 @@ class GraphPlan:
 
     def request_flags(self) -> None:
         """Enqueue the 16-byte read back of the flags behind everything launched so far (non-blocking)."""
+        if self._flags_host is None:
+            self._flags_host = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, pin_memory=True)
+            self._event = torch.cuda.Event()
         self._flags_host.copy_(self.flags, non_blocking=True)
         self._event.record()
         self._requested = True
@@ -53,6 +58,11 @@ class GraphPlan:
         """flags[2]: raised by gnncca_mp_fused_fwd when a frame did not fit its capacity class (valid after
         ``source_major()``)."""
         return bool(int(self._flags_host[2]))
+
+    def key(self):
+        """Identity of the edge_index this CSR was built from (tensor storage, shape and in-place version)."""
+        t = self.edge_index
+        return (t.data_ptr(), tuple(t.shape), t._version, self.N)
 
     def clear_overflow(self) -> None:
         self.flags[2:3].zero_()
