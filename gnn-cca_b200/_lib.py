@@ -30,6 +30,15 @@ class MpWeights(C.Structure):
                 ("bn_eps", C.c_float), ("pad_", i32)]
 
 
+class FinSeg(C.Structure):
+    _fields_ = [("partial", vp), ("dst", vp), ("n_blocks", i32), ("width", i32), ("src_off", i32), ("src_stride", i32),
+                ("rows", i32), ("cols", i32), ("dst_stride", i32), ("accumulate", i32)]
+
+
+MAX_FIN_SEGS = 24
+CLS_ACC = 41
+BLOCKS_PER_EDGE, BLOCKS_PER_NODE_WARP, BLOCKS_NODE_PROJECT, BLOCKS_ROW_CHUNKS = 0, 1, 2, 3
+
 # name -> (restype, argtypes); must list every symbol include/gnncca.h declares (tests check this)
 SIGNATURES = {
     "gnncca_abi_version": (C.c_int, []),
@@ -48,6 +57,18 @@ SIGNATURES = {
                                      vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_mp_fused_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i32, vp, i64, vp, vp, vp, i64, i64, vp, vp,
                                       i32, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "gnncca_train_blocks": (i32, [i64, i32]),
+    "gnncca_node_agg_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gnncca_edge_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gnncca_cls_moments": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, vp, vp]),
+    "gnncca_cls_bn_prepare": (C.c_int, [i32, vp, i64, vp, vp, C.c_float, C.c_float, vp, vp, vp, vp]),
+    "gnncca_cls_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, vp, vp]),
+    "gnncca_cls_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, i32, vp, vp, vp, vp, vp]),
+    "gnncca_pq_reduce": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, vp]),
+    "gnncca_node_project_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, vp, i64, vp, vp, vp, vp]),
+    "gnncca_edge_enc_bwd": (C.c_int, [vp, i32, vp, vp, i64, vp, vp]),
+    "gnncca_linear_bwd": (C.c_int, [vp, vp, vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, i32, vp]),
+    "gnncca_finalize_grads": (C.c_int, [C.POINTER(FinSeg), i32, vp]),
     "gnncca_edge_mlp": (C.c_int, [vp, vp, i64, i32, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32), vp]),
     "gnncca_colnorm_scratch_bytes": (i64, [i64, i32]),
     "gnncca_colnorm": (C.c_int, [vp, vp, i64, i32, vp, vp]),

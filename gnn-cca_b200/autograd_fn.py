@@ -1,5 +1,261 @@
-"""Training path (autograd) of MOTMPNet.forward -- to be filled in."""
+"""Training path of ``MOTMPNet.forward``: a ``torch.autograd.Function`` whose forward runs the per-step CUDA
+pipeline keeping every step's latents, and whose backward runs the transposed kernels of ``csrc/train.cu``
+(reference: autograd through models/mpn.py:250-299 under the loss of train.py:80-97, ``loss.backward()`` at
+train.py:493).  Inputs ``x`` / ``edge_attr`` get no gradient (the CNN runs under ``no_grad``, train.py:248)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List
+
+import torch
+
+from . import _lib
+from .plan import GraphPlan, _stream
+
+P = _lib.ptr
+
+
+def _blocks(lib, n, kind):
+    return int(lib.gnncca_train_blocks(int(n), kind))
+
+
+def _bn_mode(model):
+    bn = model.classifier.edge_mlp.batchnorm(0)
+    if bn is None:
+        return None, "none"
+    return bn, ("train" if model.training else "eval")
+
+
+class _Seg:
+    """Collects gnncca_fin_seg entries and flushes them in tables of at most MAX_FIN_SEGS."""
+
+    def __init__(self, lib):
+        self.lib, self.items = lib, []
+
+    def add(self, partial, n_blocks, width, src_off, src_stride, rows, cols, dst, dst_stride, accumulate=0):
+        self.items.append(_lib.FinSeg(P(partial), dst if isinstance(dst, int) else P(dst), n_blocks, width, src_off, src_stride, rows, cols,
+                                      dst_stride, accumulate))
+
+    def flush(self):
+        for i in range(0, len(self.items), _lib.MAX_FIN_SEGS):
+            chunk = self.items[i:i + _lib.MAX_FIN_SEGS]
+            arr = (_lib.FinSeg * len(chunk))(*chunk)
+            _lib.check(self.lib.gnncca_finalize_grads(arr, len(chunk), _stream()), "finalize_grads")
+        self.items = []
+
+
+class _MPNFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, x, edge_index, edge_attr, plan, *params):
+        from . import engine
+        lib = _lib.load()
+        engine.check_supported(model)
+        engine._require_cuda(x, "data.x")
+        engine._require_cuda(edge_attr, "data.edge_attr")
+        dev = x.device
+        N, E = int(x.size(0)), int(edge_index.size(1))
+        if plan is None:
+            plan = GraphPlan(edge_index, N)
+        plan.resolve()
+        enc_n, enc_e = model.encoder.node_mlp, model.encoder.edge_mlp
+        if len(enc_e.layer_specs) != 1:
+            raise NotImplementedError("training: the edge encoder must be a single Linear+ReLU (edge_fc_dims = [])")
+        if int(edge_attr.size(1)) > 8:
+            raise NotImplementedError("training: edge_in_dim > 8 has no kernel")
+        sb = engine.StepBinding(model, _lib.MATH_FP32)
+        L, k = model.num_enc_steps, model.num_class_steps
+        first = L - k + 1
+        if L < 1:
+            raise NotImplementedError("training with num_enc_steps == 0 is not implemented")
+        bn, bn_mode = _bn_mode(model)
+        if bn is not None and bn.momentum is None:
+            raise NotImplementedError("BatchNorm1d(momentum=None) (cumulative average) has no kernel")
+
+        # transposed CSR (edges grouped by target) for the gQ reduction of the backward
+        key, other = plan.dst.clone(), plan.src.clone()
+        tperm = torch.empty(E, dtype=torch.int32, device=dev)
+        colptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+        nbytes = int(lib.gnncca_csr_sort_workspace_bytes(N, E))
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.gnncca_csr_sort(N, E, P(key), P(other), P(tperm), P(colptr), P(ws), nbytes, _stream()), "csr_sort(dst)")
+
+        # node encoder, layer by layer (FP32: the training path keeps every activation)
+        acts = [x.contiguous()]
+        for i, sp in enumerate(enc_n.layer_specs):
+            acts.append(engine.linear(acts[-1], enc_n.linear(i), sp.relu, None, _lib.MATH_FP32))
+        h0 = acts[-1]
+        ea = plan.to_sorted(edge_attr.contiguous())
+        e0 = engine.small_mlp_rows(enc_e, ea)
+
+        hs, es, affs, outs = [h0], [e0], {}, []
+        Pn = torch.empty((N, 8), dtype=torch.float32, device=dev)
+        Qn = torch.empty((N, 8), dtype=torch.float32, device=dev)
+        Rn = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
+        ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), N, E))
+        wsp = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        be = _blocks(lib, E, _lib.BLOCKS_PER_EDGE)
+        for step in range(1, L + 1):
+            _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), P(h0), P(hs[-1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
+            e_out = torch.empty_like(e0)
+            h_out = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev) if step < L else None
+            classify = step >= first
+            inline = classify and bn_mode != "train"
+            logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if classify else None
+            _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(Pn), P(Qn), P(Rn),
+                                              P(e0) if model.reattach_initial_edges else 0, P(es[-1]), P(e_out), P(h_out),
+                                              P(logits) if inline else 0, 0, P(wsp), ws_bytes, _stream()), "mp_step_fwd")
+            es.append(e_out)
+            hs.append(h_out)
+            if classify and bn_mode == "train":       # BatchNorm1d with batch statistics over all E edges (mlp.py:16)
+                aff = torch.empty(16, dtype=torch.float32, device=dev)
+                part = torch.empty((be, 8), dtype=torch.float32, device=dev)
+                sums = torch.empty(8, dtype=torch.float32, device=dev)
+                for mode in (0, 1):
+                    _lib.check(lib.gnncca_cls_moments(C.byref(sb.cfg), C.byref(sb.w), P(e_out), E, 0 if mode == 0 else aff[8:12].data_ptr(),
+                                                      P(part), _stream()), "cls_moments")
+                    seg = _Seg(lib); seg.add(part, be, 8, 0, 8, 1, 8, sums, 8); seg.flush()
+                    _lib.check(lib.gnncca_cls_bn_prepare(mode, P(sums), E, P(bn.weight), P(bn.bias), float(bn.eps), float(bn.momentum),
+                                                         P(bn.running_mean), P(bn.running_var), P(aff), _stream()), "cls_bn_prepare")
+                bn.num_batches_tracked += 1
+                _lib.check(lib.gnncca_cls_fwd(C.byref(sb.cfg), C.byref(sb.w), P(e_out), E, P(aff), P(logits), _stream()), "cls_fwd")
+                affs[step] = aff
+            elif classify and bn_mode == "eval":
+                invstd = torch.rsqrt(bn.running_var.detach() + bn.eps)
+                scale = bn.weight.detach() * invstd
+                affs[step] = torch.cat([scale, bn.bias.detach() - bn.running_mean * scale, bn.running_mean.detach(), invstd]).contiguous()
+            if classify:
+                outs.append(plan.to_caller(logits))
+        ctx.model, ctx.plan, ctx.sb = model, plan, sb
+        ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
+                         names=[n for n, _ in model.named_parameters()])
+        ctx.set_materialize_grads(False)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *g_outs):
+        from . import engine
+        lib = _lib.load()
+        model, plan, sb, sv = ctx.model, ctx.plan, ctx.sb, ctx.saved
+        hs, es, acts, ea = sv["hs"], sv["es"], sv["acts"], sv["ea"]
+        dev = ea.device
+        N, E = plan.N, plan.E
+        L, first, bn_mode = model.num_enc_steps, sv["first"], sv["bn_mode"]
+        cfg, w = C.byref(sb.cfg), C.byref(sb.w)
+        FN, FE = sb.f_node, sb.f_edge
+        rn, re = bool(model.reattach_initial_nodes), bool(model.reattach_initial_edges)
+        K, EIN = (2 * FN if rn else FN), (2 * FE if re else FE)
+        edge_row, node_row = 2 * K + EIN, K + FE
+        named = dict(model.named_parameters())
+        grads = {n: torch.zeros_like(p) for n, p in named.items()}
+        em, nm = "MPNet.edge_model.edge_mlp.fc_layers.0.", "MPNet.node_model.node_mlp.fc_layers.0."
+        cls = model.classifier.edge_mlp
+        cpre = "classifier.edge_mlp.fc_layers."
+        c1, c2 = cpre + "%d." % cls.layer_specs[0].linear, cpre + "%d." % cls.layer_specs[1].linear
+        cbn = cpre + "%d." % cls.layer_specs[0].bn if cls.layer_specs[0].bn is not None else None
+
+        be, bnw, bp = _blocks(lib, E, _lib.BLOCKS_PER_EDGE), _blocks(lib, N, _lib.BLOCKS_PER_NODE_WARP), _blocks(lib, N, _lib.BLOCKS_NODE_PROJECT)
+        z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
+        pa_agg, pa_edge, pa_proj = z(L, bnw, FN * FE), z(L, be, FE * EIN), z(L, bp, 44 * (K + 1))
+        n_cls = L - first + 1
+        pa_cls, pa_cls1 = z(n_cls, be, _lib.CLS_ACC), (z(n_cls, be, _lib.CLS_ACC) if bn_mode == "train" else None)
+        Pn, Qn, Rn = z(N, 8), z(N, 8), z(N, FN)
+        gP, gQ, gR = z(N, 8), z(N, 8), z(N, FN)
+        gze = z(E, 8)
+        ge0_acc = z(E, FE) if re else None
+        gh0_acc = z(N, FN) if rn else None
+        gh, ge_next = None, None
+        is_max = model.node_agg_name == "max"
+        for t in range(L, 0, -1):
+            ge_cls = None
+            if t >= first and g_outs[t - first] is not None:
+                ci = t - first
+                g = plan.to_sorted(g_outs[ci].contiguous().view(E, 1)).contiguous()
+                aff = sv["affs"].get(t)
+                ge_cls = torch.empty((E, FE), dtype=torch.float32, device=dev)
+                if bn_mode == "train":
+                    _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 1, P(g), 0, 0, P(pa_cls1[ci]), _stream()), "cls_bwd pass 1")
+                    sums = torch.empty(_lib.CLS_ACC, dtype=torch.float32, device=dev)
+                    seg = _Seg(lib); seg.add(pa_cls1[ci], be, _lib.CLS_ACC, 0, _lib.CLS_ACC, 1, _lib.CLS_ACC, sums, _lib.CLS_ACC); seg.flush()
+                    _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 2, P(g), P(sums), P(ge_cls), P(pa_cls[ci]), _stream()), "cls_bwd pass 2")
+                else:
+                    _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 0, P(g), 0, P(ge_cls), P(pa_cls[ci]), _stream()), "cls_bwd")
+            _lib.check(lib.gnncca_node_project(cfg, w, P(hs[0]), P(hs[t - 1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
+            if gh is not None:
+                gh_eff = torch.empty_like(gh) if is_max else None
+                _lib.check(lib.gnncca_node_agg_bwd(cfg, w, P(plan.rowptr), N, P(Rn), P(es[t]), P(gh), P(hs[t]), P(gR), P(gh_eff), P(pa_agg[t - 1]),
+                                                   _stream()), "node_agg_bwd")
+                if is_max:
+                    gh = gh_eff      # ties at the max share the gradient
+            else:
+                gR.zero_()
+            ge_prev = torch.empty((E, FE), dtype=torch.float32, device=dev)
+            _lib.check(lib.gnncca_edge_bwd(cfg, w, P(plan.rowptr), P(plan.src), E, P(Rn), P(es[t]), P(es[t - 1]), P(es[0]) if re else 0, P(gh),
+                                           P(hs[t]) if gh is not None else 0, P(ge_next), P(ge_cls), P(gze), P(ge_prev), P(ge0_acc),
+                                           P(pa_edge[t - 1]), _stream()), "edge_bwd")
+            _lib.check(lib.gnncca_pq_reduce(P(plan.rowptr), P(sv["colptr"]), P(sv["tperm"]), P(gze), N, P(gP), P(gQ), _stream()), "pq_reduce")
+            gh_prev = torch.zeros((N, FN), dtype=torch.float32, device=dev)
+            _lib.check(lib.gnncca_node_project_bwd(cfg, w, P(gP), P(gQ), P(gR), P(hs[0]), P(hs[t - 1]), N, P(gh_prev), P(gh0_acc), P(pa_proj[t - 1]),
+                                                   _stream()), "node_project_bwd")
+            gh, ge_next = gh_prev, ge_prev
+        ge0 = ge_next + ge0_acc if re else ge_next
+        gh0 = gh + gh0_acc if rn else gh
+
+        seg = _Seg(lib)
+        gWe, gWn = grads[em + "weight"], grads[nm + "weight"]
+        seg.add(pa_agg, L * bnw, FN * FE, 0, FE, FN, FE, gWn.data_ptr() + 4 * K, node_row)
+        seg.add(pa_edge, L * be, FE * EIN, 0, EIN, FE, EIN, gWe.data_ptr() + 4 * 2 * K, edge_row)
+        wp = 44 * (K + 1)
+        seg.add(pa_proj, L * bp, wp, 0, K + 1, FE, K, gWe, edge_row)
+        seg.add(pa_proj, L * bp, wp, FE * (K + 1), K + 1, FE, K, gWe.data_ptr() + 4 * K, edge_row)
+        seg.add(pa_proj, L * bp, wp, 2 * FE * (K + 1), K + 1, FN, K, gWn, node_row)
+        seg.add(pa_proj, L * bp, wp, K, K + 1, FE, 1, grads[em + "bias"], 1)
+        seg.add(pa_proj, L * bp, wp, 2 * FE * (K + 1) + K, K + 1, FN, 1, grads[nm + "bias"], 1)
+        A = _lib.CLS_ACC
+        HC = sb.cfg.cls_hidden
+        seg.add(pa_cls, n_cls * be, A, 0, FE, HC, FE, grads[c1 + "weight"], FE)
+        seg.add(pa_cls, n_cls * be, A, HC * FE, HC, 1, HC, grads[c1 + "bias"], HC)
+        last = pa_cls1 if bn_mode == "train" else pa_cls
+        seg.add(last, n_cls * be, A, HC * FE + HC, HC, 1, HC, grads[c2 + "weight"], HC)
+        seg.add(last, n_cls * be, A, HC * FE + 2 * HC, 1, 1, 1, grads[c2 + "bias"], 1)
+        if cbn is not None:
+            seg.add(last, n_cls * be, A, HC * FE + 2 * HC + 1, HC, 1, HC, grads[cbn + "weight"], HC)
+            seg.add(last, n_cls * be, A, HC * FE + 3 * HC + 1, HC, 1, HC, grads[cbn + "bias"], HC)
+        # edge encoder
+        enc_e = model.encoder.edge_mlp
+        fa = int(ea.size(1))
+        pa_enc = torch.empty((be, FE * 8 + FE), dtype=torch.float32, device=dev)
+        _lib.check(lib.gnncca_edge_enc_bwd(P(ea), fa, P(es[0]), P(ge0), E, P(pa_enc), _stream()), "edge_enc_bwd")
+        epre = "encoder.edge_mlp.fc_layers.%d." % enc_e.layer_specs[0].linear
+        seg.add(pa_enc, be, FE * 8 + FE, 0, 8, FE, fa, grads[epre + "weight"], fa)
+        seg.add(pa_enc, be, FE * 8 + FE, FE * 8, FE, 1, FE, grads[epre + "bias"], FE)
+        # node encoder, last layer first
+        enc_n = model.encoder.node_mlp
+        keep = [pa_agg, pa_edge, pa_proj, pa_cls, pa_cls1, pa_enc]
+        gy = gh0.contiguous()
+        rows = N
+        chunks = _blocks(lib, rows, _lib.BLOCKS_ROW_CHUNKS)
+        for i in range(len(enc_n.layer_specs) - 1, -1, -1):
+            sp, lin = enc_n.layer_specs[i], enc_n.linear(i)
+            splits = max(1, min(8, rows // 256))
+            gz = torch.empty((rows, sp.out_dim), dtype=torch.float32, device=dev)
+            gx = torch.empty((rows, sp.in_dim), dtype=torch.float32, device=dev) if i > 0 else None
+            gbp = torch.empty((chunks, sp.out_dim), dtype=torch.float32, device=dev)
+            gwp = torch.empty((splits, sp.out_dim * sp.in_dim), dtype=torch.float32, device=dev)
+            _lib.check(lib.gnncca_linear_bwd(P(acts[i]), P(lin.weight), P(acts[i + 1]), P(gy), int(sp.relu), rows, sp.in_dim, sp.out_dim, P(gz), P(gx),
+                                             P(gbp), P(gwp), splits, _stream()), "linear_bwd")
+            npre = "encoder.node_mlp.fc_layers.%d." % sp.linear
+            seg.add(gwp, splits, sp.out_dim * sp.in_dim, 0, sp.in_dim, sp.out_dim, sp.in_dim, grads[npre + "weight"], sp.in_dim)
+            seg.add(gbp, chunks, sp.out_dim, 0, sp.out_dim, 1, sp.out_dim, grads[npre + "bias"], sp.out_dim)
+            keep += [gz, gbp, gwp]
+            gy = gx
+        seg.flush()
+        out: List = [None, None, None, None, None]
+        for n in sv["names"]:
+            out.append(grads[n] if named[n].requires_grad else None)
+        return tuple(out)
 
 
 def forward_training(model, x, edge_index, edge_attr, plan=None):
-    raise NotImplementedError("gnn-cca_b200: training (autograd) path not built yet")
+    """``MOTMPNet.forward`` with an autograd graph: returns the list of per-step logits [E,1]."""
+    params = [p for _, p in model.named_parameters()]
+    return list(_MPNFunction.apply(model, x, edge_index, edge_attr, plan, *params))

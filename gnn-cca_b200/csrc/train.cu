@@ -1,0 +1,695 @@
+// Backward of the message-passing network (autograd of reference models/mpn.py:250-299 as driven by
+// train.py:80-97,493: loss = sum over classified steps of BCE-with-logits, loss.backward()).
+//
+// Same split algebra as the forward kernels, transposed.  For step t (inputs h = h^{t-1}, e_prev = e^{t-1};
+// outputs e = e^t, h^t), with P/Q/R the per-node projections of h:
+//   z_m = R[src] + W_ne e         m = relu(z_m)        h^t[v] = agg_{src=v} m
+//   z_e = P[src] + Q[dst] + W_ee [e0,] e_prev          e = relu(z_e)
+// the gradients are
+//   gz_m = dAgg(gh^t[src]) * [z_m > 0]                  (sum: gh; mean: gh/deg; max: gh where m == h^t[src])
+//   gR[v] = sum_{src=v} gz_m                            ge = W_ne^T gz_m + ge_in + ge_cls
+//   gz_e = ge * [e > 0]      gP[v] = sum_{src=v} gz_e    gQ[v] = sum_{dst=v} gz_e     ge_prev = W_ee^T gz_e
+//   gh^{t-1} = gP W_s + gQ W_d + gR W_nx
+// z_m is RECOMPUTED from the saved e^t and h^{t-1} (nothing of width 32 per edge is ever stored).
+// Every reduction has a fixed order (per-thread register accumulators -> per-block partials -> one in-order
+// pass), so gradients are bit-identical run to run; there are no floating-point atomics.
+#include "common.cuh"
+
+namespace gnncca {
+namespace train {
+
+constexpr int FN = 32, FE = 6, HC = 4, EP = 8;
+constexpr int TB = 256;                 // threads per block of the per-edge kernels
+constexpr int NW = TB / 32;
+
+// Sum K per-thread accumulators over the block in a fixed order and store them at out[0..K).
+template <int K>
+__device__ __forceinline__ void block_reduce_store(float (&acc)[K], float* smem /* [NW][K] */, float* out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    float v = acc[k];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0) smem[warp * K + k] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    float v = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += smem[w * K + k];
+    out[k] = v;
+  }
+  __syncthreads();
+}
+
+// dAgg: gradient of the aggregation wrt one message, given the gradient of the aggregated node feature
+__device__ __forceinline__ float agg_grad(int agg, float gh, float z, float hval, float inv_deg) {
+  if (z <= 0.f) return 0.f;                                   // ReLU gate of the node MLP (mlp.py:18)
+  if (agg == GNNCCA_AGG_SUM) return gh;
+  if (agg == GNNCCA_AGG_MEAN) return gh * inv_deg;
+  return z == hval ? gh : 0.f;                                // max: the attaining edge (ties only at 0, where the gate is closed)
+}
+
+// ------------------------------------------------------------------------------------------------
+// A. node side of the node model: warp per node, lane = feature.
+//    gR[v][c] = sum_{j in seg(v)} gz_m[j][c];   per-block partial of gW_node[c][K + k] += gz_m[j][c] * e[j][k]
+// ------------------------------------------------------------------------------------------------
+struct NodeAggBwd {
+  const int32_t* rowptr; const float* R; const float* e; const float* gh; const float* h_out;
+  const float* w_node; int node_row, K;       // w_node[c * node_row + K + k]
+  int64_t n_nodes; int agg;
+  float* gR; float* partial;                  // partial [gridDim][FN*FE], index c * FE + k
+  float* gh_eff;                              // max only: gh / (number of edges attaining the max), what gnncca_edge_bwd must be given as gh
+};
+
+__global__ void __launch_bounds__(TB) node_agg_bwd_kernel(const NodeAggBwd p) {
+  __shared__ float s_red[NW][FE * FN];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float wne[FE], gw[FE];
+#pragma unroll
+  for (int k = 0; k < FE; ++k) { wne[k] = p.w_node[lane * p.node_row + p.K + k]; gw[k] = 0.f; }
+  for (int64_t v = (int64_t)blockIdx.x * NW + warp; v < p.n_nodes; v += (int64_t)gridDim.x * NW) {
+    const int j0 = p.rowptr[v], j1 = p.rowptr[v + 1];
+    const float r = p.R[v * FN + lane], gh_in = p.gh[v * FN + lane];
+    const float hval = p.agg == GNNCCA_AGG_MAX ? p.h_out[v * FN + lane] : 0.f;
+    const float inv_deg = j1 > j0 ? 1.f / (float)(j1 - j0) : 0.f;
+    float gh = gh_in;
+    if (p.agg == GNNCCA_AGG_MAX) {
+      // Several edges can attain the max exactly (every edge whose updated feature row is all zero has z == R[v]);
+      // the gradient is shared between them (torch amax semantics; the total is what torch_scatter's argmax gives too).
+      int ties = 0;
+      for (int j = j0; j < j1; ++j) {
+        float z = r;
+#pragma unroll
+        for (int k = 0; k < FE; ++k) z = fmaf(p.e[(int64_t)j * FE + k], wne[k], z);
+        ties += (z > 0.f && z == hval) ? 1 : 0;
+      }
+      gh = ties > 0 ? gh_in / (float)ties : 0.f;
+      p.gh_eff[v * FN + lane] = gh;
+    }
+    float acc = 0.f;
+    for (int j = j0; j < j1; ++j) {
+      float ev[FE];
+#pragma unroll
+      for (int k = 0; k < FE; ++k) ev[k] = p.e[(int64_t)j * FE + k];
+      float z = r;
+#pragma unroll
+      for (int k = 0; k < FE; ++k) z = fmaf(ev[k], wne[k], z);
+      const float g = agg_grad(p.agg, gh, z, hval, inv_deg);
+      acc += g;
+#pragma unroll
+      for (int k = 0; k < FE; ++k) gw[k] = fmaf(g, ev[k], gw[k]);
+    }
+    p.gR[v * FN + lane] = acc;
+  }
+#pragma unroll
+  for (int k = 0; k < FE; ++k) s_red[warp][lane * FE + k] = gw[k];
+  __syncthreads();
+  for (int i = threadIdx.x; i < FE * FN; i += TB) {
+    float v = 0.f;
+    for (int w = 0; w < NW; ++w) v += s_red[w][i];
+    p.partial[(int64_t)blockIdx.x * (FE * FN) + i] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// B. per-edge backward of node model (edge side) + edge model: thread per edge.
+// ------------------------------------------------------------------------------------------------
+struct EdgeBwd {
+  const int32_t* rowptr; const int32_t* src;
+  const float* R; const float* e; const float* e_prev; const float* e0;
+  const float* gh; const float* h_out;          // gh == nullptr: the node update of this step is dead (last step)
+  const float* ge_in; const float* ge_cls;      // optional [E][FE] gradients wrt e arriving from step t+1 / the classifier
+  const float* w_node; const float* w_edge; int node_row, edge_row, K;
+  int64_t n_edges; int agg;
+  float* gze;        // [E][EP]  gradient wrt the edge-update pre-activation (consumed by the P/Q reductions)
+  float* ge_prev;    // [E][FE]  gradient wrt e^{t-1}
+  float* ge0_acc;    // [E][FE]  += gradient wrt the encoder's edge output through the reattached block (REATT_E)
+  float* partial;    // [gridDim][FE * EIN], index o * EIN + kk  -> gW_edge[o][2K + kk]
+};
+
+template <bool REATT_E>
+__global__ void __launch_bounds__(TB) edge_bwd_kernel(const EdgeBwd p) {
+  constexpr int EIN = REATT_E ? 2 * FE : FE;
+  constexpr int OFF = REATT_E ? FE : 0;
+  __shared__ float s_wne[FE][FN];
+  __shared__ float s_wee[FE][EIN];
+  __shared__ float s_red[NW * FE * EIN];
+  for (int i = threadIdx.x; i < FE * FN; i += TB) s_wne[i / FN][i % FN] = p.w_node[(i % FN) * p.node_row + p.K + i / FN];
+  for (int i = threadIdx.x; i < FE * EIN; i += TB) s_wee[i / EIN][i % EIN] = p.w_edge[(i / EIN) * p.edge_row + 2 * p.K + i % EIN];
+  __syncthreads();
+  float gw[FE * EIN];
+#pragma unroll
+  for (int i = 0; i < FE * EIN; ++i) gw[i] = 0.f;
+  const int64_t stride = (int64_t)gridDim.x * TB;
+  for (int64_t j = (int64_t)blockIdx.x * TB + threadIdx.x; j < p.n_edges; j += stride) {
+    float ev[FE], ge[FE];
+#pragma unroll
+    for (int k = 0; k < FE; ++k) {
+      ev[k] = p.e[j * FE + k];
+      ge[k] = (p.ge_in ? p.ge_in[j * FE + k] : 0.f) + (p.ge_cls ? p.ge_cls[j * FE + k] : 0.f);
+    }
+    if (p.gh != nullptr) {
+      const int s = p.src[j];
+      const float inv_deg = 1.f / (float)max(p.rowptr[s + 1] - p.rowptr[s], 1);
+      const float4* R4 = reinterpret_cast<const float4*>(p.R + (int64_t)s * FN);
+      const float4* G4 = reinterpret_cast<const float4*>(p.gh + (int64_t)s * FN);
+      const float4* H4 = reinterpret_cast<const float4*>(p.h_out + (int64_t)s * FN);
+#pragma unroll
+      for (int c4 = 0; c4 < FN / 4; ++c4) {
+        const float4 r = R4[c4], g = G4[c4];
+        const float4 hv = p.agg == GNNCCA_AGG_MAX ? H4[c4] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float rr[4] = {r.x, r.y, r.z, r.w}, gg[4] = {g.x, g.y, g.z, g.w}, hh[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int c = c4 * 4 + u;
+          float z = rr[u];
+#pragma unroll
+          for (int k = 0; k < FE; ++k) z = fmaf(ev[k], s_wne[k][c], z);
+          const float gz = agg_grad(p.agg, gg[u], z, hh[u], inv_deg);
+#pragma unroll
+          for (int k = 0; k < FE; ++k) ge[k] = fmaf(gz, s_wne[k][c], ge[k]);
+        }
+      }
+    }
+    float gze[FE];
+#pragma unroll
+    for (int o = 0; o < FE; ++o) gze[o] = ev[o] > 0.f ? ge[o] : 0.f;          // ReLU gate of the edge MLP
+    *reinterpret_cast<float4*>(p.gze + j * EP) = make_float4(gze[0], gze[1], gze[2], gze[3]);
+    *reinterpret_cast<float4*>(p.gze + j * EP + 4) = make_float4(gze[4], gze[5], 0.f, 0.f);
+    float ein[EIN];
+    if (REATT_E) {
+#pragma unroll
+      for (int k = 0; k < FE; ++k) ein[k] = p.e0[j * FE + k];
+    }
+#pragma unroll
+    for (int k = 0; k < FE; ++k) ein[OFF + k] = p.e_prev[j * FE + k];
+#pragma unroll
+    for (int k = 0; k < FE; ++k) {
+      float a = 0.f;
+#pragma unroll
+      for (int o = 0; o < FE; ++o) a = fmaf(gze[o], s_wee[o][OFF + k], a);
+      p.ge_prev[j * FE + k] = a;
+    }
+    if (REATT_E) {
+#pragma unroll
+      for (int k = 0; k < FE; ++k) {
+        float a = p.ge0_acc[j * FE + k];
+#pragma unroll
+        for (int o = 0; o < FE; ++o) a = fmaf(gze[o], s_wee[o][k], a);
+        p.ge0_acc[j * FE + k] = a;
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < FE; ++o)
+#pragma unroll
+      for (int kk = 0; kk < EIN; ++kk) gw[o * EIN + kk] = fmaf(gze[o], ein[kk], gw[o * EIN + kk]);
+  }
+  block_reduce_store<FE * EIN>(gw, s_red, p.partial + (int64_t)blockIdx.x * (FE * EIN));
+}
+
+// ------------------------------------------------------------------------------------------------
+// C. classifier (mpn.py:290-293; mlp.py:12-23: Linear(FE,HC) [BatchNorm1d] ReLU Linear(HC,1)).
+//    The BatchNorm (absent / eval / train) enters as a per-feature affine  y = c * scale + shift  with
+//    c_hat = (c - mean) * invstd; train mode additionally needs the batch sums S1, S2 of its backward.
+// ------------------------------------------------------------------------------------------------
+struct ClsParams {
+  const float* e; int64_t n_edges;
+  const float* w1; const float* b1; const float* w2; const float* b2;
+  const float* scale; const float* shift; const float* mean; const float* invstd;   // [HC] each (device)
+};
+
+__device__ __forceinline__ void cls_load(const ClsParams& p, float (*s_w1)[FE], float* s_b1, float* s_w2, float* s_aff) {
+  for (int i = threadIdx.x; i < HC * FE; i += blockDim.x) s_w1[i / FE][i % FE] = p.w1[i];
+  for (int i = threadIdx.x; i < HC; i += blockDim.x) {
+    s_b1[i] = p.b1[i]; s_w2[i] = p.w2[i];
+    s_aff[i] = p.scale ? p.scale[i] : 1.f; s_aff[HC + i] = p.shift ? p.shift[i] : 0.f;
+    s_aff[2 * HC + i] = p.mean ? p.mean[i] : 0.f; s_aff[3 * HC + i] = p.invstd ? p.invstd[i] : 1.f;
+  }
+  __syncthreads();
+}
+
+// per-feature sums of (c - center) and (c - center)^2 -> partial [gridDim][2*HC]
+__global__ void __launch_bounds__(TB) cls_moments_kernel(const ClsParams p, const float* center, float* partial) {
+  __shared__ float s_w1[HC][FE], s_b1[HC], s_w2[HC], s_aff[4 * HC], s_red[NW * 2 * HC];
+  cls_load(p, s_w1, s_b1, s_w2, s_aff);
+  float acc[2 * HC];
+#pragma unroll
+  for (int i = 0; i < 2 * HC; ++i) acc[i] = 0.f;
+  float ctr[HC];
+#pragma unroll
+  for (int f = 0; f < HC; ++f) ctr[f] = center ? center[f] : 0.f;
+  const int64_t stride = (int64_t)gridDim.x * TB;
+  for (int64_t j = (int64_t)blockIdx.x * TB + threadIdx.x; j < p.n_edges; j += stride) {
+    float ev[FE];
+#pragma unroll
+    for (int k = 0; k < FE; ++k) ev[k] = p.e[j * FE + k];
+#pragma unroll
+    for (int f = 0; f < HC; ++f) {
+      float c = s_b1[f];
+#pragma unroll
+      for (int k = 0; k < FE; ++k) c = fmaf(ev[k], s_w1[f][k], c);
+      const float d = c - ctr[f];
+      acc[f] += d; acc[HC + f] = fmaf(d, d, acc[HC + f]);
+    }
+  }
+  block_reduce_store<2 * HC>(acc, s_red, partial + (int64_t)blockIdx.x * (2 * HC));
+}
+
+// BatchNorm1d training-mode statistics (torch semantics: biased variance normalises, unbiased one updates the
+// running estimate with momentum).  mode 0: sums -> mean.  mode 1: centred sums -> invstd, scale, shift, running stats.
+__global__ void cls_bn_prepare_kernel(int mode, const float* sums, int64_t n, const float* gamma, const float* beta, float eps,
+                                      float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                                      float* scale, float* shift) {
+  const int f = threadIdx.x;
+  if (f >= HC) return;
+  if (mode == 0) { mean[f] = sums[f] / (float)n; return; }
+  const float var = sums[HC + f] / (float)n;
+  const float is = 1.f / sqrtf(var + eps);
+  invstd[f] = is;
+  scale[f] = gamma[f] * is;
+  shift[f] = beta[f] - mean[f] * gamma[f] * is;
+  if (running_mean) {
+    running_mean[f] = (1.f - momentum) * running_mean[f] + momentum * mean[f];
+    const float unbiased = n > 1 ? var * ((float)n / (float)(n - 1)) : var;
+    running_var[f] = (1.f - momentum) * running_var[f] + momentum * unbiased;
+  }
+}
+
+__global__ void __launch_bounds__(TB) cls_fwd_kernel(const ClsParams p, float* logits) {
+  __shared__ float s_w1[HC][FE], s_b1[HC], s_w2[HC], s_aff[4 * HC];
+  cls_load(p, s_w1, s_b1, s_w2, s_aff);
+  const float b2 = p.b2[0];
+  const int64_t stride = (int64_t)gridDim.x * TB;
+  for (int64_t j = (int64_t)blockIdx.x * TB + threadIdx.x; j < p.n_edges; j += stride) {
+    float ev[FE];
+#pragma unroll
+    for (int k = 0; k < FE; ++k) ev[k] = p.e[j * FE + k];
+    float logit = b2;
+#pragma unroll
+    for (int f = 0; f < HC; ++f) {
+      float c = s_b1[f];
+#pragma unroll
+      for (int k = 0; k < FE; ++k) c = fmaf(ev[k], s_w1[f][k], c);
+      logit = fmaf(fmaxf(fmaf(c, s_aff[f], s_aff[HC + f]), 0.f), s_w2[f], logit);
+    }
+    logits[j] = logit;
+  }
+}
+
+// accumulator layout of the classifier backward: [0,24) gW1 | [24,28) gb1 | [28,32) gw2 | 32 gb2 | [33,37) S2 = g_gamma | [37,41) S1 = g_beta
+constexpr int CLS_ACC = HC * FE + HC + HC + 1 + HC + HC;
+// pass 0: no BatchNorm / eval-mode BatchNorm, everything in one sweep.  pass 1 / 2: training-mode BatchNorm
+// (1: batch sums S1 = sum gy, S2 = sum gy * c_hat and the last layer; 2: gc = scale * (gy - S1/E - c_hat * S2/E), ge, gW1, gb1).
+__global__ void __launch_bounds__(TB) cls_bwd_kernel(const ClsParams p, int pass, const float* g_logits, const float* S, float* ge_cls,
+                                                     float* partial) {
+  __shared__ float s_w1[HC][FE], s_b1[HC], s_w2[HC], s_aff[4 * HC], s_red[NW * CLS_ACC];
+  cls_load(p, s_w1, s_b1, s_w2, s_aff);
+  float acc[CLS_ACC];
+#pragma unroll
+  for (int i = 0; i < CLS_ACC; ++i) acc[i] = 0.f;
+  float s1[HC], s2[HC];
+  const float inv_n = 1.f / (float)p.n_edges;
+#pragma unroll
+  for (int f = 0; f < HC; ++f) {
+    s1[f] = (pass == 2) ? S[HC * FE + 3 * HC + 1 + f] * inv_n : 0.f;     // mean of gy
+    s2[f] = (pass == 2) ? S[HC * FE + 2 * HC + 1 + f] * inv_n : 0.f;     // mean of gy * c_hat
+  }
+  const int64_t stride = (int64_t)gridDim.x * TB;
+  for (int64_t j = (int64_t)blockIdx.x * TB + threadIdx.x; j < p.n_edges; j += stride) {
+    float ev[FE], ge[FE];
+#pragma unroll
+    for (int k = 0; k < FE; ++k) { ev[k] = p.e[j * FE + k]; ge[k] = 0.f; }
+    const float g = g_logits[j];
+    if (pass != 2) acc[HC * FE + 2 * HC] += g;
+#pragma unroll
+    for (int f = 0; f < HC; ++f) {
+      float c = s_b1[f];
+#pragma unroll
+      for (int k = 0; k < FE; ++k) c = fmaf(ev[k], s_w1[f][k], c);
+      const float y = fmaf(c, s_aff[f], s_aff[HC + f]);
+      const float chat = (c - s_aff[2 * HC + f]) * s_aff[3 * HC + f];
+      const float gy = y > 0.f ? g * s_w2[f] : 0.f;
+      if (pass != 2) {
+        acc[HC * FE + HC + f] = fmaf(g, fmaxf(y, 0.f), acc[HC * FE + HC + f]);        // gw2
+        acc[HC * FE + 2 * HC + 1 + f] = fmaf(gy, chat, acc[HC * FE + 2 * HC + 1 + f]);  // S2 / g_gamma
+        acc[HC * FE + 3 * HC + 1 + f] += gy;                                              // S1 / g_beta
+      }
+      if (pass != 1) {
+        const float gc = s_aff[f] * (gy - s1[f] - chat * s2[f]);
+        acc[HC * FE + f] += gc;
+#pragma unroll
+        for (int k = 0; k < FE; ++k) { acc[f * FE + k] = fmaf(gc, ev[k], acc[f * FE + k]); ge[k] = fmaf(gc, s_w1[f][k], ge[k]); }
+      }
+    }
+    if (pass != 1) {
+#pragma unroll
+      for (int k = 0; k < FE; ++k) ge_cls[j * FE + k] = ge[k];
+    }
+  }
+  block_reduce_store<CLS_ACC>(acc, s_red, partial + (int64_t)blockIdx.x * CLS_ACC);
+}
+
+// ------------------------------------------------------------------------------------------------
+// D. gP[v] = sum over out-edges of gz_e, gQ[v] = sum over in-edges (transposed CSR: colptr + tperm).  Warp per node:
+//    lane = (edge slot 0..3) x (component 0..7); fixed tree over the 4 slots.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TB) pq_reduce_kernel(const int32_t* rowptr, const int32_t* colptr, const int32_t* tperm,
+                                                       const float* gze, int64_t n_nodes, float* gP, float* gQ) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, o = lane & 7, slot = lane >> 3;
+  for (int64_t v = (int64_t)blockIdx.x * NW + warp; v < n_nodes; v += (int64_t)gridDim.x * NW) {
+    float a = 0.f, b = 0.f;
+    for (int j = rowptr[v] + slot; j < rowptr[v + 1]; j += 4) a += gze[(int64_t)j * EP + o];
+    for (int t = colptr[v] + slot; t < colptr[v + 1]; t += 4) b += gze[(int64_t)tperm[t] * EP + o];
+    a += __shfl_xor_sync(0xffffffffu, a, 8); a += __shfl_xor_sync(0xffffffffu, a, 16);
+    b += __shfl_xor_sync(0xffffffffu, b, 8); b += __shfl_xor_sync(0xffffffffu, b, 16);
+    if (slot == 0) { gP[v * EP + o] = a; gQ[v * EP + o] = b; }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// E. backward of the per-node projections: gh_prev = gP W_s + gQ W_d + gR W_nx, weight-gradient partials.
+//    One block = 64 nodes.  partial [gridDim][44 * (K + 1)], index o * (K+1) + k; column K is the bias sum.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TB) node_project_bwd_kernel(const float* w_edge, const float* w_node, int edge_row, int node_row, int K,
+                                                              const float* gP, const float* gQ, const float* gR, const float* h0,
+                                                              const float* h, int64_t n_nodes, float* gh_prev, float* gh0_acc,
+                                                              float* partial) {
+  constexpr int OUT = 2 * FE + FN, NODES = 64;
+  extern __shared__ float sm[];
+  float* w = sm;                       // [OUT][K]
+  float* g = w + OUT * K;              // [NODES][OUT + 1]
+  float* hs = g + NODES * (OUT + 1);   // [NODES][K + 1], last column = 1 (bias)
+  for (int i = threadIdx.x; i < OUT * K; i += TB) {
+    const int o = i / K, k = i - o * K;
+    w[i] = o < FE ? w_edge[o * edge_row + k] : (o < 2 * FE ? w_edge[(o - FE) * edge_row + K + k] : w_node[(o - 2 * FE) * node_row + k]);
+  }
+  const int64_t n0 = (int64_t)blockIdx.x * NODES;
+  for (int i = threadIdx.x; i < NODES * OUT; i += TB) {
+    const int v = i / OUT, o = i - v * OUT;
+    const int64_t node = n0 + v;
+    float val = 0.f;
+    if (node < n_nodes) val = o < FE ? gP[node * EP + o] : (o < 2 * FE ? gQ[node * EP + o - FE] : gR[node * FN + o - 2 * FE]);
+    g[v * (OUT + 1) + o] = val;
+  }
+  for (int i = threadIdx.x; i < NODES * (K + 1); i += TB) {
+    const int v = i / (K + 1), k = i - v * (K + 1);
+    const int64_t node = n0 + v;
+    float val = 0.f;
+    if (node < n_nodes) val = k == K ? 1.f : (K == 2 * FN ? (k < FN ? h0[node * FN + k] : h[node * FN + k - FN]) : h[node * FN + k]);
+    hs[i] = val;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NODES * K; i += TB) {
+    const int v = i / K, k = i - v * K;
+    const int64_t node = n0 + v;
+    if (node >= n_nodes) continue;
+    float a = 0.f;
+    for (int o = 0; o < OUT; ++o) a = fmaf(g[v * (OUT + 1) + o], w[o * K + k], a);
+    if (K == 2 * FN && k < FN) gh0_acc[node * FN + k] += a;        // the reattached block is the encoder output (mpn.py:285)
+    else gh_prev[node * FN + (K == 2 * FN ? k - FN : k)] = a;
+  }
+  for (int i = threadIdx.x; i < OUT * (K + 1); i += TB) {
+    const int o = i / (K + 1), k = i - o * (K + 1);
+    float a = 0.f;
+    for (int v = 0; v < NODES; ++v) a = fmaf(g[v * (OUT + 1) + o], hs[v * (K + 1) + k], a);
+    partial[(int64_t)blockIdx.x * (OUT * (K + 1)) + i] = a;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F. edge encoder (single Linear(fa, FE) + ReLU, mpn.py:116-126 with edge_fc_dims = []): weight-gradient partials.
+//    accumulators [FE][MAX_FA] then gb [FE]
+// ------------------------------------------------------------------------------------------------
+constexpr int MAX_FA = 8;
+__global__ void __launch_bounds__(TB) edge_enc_bwd_kernel(const float* edge_attr, int fa, const float* e0, const float* ge0, int64_t n_edges,
+                                                          float* partial) {
+  __shared__ float s_red[NW * (FE * MAX_FA + FE)];
+  float acc[FE * MAX_FA + FE];
+#pragma unroll
+  for (int i = 0; i < FE * MAX_FA + FE; ++i) acc[i] = 0.f;
+  const int64_t stride = (int64_t)gridDim.x * TB;
+  for (int64_t j = (int64_t)blockIdx.x * TB + threadIdx.x; j < n_edges; j += stride) {
+    float ea[MAX_FA];
+#pragma unroll
+    for (int k = 0; k < MAX_FA; ++k) ea[k] = k < fa ? edge_attr[j * fa + k] : 0.f;
+#pragma unroll
+    for (int o = 0; o < FE; ++o) {
+      const float gz = e0[j * FE + o] > 0.f ? ge0[j * FE + o] : 0.f;
+      acc[FE * MAX_FA + o] += gz;
+#pragma unroll
+      for (int k = 0; k < MAX_FA; ++k) acc[o * MAX_FA + k] = fmaf(gz, ea[k], acc[o * MAX_FA + k]);
+    }
+  }
+  block_reduce_store<FE * MAX_FA + FE>(acc, s_red, partial + (int64_t)blockIdx.x * (FE * MAX_FA + FE));
+}
+
+// ------------------------------------------------------------------------------------------------
+// G. dense layer backward (node encoder, mlp.py:14,18): gz = gy * [y > 0]; gb partials; gW = gz^T x (split over rows);
+//    gx = gz W.
+// ------------------------------------------------------------------------------------------------
+constexpr int RG_ROWS = 128;
+__global__ void __launch_bounds__(256) relu_grad_bias_kernel(const float* y, const float* gy, int relu, int64_t rows, int out_dim, float* gz,
+                                                             float* partial /* [chunks][out] */) {
+  const int64_t r0 = (int64_t)blockIdx.x * RG_ROWS, r1 = min(r0 + RG_ROWS, rows);
+  for (int c = threadIdx.x; c < out_dim; c += blockDim.x) {
+    float acc = 0.f;
+    for (int64_t r = r0; r < r1; ++r) {
+      const float g = (!relu || y[r * out_dim + c] > 0.f) ? gy[r * out_dim + c] : 0.f;
+      gz[r * out_dim + c] = g;
+      acc += g;
+    }
+    partial[(int64_t)blockIdx.x * out_dim + c] = acc;
+  }
+}
+
+// C[m][n] = sum_r A[r][m] * B[r][n] over this split's rows; 64 x 64 tile, 16 rows per iteration
+__global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t rows, int M, int Nn,
+                                                  int64_t rows_per_split, float* __restrict__ partial /* [splits][M*Nn] */) {
+  __shared__ float as[16][64 + 4], bs[16][64 + 4];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int64_t r_begin = (int64_t)blockIdx.z * rows_per_split, r_end = min(r_begin + rows_per_split, rows);
+  float acc[4][4] = {};
+  const int lr = tid >> 4, lc = (tid & 15) * 4;       // 16 rows x 64 columns per load wave
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += 16) {
+    const int64_t r = r0 + lr;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      as[lr][lc + u] = (r < r_end && m0 + lc + u < M) ? A[r * M + m0 + lc + u] : 0.f;
+      bs[lr][lc + u] = (r < r_end && n0 + lc + u < Nn) ? B[r * Nn + n0 + lc + u] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&as[k][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&bs[k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* out = partial + (int64_t)blockIdx.z * M * Nn;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
+      if (m < M && n < Nn) out[(int64_t)m * Nn + n] = acc[i][j];
+    }
+}
+
+// gx[r][i] = sum_o gz[r][o] * W[o][i]
+__global__ void __launch_bounds__(256) gz_times_w_kernel(const float* gz, const float* W, int64_t rows, int out_dim, int in_dim, float* gx) {
+  const int64_t total = rows * in_dim, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+    const int64_t r = t / in_dim;
+    const int i = (int)(t - r * in_dim);
+    float a = 0.f;
+    for (int o = 0; o < out_dim; ++o) a = fmaf(gz[r * out_dim + o], W[(int64_t)o * in_dim + i], a);
+    gx[t] = a;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// H. dst[r * dst_stride + c] (+)= sum_b partial[b * width + src_off + r * src_stride + c], b ascending: the one place
+//    where per-block partial sums meet, in a fixed order.  One block per table entry.
+// ------------------------------------------------------------------------------------------------
+struct FinTable { gnncca_fin_seg s[GNNCCA_MAX_FIN_SEGS]; int n; };
+__global__ void __launch_bounds__(256) finalize_kernel(const FinTable t) {
+  const gnncca_fin_seg sg = t.s[blockIdx.x];
+  const int total = sg.rows * sg.cols;
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += blockDim.x * gridDim.y) {
+    const int r = i / sg.cols, c = i - r * sg.cols;
+    float acc = 0.f;
+    for (int b = 0; b < sg.n_blocks; ++b) acc += sg.partial[(int64_t)b * sg.width + sg.src_off + r * sg.src_stride + c];
+    float* d = sg.dst + (int64_t)r * sg.dst_stride + c;
+    *d = sg.accumulate ? *d + acc : acc;
+  }
+}
+
+}  // namespace train
+}  // namespace gnncca
+
+using namespace gnncca;
+namespace tr = gnncca::train;
+
+static int blocks_for(int64_t n, int per_block) {
+  int64_t b = ceil_div(n > 0 ? n : 1, per_block);
+  const int64_t cap = (int64_t)kNumSMs * 4;
+  return (int)(b < cap ? b : cap);
+}
+
+extern "C" int32_t gnncca_train_blocks(int64_t n_items, int32_t kind) {
+  switch (kind) {
+    case GNNCCA_BLOCKS_PER_EDGE: return blocks_for(n_items, tr::TB);
+    case GNNCCA_BLOCKS_PER_NODE_WARP: return blocks_for(n_items, tr::NW);
+    case GNNCCA_BLOCKS_NODE_PROJECT: return (int32_t)ceil_div(n_items > 0 ? n_items : 1, 64);
+    case GNNCCA_BLOCKS_ROW_CHUNKS: return (int32_t)ceil_div(n_items > 0 ? n_items : 1, tr::RG_ROWS);
+    default: return -1;
+  }
+}
+
+static bool dims_ok(const gnncca_mp_cfg* cfg) { return cfg && cfg->f_node == tr::FN && cfg->f_edge == tr::FE; }
+
+extern "C" int gnncca_node_agg_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, int64_t n_nodes,
+                                   const float* R, const float* e, const float* gh, const float* h_out, float* gR, float* gh_eff,
+                                   float* partial, void* stream) {
+  if (!dims_ok(cfg)) return cfg ? GNNCCA_ERR_UNSUPPORTED : GNNCCA_ERR_BAD_ARG;
+  if (n_nodes == 0) return GNNCCA_OK;
+  if (!w || !rowptr || !R || !e || !gh || !gR || !partial || (cfg->agg == GNNCCA_AGG_MAX && (!h_out || !gh_eff))) return GNNCCA_ERR_BAD_ARG;
+  const int K = cfg->reattach_nodes ? 2 * tr::FN : tr::FN;
+  tr::NodeAggBwd p{rowptr, R, e, gh, h_out, w->w_node, K + tr::FE, K, n_nodes, cfg->agg, gR, partial, gh_eff};
+  tr::node_agg_bwd_kernel<<<blocks_for(n_nodes, tr::NW), tr::TB, 0, (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
+extern "C" int gnncca_edge_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, const int32_t* src,
+                               int64_t n_edges, const float* R, const float* e, const float* e_prev, const float* e0, const float* gh,
+                               const float* h_out, const float* ge_in, const float* ge_cls, float* gze, float* ge_prev, float* ge0_acc,
+                               float* partial, void* stream) {
+  if (!dims_ok(cfg)) return cfg ? GNNCCA_ERR_UNSUPPORTED : GNNCCA_ERR_BAD_ARG;
+  if (n_edges == 0) return GNNCCA_OK;
+  if (!w || !rowptr || !src || !e || !e_prev || !gze || !ge_prev || !partial) return GNNCCA_ERR_BAD_ARG;
+  if (gh && (!R || (cfg->agg == GNNCCA_AGG_MAX && !h_out))) return GNNCCA_ERR_BAD_ARG;
+  if (cfg->reattach_edges && (!e0 || !ge0_acc)) return GNNCCA_ERR_BAD_ARG;
+  const int K = cfg->reattach_nodes ? 2 * tr::FN : tr::FN;
+  const int EIN = cfg->reattach_edges ? 2 * tr::FE : tr::FE;
+  tr::EdgeBwd p{rowptr, src, R, e, e_prev, e0, gh, h_out, ge_in, ge_cls, w->w_node, w->w_edge, K + tr::FE, 2 * K + EIN, K,
+                n_edges, cfg->agg, gze, ge_prev, ge0_acc, partial};
+  const int grid = blocks_for(n_edges, tr::TB);
+  if (cfg->reattach_edges) tr::edge_bwd_kernel<true><<<grid, tr::TB, 0, (cudaStream_t)stream>>>(p);
+  else tr::edge_bwd_kernel<false><<<grid, tr::TB, 0, (cudaStream_t)stream>>>(p);
+  return check_launch();
+}
+
+static tr::ClsParams cls_params(const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* aff) {
+  // aff: device [4][HC] = scale | shift | mean | invstd, or NULL for "no BatchNorm"
+  return tr::ClsParams{e, n_edges, w->w_c1, w->b_c1, w->w_c2, w->b_c2, aff, aff ? aff + tr::HC : nullptr, aff ? aff + 2 * tr::HC : nullptr,
+                       aff ? aff + 3 * tr::HC : nullptr};
+}
+
+extern "C" int gnncca_cls_moments(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* center,
+                                  float* partial, void* stream) {
+  if (!cfg || !w || cfg->cls_hidden != tr::HC || cfg->f_edge != tr::FE) return GNNCCA_ERR_UNSUPPORTED;
+  if (n_edges <= 0 || !e || !partial || !w->w_c1 || !w->b_c1) return GNNCCA_ERR_BAD_ARG;
+  tr::cls_moments_kernel<<<blocks_for(n_edges, tr::TB), tr::TB, 0, (cudaStream_t)stream>>>(cls_params(w, e, n_edges, nullptr), center, partial);
+  return check_launch();
+}
+
+extern "C" int gnncca_cls_bn_prepare(int32_t mode, const float* sums, int64_t n_edges, const float* gamma, const float* beta, float eps,
+                                     float momentum, float* running_mean, float* running_var, float* aff, void* stream) {
+  if (!sums || !aff || n_edges <= 0 || (mode != 0 && mode != 1) || (mode == 1 && (!gamma || !beta))) return GNNCCA_ERR_BAD_ARG;
+  tr::cls_bn_prepare_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(mode, sums, n_edges, gamma, beta, eps, momentum, running_mean, running_var,
+                                                               aff + 2 * tr::HC, aff + 3 * tr::HC, aff, aff + tr::HC);
+  return check_launch();
+}
+
+extern "C" int gnncca_cls_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* aff,
+                              float* logits, void* stream) {
+  if (!cfg || !w || cfg->cls_hidden != tr::HC || cfg->f_edge != tr::FE) return GNNCCA_ERR_UNSUPPORTED;
+  if (n_edges == 0) return GNNCCA_OK;
+  if (!e || !logits || !w->w_c1 || !w->b_c1 || !w->w_c2 || !w->b_c2) return GNNCCA_ERR_BAD_ARG;
+  tr::cls_fwd_kernel<<<blocks_for(n_edges, tr::TB), tr::TB, 0, (cudaStream_t)stream>>>(cls_params(w, e, n_edges, aff), logits);
+  return check_launch();
+}
+
+extern "C" int gnncca_cls_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* aff,
+                              int32_t pass, const float* g_logits, const float* batch_sums, float* ge_cls, float* partial, void* stream) {
+  if (!cfg || !w || cfg->cls_hidden != tr::HC || cfg->f_edge != tr::FE) return GNNCCA_ERR_UNSUPPORTED;
+  if (n_edges == 0) return GNNCCA_OK;
+  if (!e || !g_logits || !partial || pass < 0 || pass > 2 || (pass != 1 && !ge_cls) || (pass == 2 && !batch_sums)) return GNNCCA_ERR_BAD_ARG;
+  tr::cls_bwd_kernel<<<blocks_for(n_edges, tr::TB), tr::TB, 0, (cudaStream_t)stream>>>(cls_params(w, e, n_edges, aff), pass, g_logits,
+                                                                                       batch_sums, ge_cls, partial);
+  return check_launch();
+}
+
+extern "C" int gnncca_pq_reduce(const int32_t* rowptr, const int32_t* colptr, const int32_t* tperm, const float* gze, int64_t n_nodes,
+                                float* gP, float* gQ, void* stream) {
+  if (n_nodes == 0) return GNNCCA_OK;
+  if (!rowptr || !colptr || !tperm || !gze || !gP || !gQ) return GNNCCA_ERR_BAD_ARG;
+  tr::pq_reduce_kernel<<<blocks_for(n_nodes, tr::NW), tr::TB, 0, (cudaStream_t)stream>>>(rowptr, colptr, tperm, gze, n_nodes, gP, gQ);
+  return check_launch();
+}
+
+extern "C" int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* gP, const float* gQ, const float* gR,
+                                       const float* h0, const float* h, int64_t n_nodes, float* gh_prev, float* gh0_acc, float* partial,
+                                       void* stream) {
+  if (!dims_ok(cfg)) return cfg ? GNNCCA_ERR_UNSUPPORTED : GNNCCA_ERR_BAD_ARG;
+  if (n_nodes == 0) return GNNCCA_OK;
+  if (!w || !gP || !gQ || !gR || !h || !gh_prev || !partial || (cfg->reattach_nodes && (!h0 || !gh0_acc))) return GNNCCA_ERR_BAD_ARG;
+  const int K = cfg->reattach_nodes ? 2 * tr::FN : tr::FN, EIN = cfg->reattach_edges ? 2 * tr::FE : tr::FE, OUT = 2 * tr::FE + tr::FN;
+  const size_t smem = sizeof(float) * (OUT * K + 64 * (OUT + 1) + 64 * (K + 1));
+  auto kern = tr::node_project_bwd_kernel;
+  if (smem > 48 * 1024) {
+    int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (rc) return rc;
+  }
+  kern<<<(unsigned)ceil_div(n_nodes, 64), tr::TB, smem, (cudaStream_t)stream>>>(w->w_edge, w->w_node, 2 * K + EIN, K + tr::FE, K, gP, gQ, gR, h0,
+                                                                               h, n_nodes, gh_prev, gh0_acc, partial);
+  return check_launch();
+}
+
+extern "C" int gnncca_edge_enc_bwd(const float* edge_attr, int32_t edge_in_dim, const float* e0, const float* ge0, int64_t n_edges,
+                                   float* partial, void* stream) {
+  if (edge_in_dim < 1 || edge_in_dim > tr::MAX_FA) return GNNCCA_ERR_UNSUPPORTED;
+  if (n_edges == 0) return GNNCCA_OK;
+  if (!edge_attr || !e0 || !ge0 || !partial) return GNNCCA_ERR_BAD_ARG;
+  tr::edge_enc_bwd_kernel<<<blocks_for(n_edges, tr::TB), tr::TB, 0, (cudaStream_t)stream>>>(edge_attr, edge_in_dim, e0, ge0, n_edges, partial);
+  return check_launch();
+}
+
+extern "C" int gnncca_linear_bwd(const float* x, const float* W, const float* y, const float* gy, int32_t relu, int64_t rows, int32_t in_dim,
+                                 int32_t out_dim, float* gz, float* gx, float* gb_partial, float* gw_partial, int32_t n_splits,
+                                 void* stream) {
+  if (rows <= 0 || in_dim <= 0 || out_dim <= 0 || n_splits < 1) return GNNCCA_ERR_BAD_ARG;
+  if (!x || !y || !gy || !gz || !gb_partial || !gw_partial || (gx && !W)) return GNNCCA_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  tr::relu_grad_bias_kernel<<<(unsigned)ceil_div(rows, tr::RG_ROWS), 256, 0, st>>>(y, gy, relu, rows, out_dim, gz, gb_partial);
+  const int64_t rps = ceil_div(ceil_div(rows, n_splits), 16) * 16;
+  dim3 grid((unsigned)ceil_div(in_dim, 64), (unsigned)ceil_div(out_dim, 64), (unsigned)n_splits);
+  tr::atb_kernel<<<grid, 256, 0, st>>>(gz, x, rows, out_dim, in_dim, rps, gw_partial);
+  int n = 2;
+  if (gx) { tr::gz_times_w_kernel<<<grid_for(rows * in_dim, 256), 256, 0, st>>>(gz, W, rows, out_dim, in_dim, gx); ++n; }
+  return check_launch(n);
+}
+
+extern "C" int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_segs, void* stream) {
+  if (n_segs < 0 || n_segs > GNNCCA_MAX_FIN_SEGS || (n_segs > 0 && !host_segs)) return GNNCCA_ERR_BAD_ARG;
+  if (n_segs == 0) return GNNCCA_OK;
+  tr::FinTable t{};
+  t.n = n_segs;
+  int max_elems = 1;
+  for (int i = 0; i < n_segs; ++i) {
+    t.s[i] = host_segs[i];
+    if (!t.s[i].partial || !t.s[i].dst || t.s[i].rows < 0 || t.s[i].cols < 0 || t.s[i].n_blocks < 0) return GNNCCA_ERR_BAD_ARG;
+    if (t.s[i].rows * t.s[i].cols > max_elems) max_elems = t.s[i].rows * t.s[i].cols;
+  }
+  int gy = (int)ceil_div(max_elems, 256 * 4);
+  if (gy > 64) gy = 64;
+  tr::finalize_kernel<<<dim3((unsigned)n_segs, (unsigned)gy), 256, 0, (cudaStream_t)stream>>>(t);
+  return check_launch();
+}

@@ -146,9 +146,6 @@ int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes
  * Edges must be source-sorted (rowptr consistent with src).  Deterministic: no floating-point atomics;
  * segments that span tiles are combined in tile order by the last tile to arrive.
  * e_out may alias e_in.  h_out may be NULL (last step: the node update is dead, mpn.py:288-299).
- * cls_stats (training-mode classifier BatchNorm): when non-NULL, logits are NOT written; instead
- * per-tile partial sums of the classifier's hidden pre-activation are written for
- * gnncca_cls_bn_finalize.
  * guard_flags (optional): the flags[] of gnncca_csr_from_edge_index; when any is set the launch is a
  * no-op, so a caller may enqueue the whole forward before reading the flags back. */
 int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
@@ -182,6 +179,81 @@ int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
  * dims[0..n_layers] are the layer widths, W[l]/b[l] the torch weights, relu[l] per layer. */
 int gnncca_edge_mlp(const float* x, float* y, int64_t n_rows, int32_t n_layers, const int32_t* host_dims,
                     const float* const* host_W, const float* const* host_b, const int32_t* host_relu, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Backward (autograd of models/mpn.py:250-299 under the loss of train.py:80-97; SURVEY 8b "autograd").
+ * Notation for step t: h = h^{t-1}, e_prev = e^{t-1} (inputs), e = e^t, h_out = h^t (outputs), P/Q/R =
+ * gnncca_node_project(h).  All reductions are fixed-order: kernels write per-block partial sums into
+ * `partial` ([gnncca_train_blocks(...)][width] floats) and gnncca_finalize_grads adds them up in block
+ * order.  No floating-point atomics: gradients are bit-identical run to run.
+ * ---------------------------------------------------------------------------------------------- */
+enum { GNNCCA_BLOCKS_PER_EDGE = 0, GNNCCA_BLOCKS_PER_NODE_WARP = 1, GNNCCA_BLOCKS_NODE_PROJECT = 2, GNNCCA_BLOCKS_ROW_CHUNKS = 3 };
+/* Number of blocks (= rows of `partial`) the kernels of a kind launch for n_items edges / nodes / rows. */
+int32_t gnncca_train_blocks(int64_t n_items, int32_t kind);
+
+/* gR[v] = sum over out-edges of d(agg)/d(message) * [z_m > 0] (z_m recomputed from R and e); partial
+ * [GNNCCA_BLOCKS_PER_NODE_WARP blocks][f_edge * f_node] holds gW_node[c][K + k] at index c * f_edge + k.
+ * gh = gradient wrt h_out; h_out itself is only read for GNNCCA_AGG_MAX, where gh_eff[N][f_node] receives gh divided
+ * by the number of edges attaining the max (ties share the gradient) -- pass THAT as gh to gnncca_edge_bwd. */
+int gnncca_node_agg_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, int64_t n_nodes,
+                        const float* R, const float* e, const float* gh, const float* h_out, float* gR, float* gh_eff,
+                        float* partial, void* stream);
+
+/* Per edge: ge = W_ne^T gz_m + ge_in + ge_cls (gh == NULL: dead node update, first term absent);
+ * gze[E][8] = ge * [e > 0]; ge_prev[E][f_edge] = W_ee^T gze (current-edge block); with reattach_edges
+ * ge0_acc += (initial-edge block); partial [GNNCCA_BLOCKS_PER_EDGE blocks][f_edge * EIN] = gW_edge[o][2K + kk]. */
+int gnncca_edge_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, const int32_t* src,
+                    int64_t n_edges, const float* R, const float* e, const float* e_prev, const float* e0, const float* gh,
+                    const float* h_out, const float* ge_in, const float* ge_cls, float* gze, float* ge_prev, float* ge0_acc,
+                    float* partial, void* stream);
+
+/* Classifier with an explicit per-feature affine `aff` (device float[4][cls_hidden]: scale | shift | mean | invstd;
+ * NULL = no BatchNorm): logit = w2 . relu((W1 e + b1) * scale + shift) + b2.
+ * Training-mode BatchNorm1d: gnncca_cls_moments(center = NULL) -> finalize -> gnncca_cls_bn_prepare(mode 0) gives
+ * the batch mean; gnncca_cls_moments(center = mean) -> finalize -> gnncca_cls_bn_prepare(mode 1) gives invstd,
+ * scale, shift and updates the running statistics (momentum, unbiased variance) like torch.nn.BatchNorm1d.
+ * moments partial: [blocks][2 * cls_hidden] = sum(c - center) | sum((c - center)^2). */
+int gnncca_cls_moments(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* center,
+                       float* partial, void* stream);
+int gnncca_cls_bn_prepare(int32_t mode, const float* sums, int64_t n_edges, const float* gamma, const float* beta, float eps,
+                          float momentum, float* running_mean, float* running_var, float* aff, void* stream);
+int gnncca_cls_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* aff,
+                   float* logits, void* stream);
+/* pass 0: no / eval-mode BatchNorm (one sweep); pass 1 then 2: training-mode BatchNorm (1 = batch sums, 2 = input
+ * gradients given the finalized sums `batch_sums` = the 41-float accumulator vector).  Accumulator layout of
+ * partial [blocks][41]: [0,24) gW1 | [24,28) gb1 | [28,32) gw2 | 32 gb2 | [33,37) g_gamma | [37,41) g_beta. */
+#define GNNCCA_CLS_ACC 41
+int gnncca_cls_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* e, int64_t n_edges, const float* aff,
+                   int32_t pass, const float* g_logits, const float* batch_sums, float* ge_cls, float* partial, void* stream);
+
+/* gP[v] / gQ[v] ([N][8]) = sums of gze over the out- / in-edges of v; (colptr, tperm) = CSR of the edges sorted by
+ * target (gnncca_csr_sort on the dst array), tperm[i] = id (in source-sorted order) of the i-th in-edge. */
+int gnncca_pq_reduce(const int32_t* rowptr, const int32_t* colptr, const int32_t* tperm, const float* gze, int64_t n_nodes,
+                     float* gP, float* gQ, void* stream);
+
+/* gh_prev[N][f_node] = gP W_s + gQ W_d + gR W_nx (current-node block; with reattach_nodes the initial-node block is
+ * added into gh0_acc).  partial [ceil(N/64)][44 * (K + 1)]: row o < 6 -> gW_edge[o][0:K], 6 <= o < 12 ->
+ * gW_edge[o-6][K:2K], o >= 12 -> gW_node[o-12][0:K]; column K = bias sums (b_edge for o < 6, b_node for o >= 12). */
+int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* gP, const float* gQ, const float* gR,
+                            const float* h0, const float* h, int64_t n_nodes, float* gh_prev, float* gh0_acc, float* partial,
+                            void* stream);
+
+/* Edge encoder Linear(edge_in_dim, f_edge)+ReLU: partial [GNNCCA_BLOCKS_PER_EDGE blocks][f_edge * 8 + f_edge] = gW[o][k] at o*8+k | gb. */
+int gnncca_edge_enc_bwd(const float* edge_attr, int32_t edge_in_dim, const float* e0, const float* ge0, int64_t n_edges,
+                        float* partial, void* stream);
+
+/* Dense layer y = act(x W^T + b): gz[rows,out] = gy * [y > 0] (relu != 0), gb_partial [GNNCCA_BLOCKS_ROW_CHUNKS][out],
+ * gw_partial [n_splits][out * in] (row ranges), gx[rows,in] = gz W when gx != NULL. */
+int gnncca_linear_bwd(const float* x, const float* W, const float* y, const float* gy, int32_t relu, int64_t rows, int32_t in_dim,
+                      int32_t out_dim, float* gz, float* gx, float* gb_partial, float* gw_partial, int32_t n_splits, void* stream);
+
+/* dst[r * dst_stride + c] (+)= sum_{b < n_blocks} partial[b * width + src_off + r * src_stride + c]  (b ascending). */
+typedef struct {
+  const float* partial; float* dst;
+  int32_t n_blocks, width, src_off, src_stride, rows, cols, dst_stride, accumulate;
+} gnncca_fin_seg;
+#define GNNCCA_MAX_FIN_SEGS 24
+int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_segs, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Graph + edge-attribute construction, train.py:257-259,286-361,450.
