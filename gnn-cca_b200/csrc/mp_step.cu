@@ -38,6 +38,7 @@ struct StepParams {
   int num_tiles;
   float* tile_part;      // [num_tiles][2][FN]  slot 0: continuation piece (started in an earlier tile), slot 1: open tail
   int32_t* counters;     // [num_tiles] arrival counters, zeroed by the host entry before the launch
+  int phase;             // position of local edge 0 inside a 256-edge tile of the GLOBAL edge numbering (edge-partitioned graphs)
   const int32_t* guard;  // optional CSR flags (gnncca_csr_from_edge_index): the kernel is a no-op when any is set
 };
 
@@ -51,7 +52,7 @@ __device__ __forceinline__ void finalize_node(const StepParams& p, int node, flo
 // Cross-tile combination.  kind 0 = this tile continues a segment begun earlier, kind 1 = this tile opens one.
 __device__ __forceinline__ void publish_partial(const StepParams& p, int tile, int kind, int node, float total, int lane) {
   const int rs = p.rowptr[node], re = p.rowptr[node + 1];
-  const int t0 = rs / TILE, t1 = (re - 1) / TILE;
+  const int t0 = (rs + p.phase) / TILE, t1 = (re - 1 + p.phase) / TILE;
   p.tile_part[((int64_t)tile * 2 + kind) * FN + lane] = total;
   __threadfence();
   __syncwarp();
@@ -105,10 +106,10 @@ __global__ void __launch_bounds__(TILE, 3) mp_step_fwd_kernel(const StepParams p
   for (int k = 0; k < FE; ++k) wne[k] = s_wne[k][lane];
 
   for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-    const int64_t base = (int64_t)tile * TILE;
+    const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
     const int64_t i = base + tid;
     // ------------------------------ phase A: thread per edge ------------------------------
-    if (i < p.n_edges) {
+    if (i >= 0 && i < p.n_edges) {
       const int s = ld_stream_i32(p.src + i), d = ld_stream_i32(p.dst + i);
       float ein[EIN];
       if (REATT_E) {  // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
@@ -157,7 +158,7 @@ __global__ void __launch_bounds__(TILE, 3) mp_step_fwd_kernel(const StepParams p
       const int64_t c0 = base + warp * 32;
       const int64_t c1 = min(c0 + 32, tile_end);
       int Cnode = -1, Cclosed = 0, Onode = -1;
-      int64_t j0 = c0;
+      int64_t j0 = max(c0, (int64_t)0);
       while (j0 < c1) {
         const int s = s_src[j0 - base];
         const int rs = p.rowptr[s], re = p.rowptr[s + 1];
@@ -217,7 +218,7 @@ using namespace gnncca;
 
 extern "C" int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes, int64_t n_edges) {
   (void)cfg; (void)n_nodes;
-  const int64_t tiles = ceil_div(n_edges > 0 ? n_edges : 1, TILE);
+  const int64_t tiles = ceil_div((n_edges > 0 ? n_edges : 1) + TILE, TILE);   // + one tile: the partition phase shifts the tiling
   return (int64_t)(align256(sizeof(int32_t) * tiles) + align256(sizeof(float) * tiles * 2 * FN) + 256);
 }
 
@@ -254,7 +255,9 @@ extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weig
   sp.P = P; sp.Q = Q; sp.R = R; sp.e0 = e0; sp.e_in = e_in; sp.e_out = e_out; sp.h_out = h_out; sp.logits = logits;
   sp.guard = guard_flags;
   sp.w = *w; sp.agg = cfg->agg; sp.nf = cfg->reattach_nodes ? 2 : 1;
-  sp.num_tiles = (int)ceil_div(n_edges, TILE);
+  if (cfg->edge_phase < 0 || cfg->edge_phase >= TILE) return GNNCCA_ERR_BAD_ARG;
+  sp.phase = cfg->edge_phase;
+  sp.num_tiles = (int)ceil_div(n_edges + sp.phase, TILE);
   char* ws = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   sp.counters = (int32_t*)ws;
   sp.tile_part = (float*)(ws + align256(sizeof(int32_t) * sp.num_tiles));

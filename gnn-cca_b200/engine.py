@@ -78,7 +78,7 @@ class StepBinding:
         cls = model.classifier.edge_mlp
         self.cfg = _lib.MpCfg(f_node=self.f_node, f_edge=self.f_edge, cls_hidden=cls.layer_specs[0].out_dim,
                               agg=_lib.AGG[model.node_agg_name], reattach_nodes=int(model.reattach_initial_nodes),
-                              reattach_edges=int(model.reattach_initial_edges), math=math, reserved=0)
+                              reattach_edges=int(model.reattach_initial_edges), math=math, edge_phase=0)
         em, nm = model.MPNet.edge_model.edge_mlp, model.MPNet.node_model.node_mlp
         bn = cls.batchnorm(0)
         self.w = _lib.MpWeights(

@@ -1,0 +1,195 @@
+"""Multi-GPU execution of the hot path on one 8 x B200 box: one process per GPU, ``torch.distributed`` for plumbing.
+
+The reference has no distributed code at all; the two partitionings here follow from the
+structure of ``MOTMPNet.forward`` (models/mpn.py:250-299):
+
+* **Frame sharding** (BASELINE configs 1-4).  A PyG ``Batch`` is a disjoint union of per-frame graphs and no
+  operation of the forward mixes frames in eval mode, so rank r simply takes a contiguous block of frames.
+  No collective on the data path; results are bit-identical to the single-GPU run frame by frame.
+
+* **Edge partition of one giant graph** (config 5).  Edges are source-major, the aggregation index is the source
+  (``scatter(..., row)``, mpn.py:99), so rank r owns a contiguous range of SOURCE nodes with all their out-edges:
+  the segmented reduction is rank-local and the only exchange is the updated node features (N x 32 fp32, 1 MB at
+  N = 8192) after each node update, because the next edge update reads ``x[col]`` for arbitrary targets.  Every
+  node's segment lives on one rank, so the summation order -- and therefore every bit of the result -- is the
+  same as on one GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .graph import Batch
+
+
+# ------------------------------------------------------------------------------------------------------------
+# frame sharding
+# ------------------------------------------------------------------------------------------------------------
+def frame_shard(num_frames: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous block [g0, g1) of frames for ``rank``: sizes differ by at most one, earlier ranks get the extras."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    base, extra = divmod(num_frames, world)
+    g0 = rank * base + min(rank, extra)
+    return g0, g0 + base + (1 if rank < extra else 0)
+
+
+def shard_batch(batch: Batch, rank: int, world: int) -> Batch:
+    """The sub-batch of ``rank``: its frames' nodes and edges with ``edge_index`` rebased to the first owned node.
+    Needs ``batch.ptr`` (frame node offsets) and source-major edges; ``batch.edge_ptr`` is used when present,
+    otherwise the edge offsets are found by a binary search in ``edge_index[0]``."""
+    ptr = batch.ptr
+    B = int(ptr.numel()) - 1
+    g0, g1 = frame_shard(B, rank, world)
+    sub_ptr = ptr[g0:g1 + 1]
+    n0, n1 = int(sub_ptr[0]), int(sub_ptr[-1])
+    eptr = getattr(batch, "edge_ptr", None)
+    if eptr is not None:
+        e0, e1 = int(eptr[g0]), int(eptr[g1])
+    else:
+        row = batch.edge_index[0].contiguous()
+        b = torch.searchsorted(row, torch.tensor([n0, n1], device=row.device, dtype=row.dtype))
+        e0, e1 = int(b[0]), int(b[1])
+    kw = dict(x=batch.x[n0:n1], edge_index=batch.edge_index[:, e0:e1] - n0, edge_attr=batch.edge_attr[e0:e1], ptr=sub_ptr - n0,
+              num_graphs=g1 - g0)
+    for name in ("edge_labels",):
+        if getattr(batch, name, None) is not None:
+            kw[name] = getattr(batch, name)[e0:e1]
+    for name in ("y", "batch"):
+        if getattr(batch, name, None) is not None:
+            v = getattr(batch, name)[n0:n1]
+            kw[name] = v - g0 if name == "batch" else v
+    if eptr is not None:
+        kw["edge_ptr"] = eptr[g0:g1 + 1] - e0
+    if getattr(batch, "gnncca_caps", None) is not None:
+        kw["gnncca_caps"] = batch.gnncca_caps
+    if getattr(batch, "gnncca_trusted", False):
+        kw["gnncca_trusted"] = True
+    return Batch(**kw)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# one giant graph: partition the edges by source-node range
+# ------------------------------------------------------------------------------------------------------------
+def balanced_source_ranges(rowptr: torch.Tensor, world: int) -> List[Tuple[int, int]]:
+    """Cut the node range into ``world`` contiguous pieces with (nearly) equal numbers of out-edges: piece r ends at
+    the first node whose cumulative edge count reaches E (r+1) / world.  Pure index arithmetic, bit-exact."""
+    rp = rowptr.detach().to("cpu", torch.int64)
+    N, E = int(rp.numel()) - 1, int(rp[-1])
+    cuts = [0]
+    for r in range(1, world):
+        target = (E * r + world - 1) // world
+        c = int(torch.searchsorted(rp, torch.tensor(target, dtype=torch.int64), right=False))
+        cuts.append(min(max(c, cuts[-1]), N))
+    cuts.append(N)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def exchange_node_rows(h_partial: torch.Tensor, ranges: Sequence[Tuple[int, int]], group=None) -> torch.Tensor:
+    """Assemble the full node-feature matrix from per-rank row ranges.  ``h_partial`` is [N, F] with this rank's rows
+    valid and all others ZERO.  Equal-sized ranges use one all-gather of the owned rows; ragged ranges one
+    all-reduce (x + 0 is exact, so both give the same bits)."""
+    if not dist.is_available() or not dist.is_initialized():
+        return h_partial
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if world == 1:
+        return h_partial
+    sizes = {b - a for a, b in ranges}
+    if len(sizes) == 1 and ranges[0][0] == 0 and all(ranges[i][1] == ranges[i + 1][0] for i in range(world - 1)):
+        out = torch.empty_like(h_partial)
+        a, b = ranges[rank]
+        dist.all_gather_into_tensor(out, h_partial[a:b].contiguous(), group=group)
+        return out
+    out = h_partial.clone()
+    dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
+    return out
+
+
+def forward_edge_partitioned(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor,
+                             ranges: Sequence[Tuple[int, int]], group=None, edge_base: int = 0) -> List[torch.Tensor]:
+    """Drive ``edge_partitioned_steps`` with the NCCL exchange of ``exchange_node_rows`` (see there).  ``edge_base``:
+    global id of this rank's first edge (the sum of the lower ranks' edge counts)."""
+    gen = edge_partitioned_steps(model, x, edge_index_local, edge_attr_local, edge_base)
+    try:
+        h_partial = next(gen)
+        while True:
+            h_partial = gen.send(exchange_node_rows(h_partial, ranges, group))
+    except StopIteration as done:
+        return done.value
+
+
+def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0):
+    """Generator form of the edge-partitioned forward: yields this rank's partial node matrix ([N, F], rows of
+    nodes it does not own are zero) at every exchange point and expects the assembled matrix back through
+    ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
+
+    ``MOTMPNet.forward`` for ONE graph whose edges are partitioned by source-node range across the ranks of
+    ``group``.  ``x`` [N, F] is the full node-feature matrix (replicated: the encoder is cheap next to E),
+    ``edge_index_local`` [2, E_r] holds GLOBAL node ids of the edges whose source lies in ``ranges[rank]``
+    (source-major), ``edge_attr_local`` their attributes.  Returns this rank's slice of every classified step's
+    logits ([E_r, 1] each), identical to the corresponding rows of the single-GPU result."""
+    from . import engine
+    from .plan import GraphPlan, _stream
+    lib = _lib.load()
+    engine.check_supported(model)
+    engine._require_cuda(x, "x")
+    engine._require_cuda(edge_attr_local, "edge_attr")
+    if torch.is_grad_enabled() and any(p.requires_grad for p in model.parameters()):
+        raise NotImplementedError("the edge-partitioned path is inference only (use torch.no_grad())")
+    dev = x.device
+    N, E = int(x.size(0)), int(edge_index_local.size(1))
+    math = engine.MATH_MODES[model.math]
+    plan = GraphPlan(edge_index_local, N).resolve()      # rowptr spans all N nodes; segments outside the owned range are empty
+    if plan.perm is not None:
+        raise ValueError("the local edge slice must be source-major")
+    h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math)
+    e = engine.small_mlp_rows(model.encoder.edge_mlp, edge_attr_local.contiguous())
+    h0, e0 = h, e
+    sb = engine.StepBinding(model, math)
+    sb.cfg.edge_phase = int(edge_base) % 256      # tile the local slice like the whole graph: bit-identical reductions
+    L, k = model.num_enc_steps, model.num_class_steps
+    first = L - k + 1
+    outs: List[torch.Tensor] = []
+    if L == 0:
+        return [engine.small_mlp_rows_cls(model, e)]
+    P = torch.empty((N, 8), dtype=torch.float32, device=dev)
+    Q = torch.empty((N, 8), dtype=torch.float32, device=dev)
+    R = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
+    ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), N, E))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    for step in range(1, L + 1):
+        _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
+                                           _stream()), "node_project")
+        last = step == L
+        e_out = torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e
+        h_out = None if last else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
+        logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if step >= first else None
+        _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
+                                          _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
+                                          _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+        e = e_out
+        if logits is not None:
+            outs.append(logits)
+        if h_out is not None:
+            h = yield h_out                                  # the one exchange of the step: N x 32 fp32 over NVLink
+    return outs
+
+
+def complete_multipartite_slice(n_cams: int, n_dets: int, node_range: Tuple[int, int], device) -> torch.Tensor:
+    """edge_index [2, E_r] (global ids, source-major) of the cross-camera complete graph on n_cams x n_dets
+    camera-major detections, restricted to sources in ``node_range`` -- the enumeration rule of train.py:292-299 in
+    closed form, generated on the device so that no rank ever holds the whole edge list."""
+    a, b = node_range
+    n = n_cams * n_dets
+    src = torch.arange(a, b, device=device, dtype=torch.int64)
+    cam = src // n_dets
+    deg = n - n_dets
+    k = torch.arange(deg, device=device, dtype=torch.int64)
+    # targets of a source in camera c: every node id except [c * D, (c + 1) * D), ascending
+    dst = k[None, :] + (k[None, :] >= (cam * n_dets)[:, None]).to(torch.int64) * n_dets
+    return torch.stack([src[:, None].expand(-1, deg).reshape(-1), dst.reshape(-1)])

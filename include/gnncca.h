@@ -110,7 +110,8 @@ typedef struct {
   int32_t reattach_nodes;  /* mpn.py:284-285                                                      */
   int32_t reattach_edges;  /* mpn.py:282-283                                                      */
   int32_t math;            /* GNNCCA_MATH_*: how the 6->32 message product is computed            */
-  int32_t reserved;
+  int32_t edge_phase;      /* 0, or (global id of local edge 0) % 256 when the edges are one rank's slice of a larger
+                              source-major list: keeps the reduction tiling -- and so every bit -- of the whole graph */
 } gnncca_mp_cfg;
 
 /* Weights of one step, all device pointers into the caller's parameters (read at every call, so
