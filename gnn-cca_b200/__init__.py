@@ -9,5 +9,6 @@ from .plan import GraphPlan
 from .graph import Batch, build_graph_batch, column_normalize
 from . import _lib
 from .engine import forward_host, StageTimer
+from . import multigpu
 
 __all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer"]
