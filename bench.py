@@ -34,7 +34,8 @@ WORKLOADS = {
     # name: (cams, dets, frames per GPU, CONV_TO_M of the dataset the shape comes from, data seed)
     "cfg1": dict(cams=4, dets=9, frames=64, max_dist=50.83, seed=1235, desc="EPFL-Terrace-shaped 4x9, batch 64"),
     "cfg2": dict(cams=4, dets=6, frames=1024, max_dist=44.23, seed=1236, desc="EPFL-Laboratory-shaped 4x6, batch 1024"),
-    "cfg3": dict(cams=4, dets=10, frames=64, max_dist=153.54, seed=1237, desc="EPFL-Basketball-shaped 4x10, batch 64"),
+    "cfg3": dict(cams=4, dets=10, frames=64, max_dist=153.54, seed=1237, train=True,
+                 desc="EPFL-Basketball-shaped 4x10, batch 64, BCE training step (fwd + loss + bwd + SGD)"),
     "cfg4s": dict(cams=8, dets=64, frames=64, max_dist=50.83, seed=1238, desc="scaled 8x64, 64-graph slice of cfg 4"),
 }
 METRIC = "MPN edges/sec (4 MP steps)"
@@ -48,7 +49,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--math", default=os.environ.get("GNNCCA_MATH", "fp32"), choices=["fp32", "tf32"])
+    ap.add_argument("--math", default=os.environ.get("GNNCCA_MATH", "tf32"), choices=["fp32", "tf32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     return ap.parse_args()
@@ -212,10 +213,155 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------------------
+# BASELINE config 3: training step (forward + summed BCE over the classified steps + backward + SGD), train.py:454-494
+# ------------------------------------------------------------------------------------------------------------
+def cpu_train_timer(params, sd0, x, ei, ea, labels, budget_s, steps=None):
+    import torch
+    from oracle import mpn_oracle
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = mpn_oracle.MPNSpec(params, "resnet50")
+    sd = {k: v.detach().clone().requires_grad_(v.is_floating_point()) for k, v in sd0.items()}
+    opt = torch.optim.SGD([v for v in sd.values() if v.requires_grad], lr=1e-3, momentum=0.9, weight_decay=1e-4)
+    crit = torch.nn.BCEWithLogitsLoss()
+    times, t_begin = [], time.perf_counter()
+    while True:
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        out = mpn_oracle.motmpnet_forward(spec, sd, x, ei, ea, training=True)["classified_edges"]
+        loss = sum(crit(r.view(-1), labels) for r in out)
+        loss.backward()
+        opt.step()
+        times.append(time.perf_counter() - t0)
+        if (steps is not None and len(times) >= steps + 1) or (steps is None and time.perf_counter() - t_begin > budget_s and len(times) >= 4):
+            break
+    return times[1:], cores
+
+
+def run_training(args):
+    import torch
+    import torch.distributed as dist
+    wl = WORKLOADS[args.workload]
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    cfgmod = importlib.import_module("gnn-cca_b200.config")
+    params = cfgmod.graph_net_params()
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        from oracle import mpn_oracle
+        b = host_inputs(wl)
+        sd = mpn_oracle.init_state_dict(mpn_oracle.MPNSpec(params, "resnet50"), seed=0)
+        times, cores = cpu_train_timer(params, sd, b.x, b.edge_index, b.edge_attr, b.edge_labels, 0.0, steps=args.steps)
+        E = int(b.edge_index.size(1))
+        val = E * len(times) / sum(times)
+        print(json.dumps({"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": len(times),
+                          "warmup": 1, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": "%s: %s" % (args.workload, wl["desc"])},
+                          "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": "full batch per step, oracle + torch autograd"},
+                          "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}), flush=True)
+        return
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    gnncca = importlib.import_module("gnn-cca_b200")
+    syn = importlib.import_module("gnn-cca_b200.synthetic")
+    lib = gnncca._lib.load(build_if_missing=False)
+    torch.manual_seed(0)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50").to(dev).train()
+    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4)
+    crit = torch.nn.BCEWithLogitsLoss()
+    batches = [gnncca.build_graph_batch(**syn.make_detections(wl["cams"], wl["dets"], wl["frames"], seed=wl["seed"] + 100 * rank + 7919 * s,
+                                                               device=dev, max_dist=wl["max_dist"])) for s in range(8)]
+    N, E = batches[0].num_nodes, batches[0].num_edges
+    in_bytes = sum(t.numel() * t.element_size() for t in (batches[0].x, batches[0].edge_index, batches[0].edge_attr, batches[0].edge_labels))
+
+    def step(b):
+        opt.zero_grad(set_to_none=True)
+        out = model(b)["classified_edges"]
+        loss = sum(crit(r.view(-1), b.edge_labels) for r in out)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(batches[i % 8])
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
+    l0 = int(lib.gnncca_launch_count())
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        step(batches[i % 8])
+    ev1.record()
+    barrier()
+    launches = int(lib.gnncca_launch_count()) - l0
+    ms = ev0.elapsed_time(ev1)
+    t_end = time.perf_counter() + 0.3
+    while time.perf_counter() < t_end:
+        step(batches[0])
+    torch.cuda.synchronize()
+    sampler.stop_flag.set(); sampler.join()
+    # end to end: inputs from pinned host memory every step, loss read back
+    hosts = [[t.cpu().pin_memory() for t in (b.x, b.edge_index, b.edge_attr, b.edge_labels)] for b in batches[:2]]
+    e2e_steps = max(3, min(args.steps, 20))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        hx, hei, hea, hl = hosts[i & 1]
+        b = gnncca.Batch(x=hx.to(dev, non_blocking=True), edge_index=hei.to(dev, non_blocking=True), edge_attr=hea.to(dev, non_blocking=True),
+                         edge_labels=hl.to(dev, non_blocking=True))
+        float(step(b).item())
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        ms_max, e2e_max = float(t[0]), float(t[1])
+        fb = forward_bytes(N, E, int(batches[0].x.size(1)))
+        train_bytes = fb + 4 * E * (24 + 24 + 24 + 32) + 3 * N * 8 * 2048          # + saved latents, gradient passes, dW1/x re-reads
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        ach = train_bytes / (ms_max / args.steps * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": world * E * args.steps / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "%s: %s per GPU (N=%d, E=%d)" % (args.workload, wl["desc"], N, E), "l2": "8 batches rotate; a batch is 22 MB (fits L2: launch-bound regime)",
+                           "optimizer": "SGD lr 1e-3 momentum 0.9 wd 1e-4", "parallelism": "graph-sharded x%d, no gradient all-reduce (independent replicas)" % world},
+                "clocks": sampler.result(), "gpu_launches": launches,
+                "e2e": {"value": world * E * e2e_steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps,
+                        "api": "MOTMPNet.forward + BCEWithLogitsLoss + backward + SGD.step on a batch copied from pinned host memory"},
+                "roofline": {"bound": "hbm", "kernel": "whole training step (launch-bound at this size)", "achieved": ach, "peak": peak, "unit": "GB/s",
+                             "frac": ach / peak, "traffic": None, "algorithmic_bytes_per_launch": train_bytes}}
+        if world == 1 and not args.no_cpu_baseline:
+            sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+            b = batches[0]
+            times, cores = cpu_train_timer(params, sd, b.x.cpu(), b.edge_index.cpu(), b.edge_attr.cpu(), b.edge_labels.cpu(), args.cpu_seconds)
+            line["cpu_baseline"] = {"value": E / statistics.median(times), "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": "%d training steps of the full batch (oracle forward + torch autograd + SGD), median" % len(times)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------------
 def main():
     args = parse()
+    if WORKLOADS[args.workload].get("train"):
+        run_training(args)
+        return
     if args.impl == "reference":
         run_reference(args)
         return

@@ -6,6 +6,7 @@ There is no CPU path and no eager fallback: CPU tensors, or configurations the k
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -85,15 +86,18 @@ class MLPGraphIndependent(nn.Module):
 class MOTMPNet(nn.Module):
     """Encoder -> L x (edge update, node update) -> per-step edge classifier (mpn.py:144-299).
 
-    Extra, optional keyword (not in the reference): ``math`` = 'tf32' (tcgen05 tensor cores for the dense
-    contractions, default) or 'fp32' (FFMA everywhere; the tight-tolerance path).
+    Extra, optional keyword (not in the reference): ``math`` = 'tf32' (default, or $GNNCCA_MATH: the node encoder's
+    2048-wide contraction runs on tcgen05 tensor cores with TF32 operands, everything else in FP32) or 'fp32' (FFMA
+    everywhere; the tight-tolerance path).  Training always runs in FP32.
     """
 
-    def __init__(self, model_params, bb_encoder=None, arch=None, math: str = "fp32"):
+    def __init__(self, model_params, bb_encoder=None, arch=None, math: Optional[str] = None):
         super().__init__()
         self.node_cnn = bb_encoder          # stored and never used, like the reference (mpn.py:163)
         self.model_params = model_params
-        self.math = math
+        self.math = math if math is not None else os.environ.get("GNNCCA_MATH", "tf32")
+        if self.math not in ("tf32", "fp32"):
+            raise ValueError("math must be 'tf32' or 'fp32'")
 
         edges_params = model_params['encoder_feats_dict']['edges']
         nodes_params = model_params['encoder_feats_dict']['nodes'][arch]

@@ -112,7 +112,7 @@ def test_forward_matches_oracle_on_synthetic_graphs(shape, agg, path, cuda_devic
     params = cfgmod.graph_net_params()
     params["node_agg_fn"] = agg
     torch.manual_seed(0)
-    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market", math="fp32").eval()
     spec = mpn_oracle.MPNSpec(params, "bdnet_market")
     x, ei, ea = synthetic_graph(*shape[:3], seed=42, ragged=shape[3])
     with torch.no_grad():
@@ -142,7 +142,7 @@ def test_forward_is_bit_reproducible(cuda_device):
     from importlib import import_module
     params = import_module("gnn-cca_b200.config").graph_net_params()
     torch.manual_seed(1)
-    model = gnncca.MOTMPNet(params, None, "bdnet_market").to(cuda_device).eval()
+    model = gnncca.MOTMPNet(params, None, "bdnet_market", math="fp32").to(cuda_device).eval()
     x, ei, ea = synthetic_graph(8, 40, 3, seed=3)
     data = D(x.to(cuda_device), ei.to(cuda_device), ea.to(cuda_device))
     with torch.no_grad():
@@ -157,7 +157,7 @@ def test_cpu_tensors_fail_loudly():
     import gnncca
     from importlib import import_module
     params = import_module("gnn-cca_b200.config").graph_net_params()
-    model = gnncca.MOTMPNet(params, None, "bdnet_market").eval()
+    model = gnncca.MOTMPNet(params, None, "bdnet_market", math="fp32").eval()
     x, ei, ea = synthetic_graph(2, 2, 1, seed=0)
     with pytest.raises(RuntimeError):
         with torch.no_grad():
@@ -186,7 +186,7 @@ def test_fused_pipeline_resizes_or_falls_back_to_step_kernels(sizes, expect, cud
     from importlib import import_module
     params = import_module("gnn-cca_b200.config").graph_net_params()
     torch.manual_seed(2)
-    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market", math="fp32").eval()
     spec = mpn_oracle.MPNSpec(params, "bdnet_market")
     x, ei, ea = _frames(sizes)
     with torch.no_grad():
@@ -209,7 +209,7 @@ def test_fused_pipeline_rejects_a_ptr_that_cuts_through_edges(cuda_device):
     from importlib import import_module
     params = import_module("gnn-cca_b200.config").graph_net_params()
     torch.manual_seed(2)
-    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").eval()
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market", math="fp32").eval()
     spec = mpn_oracle.MPNSpec(params, "bdnet_market")
     x, ei, ea = _frames([3, 4, 5])
     with torch.no_grad():
@@ -221,3 +221,23 @@ def test_fused_pipeline_rejects_a_ptr_that_cuts_through_edges(cuda_device):
     assert model.last_plan.last_path == "steps"
     for o, r in zip(out, ref):
         assert close(o, r) <= FP32_RTOL
+
+
+def test_default_tf32_pipeline_matches_reference_vectors_within_tf32_tolerance(cuda_device):
+    """The default math mode runs the node encoder on tcgen05 kind::tf32: logits stay within the TF32 tolerance of the
+    reference's own outputs and agree on every decision that is not within tolerance of the threshold."""
+    TF32_TOL = 5e-3
+    z = load_golden("mpn_shipped_resnet50_eval")
+    model = build_model(z, cuda_device, math="tf32").eval()
+    import gnncca
+    assert gnncca.MOTMPNet(json.loads(str(z["config"])), None, "resnet50").math == "tf32"      # the default
+    ei = torch.from_numpy(z["edge_index"])
+    data = D(torch.from_numpy(z["x"]).to(cuda_device), ei.to(cuda_device), torch.from_numpy(z["edge_attr"]).to(cuda_device),
+             frame_ptr(ei, z["x"].shape[0]).to(cuda_device))
+    with torch.no_grad():
+        out = model(data)["classified_edges"]
+    for i, o in enumerate(out):
+        ref = torch.from_numpy(z["logits/%d" % i])
+        assert close(o, ref) <= TF32_TOL, (i, close(o, ref))
+        sure = ref.view(-1).abs() > TF32_TOL * (1 + ref.abs().max())
+        assert torch.equal(o.cpu().view(-1)[sure] >= 0, ref.view(-1)[sure] >= 0)

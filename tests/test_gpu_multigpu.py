@@ -19,7 +19,7 @@ def _model(dev, agg="sum"):
     params = importlib.import_module("gnn-cca_b200.config").graph_net_params()
     params["node_agg_fn"] = agg
     torch.manual_seed(0)
-    return gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market").to(dev).eval()
+    return gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market", math="fp32").to(dev).eval()
 
 
 def test_frame_shards_equal_the_single_gpu_result(cuda_device):
