@@ -17,6 +17,20 @@ namespace gnncca {
 namespace fused {
 
 constexpr int FN = 32, FE = 6, HC = 4, EP = 8;   // node width, edge width, classifier hidden, padded edge row
+// Edge latents live in shared memory as PAIRS of edges, component-interleaved: pair p = edges (2p, 2p+1) occupies 12
+// floats [k][2], so one 16-byte load yields two components of both edges in the operand order of the packed FFMA2
+// (fma.rn.f32x2) that evaluates two messages per instruction.
+__device__ __forceinline__ int eidx(int j, int k) { return (j >> 1) * 12 + k * 2 + (j & 1); }
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t ra, rb, rc, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
 constexpr int HS = 36;                            // shared-memory row stride of the node latents: rows of different nodes start in different banks
 constexpr int MAX_FA = 8;                         // widest raw edge attribute row supported
 
@@ -51,8 +65,8 @@ struct Smem {
   int h;       // [cap_n][HS]
   int h0;      // [cap_n][HS] (reattach_nodes)
   int pqr;     // [cap_n][44]  per node: P (6, edge-update source part + bias) | Q (6, target part) | R (32, node-update part + bias)
-  int e;       // [cap_e][EP]
-  int e0;      // [cap_e][EP] (reattach_edges)
+  int e;       // [cap_e / 2][12]  pair-interleaved, see eidx()
+  int e0;      // same layout (reattach_edges)
   int rp;      // int [cap_n + 1]
   int sl, dl;  // uint16 [cap_e] local source / target
 };
@@ -71,8 +85,8 @@ __host__ __device__ inline size_t carve(Smem& s, int K, int EIN, int cap_n, int 
   s.h = p; p += cap_n * HS;
   s.h0 = p; if (rn) p += cap_n * HS;
   s.pqr = p; p += cap_n * 44;
-  s.e = p; p += cap_e * EP;
-  s.e0 = p; if (re) p += cap_e * EP;
+  s.e = p; p += ((cap_e + 1) / 2) * 12;
+  s.e0 = p; if (re) p += ((cap_e + 1) / 2) * 12;
   s.rp = p; p += ((cap_n + 1 + 3) & ~3);
   s.sl = p; p += ((cap_e + 1) / 2 + 3) & ~3;
   s.dl = p; p += ((cap_e + 1) / 2 + 3) & ~3;
@@ -122,9 +136,9 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
     }
   }
   __syncthreads();
-  float wne[FE];
+  float wlo[FE], whi[FE];      // node-update weights of this lane's two features (c, c + 16)
 #pragma unroll
-  for (int k = 0; k < FE; ++k) wne[k] = (smem_f + so.wne)[k * FN + lane];
+  for (int k = 0; k < FE; ++k) { wlo[k] = (smem_f + so.wne)[k * FN + (lane & 15)]; whi[k] = (smem_f + so.wne)[k * FN + (lane & 15) + 16]; }
 
   for (int64_t g = blockIdx.x; g < p.n_graphs; g += gridDim.x) {
     const int64_t a = p.graph_ptr[g], b = p.graph_ptr[g + 1];
@@ -167,11 +181,10 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
         en[o] = fmaxf(acc, 0.f);                     // Linear + ReLU (edge_out_dim != 1), mlp.py:14,18
       }
       en[6] = 0.f; en[7] = 0.f;
-      *reinterpret_cast<float4*>((smem_f + so.e) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-      *reinterpret_cast<float4*>((smem_f + so.e) + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
-      if (REATT_E) {
-        *reinterpret_cast<float4*>((smem_f + so.e0) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-        *reinterpret_cast<float4*>((smem_f + so.e0) + j * EP + 4) = make_float4(en[4], en[5], 0.f, 0.f);
+#pragma unroll
+      for (int o = 0; o < FE; ++o) {
+        (smem_f + so.e)[eidx(j, o)] = en[o];
+        if (REATT_E) (smem_f + so.e0)[eidx(j, o)] = en[o];
       }
       if (p.e_dump) {
 #pragma unroll
@@ -184,28 +197,34 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
 
     for (int step = 1; step <= p.L; ++step) {
       // ---- per-node projections P | Q | R  (Linear over a concatenation = sum of per-block products)
-      for (int item = tid; item < n * 11; item += NT) {
-        const int v = item / 11, q = item - v * 11;
-        float4 acc = *reinterpret_cast<const float4*>((smem_f + so.bproj) + 4 * q);
+      // register tile: 2 nodes x 4 outputs per thread -- every weight quad fetched from shared memory feeds 8 FMAs
+      // (the shared-memory pipe, not the FMA pipe, is what this kernel saturates first)
+      const int npairs = (n + 1) >> 1;
+      for (int item = tid; item < npairs * 11; item += NT) {
+        const int vp = item / 11, q = item - vp * 11;
+        const int v0 = 2 * vp, v1 = min(2 * vp + 1, n - 1);
+        float4 a = *reinterpret_cast<const float4*>((smem_f + so.bproj) + 4 * q), b = a;
         const float* wq = (smem_f + so.wproj) + 4 * q;
-        if (p.reatt_n) {
-          const float* hv0 = (smem_f + so.h0) + v * HS;         // cat(initial, current), mpn.py:285
-#pragma unroll 8
-          for (int k = 0; k < FN; ++k) {
-            const float x = hv0[k];
-            const float4 w = *reinterpret_cast<const float4*>(wq + k * 44);
-            acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y); acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
+        auto block = [&](const float* hbase) {
+          const float4* ha = reinterpret_cast<const float4*>(hbase + v0 * HS);
+          const float4* hb = reinterpret_cast<const float4*>(hbase + v1 * HS);
+#pragma unroll 2
+          for (int k4 = 0; k4 < FN / 4; ++k4) {
+            const float4 xa = ha[k4], xb = hb[k4];
+            const float xs[4] = {xa.x, xa.y, xa.z, xa.w}, ys[4] = {xb.x, xb.y, xb.z, xb.w};
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const float4 w = *reinterpret_cast<const float4*>(wq + (4 * k4 + kk) * 44);
+              a.x = fmaf(xs[kk], w.x, a.x); a.y = fmaf(xs[kk], w.y, a.y); a.z = fmaf(xs[kk], w.z, a.z); a.w = fmaf(xs[kk], w.w, a.w);
+              b.x = fmaf(ys[kk], w.x, b.x); b.y = fmaf(ys[kk], w.y, b.y); b.z = fmaf(ys[kk], w.z, b.z); b.w = fmaf(ys[kk], w.w, b.w);
+            }
           }
           wq += FN * 44;
-        }
-        const float* hv = (smem_f + so.h) + v * HS;
-#pragma unroll 8
-        for (int k = 0; k < FN; ++k) {
-          const float x = hv[k];
-          const float4 w = *reinterpret_cast<const float4*>(wq + k * 44);
-          acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y); acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
-        }
-        *reinterpret_cast<float4*>((smem_f + so.pqr) + v * 44 + 4 * q) = acc;
+        };
+        if (p.reatt_n) block(smem_f + so.h0);          // cat(initial, current), mpn.py:285
+        block(smem_f + so.h);
+        *reinterpret_cast<float4*>((smem_f + so.pqr) + v0 * 44 + 4 * q) = a;
+        if (2 * vp + 1 < n) *reinterpret_cast<float4*>((smem_f + so.pqr) + v1 * 44 + 4 * q) = b;
       }
       __syncthreads();
       // ---- phase A: thread per edge -- edge update (+ classifier)
@@ -220,13 +239,13 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
         const float pq[FE] = {p0.x + q0.x, p0.y + q0.y, p0.z + q1.x, p0.w + q1.y, p1.x + q2.x, p1.y + q2.y};
         float ein[EIN];
         if (REATT_E) {   // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
-          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e0) + j * EP), u1 = *reinterpret_cast<const float4*>((smem_f + so.e0) + j * EP + 4);
-          ein[0] = u0.x; ein[1] = u0.y; ein[2] = u0.z; ein[3] = u0.w; ein[4] = u1.x; ein[5] = u1.y;
+#pragma unroll
+          for (int k = 0; k < FE; ++k) ein[k] = (smem_f + so.e0)[eidx(j, k)];
         }
         constexpr int OFF = REATT_E ? FE : 0;
         {
-          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP), u1 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP + 4);
-          ein[OFF] = u0.x; ein[OFF + 1] = u0.y; ein[OFF + 2] = u0.z; ein[OFF + 3] = u0.w; ein[OFF + 4] = u1.x; ein[OFF + 5] = u1.y;
+#pragma unroll
+          for (int k = 0; k < FE; ++k) ein[OFF + k] = (smem_f + so.e)[eidx(j, k)];
         }
         float en[FE];
 #pragma unroll
@@ -236,8 +255,8 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
           for (int k = 0; k < EIN; ++k) acc = fmaf(ein[k], (smem_f + so.wee)[o * EIN + k], acc);
           en[o] = fmaxf(acc, 0.f);
         }
-        *reinterpret_cast<float4*>((smem_f + so.e) + j * EP) = make_float4(en[0], en[1], en[2], en[3]);
-        *reinterpret_cast<float2*>((smem_f + so.e) + j * EP + 4) = make_float2(en[4], en[5]);
+#pragma unroll
+        for (int o = 0; o < FE; ++o) (smem_f + so.e)[eidx(j, o)] = en[o];
         if (p.e_dump) {
 #pragma unroll
           for (int o = 0; o < FE; ++o) p.e_dump[((int64_t)step * p.n_edges + eb + j) * FE + o] = en[o];
@@ -256,38 +275,53 @@ __global__ void __launch_bounds__(256) mp_fused_fwd_kernel(const Params p) {
       }
       if (step == p.L && !p.h_dump) break;           // the last node update is dead (mpn.py:288-299)
       __syncthreads();
-      // ---- phase B: a warp owns a node's whole out-edge segment, lane = feature; fixed summation order
-      for (int v = warp; v < n; v += nwarps) {
-        const float r = (smem_f + so.pqr)[v * 44 + 2 * FE + lane];
-        const int j0 = (smem_i + so.rp)[v], j1 = (smem_i + so.rp)[v + 1];
-        float acc = agg_init(AGG);
-        int j = j0;
-        for (; j + 4 <= j1; j += 4) {      // four independent message evaluations in flight, folded in edge order
-          float m[4];
+      // ---- phase B: a HALF-warp owns a node's whole out-edge segment, lane = two features (c, c + 16); fixed
+      //      summation order.  Two nodes per warp: one shared-memory wavefront serves an edge pair of each node.
+      {
+        const int half = lane >> 4, c0 = lane & 15;
+        const float* eb_ = smem_f + so.e;
+        for (int vb = 2 * warp; vb < n; vb += 2 * nwarps) {
+          const int v = vb + half;
+          const bool live = v < n;
+          const int j0 = live ? (smem_i + so.rp)[v] : 0, j1 = live ? (smem_i + so.rp)[v + 1] : 0;
+          const float r0 = live ? (smem_f + so.pqr)[v * 44 + 2 * FE + c0] : 0.f, r1 = live ? (smem_f + so.pqr)[v * 44 + 2 * FE + c0 + 16] : 0.f;
+          float acc0 = agg_init(AGG), acc1 = agg_init(AGG);
+          auto single = [&](int j) {          // one edge, scalar FFMA (odd segment ends)
+            float t0 = r0, t1 = r1;
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + (j + u) * EP);
-            const float2 u1 = *reinterpret_cast<const float2*>((smem_f + so.e) + (j + u) * EP + 4);
-            float t = r;
-            t = fmaf(u0.x, wne[0], t); t = fmaf(u0.y, wne[1], t); t = fmaf(u0.z, wne[2], t);
-            t = fmaf(u0.w, wne[3], t); t = fmaf(u1.x, wne[4], t); t = fmaf(u1.y, wne[5], t);
-            m[u] = fmaxf(t, 0.f);
+            for (int k = 0; k < FE; ++k) { const float x = eb_[eidx(j, k)]; t0 = fmaf(x, wlo[k], t0); t1 = fmaf(x, whi[k], t1); }
+            acc0 = agg_comb(AGG, acc0, fmaxf(t0, 0.f)); acc1 = agg_comb(AGG, acc1, fmaxf(t1, 0.f));
+          };
+          int j = j0;
+          if (j < j1 && (j & 1)) { single(j); ++j; }
+          const float2 rr0 = make_float2(r0, r0), rr1 = make_float2(r1, r1);
+          for (; j + 2 <= j1; j += 2) {        // an edge pair per iteration, messages folded in edge order
+            const float4* pa = reinterpret_cast<const float4*>(eb_ + (j >> 1) * 12);
+            const float4 a0 = pa[0], a1 = pa[1], a2 = pa[2];
+            const float2 x0 = make_float2(a0.x, a0.y), x1 = make_float2(a0.z, a0.w), x2 = make_float2(a1.x, a1.y),
+                         x3 = make_float2(a1.z, a1.w), x4 = make_float2(a2.x, a2.y), x5 = make_float2(a2.z, a2.w);
+            float2 m0 = rr0, m1 = rr1;
+            m0 = ffma2(x0, make_float2(wlo[0], wlo[0]), m0); m1 = ffma2(x0, make_float2(whi[0], whi[0]), m1);
+            m0 = ffma2(x1, make_float2(wlo[1], wlo[1]), m0); m1 = ffma2(x1, make_float2(whi[1], whi[1]), m1);
+            m0 = ffma2(x2, make_float2(wlo[2], wlo[2]), m0); m1 = ffma2(x2, make_float2(whi[2], whi[2]), m1);
+            m0 = ffma2(x3, make_float2(wlo[3], wlo[3]), m0); m1 = ffma2(x3, make_float2(whi[3], whi[3]), m1);
+            m0 = ffma2(x4, make_float2(wlo[4], wlo[4]), m0); m1 = ffma2(x4, make_float2(whi[4], whi[4]), m1);
+            m0 = ffma2(x5, make_float2(wlo[5], wlo[5]), m0); m1 = ffma2(x5, make_float2(whi[5], whi[5]), m1);
+            acc0 = agg_comb(AGG, acc0, fmaxf(m0.x, 0.f)); acc0 = agg_comb(AGG, acc0, fmaxf(m0.y, 0.f));
+            acc1 = agg_comb(AGG, acc1, fmaxf(m1.x, 0.f)); acc1 = agg_comb(AGG, acc1, fmaxf(m1.y, 0.f));
           }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) acc = agg_comb(AGG, acc, m[u]);
+          if (j < j1) single(j);
+          if (j1 == j0) { acc0 = 0.f; acc1 = 0.f; }                        // no out-edge: torch_scatter leaves 0
+          else if (AGG == GNNCCA_AGG_MEAN) { const float inv = 1.f / (float)(j1 - j0); acc0 = acc0 * inv; acc1 = acc1 * inv; }
+          if (live) {
+            (smem_f + so.h)[v * HS + c0] = acc0;
+            (smem_f + so.h)[v * HS + c0 + 16] = acc1;
+            if (p.h_dump) {
+              p.h_dump[((int64_t)step * p.n_nodes + a + v) * FN + c0] = acc0;
+              p.h_dump[((int64_t)step * p.n_nodes + a + v) * FN + c0 + 16] = acc1;
+            }
+          }
         }
-        for (; j < j1; ++j) {
-          const float4 u0 = *reinterpret_cast<const float4*>((smem_f + so.e) + j * EP);
-          const float2 u1 = *reinterpret_cast<const float2*>((smem_f + so.e) + j * EP + 4);
-          float t = r;
-          t = fmaf(u0.x, wne[0], t); t = fmaf(u0.y, wne[1], t); t = fmaf(u0.z, wne[2], t);
-          t = fmaf(u0.w, wne[3], t); t = fmaf(u1.x, wne[4], t); t = fmaf(u1.y, wne[5], t);
-          acc = agg_comb(AGG, acc, fmaxf(t, 0.f));
-        }
-        if (j1 == j0) acc = 0.f;                                        // no out-edge: torch_scatter leaves 0
-        else if (AGG == GNNCCA_AGG_MEAN) acc = acc / (float)(j1 - j0);
-        (smem_f + so.h)[v * HS + lane] = acc;
-        if (p.h_dump) p.h_dump[((int64_t)step * p.n_nodes + a + v) * FN + lane] = acc;
       }
       __syncthreads();
     }
