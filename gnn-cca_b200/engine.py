@@ -8,7 +8,7 @@ from typing import List, Optional
 import torch
 
 from . import _lib
-from .plan import GraphPlan, _stream
+from .plan import GraphPlan, TrustedPlan, _stream
 
 MATH_MODES = {"fp32": _lib.MATH_FP32, "tf32": _lib.MATH_TF32}
 
@@ -183,7 +183,8 @@ def measure_frames(graph_ptr: torch.Tensor, rowptr: torch.Tensor):
 def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
                       plan: Optional[GraphPlan] = None, return_latents: bool = False, prof: Optional[StageTimer] = None,
                       h_encoded: Optional[torch.Tensor] = None, graph_ptr: Optional[torch.Tensor] = None, caps=None,
-                      allow_fused: bool = True, return_plan: bool = False, trusted: bool = False):
+                      allow_fused: bool = True, return_plan: bool = False, trusted: bool = False,
+                      edge_ptr: Optional[torch.Tensor] = None):
     """``MOTMPNet.forward`` (models/mpn.py:250-299), no autograd graph.  Returns the list of per-step logits
     [E,1] in the caller's edge order.
 
@@ -194,7 +195,9 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     so the device never waits for the host; a batch that fails a check is then re-run on the safe path.
     ``h_encoded``: node latents already produced by the node encoder (used by ``forward_host``).
     ``trusted``: the batch comes from ``build_graph_batch`` (source-major, in range, frames closed, exact ``caps``
-    by construction) or was verified by an earlier forward: nothing is read back and the call never synchronises."""
+    by construction) or was verified by an earlier forward: nothing is read back and the call never synchronises.
+    ``edge_ptr`` (trusted batches only): int64 [B+1] edge offsets of the frames; with it the fused kernel reads the
+    caller's int64 ``edge_index`` directly (RAW form) and no CSR is built at all."""
     lib = _lib.load()
     _require_cuda(edge_attr, "data.edge_attr")
     check_supported(model)
@@ -204,7 +207,15 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         raise ValueError("edge_attr has %d rows but edge_index has %d edges" % (edge_attr.size(0), E))
     if prof is not None:
         prof.mark("begin")
-    if plan is None:
+    L, k = model.num_enc_steps, model.num_class_steps
+    first_class_step = L - k + 1                                            # mpn.py:277
+    B = int(graph_ptr.numel()) - 1 if graph_ptr is not None else 0
+    fused_ok = allow_fused and graph_ptr is not None and L >= 1 and E > 0 and edge_attr.size(1) <= 8 and first_class_step >= 1
+    cap = frame_capacity(model, N, E, B, caps) if fused_ok else None
+    raw = plan is None and trusted and cap is not None and edge_ptr is not None and not return_latents
+    if raw:
+        plan = TrustedPlan(edge_index, N, edge_ptr)
+    elif plan is None:
         plan = GraphPlan(edge_index, N)          # async: narrow + order check + rowptr
     optimistic = not plan.resolved and not trusted
     if prof is not None:
@@ -219,14 +230,8 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     if prof is not None:
         prof.mark("encoder_node")
     sb = StepBinding(model, math)
-    L, k = model.num_enc_steps, model.num_class_steps
-    first_class_step = L - k + 1                                            # mpn.py:277
     ea_sorted = plan.to_sorted(edge_attr.contiguous())
 
-    cap = None
-    B = int(graph_ptr.numel()) - 1 if graph_ptr is not None else 0
-    if allow_fused and graph_ptr is not None and L >= 1 and E > 0 and ea_sorted.size(1) <= 8 and first_class_step >= 1:
-        cap = frame_capacity(model, N, E, B, caps)
     if cap is not None:
         gp = graph_ptr.to(device=dev, dtype=torch.int64).contiguous()
         n_cls = max(0, L - first_class_step + 1)
@@ -237,7 +242,8 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         if len(enc_e.layer_specs) != 1 or not enc_e.layer_specs[0].relu or enc_e.layer_specs[0].bn is not None:
             raise NotImplementedError("fused pipeline: the edge encoder must be a single Linear+ReLU (edge_fc_dims=[])")
         _lib.check(lib.gnncca_mp_fused_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(enc_e.linear(0).weight), _lib.ptr(enc_e.linear(0).bias),
-                                           int(ea_sorted.size(1)), _lib.ptr(gp), B, _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
+                                           int(ea_sorted.size(1)), _lib.ptr(gp), B, _lib.ptr(plan.raw_edge_index), _lib.ptr(plan.edge_ptr),
+                                           _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
                                            _lib.ptr(plan.dst), N, E, _lib.ptr(h), _lib.ptr(ea_sorted), L, first_class_step, cap[0], cap[1],
                                            _lib.ptr(logits), _lib.ptr(h_dump), _lib.ptr(e_dump), _lib.ptr(plan.flags), _stream()),
                    "mp_fused_fwd")

@@ -156,8 +156,9 @@ class MOTMPNet(nn.Module):
         if needs_grad or (self.training and self._has_batchnorm()):
             outs = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan)
         else:
+            edge_ptr = getattr(data, "edge_ptr", None) if getattr(data, "gnncca_trusted", False) else None
             outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps,
-                                                  return_plan=True, trusted=trusted, allow_fused=allow_fused)
+                                                  return_plan=True, trusted=trusted, allow_fused=allow_fused, edge_ptr=edge_ptr)
             self.last_plan = plan       # introspection only (which device pipeline ran, the CSR)
             if engine.CACHE_PLANS and not getattr(data, "gnncca_trusted", False):
                 try:                    # a verified CSR is reused by later forwards on the same, unmodified Batch

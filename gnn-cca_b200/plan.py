@@ -32,6 +32,8 @@ class GraphPlan:
         self.rowptr = torch.empty(self.N + 1, dtype=torch.int32, device=dev)
         self.flags = torch.empty(_lib.CSR_NFLAGS, dtype=torch.int32, device=dev)
         self.perm: Optional[torch.Tensor] = None
+        self.raw_edge_index = None      # CSR form of gnncca_mp_fused_fwd
+        self.edge_ptr = None
         self._flags_host = None     # pinned read-back buffer + event, created on first use only
         self._event = None
         self._resolved = False
@@ -110,3 +112,40 @@ class GraphPlan:
         _lib.check(self.lib.gnncca_permute_rows(_lib.ptr(rows), _lib.ptr(out), _lib.ptr(self.perm), rows.size(0),
                                                 rows.size(1), 1, _stream()), "permute_rows")
         return out
+
+
+_TRUSTED_FLAGS = {}
+
+
+class TrustedPlan:
+    """Stand-in for ``GraphPlan`` when the batch was built by ``build_graph_batch`` (source-major, frames closed,
+    per-frame edge offsets known): the fused kernel reads the caller's int64 ``edge_index`` itself (RAW form of
+    gnncca_mp_fused_fwd), no CSR arrays exist and nothing is read back."""
+
+    resolved = True
+    perm = None
+    rowptr = src = dst = None
+
+    def __init__(self, edge_index: torch.Tensor, num_nodes: int, edge_ptr: torch.Tensor):
+        if edge_index.dim() != 2 or edge_index.size(0) != 2 or edge_index.dtype != torch.int64 or not edge_index.is_cuda:
+            raise ValueError("edge_index must be a CUDA int64 tensor of shape [2, E]")
+        dev = edge_index.device
+        self.edge_index = self.raw_edge_index = edge_index.contiguous()
+        self.edge_ptr = edge_ptr.to(device=dev, dtype=torch.int64).contiguous()
+        self.N, self.E = int(num_nodes), int(edge_index.size(1))
+        key = (dev.type, dev.index)
+        if key not in _TRUSTED_FLAGS:          # write-only scratch for the kernel's overflow flag (never read back)
+            _TRUSTED_FLAGS[key] = torch.zeros(_lib.CSR_NFLAGS, dtype=torch.int32, device=dev)
+        self.flags = _TRUSTED_FLAGS[key]
+        self._resolved = True
+        self.last_path = None
+
+    def key(self):
+        t = self.edge_index
+        return (t.data_ptr(), tuple(t.shape), t._version, self.N)
+
+    def to_sorted(self, rows: torch.Tensor) -> torch.Tensor:
+        return rows
+
+    def to_caller(self, rows: torch.Tensor) -> torch.Tensor:
+        return rows

@@ -158,18 +158,26 @@ int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
 
 /* ALL message-passing steps for a batch of SMALL frame graphs in one launch (MOTMPNet.forward, mpn.py:270-299,
  * after the node encoder): edge encoder (Linear(edge_in_dim, f_edge)+ReLU), num_steps x (edge update, node
- * update), classifier at steps >= first_class_step.  One CTA holds one frame's latents in shared memory
- * across the steps; HBM sees only h_enc, edge_attr, the CSR and the logits.
+ * update), classifier at steps >= first_class_step.  One persistent CTA per SM runs up to 8 warp groups; a
+ * group holds one frame's latents in shared memory across the steps; HBM sees only h_enc, edge_attr, the edge
+ * list and the logits.
  *   graph_ptr[n_graphs+1] int64: node offsets of the frames (PyG Batch.ptr); every edge of a frame must
- *   stay inside it.  rowptr/src/dst: source-sorted CSR (gnncca_csr_from_edge_index), edge_attr in that order.
- *   cap_nodes / cap_edges: capacity class the launch is sized for (shared memory per CTA).
+ *   stay inside it.
+ *   Edge list, one of two forms:
+ *     RAW  edge_index != NULL: the caller's [2][E] int64 (train.py:292-299 order) and edge_ptr[n_graphs+1]
+ *          int64, the edge offsets of the frames; source order, range and closedness are verified on the fly;
+ *          rowptr/src/dst may be NULL; edge_attr in the caller's order.
+ *     CSR  edge_index == NULL: rowptr/src/dst of gnncca_csr_from_edge_index, edge_attr in that order.
+ *   cap_nodes / cap_edges: capacity class the launch is sized for (shared memory per group).
  *   logits [(num_steps - first_class_step + 1)][E]; h_dump [num_steps+1][N][f_node] and e_dump
  *   [num_steps+1][E][f_edge] optional per-step latents (index 0 = encoder outputs).
- *   flags: the int32[4] of gnncca_csr_from_edge_index.  flags[0]|flags[1] set -> the launch is a no-op;
- *   flags[2] is SET by this kernel when a frame exceeds the capacity class or has an edge leaving it: the
- *   outputs are then incomplete and the caller must use the per-step entry points instead. */
+ *   flags int32[4]: CSR form: the flags of gnncca_csr_from_edge_index, flags[0]|flags[1] set -> the launch is a
+ *   no-op.  Both forms: flags[2] is SET by this kernel when a frame exceeds the capacity class, has an edge
+ *   leaving it or (RAW) is not source-major: the outputs are then incomplete and the caller must use the
+ *   CSR form / the per-step entry points instead. */
 int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* w_enc_edge,
                         const float* b_enc_edge, int32_t edge_in_dim, const int64_t* graph_ptr, int64_t n_graphs,
+                        const int64_t* edge_index, const int64_t* edge_ptr,
                         const int32_t* rowptr, const int32_t* src, const int32_t* dst, int64_t n_nodes,
                         int64_t n_edges, const float* h_enc, const float* edge_attr, int32_t num_steps,
                         int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges, float* logits,

@@ -241,3 +241,78 @@ def test_default_tf32_pipeline_matches_reference_vectors_within_tf32_tolerance(c
         assert close(o, ref) <= TF32_TOL, (i, close(o, ref))
         sure = ref.view(-1).abs() > TF32_TOL * (1 + ref.abs().max())
         assert torch.equal(o.cpu().view(-1)[sure] >= 0, ref.view(-1)[sure] >= 0)
+
+
+def _trusted_batch(cuda_device, cams=4, dets=6, frames=37, seed=11):
+    import gnncca
+    from importlib import import_module
+    syn = import_module("gnn-cca_b200.synthetic")
+    det = syn.make_detections(cams, dets, frames, seed=seed, device=cuda_device)
+    return gnncca.build_graph_batch(**det)
+
+
+@pytest.mark.parametrize("agg", ["sum", "max"])
+def test_raw_edge_index_form_equals_csr_form_bit_for_bit(agg, cuda_device):
+    """Batches built by build_graph_batch carry edge_ptr: the fused kernel then reads the int64 edge_index itself
+    (no CSR kernel).  Same logits, bit for bit, as the CSR form on the same batch, and both match the oracle."""
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    params["node_agg_fn"] = agg
+    torch.manual_seed(4)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50", math="fp32").to(cuda_device).eval()
+    b = _trusted_batch(cuda_device)
+    with torch.no_grad():
+        raw = model(b)["classified_edges"]
+        assert type(model.last_plan).__name__ == "TrustedPlan" and model.last_plan.last_path == "fused"
+        csr = model(D(b.x, b.edge_index, b.edge_attr, b.ptr))["classified_edges"]
+        assert type(model.last_plan).__name__ == "GraphPlan" and model.last_plan.last_path == "fused"
+    for a, c in zip(raw, csr):
+        assert torch.equal(a, c)
+    spec = mpn_oracle.MPNSpec(params, "resnet50")
+    sd = {k: v.cpu() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        ref = mpn_oracle.motmpnet_forward(spec, sd, b.x.cpu(), b.edge_index.cpu(), b.edge_attr.cpu())["classified_edges"]
+    for o, r in zip(raw, ref):
+        assert close(o, r) <= FP32_RTOL
+
+
+@pytest.mark.parametrize("violation", ["none", "unsorted", "leaves_frame", "bad_edge_ptr", "too_large"])
+def test_raw_form_verifies_the_frames_on_the_device(violation, cuda_device):
+    """C-ABI level: the RAW form raises flags[2] for edges that are not source-major, leave their frame, for
+    inconsistent edge offsets and for frames above the capacity class; a clean batch leaves it 0."""
+    import ctypes as C
+    import gnncca
+    from importlib import import_module
+    _lib = import_module("gnn-cca_b200._lib")
+    engine = import_module("gnn-cca_b200.engine")
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(4)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50", math="fp32").to(cuda_device).eval()
+    b = _trusted_batch(cuda_device, frames=9)
+    ei, ep, caps = b.edge_index.clone(), b.edge_ptr.clone(), list(b.gnncca_caps)
+    if violation == "unsorted":
+        ei[:, [5, 40]] = ei[:, [40, 5]]
+    elif violation == "leaves_frame":
+        ei[1, 3] = int(b.ptr[3])
+    elif violation == "bad_edge_ptr":
+        ep[4] = ep[5] + 1
+    elif violation == "too_large":
+        caps[1] -= 32
+    lib = _lib.load()
+    sb = engine.StepBinding(model, _lib.MATH_FP32)
+    N, E, B = b.num_nodes, b.num_edges, b.num_graphs
+    h = torch.rand(N, 32, device=cuda_device)
+    logits = torch.zeros(3, E, device=cuda_device)
+    flags = torch.zeros(4, dtype=torch.int32, device=cuda_device)
+    enc_e = model.encoder.edge_mlp
+    cap_n, cap_e = (caps[0] + 7) & ~7, (caps[1] + 31) & ~31
+    if violation == "too_large":
+        cap_e = caps[1] & ~31
+    rc = lib.gnncca_mp_fused_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(enc_e.linear(0).weight), _lib.ptr(enc_e.linear(0).bias), 4,
+                                 _lib.ptr(b.ptr), B, _lib.ptr(ei), _lib.ptr(ep), None, None, None, N, E, _lib.ptr(h), _lib.ptr(b.edge_attr),
+                                 4, 2, cap_n, cap_e, _lib.ptr(logits), None, None, _lib.ptr(flags), 0)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert int(flags[2]) == (0 if violation == "none" else 1)
+    assert bool(torch.isfinite(logits).all())
