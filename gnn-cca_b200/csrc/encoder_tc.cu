@@ -8,9 +8,10 @@
 //   warp 1      MMA issuer   : tcgen05.mma kind::tf32, M=128, N=H, K=8 per instruction, accumulators in TMEM
 //                              (double buffered: 2 x H columns) -- fp32 bits are consumed as TF32 in place, so
 //                              x is never converted or re-written
-//   warps 2..5  epilogue     : tcgen05.ld the accumulator row of "their" node, + b1, ReLU, then the 128 -> 32
-//                              layer in exact FP32 FFMA against W2 held in shared memory, + b2, ReLU, one 128 B
-//                              store per node.  The hidden activations never touch HBM.
+//   warps 2..9  epilogue     : tcgen05.ld the accumulator row of "their" node (warps 2-5 sub-tile 0, 6-9 sub-tile 1),
+//                              + b1, ReLU, then the 128 -> 32 layer in exact FP32 (packed FFMA2) against W2 held in
+//                              shared memory, + b2, ReLU, one 128 B store per node.  The hidden activations never
+//                              touch HBM.
 // Roofline: HBM.  Algorithmic bytes per launch = N * (4 K + 128) + weights.
 #include <cuda.h>
 #include "common.cuh"
@@ -22,7 +23,7 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 32;            // floats per k-block = 128 bytes = one swizzle row
 constexpr int UMMA_K = 8;              // tf32: 32 bytes per instruction along K
 constexpr int F_OUT = 32;              // node latent width
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;
 constexpr int MAX_STAGES = 8;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -51,6 +52,16 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t ra, rb, rc, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -81,6 +92,36 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// the same 32 columns written back from registers
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+        "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+        "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+        "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+        "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+        "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+        "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+        "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+// D[tmem] (+)= A[tmem: lane = row, one 32-bit column per k] * B[smem descriptor]
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ float tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart (cute::UMMA::SmemDescriptor)
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
   uint64_t d = 0;
@@ -102,9 +143,22 @@ struct Params {
   int64_t rows;
   int K, H, stages;
   int rows_per_cta;          // multiple of 8: CTA c owns rows [c * rows_per_cta, (c+1) * rows_per_cta)
+  uint32_t a_bytes;          // bytes of a stage given to the x rows: min(rows_per_cta, 256) rows, 1024-aligned
+  unsigned long long* trace; // development aid (tools/micro/enc_trace.cu): [grid][8] globaltimer stamps, normally NULL
+
 };
 
-struct XMaps { CUtensorMap m[5]; };   // x viewed with boxes of 8, 16, 32, 64, 128 rows x 32 floats
+#ifdef GNNCCA_ENC_TRACE
+__device__ __forceinline__ void stamp(const Params& p, int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  if (p.trace) p.trace[(size_t)blockIdx.x * 12 + slot] = t;
+}
+#else
+__device__ __forceinline__ void stamp(const Params&, int) {}
+#endif
+
+struct XMaps { CUtensorMap m[6]; int tail_rows; };   // x viewed with boxes of 8, 16, 32, 64, 128 and tail_rows rows x 32 floats
 
 // Work decomposition.  A CTA owns ONE contiguous row range sized so that all SMs finish together (rows / grid, a
 // multiple of 8) and walks it in "super tiles" of up to 256 rows = two M=128 MMA tiles that SHARE every W1 stage:
@@ -116,157 +170,196 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_constant__ CUtensorMap tmap_w, const Params p) {
   constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;       // 16 KB per sub-tile
   constexpr uint32_t B_BYTES = H * BLOCK_K * 4;
-  constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + B_BYTES;
-  constexpr int NBUF = (4 * H <= 512) ? 2 : 1;              // accumulator double buffering when TMEM allows
-  constexpr uint32_t TMEM_NEED = 2 * H * NBUF;
-  constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+  // TMEM columns: [0, 2H) the two layer-1 accumulators (overwritten in place by ReLU(acc + b1) as the A operand of
+  // layer 2), [2H, 2H + 64) the two layer-2 accumulators
+  constexpr uint32_t TMEM_NEED = 2 * H + 2 * F_OUT;
+  constexpr uint32_t TMEM_COLS = TMEM_NEED <= 256 ? 256 : 512;
+  static_assert(TMEM_NEED <= 512, "hidden width too large for one CTA's tensor memory");
   constexpr uint32_t IDESC = make_idesc(BLOCK_M, H);
+  constexpr uint32_t IDESC2 = make_idesc(BLOCK_M, F_OUT);
   constexpr uint64_t HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull;
+  const uint32_t STAGE_BYTES = p.a_bytes + B_BYTES;       // sized to the rows this launch gives a CTA: more stages in flight
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // 128B swizzle atoms need 1024 B alignment
   const int NS = p.stages;
   uint8_t* tiles = smem;
-  float* w2t = (float*)(tiles + (size_t)NS * STAGE_BYTES);     // [H][32]: W2 transposed, row j = the 32 output weights of hidden j
-  float* b1s = w2t + H * F_OUT;
+  float* w2s = (float*)(tiles + (size_t)NS * STAGE_BYTES);     // W2 [32][H] as a K-major 128B-swizzled B operand (tf32, rna)
+  float* b1s = w2s + H * F_OUT;
   float* b2s = b1s + H;
   uint64_t* full = (uint64_t*)(b2s + F_OUT);
   uint64_t* empty = full + MAX_STAGES;
   uint64_t* tmem_full = empty + MAX_STAGES;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint64_t* d2_full = tmem_empty + 1;               // [2]: layer-2 accumulator of sub-tile t is complete
+  uint32_t* tmem_slot = (uint32_t*)(d2_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) stamp(p, 0);
   const int64_t row_begin = (int64_t)blockIdx.x * p.rows_per_cta;
   const int64_t row_end = min(row_begin + p.rows_per_cta, p.rows);
   const int my_rows = (int)(row_end - row_begin);
   const int n_super = (my_rows + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+  const int KB = p.K / BLOCK_K;
 
-  if (warp == 0 && lane == 0) {
+  // producer state (warp 0, lane 0): the first ring of stages is issued BEFORE the set-up barrier, so x is already
+  // streaming while the other warps allocate tensor memory and stage the small second layer
+  int pr_s = 0, pr_st = 0, pr_kb = 0; uint32_t pr_ph = 0;
+  auto produce = [&](int count) {
+    for (; count > 0 && pr_st < n_super; --count) {
+      const int64_t r0 = row_begin + (int64_t)pr_st * 2 * BLOCK_M;
+      const int rem = my_rows - pr_st * 2 * BLOCK_M;
+      const int rows8 = (min(rem, 2 * BLOCK_M) + 7) & ~7;          // rows of x this super tile loads (8-row boxes)
+      mbar_wait(empty + pr_s, pr_ph ^ 1);
+      uint8_t* a = tiles + (size_t)pr_s * STAGE_BYTES;
+      mbar_expect_tx(full + pr_s, (uint32_t)rows8 * (BLOCK_K * 4) + B_BYTES);
+      tma_load_2d(a + p.a_bytes, &tmap_w, full + pr_s, pr_kb * BLOCK_K, 0, HINT_EVICT_LAST);
+      // sub-tile 0 at byte 0, sub-tile 1 at row 128 = byte offset A_BYTES; one box each when the row count is 128
+      // or the launch's tail size (every CTA but the last), 8-row granular greedy boxes otherwise
+#pragma unroll 1
+      for (int sub = 0; sub < 2; ++sub) {
+        int need = min(rows8 - sub * BLOCK_M, BLOCK_M), off = sub * BLOCK_M;
+        if (need <= 0) break;
+        if (need == BLOCK_M) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[4], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
+        if (need == xmaps.tail_rows) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[5], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
 #pragma unroll
-    for (int i = 0; i < 5; ++i) asm volatile("prefetch.tensormap [%0];" ::"l"(&xmaps.m[i]) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
+        for (int b = 3; b >= 0; --b) {
+          const int sz = 8 << b;
+          if (need >= sz) {
+            tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[b], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST);
+            off += sz; need -= sz;
+          }
+        }
+      }
+      if (++pr_s == NS) { pr_s = 0; pr_ph ^= 1; }
+      if (++pr_kb == KB) { pr_kb = 0; ++pr_st; }
+    }
+  };
+
+  if (warp == 0 && lane < 7) {       // seven descriptors fetched in parallel
+    const CUtensorMap* m = lane < 6 ? &xmaps.m[lane] : &tmap_w;
+    asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
+  }
+  if (warp == 0 && lane == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, 4); }
+    mbar_init(tmem_full, 1); mbar_init(tmem_empty, 8);
+    mbar_init(d2_full, 1); mbar_init(d2_full + 1, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    stamp(p, 9);
+    produce(NS);
+    stamp(p, 10);
   }
   if (warp == 1) {   // TMEM accumulators (this warp also frees them)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (lane == 0) stamp(p, 7);
   }
-  if (warp >= 2) {   // epilogue warps stage the small second layer
+  if (warp >= 2) {   // epilogue warps stage the small second layer: coalesced reads of W2 [32][H], swizzled writes
     const int t = threadIdx.x - 64;
-    for (int idx = t; idx < H * F_OUT; idx += 128) { const int j = idx / F_OUT, o = idx % F_OUT; w2t[idx] = p.W2[o * H + j]; }
-    for (int idx = t; idx < H; idx += 128) b1s[idx] = p.b1[idx];
+    constexpr int PER = H * F_OUT / 256;             // all loads in flight first (one DRAM round trip), then the stores
+    float wv[PER];
+#pragma unroll
+    for (int i = 0; i < PER; ++i) wv[i] = __ldg(p.W2 + t + i * 256);
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int idx = t + i * 256;
+      const int n = idx / H, k = idx - n * H;
+      const int kb = k >> 5, kk = k & 31;
+      const int off = kb * (F_OUT * 32) + (n >> 3) * 256 + (n & 7) * 32 + (((kk >> 2) ^ (n & 7)) << 2) + (kk & 3);   // floats
+      w2s[off] = tf32_rna(wv[i]);
+    }
+    for (int idx = t; idx < H; idx += 256) b1s[idx] = p.b1[idx];
     if (t < F_OUT) b2s[t] = p.b2[t];
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes of w2s -> tensor-core reads
+    if (threadIdx.x == 64) stamp(p, 8);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int KB = p.K / BLOCK_K;
+  if (threadIdx.x == 0) stamp(p, 1);
 
   if (warp == 0) {
-    if (lane == 0) {   // ------------------------------------------------ TMA producer
-      int s = 0; uint32_t ph = 0;
-      for (int st = 0; st < n_super; ++st) {
-        const int64_t r0 = row_begin + (int64_t)st * 2 * BLOCK_M;
-        const int rem = my_rows - st * 2 * BLOCK_M;
-        const int rows8 = (min(rem, 2 * BLOCK_M) + 7) & ~7;          // rows of x this super tile loads (8-row boxes)
-        for (int kb = 0; kb < KB; ++kb) {
-          mbar_wait(empty + s, ph ^ 1);
-          uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
-          mbar_expect_tx(full + s, (uint32_t)rows8 * (BLOCK_K * 4) + B_BYTES);
-          tma_load_2d(a + 2 * A_BYTES, &tmap_w, full + s, kb * BLOCK_K, 0, HINT_EVICT_LAST);
-          int off = 0;                                               // sub-tile 1 continues at row 128 = byte offset A_BYTES
-#pragma unroll
-          for (int b = 4; b >= 0; --b) {
-            const int sz = 8 << b;
-            while (rows8 - off >= sz && (off % BLOCK_M) + sz <= BLOCK_M) {
-              tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[b], full + s, kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST);
-              off += sz;
-            }
-          }
-          if (++s == NS) { s = 0; ph ^= 1; }
-        }
-      }
-    }
+    if (lane == 0) produce(INT32_MAX);   // ---------------------------------- TMA producer: the rest of the stream
   } else if (warp == 1) {
-    if (lane == 0) {   // ------------------------------------------------ MMA issuer
+    if (lane == 0) {   // ------------------------------------------------ MMA issuer (layer 1)
       int s = 0; uint32_t ph = 0;
       for (int st = 0; st < n_super; ++st) {
-        const int as = NBUF == 2 ? (st & 1) : 0;
-        const uint32_t aph = NBUF == 2 ? ((st >> 1) & 1) : (st & 1);
         const int rem = my_rows - st * 2 * BLOCK_M;
         const int nt = rem > BLOCK_M ? 2 : 1;
-        mbar_wait(tmem_empty + as, aph ^ 1);     // epilogue has drained this accumulator pair
+        mbar_wait(tmem_empty, (uint32_t)(st & 1) ^ 1);     // epilogue has drained the accumulators
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(as * 2 * H);
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(full + s, ph);
+          if (st == 0 && kb == 0) stamp(p, 2);
+          if (st == n_super - 1 && kb == KB - 1) stamp(p, 3);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
-          const uint64_t bdesc = make_smem_desc(a_addr + 2 * A_BYTES);
+          const uint64_t bdesc = make_smem_desc(a_addr + p.a_bytes);
           for (int t = 0; t < nt; ++t) {
             const uint64_t adesc = make_smem_desc(a_addr + t * A_BYTES);
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k)   // +32 bytes along K inside the swizzle atom = +2 in the (>>4) address field
-              umma_tf32(d_tmem + (uint32_t)(t * H), adesc + 2 * k, bdesc + 2 * k, IDESC, (uint32_t)((kb | k) != 0));
+              umma_tf32(tmem_base + (uint32_t)(t * H), adesc + 2 * k, bdesc + 2 * k, IDESC, (uint32_t)((kb | k) != 0));
           }
           umma_commit(empty + s);                  // stage reusable once these MMAs have read it
-          if (kb == KB - 1) umma_commit(tmem_full + as);
+          if (kb == KB - 1) umma_commit(tmem_full);
           if (++s == NS) { s = 0; ph ^= 1; }
         }
       }
     }
   } else {             // ---------------------------------------------------- epilogue: one node row per thread
     const int q = warp & 3;                         // TMEM lane quarter this warp may access
+    const int t = (warp - 2) >> 2;                  // sub-tile: warps 2-5 -> 0, warps 6-9 -> 1
     const int row_in_tile = q * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int st = 0; st < n_super; ++st) {
-      const int as = NBUF == 2 ? (st & 1) : 0;
-      const uint32_t aph = NBUF == 2 ? ((st >> 1) & 1) : (st & 1);
       const int rem = my_rows - st * 2 * BLOCK_M;
-      mbar_wait(tmem_full + as, aph);
+      mbar_wait(tmem_full, (uint32_t)(st & 1));
+      if (st == n_super - 1 && threadIdx.x == 64) stamp(p, 4);
       tc_fence_after();
+      const int valid = min(rem - t * BLOCK_M, BLOCK_M);               // rows of this sub-tile that exist
+      if (valid > 0) {                                                 // uniform over the sub-tile's four warps
+        // hidden layer: ReLU(acc + b1) (mlp.py:14,18), rounded to tf32, written back over the accumulator
 #pragma unroll 1
-      for (int t = 0; t < 2; ++t) {
-        const int valid = min(rem - t * BLOCK_M, BLOCK_M);             // rows of this sub-tile that exist
-        if (q * 32 < valid) {                                          // warp-uniform: skip quarters with no row at all
-          float out[F_OUT];
+        for (int c = 0; c < H / 32; ++c) {
+          float v[32];
+          tmem_ld32(lane_base + (uint32_t)(t * H + c * 32), v);
 #pragma unroll
-          for (int o = 0; o < F_OUT; ++o) out[o] = b2s[o];
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 2 * H + t * H);
-#pragma unroll 1
-          for (int c = 0; c < H / 32; ++c) {
-            float v[32];
-            tmem_ld32(taddr + c * 32, v);
+          for (int j = 0; j < 32; ++j) v[j] = tf32_rna(fmaxf(v[j] + b1s[c * 32 + j], 0.f));
+          tmem_st32(lane_base + (uint32_t)(t * H + c * 32), v);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");     // all 128 rows of the sub-tile are in tensor memory
+        if (q == 2 && lane == 0) {                                     // first warp of the group issues layer 2
+          tc_fence_after();
+          const uint32_t w2_addr = smem_u32(w2s);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float hj = fmaxf(v[j] + b1s[c * 32 + j], 0.f);            // Linear + ReLU (mlp.py:14,18)
-              const float4* wr = reinterpret_cast<const float4*>(w2t + (c * 32 + j) * F_OUT);
-#pragma unroll
-              for (int o4 = 0; o4 < F_OUT / 4; ++o4) {
-                const float4 w = wr[o4];                                        // same address in every lane: broadcast
-                out[4 * o4 + 0] = fmaf(hj, w.x, out[4 * o4 + 0]);
-                out[4 * o4 + 1] = fmaf(hj, w.y, out[4 * o4 + 1]);
-                out[4 * o4 + 2] = fmaf(hj, w.z, out[4 * o4 + 2]);
-                out[4 * o4 + 3] = fmaf(hj, w.w, out[4 * o4 + 3]);
-              }
-            }
+          for (int ks = 0; ks < H / UMMA_K; ++ks) {
+            const uint64_t bdesc = make_smem_desc(w2_addr + (uint32_t)(ks >> 2) * (F_OUT * BLOCK_K * 4)) + 2 * (ks & 3);
+            umma_tf32_ts(tmem_base + (uint32_t)(2 * H + t * F_OUT), tmem_base + (uint32_t)(t * H + ks * UMMA_K), bdesc, IDESC2, (uint32_t)(ks != 0));
           }
-          if (row_in_tile < valid) {
-            const int64_t row = row_begin + (int64_t)st * 2 * BLOCK_M + t * BLOCK_M + row_in_tile;
-            float4* dst = reinterpret_cast<float4*>(p.h_out + row * F_OUT);
+          umma_commit(d2_full + t);
+        }
+        mbar_wait(d2_full + t, (uint32_t)(st & 1));
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(lane_base + (uint32_t)(2 * H + t * F_OUT), v);
+        if (row_in_tile < valid) {
+          const int64_t row = row_begin + (int64_t)st * 2 * BLOCK_M + t * BLOCK_M + row_in_tile;
+          float4* dst = reinterpret_cast<float4*>(p.h_out + row * F_OUT);
 #pragma unroll
-            for (int o4 = 0; o4 < F_OUT / 4; ++o4)
-              dst[o4] = make_float4(fmaxf(out[4 * o4], 0.f), fmaxf(out[4 * o4 + 1], 0.f), fmaxf(out[4 * o4 + 2], 0.f), fmaxf(out[4 * o4 + 3], 0.f));
-          }
+          for (int o4 = 0; o4 < F_OUT / 4; ++o4)
+            dst[o4] = make_float4(fmaxf(v[4 * o4] + b2s[4 * o4], 0.f), fmaxf(v[4 * o4 + 1] + b2s[4 * o4 + 1], 0.f),
+                                  fmaxf(v[4 * o4 + 2] + b2s[4 * o4 + 2], 0.f), fmaxf(v[4 * o4 + 3] + b2s[4 * o4 + 3], 0.f));
         }
       }
-      tc_fence_before();                              // both accumulators fully read: hand the pair back to the MMA warp
+      tc_fence_before();                              // accumulators fully consumed: hand them back to the MMA warp
       __syncwarp();
-      if (lane == 0) mbar_arrive(tmem_empty + as);
+      if (lane == 0) mbar_arrive(tmem_empty);
+      if (st == n_super - 1 && threadIdx.x == 64) stamp(p, 5);
     }
   }
   tc_fence_before();
@@ -275,6 +368,7 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
   }
+  if (threadIdx.x == 0) stamp(p, 6);
 }
 
 }  // namespace enc
@@ -316,25 +410,43 @@ bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, i
 }
 
 
+#ifdef GNNCCA_ENC_TRACE
+unsigned long long* g_enc_trace = nullptr;
+int g_enc_force_stages = 0;
+#endif
+
 template <int H>
 int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaStream_t st) {
   enc::Params p = p0;
-  const size_t stage = (size_t)(2 * enc::BLOCK_M + H) * enc::BLOCK_K * 4;
-  const size_t fixed = 1024 /*alignment slack*/ + sizeof(float) * (H * enc::F_OUT + H + enc::F_OUT) + 8 * (2 * enc::MAX_STAGES + 4) + 16;
-  int stages = (int)((227 * 1024 - fixed) / stage);
-  if (stages > enc::MAX_STAGES) stages = enc::MAX_STAGES;
-  if (stages < 2) return GNNCCA_ERR_UNSUPPORTED;
-  p.stages = stages;
-  const size_t smem = fixed + stage * stages;
+#ifdef GNNCCA_ENC_TRACE
+  p.trace = g_enc_trace;
+#endif
   // every SM gets the same number of rows (8-row granules); grids smaller than the machine only for tiny inputs
   int64_t rpc = (ceil_div(p.rows, kNumSMs) + 7) & ~(int64_t)7;
   if (rpc < 8) rpc = 8;
   p.rows_per_cta = (int)rpc;
   const int grid = (int)ceil_div(p.rows, rpc);
+  const int64_t tile_rows = rpc < 2 * enc::BLOCK_M ? rpc : 2 * enc::BLOCK_M;
+  p.a_bytes = (uint32_t)((tile_rows * enc::BLOCK_K * 4 + 1023) & ~(int64_t)1023);
+  const size_t stage = (size_t)p.a_bytes + (size_t)H * enc::BLOCK_K * 4;
+  const size_t fixed = 1024 /*alignment slack*/ + sizeof(float) * (H * enc::F_OUT + H + enc::F_OUT) + 8 * (2 * enc::MAX_STAGES + 4) + 32;
+  int stages = (int)((227 * 1024 - fixed) / stage);
+  if (stages > enc::MAX_STAGES) stages = enc::MAX_STAGES;
+  if (stages < 2) return GNNCCA_ERR_UNSUPPORTED;
+#ifdef GNNCCA_ENC_TRACE
+  if (g_enc_force_stages > 0 && g_enc_force_stages < stages) stages = g_enc_force_stages;
+#endif
+  p.stages = stages;
+  const size_t smem = fixed + stage * stages;
   enc::XMaps xm;
   CUtensorMap mw;
   for (int b = 0; b < 5; ++b)
     if (!make_map(&xm.m[b], x, p.rows, p.K, 8 << b)) return GNNCCA_ERR_LAUNCH;
+  {   // the partial sub-tile every full CTA ends with
+    const int64_t last = rpc - 2 * enc::BLOCK_M * (ceil_div(rpc, 2 * enc::BLOCK_M) - 1);
+    xm.tail_rows = (int)(last > enc::BLOCK_M ? last - enc::BLOCK_M : last);
+    if (!make_map(&xm.m[5], x, p.rows, p.K, xm.tail_rows)) return GNNCCA_ERR_LAUNCH;
+  }
   if (!make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
   auto kern = enc::node_encoder_tf32_kernel<H>;
   static bool configured = false;
@@ -350,7 +462,7 @@ int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaS
 }  // namespace
 
 // Fused two-layer node encoder on the tensor cores (see the header of this file).  Requirements: in_dim % 32 == 0,
-// hidden in {64, 128, 256}, out_dim == 32, x and W1 16-byte aligned.
+// hidden in {64, 128}, out_dim == 32, x and W1 16-byte aligned.
 int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
                              int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream) {
   if (out_dim != enc::F_OUT || in_dim % enc::BLOCK_K != 0 || in_dim < enc::BLOCK_K) return GNNCCA_ERR_UNSUPPORTED;
@@ -362,7 +474,6 @@ int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, c
   switch (hidden) {
     case 64: return launch_encoder<64>(x, W1, p, st);
     case 128: return launch_encoder<128>(x, W1, p, st);
-    case 256: return launch_encoder<256>(x, W1, p, st);
     default: return GNNCCA_ERR_UNSUPPORTED;
   }
 }

@@ -394,7 +394,7 @@ FUSED_NODE_ENCODER = True   # bench.py: the node encoder is one kernel in tf32 m
 def node_encoder_fused_ok(mlp, inp) -> bool:
     """Shapes the tcgen05 encoder kernel covers: Linear+ReLU, Linear+ReLU, in % 32 == 0, hidden in {64,128,256}, out 32."""
     sp = mlp.layer_specs
-    return (len(sp) == 2 and all(s.relu and s.bn is None for s in sp) and sp[0].in_dim % 32 == 0 and sp[0].out_dim in (64, 128, 256)
+    return (len(sp) == 2 and all(s.relu and s.bn is None for s in sp) and sp[0].in_dim % 32 == 0 and sp[0].out_dim in (64, 128)
             and sp[1].out_dim == 32 and inp.data_ptr() % 16 == 0)
 
 

@@ -31,7 +31,8 @@ def _run(rows, in_dim, hidden, dev, seed=0, scale=1.0, keep=None):
 
 
 @pytest.mark.parametrize("rows,in_dim,hidden", [(128, 2048, 128), (24576, 2048, 128), (1, 512, 128), (777, 512, 128),
-                                                 (300, 2048, 64), (5000, 256, 256), (129, 32, 128)])
+                                                 (300, 2048, 64), (5000, 256, 64), (129, 32, 128), (60000, 64, 128), (148 * 256 + 5, 32, 128),
+                                                 (148 * 512 + 136, 32, 64)])
 def test_node_encoder_tf32_matches_fp32_reference(rows, in_dim, hidden, cuda_device):
     torch.manual_seed(3)
     got, ref = _run(rows, in_dim, hidden, cuda_device)
@@ -51,3 +52,9 @@ def test_node_encoder_tf32_is_deterministic_and_row_local(cuda_device):
     torch.manual_seed(4)
     c, _ = _run(1000, 2048, 128, cuda_device, seed=7, keep=333)    # a shorter batch of the same rows
     assert torch.equal(a[:333], c)
+
+
+def test_node_encoder_rejects_hidden_widths_without_a_kernel(cuda_device):
+    """hidden = 256 does not fit one CTA's tensor memory next to the layer-2 accumulators: UNSUPPORTED, never a fallback."""
+    with pytest.raises(NotImplementedError):
+        _run(64, 64, 256, cuda_device)
