@@ -57,6 +57,8 @@ SIGNATURES = {
                                      vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_mp_fused_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i32, vp, i64, vp, vp, vp, vp, vp, i64, i64,
                                       vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "gnncca_mpn_forward_frames": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp,
+                                            i64, i64, i64, i32, i32, i32, i32, vp, vp, vp, vp]),
     "gnncca_train_blocks": (i32, [i64, i32]),
     "gnncca_node_agg_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gnncca_edge_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),

@@ -377,6 +377,10 @@ def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: to
     return out
 
 
+FAST_PLAN = TrustedPlan.__new__(TrustedPlan)     # what ``last_plan`` reports after the single-call path
+FAST_PLAN.last_path = "fused"
+FAST_PLAN.caps = None
+
 _SIDE_STREAMS = {}
 
 
@@ -425,3 +429,80 @@ def small_mlp_rows_cls(model, e):
     if any(sp.bn is not None for sp in cls.layer_specs):
         raise NotImplementedError("num_enc_steps == 0 with a BatchNorm classifier is not implemented")
     return small_mlp_rows(cls, e)
+
+
+class FastPath:
+    """Everything ``MOTMPNet.forward`` needs to run a trusted batch (``build_graph_batch``) with ONE library call
+    (gnncca_mpn_forward_frames): the ctypes views of the configuration and of the live parameter pointers, built once
+    per model and re-validated per call by comparing the parameters' device pointers."""
+
+    def __init__(self, model):
+        check_supported(model)
+        enc_n, enc_e = model.encoder.node_mlp, model.encoder.edge_mlp
+        sp = enc_n.layer_specs
+        if not (len(sp) == 2 and all(s.relu and s.bn is None for s in sp) and sp[0].in_dim % 32 == 0 and sp[0].out_dim in (64, 128)
+                and sp[1].out_dim == 32):
+            raise NotImplementedError("node encoder shape without a fused kernel")
+        if len(enc_e.layer_specs) != 1 or not enc_e.layer_specs[0].relu or enc_e.layer_specs[0].bn is not None:
+            raise NotImplementedError("edge encoder must be a single Linear+ReLU")
+        self.L, k = model.num_enc_steps, model.num_class_steps
+        self.first = self.L - k + 1
+        if self.L < 1 or self.first < 1 or model.math != "tf32":
+            raise NotImplementedError("fast path needs L >= 1, k <= L and tf32 math")
+        self.n_cls = self.L - self.first + 1
+        self.fa = enc_e.layer_specs[0].in_dim
+        # (dict, name) of every parameter / buffer slot of the module tree: a re-assigned nn.Parameter is seen too
+        self.slots = [(d, n) for m in model.modules() for d in (m._parameters, m._buffers) for n, t in d.items() if t is not None]
+        self.key = tuple(d[n].data_ptr() for d, n in self.slots)
+        self.sb = StepBinding(model, _lib.MATH_TF32)
+        l1, l2, le = enc_n.linear(0), enc_n.linear(1), enc_e.linear(0)
+        self.prefix = (C.byref(self.sb.cfg), C.byref(self.sb.w), l1.weight.data_ptr(), l1.bias.data_ptr(), l2.weight.data_ptr(),
+                       l2.bias.data_ptr(), l1.in_features, l1.out_features, le.weight.data_ptr(), le.bias.data_ptr(), self.fa)
+        self.in_dim = l1.in_features
+        self.device = l1.weight.device
+        self.fn = _lib.load().gnncca_mpn_forward_frames
+        self.flags = torch.zeros(_lib.CSR_NFLAGS, dtype=torch.int32, device=self.device)   # write-only scratch (never read back)
+        self.training = model.training
+
+    def valid(self, model) -> bool:
+        try:
+            return self.training == model.training and self.key == tuple(d[n].data_ptr() for d, n in self.slots)
+        except (KeyError, AttributeError):
+            return False
+
+    def run(self, model, x, edge_index, edge_attr, graph_ptr, edge_ptr, caps):
+        """The logits list, or None when this batch is not eligible (the caller then takes the general path)."""
+        N, E = x.size(0), edge_index.size(1)
+        if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.size(1) == self.in_dim and x.is_contiguous()
+                and edge_attr.dtype == torch.float32 and edge_attr.dim() == 2 and edge_attr.size(1) == self.fa and edge_attr.is_contiguous()
+                and edge_attr.size(0) == E and edge_index.dtype == torch.int64 and edge_index.is_contiguous() and E > 0
+                and graph_ptr.is_cuda and graph_ptr.dtype == torch.int64 and edge_ptr.is_cuda and edge_ptr.dtype == torch.int64
+                and x.device == self.device and x.data_ptr() % 16 == 0 and edge_attr.data_ptr() % 16 == 0):
+            return None
+        B = graph_ptr.numel() - 1
+        cap = frame_capacity(model, N, E, B, caps)
+        if cap is None or edge_ptr.numel() != B + 1:
+            return None
+        h = torch.empty((N, 32), dtype=torch.float32, device=self.device)
+        logits = torch.empty((self.n_cls, E), dtype=torch.float32, device=self.device)
+        rc = self.fn(*self.prefix, x.data_ptr(), edge_index.data_ptr(), edge_attr.data_ptr(), graph_ptr.data_ptr(), edge_ptr.data_ptr(),
+                     N, E, B, self.L, self.first, cap[0], cap[1], h.data_ptr(), logits.data_ptr(), self.flags.data_ptr(), _stream())
+        if rc:
+            _lib.check(rc, "mpn_forward_frames")
+        return [logits[i].view(E, 1) for i in range(self.n_cls)]
+
+
+def fast_path(model):
+    """Cached ``FastPath`` of a model (None when its configuration has no single-call kernel path)."""
+    fp = getattr(model, "_gnncca_fast", None)
+    if fp is not None and fp is not False and fp.valid(model):
+        return fp
+    if fp is False and getattr(model, "_gnncca_fast_training", None) == model.training:
+        return None
+    try:
+        fp = FastPath(model)
+    except NotImplementedError:
+        fp = False
+        model.__dict__["_gnncca_fast_training"] = model.training
+    model.__dict__["_gnncca_fast"] = fp
+    return fp or None

@@ -153,6 +153,14 @@ class MOTMPNet(nn.Module):
             trusted, allow_fused = True, plan.last_path == "fused"
             caps = getattr(plan, "caps", caps) if allow_fused else caps
         needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        if (not needs_grad and not self.training and caps is not None and getattr(data, "gnncca_trusted", False)
+                and getattr(data, "edge_ptr", None) is not None and graph_ptr is not None):
+            # batches from build_graph_batch in eval mode: one library call, two launches, nothing read back
+            fp = engine.fast_path(self)
+            outs = fp.run(self, x, edge_index, edge_attr, graph_ptr, data.edge_ptr, caps) if fp is not None else None
+            if outs is not None:
+                self.last_plan = engine.FAST_PLAN
+                return {'classified_edges': outs}
         if needs_grad or (self.training and self._has_batchnorm()):
             outs = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan)
         else:

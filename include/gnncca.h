@@ -90,9 +90,10 @@ int gnncca_linear(const float* x, const float* W, const float* b, float* y, int6
 
 /* Node encoder of MOTMPNet (mpn.py:128-142 node branch with node_fc_dims=[hidden], mlp.py:12-23):
  *   h[rows,out] = ReLU( ReLU( x[rows,in] @ W1^T + b1 ) @ W2^T + b2 )
- * as ONE kernel: TMA-fed tcgen05 kind::tf32 MMA for the wide first layer (x is consumed as TF32 in place),
- * exact-FP32 second layer in the epilogue; the hidden activations never reach HBM.
- * math must be GNNCCA_MATH_TF32; needs in % 32 == 0, hidden in {64,128,256}, out == 32, 16-byte aligned
+ * as ONE kernel: TMA-fed tcgen05 kind::tf32 MMA for the wide first layer (x is consumed as TF32 in place);
+ * ReLU(acc + b1) is written back to tensor memory and is the A operand of a second tcgen05 MMA against W2
+ * (tf32, round-to-nearest); the hidden activations never reach HBM or shared memory.
+ * math must be GNNCCA_MATH_TF32; needs in % 32 == 0, hidden in {64,128}, out == 32, 16-byte aligned
  * x / W1 / h.  Anything else returns GNNCCA_ERR_UNSUPPORTED (the caller then uses two gnncca_linear calls). */
 int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
                         int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, int32_t math, void* stream);
@@ -182,6 +183,21 @@ int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
                         int64_t n_edges, const float* h_enc, const float* edge_attr, int32_t num_steps,
                         int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges, float* logits,
                         float* h_dump, float* e_dump, int32_t* flags, void* stream);
+
+/* MOTMPNet.forward (mpn.py:250-299) for a batch of SMALL frame graphs in ONE call: node encoder
+ * (gnncca_node_encoder, tf32) + gnncca_mp_fused_fwd in its RAW form.  This is what the drop-in module calls
+ * for batches whose frame structure is known (build_graph_batch): two launches, no CSR, nothing read back.
+ *   enc_*: the node encoder's two Linear layers (in_dim -> hidden -> f_node); everything else as in
+ *   gnncca_mp_fused_fwd.  h_enc [N][f_node] is caller-provided scratch for the encoded nodes. */
+int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
+                              const float* enc_W1, const float* enc_b1, const float* enc_W2, const float* enc_b2,
+                              int32_t in_dim, int32_t hidden,
+                              const float* w_enc_edge, const float* b_enc_edge, int32_t edge_in_dim,
+                              const float* x, const int64_t* edge_index, const float* edge_attr,
+                              const int64_t* graph_ptr, const int64_t* edge_ptr,
+                              int64_t n_nodes, int64_t n_edges, int64_t n_graphs,
+                              int32_t num_steps, int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges,
+                              float* h_enc, float* logits, int32_t* flags, void* stream);
 
 /* Independent per-edge MLP chain (MLPGraphIndependent edge branch, mpn.py:128-142): encoder edge MLP
  * (4 -> 6 + ReLU) and, stand-alone, the classifier.  Up to 4 layers, widths <= 32.

@@ -316,3 +316,35 @@ def test_raw_form_verifies_the_frames_on_the_device(violation, cuda_device):
     torch.cuda.synchronize()
     assert int(flags[2]) == (0 if violation == "none" else 1)
     assert bool(torch.isfinite(logits).all())
+
+
+def test_single_call_path_equals_the_general_pipeline(cuda_device):
+    """Default (tf32) model + batch from build_graph_batch + eval: MOTMPNet.forward is ONE library call
+    (gnncca_mpn_forward_frames).  Same bits as the general pipeline (CSR kernel, encoder, fused kernel) on the same
+    batch; parameters updated in place are seen; a re-created parameter invalidates the cached binding."""
+    import gnncca
+    from importlib import import_module
+    engine = import_module("gnn-cca_b200.engine")
+    _lib = import_module("gnn-cca_b200._lib")
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(6)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50").to(cuda_device).eval()
+    b = _trusted_batch(cuda_device, frames=150)
+    lib = _lib.load()
+    with torch.no_grad():
+        n0 = int(lib.gnncca_launch_count())
+        fast = model(b)["classified_edges"]
+        assert int(lib.gnncca_launch_count()) - n0 == 2 and model.last_plan is engine.FAST_PLAN
+        general = model(D(b.x, b.edge_index, b.edge_attr, b.ptr))["classified_edges"]
+        assert len(fast) == 3
+        for a, c in zip(fast, general):
+            assert a.shape == c.shape and torch.equal(a, c)
+        model.classifier.edge_mlp.linear(1).bias.add_(1.0)                 # optimiser-style in-place update
+        shifted = model(b)["classified_edges"]
+        assert torch.allclose(shifted[-1], fast[-1] + 1.0, atol=1e-5)
+        lin = model.MPNet.edge_model.edge_mlp.linear(0)
+        lin.weight = torch.nn.Parameter(torch.zeros_like(lin.weight))      # new storage: the binding must be rebuilt
+        rebuilt = model(b)["classified_edges"]
+        again = model(D(b.x, b.edge_index, b.edge_attr, b.ptr))["classified_edges"]
+        for a, c in zip(rebuilt, again):
+            assert torch.equal(a, c)
