@@ -34,6 +34,15 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
   return d;
 }
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  uint64_t ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
 __device__ __forceinline__ float2 bc(float w) { return make_float2(w, w); }   // scalar operand of FFMA2 (no extra register)
 __device__ __forceinline__ float2 relu2(float2 v) { return make_float2(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)); }
 __device__ __forceinline__ float tf32_rna(float x) {
@@ -297,7 +306,10 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
           float ah[4], al[4];
           const float av[4] = {hb[r0 * HS + k0 + t], hb[(r0 + 8) * HS + k0 + t], hb[r0 * HS + k0 + t + 4], hb[(r0 + 8) * HS + k0 + t + 4]};
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { ah[i] = tf32_rna(av[i]); al[i] = tf32_rna(av[i] - ah[i]); }
+          for (int i = 0; i < 4; ++i) {     // hi = the tf32 prefix of the fp32 bits (what the tensor core reads anyway), lo = the exact rest
+            ah[i] = __uint_as_float(__float_as_uint(av[i]) & 0xffffe000u);
+            al[i] = av[i] - ah[i];
+          }
 #pragma unroll
           for (int i = 0; i < 3; ++i) {
             const float4 w = *reinterpret_cast<const float4*>(sw + wo.wB + ((ks * 6 + half * 3 + i) * 32 + lane) * 4);
@@ -394,17 +406,19 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
         const bool live = v < n;
         const int j0 = live ? ssi[so.rp + v] : 0, j1 = live ? ssi[so.rp + v + 1] : 0;
         const float r0 = live ? ss[so.pqr + v * PS + 2 * FE + c0] : 0.f, r1 = live ? ss[so.pqr + v * PS + 2 * FE + c0 + 16] : 0.f;
-        float acc0 = agg_init(AGG), acc1 = agg_init(AGG);
+        // even / odd edges of the segment are folded into the two halves of a packed accumulator (one FADD2 per
+        // feature and edge pair); the halves are combined at the end -- a fixed order either way
+        float2 acc0 = bc(agg_init(AGG)), acc1 = bc(agg_init(AGG));
         auto single = [&](int j) {          // one edge, scalar FFMA (odd segment ends)
           float t0 = r0, t1 = r1;
 #pragma unroll
           for (int k = 0; k < FE; ++k) { const float x = eb_[(j >> 1) * 12 + k * 2 + (j & 1)]; t0 = fmaf(x, wlo[k], t0); t1 = fmaf(x, whi[k], t1); }
-          acc0 = agg_comb(AGG, acc0, fmaxf(t0, 0.f)); acc1 = agg_comb(AGG, acc1, fmaxf(t1, 0.f));
+          acc0.x = agg_comb(AGG, acc0.x, fmaxf(t0, 0.f)); acc1.x = agg_comb(AGG, acc1.x, fmaxf(t1, 0.f));
         };
         int j = j0;
         if (j < j1 && (j & 1)) { single(j); ++j; }
         const float2 rr0 = make_float2(r0, r0), rr1 = make_float2(r1, r1);
-        for (; j + 2 <= j1; j += 2) {        // an edge pair per iteration, messages folded in edge order
+        for (; j + 2 <= j1; j += 2) {        // an edge pair per iteration
           const float4* pa = reinterpret_cast<const float4*>(eb_ + (j >> 1) * 12);
           const float4 a0 = pa[0], a1 = pa[1], a2 = pa[2];
           const float2 x0 = make_float2(a0.x, a0.y), x1 = make_float2(a0.z, a0.w), x2 = make_float2(a1.x, a1.y),
@@ -416,18 +430,23 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
           m0 = ffma2(x3, bc(wlo[3]), m0); m1 = ffma2(x3, bc(whi[3]), m1);
           m0 = ffma2(x4, bc(wlo[4]), m0); m1 = ffma2(x4, bc(whi[4]), m1);
           m0 = ffma2(x5, bc(wlo[5]), m0); m1 = ffma2(x5, bc(whi[5]), m1);
-          acc0 = agg_comb(AGG, acc0, fmaxf(m0.x, 0.f)); acc0 = agg_comb(AGG, acc0, fmaxf(m0.y, 0.f));
-          acc1 = agg_comb(AGG, acc1, fmaxf(m1.x, 0.f)); acc1 = agg_comb(AGG, acc1, fmaxf(m1.y, 0.f));
+          if (AGG == GNNCCA_AGG_MAX) {
+            acc0.x = fmaxf(acc0.x, fmaxf(m0.x, 0.f)); acc0.y = fmaxf(acc0.y, fmaxf(m0.y, 0.f));
+            acc1.x = fmaxf(acc1.x, fmaxf(m1.x, 0.f)); acc1.y = fmaxf(acc1.y, fmaxf(m1.y, 0.f));
+          } else {
+            acc0 = fadd2(acc0, relu2(m0)); acc1 = fadd2(acc1, relu2(m1));
+          }
         }
         if (j < j1) single(j);
-        if (j1 == j0) { acc0 = 0.f; acc1 = 0.f; }                        // no out-edge: torch_scatter leaves 0
-        else if (AGG == GNNCCA_AGG_MEAN) { const float inv = 1.f / (float)(j1 - j0); acc0 = acc0 * inv; acc1 = acc1 * inv; }
+        float s0 = agg_comb(AGG, acc0.x, acc0.y), s1 = agg_comb(AGG, acc1.x, acc1.y);
+        if (j1 == j0) { s0 = 0.f; s1 = 0.f; }                            // no out-edge: torch_scatter leaves 0
+        else if (AGG == GNNCCA_AGG_MEAN) { const float inv = 1.f / (float)(j1 - j0); s0 = s0 * inv; s1 = s1 * inv; }
         if (live) {
-          ss[so.h + v * HS + c0] = acc0;
-          ss[so.h + v * HS + c0 + 16] = acc1;
+          ss[so.h + v * HS + c0] = s0;
+          ss[so.h + v * HS + c0 + 16] = s1;
           if (bt.h_dump) {
-            bt.h_dump[((int64_t)step * bt.n_nodes + a + v) * FN + c0] = acc0;
-            bt.h_dump[((int64_t)step * bt.n_nodes + a + v) * FN + c0 + 16] = acc1;
+            bt.h_dump[((int64_t)step * bt.n_nodes + a + v) * FN + c0] = s0;
+            bt.h_dump[((int64_t)step * bt.n_nodes + a + v) * FN + c0 + 16] = s1;
           }
         }
       }

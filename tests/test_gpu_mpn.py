@@ -334,7 +334,7 @@ def test_single_call_path_equals_the_general_pipeline(cuda_device):
     with torch.no_grad():
         n0 = int(lib.gnncca_launch_count())
         fast = model(b)["classified_edges"]
-        assert int(lib.gnncca_launch_count()) - n0 == 2 and model.last_plan is engine.FAST_PLAN
+        assert int(lib.gnncca_launch_count()) - n0 in (1, 2) and model.last_plan is engine.FAST_PLAN
         general = model(D(b.x, b.edge_index, b.edge_attr, b.ptr))["classified_edges"]
         assert len(fast) == 3
         for a, c in zip(fast, general):
