@@ -28,6 +28,10 @@ int mpn_mega_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const flo
                  int64_t n_edges, int64_t n_graphs, int32_t num_steps, int32_t first_class_step, int32_t cap_nodes,
                  int32_t cap_edges, float* h_enc, float* logits, int32_t* flags, void* stream);
 
+// Set by gnncca_mpn_forward_frames around its second launch: gnncca_mp_fused_fwd then launches with programmatic
+// stream serialization, so its CTAs start (and load their weights) on SMs the encoder has already left.
+extern thread_local bool tl_launch_as_dependent;
+
 constexpr int kNumSMs = 148;   // B200: 2 dies x 74 SMs
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -78,7 +78,10 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
   uint32_t* tmem_slot = (uint32_t*)(d2_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) stamp(p, 0);
+  if (threadIdx.x == 0) {
+    stamp(p, 0);
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // a dependent launch may take over SMs as CTAs of this grid exit
+  }
   const int64_t row_begin = (int64_t)blockIdx.x * p.rows_per_cta;
   const int64_t row_end = min(row_begin + p.rows_per_cta, p.rows);
   const int my_rows = (int)(row_end - row_begin);

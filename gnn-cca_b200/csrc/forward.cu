@@ -31,7 +31,10 @@ extern "C" int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_
   }
   int rc = gnncca_node_encoder(x, enc_W1, enc_b1, enc_W2, enc_b2, h_enc, n_nodes, in_dim, hidden, cfg->f_node, GNNCCA_MATH_TF32, stream);
   if (rc) return rc;
-  return gnncca_mp_fused_fwd(cfg, w, w_enc_edge, b_enc_edge, edge_in_dim, graph_ptr, n_graphs, edge_index, edge_ptr, nullptr, nullptr,
-                             nullptr, n_nodes, n_edges, h_enc, edge_attr, num_steps, first_class_step, cap_nodes, cap_edges, logits,
-                             nullptr, nullptr, flags, stream);
+  gnncca::tl_launch_as_dependent = true;
+  rc = gnncca_mp_fused_fwd(cfg, w, w_enc_edge, b_enc_edge, edge_in_dim, graph_ptr, n_graphs, edge_index, edge_ptr, nullptr, nullptr,
+                           nullptr, n_nodes, n_edges, h_enc, edge_attr, num_steps, first_class_step, cap_nodes, cap_edges, logits,
+                           nullptr, nullptr, flags, stream);
+  gnncca::tl_launch_as_dependent = false;
+  return rc;
 }

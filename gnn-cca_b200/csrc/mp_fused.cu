@@ -26,6 +26,9 @@ __global__ void __launch_bounds__(896, 1) mp_fused_fwd_kernel(const __grid_const
   const mpf::WOff wo = mpf::weight_layout(K, EIN);
   const mpf::SOff so = mpf::state_layout(p.net.cap_n, p.net.cap_e, p.net.reatt_n != 0, REATT_E);
   mpf::load_weights(smem_f, wo, p.net, threadIdx.x, blockDim.x);
+  // launched as a programmatic dependent of the node encoder (gnncca_mpn_forward_frames): everything above overlapped
+  // the encoder's tail; its output is visible from here on.  A no-op for ordinary launches.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
   mpf::Group gr;
   const int gi = threadIdx.x / p.group_threads;
@@ -102,6 +105,17 @@ extern "C" int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_wei
     int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     if (rc) return rc;
   }
-  kern<<<grid, groups * gt, smem, st>>>(p);
+  if (tl_launch_as_dependent && raw) {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(grid); lc.blockDim = dim3(groups * gt); lc.dynamicSmemBytes = smem; lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    int rc = check_cuda(cudaLaunchKernelEx(&lc, kern, p));
+    if (rc) return rc;
+  } else {
+    kern<<<grid, groups * gt, smem, st>>>(p);
+  }
   return check_launch();
 }
