@@ -418,24 +418,29 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
         int j = j0;
         if (j < j1 && (j & 1)) { single(j); ++j; }
         const float2 rr0 = make_float2(r0, r0), rr1 = make_float2(r1, r1);
-        for (; j + 2 <= j1; j += 2) {        // an edge pair per iteration
+        {                                    // an edge pair per iteration; pointer-stepped so the unrolled body has no index math
           const float4* pa = reinterpret_cast<const float4*>(eb_ + (j >> 1) * 12);
-          const float4 a0 = pa[0], a1 = pa[1], a2 = pa[2];
-          const float2 x0 = make_float2(a0.x, a0.y), x1 = make_float2(a0.z, a0.w), x2 = make_float2(a1.x, a1.y),
-                       x3 = make_float2(a1.z, a1.w), x4 = make_float2(a2.x, a2.y), x5 = make_float2(a2.z, a2.w);
-          float2 m0 = rr0, m1 = rr1;
-          m0 = ffma2(x0, bc(wlo[0]), m0); m1 = ffma2(x0, bc(whi[0]), m1);
-          m0 = ffma2(x1, bc(wlo[1]), m0); m1 = ffma2(x1, bc(whi[1]), m1);
-          m0 = ffma2(x2, bc(wlo[2]), m0); m1 = ffma2(x2, bc(whi[2]), m1);
-          m0 = ffma2(x3, bc(wlo[3]), m0); m1 = ffma2(x3, bc(whi[3]), m1);
-          m0 = ffma2(x4, bc(wlo[4]), m0); m1 = ffma2(x4, bc(whi[4]), m1);
-          m0 = ffma2(x5, bc(wlo[5]), m0); m1 = ffma2(x5, bc(whi[5]), m1);
-          if (AGG == GNNCCA_AGG_MAX) {
-            acc0.x = fmaxf(acc0.x, fmaxf(m0.x, 0.f)); acc0.y = fmaxf(acc0.y, fmaxf(m0.y, 0.f));
-            acc1.x = fmaxf(acc1.x, fmaxf(m1.x, 0.f)); acc1.y = fmaxf(acc1.y, fmaxf(m1.y, 0.f));
-          } else {
-            acc0 = fadd2(acc0, relu2(m0)); acc1 = fadd2(acc1, relu2(m1));
+          const int npair = (j1 - j) >> 1;
+#pragma unroll 4
+          for (int i = 0; i < npair; ++i, pa += 3) {
+            const float4 a0 = pa[0], a1 = pa[1], a2 = pa[2];
+            const float2 x0 = make_float2(a0.x, a0.y), x1 = make_float2(a0.z, a0.w), x2 = make_float2(a1.x, a1.y),
+                         x3 = make_float2(a1.z, a1.w), x4 = make_float2(a2.x, a2.y), x5 = make_float2(a2.z, a2.w);
+            float2 m0 = rr0, m1 = rr1;
+            m0 = ffma2(x0, bc(wlo[0]), m0); m1 = ffma2(x0, bc(whi[0]), m1);
+            m0 = ffma2(x1, bc(wlo[1]), m0); m1 = ffma2(x1, bc(whi[1]), m1);
+            m0 = ffma2(x2, bc(wlo[2]), m0); m1 = ffma2(x2, bc(whi[2]), m1);
+            m0 = ffma2(x3, bc(wlo[3]), m0); m1 = ffma2(x3, bc(whi[3]), m1);
+            m0 = ffma2(x4, bc(wlo[4]), m0); m1 = ffma2(x4, bc(whi[4]), m1);
+            m0 = ffma2(x5, bc(wlo[5]), m0); m1 = ffma2(x5, bc(whi[5]), m1);
+            if (AGG == GNNCCA_AGG_MAX) {
+              acc0.x = fmaxf(acc0.x, fmaxf(m0.x, 0.f)); acc0.y = fmaxf(acc0.y, fmaxf(m0.y, 0.f));
+              acc1.x = fmaxf(acc1.x, fmaxf(m1.x, 0.f)); acc1.y = fmaxf(acc1.y, fmaxf(m1.y, 0.f));
+            } else {
+              acc0 = fadd2(acc0, relu2(m0)); acc1 = fadd2(acc1, relu2(m1));
+            }
           }
+          j += 2 * npair;
         }
         if (j < j1) single(j);
         float s0 = agg_comb(AGG, acc0.x, acc0.y), s1 = agg_comb(AGG, acc1.x, acc1.y);
