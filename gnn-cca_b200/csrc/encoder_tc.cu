@@ -341,11 +341,13 @@ int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaS
   }
   if (!enc::make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
   auto kern = enc::node_encoder_tf32_kernel<H>;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};      // the attribute is per device: one flag per device ordinal
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+  if (dev < 0 || !configured[dev]) {
     int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
     if (rc) return rc;
-    configured = true;
+    if (dev >= 0) configured[dev] = true;
   }
   kern<<<grid, enc::NUM_THREADS, smem, st>>>(xm, mw, p);
   return check_launch();
