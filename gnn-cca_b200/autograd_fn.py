@@ -46,7 +46,7 @@ class _Seg:
 
 class _MPNFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, model, x, edge_index, edge_attr, plan, *params):
+    def forward(ctx, model, x, edge_index, edge_attr, plan, trusted, *params):
         from . import engine
         lib = _lib.load()
         engine.check_supported(model)
@@ -56,6 +56,8 @@ class _MPNFunction(torch.autograd.Function):
         N, E = int(x.size(0)), int(edge_index.size(1))
         if plan is None:
             plan = GraphPlan(edge_index, N)
+        if trusted and not plan.resolved:
+            plan._resolved = True          # build_graph_batch output: source-major and in range by construction, nothing to read back
         plan.resolve()
         enc_n, enc_e = model.encoder.node_mlp, model.encoder.edge_mlp
         if len(enc_e.layer_specs) != 1:
@@ -71,13 +73,17 @@ class _MPNFunction(torch.autograd.Function):
         if bn is not None and bn.momentum is None:
             raise NotImplementedError("BatchNorm1d(momentum=None) (cumulative average) has no kernel")
 
-        # transposed CSR (edges grouped by target) for the gQ reduction of the backward
-        key, other = plan.dst.clone(), plan.src.clone()
-        tperm = torch.empty(E, dtype=torch.int32, device=dev)
-        colptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
-        nbytes = int(lib.gnncca_csr_sort_workspace_bytes(N, E))
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        _lib.check(lib.gnncca_csr_sort(N, E, P(key), P(other), P(tperm), P(colptr), P(ws), nbytes, _stream()), "csr_sort(dst)")
+        # transposed CSR (edges grouped by target) for the gQ reduction of the backward; kept with the plan, which the
+        # module caches on the batch object while edge_index is unchanged
+        if getattr(plan, "tperm", None) is None:
+            key, other = plan.dst.clone(), plan.src.clone()
+            tperm = torch.empty(E, dtype=torch.int32, device=dev)
+            colptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+            nbytes = int(lib.gnncca_csr_sort_workspace_bytes(N, E))
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            _lib.check(lib.gnncca_csr_sort(N, E, P(key), P(other), P(tperm), P(colptr), P(ws), nbytes, _stream()), "csr_sort(dst)")
+            plan.tperm, plan.colptr = tperm, colptr
+        tperm, colptr = plan.tperm, plan.colptr
 
         # node encoder, layer by layer (FP32: the training path keeps every activation)
         acts = [x.contiguous()]
@@ -127,8 +133,9 @@ class _MPNFunction(torch.autograd.Function):
                 outs.append(plan.to_caller(logits))
         ctx.model, ctx.plan, ctx.sb = model, plan, sb
         ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
-                         names=[n for n, _ in model.named_parameters()])
+                         names=[n for n, _ in model.named_parameters_fast()])
         ctx.set_materialize_grads(False)
+        model.__dict__["_gnncca_train_plan"] = plan
         return tuple(outs)
 
     @staticmethod
@@ -145,8 +152,9 @@ class _MPNFunction(torch.autograd.Function):
         rn, re = bool(model.reattach_initial_nodes), bool(model.reattach_initial_edges)
         K, EIN = (2 * FN if rn else FN), (2 * FE if re else FE)
         edge_row, node_row = 2 * K + EIN, K + FE
-        named = dict(model.named_parameters())
-        grads = {n: torch.zeros_like(p) for n, p in named.items()}
+        named = dict(model.named_parameters_fast())
+        # every buffer that must start at zero comes out of ONE zero-filled allocation (one memset instead of ~30)
+        sizes = {n: p.numel() for n, p in named.items()}
         em, nm = "MPNet.edge_model.edge_mlp.fc_layers.0.", "MPNet.node_model.node_mlp.fc_layers.0."
         cls = model.classifier.edge_mlp
         cpre = "classifier.edge_mlp.fc_layers."
@@ -154,15 +162,30 @@ class _MPNFunction(torch.autograd.Function):
         cbn = cpre + "%d." % cls.layer_specs[0].bn if cls.layer_specs[0].bn is not None else None
 
         be, bnw, bp = _blocks(lib, E, _lib.BLOCKS_PER_EDGE), _blocks(lib, N, _lib.BLOCKS_PER_NODE_WARP), _blocks(lib, N, _lib.BLOCKS_NODE_PROJECT)
-        z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
-        pa_agg, pa_edge, pa_proj = z(L, bnw, FN * FE), z(L, be, FE * EIN), z(L, bp, 44 * (K + 1))
         n_cls = L - first + 1
-        pa_cls, pa_cls1 = z(n_cls, be, _lib.CLS_ACC), (z(n_cls, be, _lib.CLS_ACC) if bn_mode == "train" else None)
-        Pn, Qn, Rn = z(N, 8), z(N, 8), z(N, FN)
-        gP, gQ, gR = z(N, 8), z(N, 8), z(N, FN)
-        gze = z(E, 8)
-        ge0_acc = z(E, FE) if re else None
-        gh0_acc = z(N, FN) if rn else None
+        shapes = [("pa_agg", (L, bnw, FN * FE)), ("pa_edge", (L, be, FE * EIN)), ("pa_proj", (L, bp, 44 * (K + 1))),
+                  ("pa_cls", (n_cls, be, _lib.CLS_ACC)), ("Pn", (N, 8)), ("Qn", (N, 8)), ("Rn", (N, FN)), ("gP", (N, 8)), ("gQ", (N, 8)),
+                  ("gR", (N, FN)), ("gze", (E, 8)), ("gh_prev", (L, N, FN))]
+        if bn_mode == "train":
+            shapes.append(("pa_cls1", (n_cls, be, _lib.CLS_ACC)))
+        if re:
+            shapes.append(("ge0_acc", (E, FE)))
+        if rn:
+            shapes.append(("gh0_acc", (N, FN)))
+        shapes += [("grad/" + n, tuple(p.shape)) for n, p in named.items()]
+        offs, total = {}, 0
+        for name, shp in shapes:
+            cnt = 1
+            for d in shp:
+                cnt *= d
+            offs[name] = (total, cnt, shp)
+            total += (cnt + 3) & ~3          # 16-byte aligned pieces
+        zeros = torch.zeros(total, dtype=torch.float32, device=dev)
+        zb = {name: zeros[o:o + c].view(shp) for name, (o, c, shp) in offs.items()}
+        grads = {n: zb["grad/" + n] for n in named}
+        pa_agg, pa_edge, pa_proj, pa_cls, pa_cls1 = zb["pa_agg"], zb["pa_edge"], zb["pa_proj"], zb["pa_cls"], zb.get("pa_cls1")
+        Pn, Qn, Rn, gP, gQ, gR, gze = zb["Pn"], zb["Qn"], zb["Rn"], zb["gP"], zb["gQ"], zb["gR"], zb["gze"]
+        ge0_acc, gh0_acc, gh_prevs = zb.get("ge0_acc"), zb.get("gh0_acc"), zb["gh_prev"]
         gh, ge_next = None, None
         is_max = model.node_agg_name == "max"
         for t in range(L, 0, -1):
@@ -193,7 +216,7 @@ class _MPNFunction(torch.autograd.Function):
                                            P(hs[t]) if gh is not None else 0, P(ge_next), P(ge_cls), P(gze), P(ge_prev), P(ge0_acc),
                                            P(pa_edge[t - 1]), _stream()), "edge_bwd")
             _lib.check(lib.gnncca_pq_reduce(P(plan.rowptr), P(sv["colptr"]), P(sv["tperm"]), P(gze), N, P(gP), P(gQ), _stream()), "pq_reduce")
-            gh_prev = torch.zeros((N, FN), dtype=torch.float32, device=dev)
+            gh_prev = gh_prevs[t - 1]
             _lib.check(lib.gnncca_node_project_bwd(cfg, w, P(gP), P(gQ), P(gR), P(hs[0]), P(hs[t - 1]), N, P(gh_prev), P(gh0_acc), P(pa_proj[t - 1]),
                                                    _stream()), "node_project_bwd")
             gh, ge_next = gh_prev, ge_prev
@@ -249,13 +272,17 @@ class _MPNFunction(torch.autograd.Function):
             keep += [gz, gbp, gwp]
             gy = gx
         seg.flush()
-        out: List = [None, None, None, None, None]
+        out: List = [None, None, None, None, None, None]
         for n in sv["names"]:
             out.append(grads[n] if named[n].requires_grad else None)
         return tuple(out)
 
 
-def forward_training(model, x, edge_index, edge_attr, plan=None):
-    """``MOTMPNet.forward`` with an autograd graph: returns the list of per-step logits [E,1]."""
-    params = [p for _, p in model.named_parameters()]
-    return list(_MPNFunction.apply(model, x, edge_index, edge_attr, plan, *params))
+def forward_training(model, x, edge_index, edge_attr, plan=None, trusted=False, return_plan=False):
+    """``MOTMPNet.forward`` with an autograd graph: returns the list of per-step logits [E,1] (and, on request, the
+    CSR plan it used, which carries the transposed CSR of the backward: the module caches it on the batch object)."""
+    params = [p for _, p in model.named_parameters_fast()]
+    outs = list(_MPNFunction.apply(model, x, edge_index, edge_attr, plan, trusted, *params))
+    if return_plan:
+        return outs, model.__dict__.pop("_gnncca_train_plan", None)
+    return outs

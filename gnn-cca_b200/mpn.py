@@ -152,7 +152,7 @@ class MOTMPNet(nn.Module):
         if plan is not None and plan.last_path is not None:      # verified before: nothing left to check
             trusted, allow_fused = True, plan.last_path == "fused"
             caps = getattr(plan, "caps", caps) if allow_fused else caps
-        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for _, p in self.named_parameters_fast())
         if (not needs_grad and not self.training and caps is not None and getattr(data, "gnncca_trusted", False)
                 and getattr(data, "edge_ptr", None) is not None and graph_ptr is not None):
             # batches from build_graph_batch in eval mode: one library call, two launches, nothing read back
@@ -162,7 +162,12 @@ class MOTMPNet(nn.Module):
                 self.last_plan = engine.FAST_PLAN
                 return {'classified_edges': outs}
         if needs_grad or (self.training and self._has_batchnorm()):
-            outs = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan)
+            outs, plan = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan, trusted=trusted, return_plan=True)
+            if engine.CACHE_PLANS and plan is not None:
+                try:                    # the CSR (and its transpose for the backward) is reused while edge_index is unchanged
+                    data.gnncca_plan = plan
+                except AttributeError:
+                    pass
         else:
             edge_ptr = getattr(data, "edge_ptr", None) if getattr(data, "gnncca_trusted", False) else None
             outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps,
@@ -184,4 +189,20 @@ class MOTMPNet(nn.Module):
         return engine.forward_host(self, x, edge_index, edge_attr, out=out, graph_ptr=graph_ptr, caps=caps)
 
     def _has_batchnorm(self) -> bool:
-        return any(isinstance(m, nn.BatchNorm1d) for m in self.modules())
+        hb = self.__dict__.get("_gnncca_has_bn")
+        if hb is None:
+            hb = self.__dict__["_gnncca_has_bn"] = any(isinstance(m, nn.BatchNorm1d) for m in self.modules())
+        return hb
+
+    def named_parameters_fast(self):
+        """``list(self.named_parameters())`` without walking the module tree on every call: the (owner dict, key) of
+        each parameter slot is recorded once (the tree is fixed after construction); re-assigned parameters are seen."""
+        slots = self.__dict__.get("_gnncca_param_slots")
+        if slots is None:
+            slots = []
+            for mname, m in self.named_modules():
+                for k, t in m._parameters.items():
+                    if t is not None:
+                        slots.append(((mname + "." if mname else "") + k, m._parameters, k))
+            self.__dict__["_gnncca_param_slots"] = slots
+        return [(n, d[k]) for n, d, k in slots]
