@@ -270,7 +270,6 @@ def run_training(args):
     torch.manual_seed(0)
     model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50").to(dev).train()
     opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4)
-    crit = torch.nn.BCEWithLogitsLoss()
     batches = [gnncca.build_graph_batch(**syn.make_detections(wl["cams"], wl["dets"], wl["frames"], seed=wl["seed"] + 100 * rank + 7919 * s,
                                                                device=dev, max_dist=wl["max_dist"])) for s in range(8)]
     N, E = batches[0].num_nodes, batches[0].num_edges
@@ -279,7 +278,7 @@ def run_training(args):
     def step(b):
         opt.zero_grad(set_to_none=True)
         out = model(b)["classified_edges"]
-        loss = sum(crit(r.view(-1), b.edge_labels) for r in out)
+        loss = gnncca.loss_stats(out, b.edge_labels).loss      # train.py:80-97 in one pass (gnncca_bce_stats_fwd/bwd)
         loss.backward()
         opt.step()
         return loss
@@ -340,7 +339,7 @@ def run_training(args):
                            "optimizer": "SGD lr 1e-3 momentum 0.9 wd 1e-4", "parallelism": "graph-sharded x%d, no gradient all-reduce (independent replicas)" % world},
                 "clocks": sampler.result(), "gpu_launches": launches,
                 "e2e": {"value": world * E * e2e_steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps,
-                        "api": "MOTMPNet.forward + BCEWithLogitsLoss + backward + SGD.step on a batch copied from pinned host memory"},
+                        "api": "MOTMPNet.forward + loss_stats (summed BCE) + backward + SGD.step on a batch copied from pinned host memory"},
                 "roofline": {"bound": "hbm", "kernel": "whole training step (launch-bound at this size)", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None, "algorithmic_bytes_per_launch": train_bytes}}
         if world == 1 and not args.no_cpu_baseline:

@@ -10,5 +10,6 @@ from .graph import Batch, build_graph_batch, column_normalize
 from . import _lib
 from .engine import forward_host, StageTimer
 from . import multigpu
+from .loss import compute_loss_acc, loss_stats, LossStats
 
-__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer"]
+__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer", "compute_loss_acc", "loss_stats", "LossStats"]

@@ -281,6 +281,24 @@ typedef struct {
 int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_segs, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Loss and statistics of the classified steps: train.py:51-133 compute_loss_acc, criteria of
+ * main_training.py:258-268 (BCE, BCE_weighted: scalar pos_weight; Focal: libs/utils.py:264-293).
+ * host_logits: n_steps (<= 8) device pointers to [n_edges] fp32 logits; labels [n_edges] fp32 in {0, 1}.
+ * Per sample l = BCEWithLogits(x, y; pos_weight); pl = l, or balance * (1 - exp(-l))^focus * l when focal != 0.
+ * out ([5 n_steps + 4] doubles): [mean l][mean_{y=1} pl][mean_{y=0} pl][mean_{y=1} sigmoid][mean_{y=0} sigmoid] per
+ * step, then n1, n0 and the number of correct last-step predictions (sigmoid >= 0.5) with y = 1 / y = 0.  A class
+ * without samples gives NaN means (as torch.mean of an empty tensor).  probs ([n_steps][n_edges], or NULL) receives
+ * the sigmoids (train.py:100-103).  partials: [gnncca_loss_blocks(n_edges)][5 n_steps + 4] doubles of scratch.
+ * Fixed-order reduction, bit-reproducible.  Two launches. */
+int32_t gnncca_loss_blocks(int64_t n_edges);
+int gnncca_bce_stats_fwd(const float* const* host_logits, int32_t n_steps, const float* labels, int64_t n_edges, float pos_weight,
+                         int32_t focal, float focus, float balance, float* probs, double* partials, double* out, void* stream);
+/* host_grads[s][i] = upstream[s] / n_edges * d l / d x_s,i: gradient of sum_s upstream[s] * mean_i l(x_s,i); upstream is a
+ * DEVICE array of n_steps doubles (d loss / d out[s] from gnncca_bce_stats_fwd).  One launch. */
+int gnncca_bce_stats_bwd(const float* const* host_logits, float* const* host_grads, int32_t n_steps, const float* labels,
+                         int64_t n_edges, float pos_weight, const double* upstream, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Graph + edge-attribute construction, train.py:257-259,286-361,450.
  * ---------------------------------------------------------------------------------------------- */
 

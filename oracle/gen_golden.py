@@ -288,12 +288,70 @@ def gen_graph():
     save_graph_case("synthetic_terrace_full", [to_df(f) for f in full], [50.83] * 2, seed=16)
 
 
+# ----------------------------------------------------------------------------------------------
+# loss + statistics: the reference's own compute_loss_acc / FocalLoss_binary source, executed as is
+# ----------------------------------------------------------------------------------------------
+def gen_loss():
+    """``loss_<case>.npz``: ``compute_loss_acc`` (train.py:51-208) run UNMODIFIED (its source text compiled with the
+    names train.py imports: torch, np, F) under the criteria of main_training.py:258-268, with ``FocalLoss_binary``
+    taken the same way from libs/utils.py:264-293; also d loss / d logits by torch autograd."""
+    import types
+    import torch.nn as nn
+    import torch.nn.functional as F
+
+    ns = {"torch": torch, "np": np, "F": F, "nn": nn}
+    fn = ref_shim.reference_def("train.py", "compute_loss_acc", ns)
+    focal_cls = ref_shim.reference_def("libs/utils.py", "FocalLoss_binary", {"torch": torch, "nn": nn})
+    cases = [  # name, criterion name, pos_weight, mode, E, k, positive rate, logit scale, seed
+        ("bce_train", "BCE", None, "train", 777, 3, 0.2, 3.0, 1),
+        ("bce_weighted_train", "BCE_weighted", 4.7, "train", 1200, 4, 0.15, 4.0, 2),
+        ("focal_train", "Focal", None, "train", 513, 2, 0.3, 2.0, 3),
+        ("validate", "", None, "validate", 2050, 3, 0.25, 6.0, 4),
+        ("no_positives", "BCE", None, "train", 100, 2, 0.0, 3.0, 5),
+        ("no_negatives", "", None, "validate", 64, 1, 1.0, 3.0, 6),
+        ("all_wrong", "BCE", None, "train", 90, 2, 0.5, 3.0, 7),
+        ("extreme_logits", "BCE_weighted", 2.5, "train", 300, 3, 0.4, 60.0, 8),
+    ]
+    for name, crit, pw, mode, E, k, rate, scale, seed in cases:
+        g = torch.Generator().manual_seed(seed)
+        labels = (torch.rand(E, generator=g) < rate).float()
+        logits = [(torch.randn(E, 1, generator=g) * scale + (labels.view(-1, 1) * 2 - 1) * (0.5 + 0.5 * s)).requires_grad_(True)
+                  for s in range(k)]
+        if name == "all_wrong":      # every last-step prediction wrong: the `sum_successes == 0` branches of train.py:108,116,124
+            with torch.no_grad():
+                logits[-1].copy_(-(labels.view(-1, 1) * 2 - 1) * 2.0)
+        if crit == "Focal":
+            c, cn = focal_cls(reduction="mean"), focal_cls(reduction="none")
+        elif crit == "BCE_weighted":
+            c, cn = nn.BCEWithLogitsLoss(reduction="mean", pos_weight=torch.tensor(pw)), nn.BCEWithLogitsLoss(reduction="none", pos_weight=torch.tensor(pw))
+        elif crit == "BCE":
+            c, cn = nn.BCEWithLogitsLoss(reduction="mean"), nn.BCEWithLogitsLoss(reduction="none")
+        else:
+            c, cn = "", ""
+        batch = types.SimpleNamespace(edge_labels=labels)
+        loss, p1, p0, pa, l1, l0, probs = fn({"classified_edges": logits}, batch, c, cn, mode)
+        grads = torch.autograd.grad(loss, logits)
+        out = dict(labels=labels.numpy(), k=np.int64(k), criterion=np.asarray(crit), mode=np.asarray(mode),
+                   pos_weight=np.float64(-1.0 if pw is None else pw), loss=loss.detach().numpy(), loss_class1=l1.detach().numpy(),
+                   loss_class0=l0.detach().numpy(), precision_class1=np.float64(p1[0]), precision_class0=np.float64(p0[0]),
+                   precision_all=np.float64(pa[0]))
+        for s in range(k):
+            out["logits%d" % s] = logits[s].detach().numpy()
+            out["probs%d" % s] = probs[s].detach().numpy()
+            out["grad%d" % s] = grads[s].numpy()
+        np.savez_compressed(os.path.join(GOLDEN, "loss_%s.npz" % name), **out)
+        print("loss_%s: E=%d k=%d loss=%.6f p1=%.3f p0=%.3f p=%.3f" % (name, E, k, float(loss), p1[0], p0[0], pa[0]))
+
+
 def main():
     if not ref_shim.reference_available():
         sys.exit("needs /root/reference (build container only)")
     os.makedirs(GOLDEN, exist_ok=True)
+    if "--loss-only" in sys.argv:
+        return gen_loss()
     gen_mpn()
     gen_graph()
+    gen_loss()
 
 
 if __name__ == "__main__":

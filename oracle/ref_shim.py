@@ -50,6 +50,7 @@ def _install_stubs() -> None:
             mpl = types.ModuleType("matplotlib")
             plt = types.ModuleType("matplotlib.pyplot")
             mpl.pyplot = plt
+            mpl.use = lambda *a, **k: None
             sys.modules["matplotlib"] = mpl
             sys.modules["matplotlib.pyplot"] = plt
 
@@ -67,3 +68,23 @@ def import_reference(module: str):
         if mod is not None and not str(getattr(mod, "__file__", "")).startswith(REFERENCE_ROOT):
             del sys.modules[name]
     return importlib.import_module(module)
+
+
+def reference_def(rel_path: str, name: str, namespace: dict):
+    """Compile ONE top-level ``def``/``class`` of a reference file, unmodified, into ``namespace`` and return it.
+
+    For modules whose import needs packages this image lacks (train.py: cv2, skimage, torchreid, networkx ...): the
+    function's own source text is taken from the file with ``ast`` (exact line range) and executed as is."""
+    import ast
+
+    if not reference_available():
+        raise RuntimeError("reference tree not present (expected on the GPU box); use the oracle restatement")
+    path = os.path.join(REFERENCE_ROOT, rel_path)
+    with open(path, "r") as f:
+        text = f.read()
+    for node in ast.parse(text).body:
+        if isinstance(node, (ast.FunctionDef, ast.ClassDef)) and node.name == name:
+            lines = text.splitlines()[node.lineno - 1:node.end_lineno]
+            exec(compile("\n" * (node.lineno - 1) + "\n".join(lines), path, "exec"), namespace)
+            return namespace[name]
+    raise KeyError("%s not found in %s" % (name, rel_path))

@@ -115,3 +115,24 @@ def test_oracle_matches_live_reference_when_present():
     assert len(ref) == len(got) == 3
     for a, b in zip(ref, got):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("case", golden_cases("loss_"))
+def test_loss_oracle_matches_the_reference_function(case):
+    """oracle/loss_oracle.py against compute_loss_acc (train.py:51-208) executed unmodified (oracle/gen_golden.py gen_loss)."""
+    from oracle import loss_oracle
+
+    z = load_golden("loss_" + case)
+    k = int(z["k"])
+    logits = [torch.from_numpy(z["logits%d" % s]).requires_grad_(True) for s in range(k)]
+    pw = None if float(z["pos_weight"]) < 0 else float(z["pos_weight"])
+    r = loss_oracle.compute_loss_acc(logits, torch.from_numpy(z["labels"]), str(z["criterion"]) or "BCE", pw, str(z["mode"]))
+    torch.testing.assert_close(r["loss"].detach(), torch.from_numpy(z["loss"]), rtol=1e-6, atol=1e-7)
+    for name in ("loss_class1", "loss_class0"):
+        torch.testing.assert_close(r[name].detach(), torch.from_numpy(z[name]), rtol=1e-6, atol=1e-7, equal_nan=True)
+    for name in ("precision_class1", "precision_class0", "precision_all"):
+        assert r[name] == float(z[name]), name                                     # integer counts: exact
+    grads = torch.autograd.grad(r["loss"], logits)
+    for s in range(k):
+        assert np.array_equal(r["probs"][s].numpy(), z["probs%d" % s].reshape(-1))
+        torch.testing.assert_close(grads[s], torch.from_numpy(z["grad%d" % s]), rtol=1e-6, atol=1e-9)
