@@ -299,6 +299,21 @@ int gnncca_bce_stats_bwd(const float* const* host_logits, float* const* host_gra
                          int64_t n_edges, float pos_weight, const double* upstream, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Edge decisions, pruning and clusters per frame graph: inference.py:286-345 with utils.py:295-317
+ * (compute_SCC_and_Clusters) and utils.py:387-404 (remove_edges_single_direction).  SURVEY 8f rank 2.
+ * decision: kind 0 = fp32 logits [n_edges] (active iff sigmoid(x) >= 0.5), 1 = fp32 labels (active iff == 1),
+ * 2 = int64 flags (active iff == 1).  Frames: nodes graph_ptr[g]..graph_ptr[g+1] (<= 64 per frame), edges
+ * edge_ptr[g]..edge_ptr[g+1] of the int64 edge_index [2, n_edges], both endpoints inside the frame.
+ * prune != 0: an active edge (u, v) stays active only if (v, u) is active.  pred ([n_edges] int64, or NULL): the
+ * decisions after pruning.  ids [n_nodes] int64: cluster (strongly connected component of the active edges; isolated
+ * nodes are their own cluster) of every node, numbered densely over the batch in order of each cluster's smallest
+ * node; n_clusters[0]: their number.  scratch: n_nodes + n_graphs int32.  flags (int32[2], zeroed by the caller):
+ * [0] an edge leaves its frame / inconsistent offsets, [1] a frame has more than 64 nodes.  Two launches; exact. */
+int gnncca_frame_clusters(const void* decision, int32_t kind, const int64_t* edge_index, int64_t n_edges, const int64_t* graph_ptr,
+                          const int64_t* edge_ptr, int64_t n_graphs, int64_t n_nodes, int32_t prune, int64_t* pred, int64_t* ids,
+                          int64_t* n_clusters, int32_t* scratch, int32_t* flags, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Graph + edge-attribute construction, train.py:257-259,286-361,450.
  * ---------------------------------------------------------------------------------------------- */
 

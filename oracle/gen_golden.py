@@ -343,15 +343,66 @@ def gen_loss():
         print("loss_%s: E=%d k=%d loss=%.6f p1=%.3f p0=%.3f p=%.3f" % (name, E, k, float(loss), p1[0], p0[0], pa[0]))
 
 
+# ----------------------------------------------------------------------------------------------
+# edge decisions + pruning + SCC clusters: the reference's utils functions, executed as is with networkx
+# ----------------------------------------------------------------------------------------------
+def gen_post():
+    """``post_<case>.npz``: inference.py:286-312 replayed with the UNMODIFIED ``remove_edges_single_direction`` and
+    ``compute_SCC_and_Clusters`` (libs/utils.py:387-404, 295-317; source text compiled with np / nx / torch) on ragged
+    cross-camera frame batches with noisy logits (asymmetric decisions, chains, isolated nodes)."""
+    import networkx as nx
+
+    ns = {"np": np, "nx": nx, "torch": torch}
+    prune_fn = ref_shim.reference_def("libs/utils.py", "remove_edges_single_direction", ns)
+    scc_fn = ref_shim.reference_def("libs/utils.py", "compute_SCC_and_Clusters", ns)
+    cases = [("small", 5, 3, 4, 1.0, 21), ("noisy", 12, 4, 6, 3.0, 22), ("wide", 6, 4, 10, 2.0, 23), ("confident", 8, 3, 5, 0.2, 24),
+             ("all_inactive", 4, 3, 4, -1.0, 25)]
+    for name, n_frames, n_cams, max_ids, noise, seed in cases:
+        rng = np.random.default_rng(seed)
+        frames = ragged_frames(rng, n_frames, n_cams, max_ids)
+        src, dst, lab, ptr, eptr = [], [], [], [0], [0]
+        for f in frames:                                  # cross-camera edges both ways, camera-ascending like train.py:286-306
+            n0, n = ptr[-1], len(f["id"])
+            for a in range(n):
+                for b in range(n):
+                    if f["id_cam"][a] != f["id_cam"][b]:
+                        src.append(n0 + a); dst.append(n0 + b); lab.append(float(f["id"][a] == f["id"][b]))
+            ptr.append(n0 + n); eptr.append(len(src))
+        edge_list = np.asarray([src, dst], np.int64)
+        labels = np.asarray(lab, np.float32)
+        if noise < 0:
+            logits = -np.abs(rng.normal(0, 1, size=len(lab))).astype(np.float32) - 0.1
+        else:
+            logits = ((labels * 2 - 1) * 2.0 + rng.normal(0, noise, size=len(lab))).astype(np.float32)
+        n_nodes = ptr[-1]
+        preds = torch.from_numpy(logits)
+        predictions = (torch.nn.Sigmoid()(preds) >= 0.5) * 1                                     # inference.py:289-291
+        act = [(edge_list[0][pos], edge_list[1][pos]) for pos, p in enumerate(predictions) if p == 1]
+        ids_raw, n_raw = scc_fn(nx.DiGraph(act), n_nodes)                                        # inference.py:300-302
+        pruned, act_p = prune_fn(act, predictions, edge_list)                                    # inference.py:307-308
+        ids_p, n_p = scc_fn(nx.DiGraph(act_p), n_nodes)
+        gt = [(edge_list[0][pos], edge_list[1][pos]) for pos, p in enumerate(labels) if p == 1]  # inference.py:297-299
+        ids_gt, n_gt = scc_fn(nx.DiGraph(gt), n_nodes)
+        np.savez_compressed(os.path.join(GOLDEN, "post_%s.npz" % name), edge_index=edge_list, labels=labels, logits=logits,
+                            ptr=np.asarray(ptr, np.int64), edge_ptr=np.asarray(eptr, np.int64), predictions=predictions.numpy().astype(np.int64),
+                            ids_raw=ids_raw.astype(np.int64), n_raw=np.int64(n_raw), pruned=pruned.numpy().astype(np.int64),
+                            ids_pruned=ids_p.astype(np.int64), n_pruned=np.int64(n_p), ids_gt=ids_gt.astype(np.int64), n_gt=np.int64(n_gt))
+        print("post_%s: N=%d E=%d active=%d pruned=%d clusters raw/pruned/gt=%d/%d/%d" % (
+            name, n_nodes, len(lab), int(predictions.sum()), int(pruned.sum()), n_raw, n_p, n_gt))
+
+
 def main():
     if not ref_shim.reference_available():
         sys.exit("needs /root/reference (build container only)")
     os.makedirs(GOLDEN, exist_ok=True)
     if "--loss-only" in sys.argv:
         return gen_loss()
+    if "--post-only" in sys.argv:
+        return gen_post()
     gen_mpn()
     gen_graph()
     gen_loss()
+    gen_post()
 
 
 if __name__ == "__main__":

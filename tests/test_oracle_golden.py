@@ -136,3 +136,23 @@ def test_loss_oracle_matches_the_reference_function(case):
     for s in range(k):
         assert np.array_equal(r["probs"][s].numpy(), z["probs%d" % s].reshape(-1))
         torch.testing.assert_close(grads[s], torch.from_numpy(z["grad%d" % s]), rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("case", golden_cases("post_"))
+def test_post_oracle_matches_the_reference_functions(case):
+    """oracle/post_oracle.py against utils.remove_edges_single_direction / compute_SCC_and_Clusters run unmodified with
+    networkx (oracle/gen_golden.py gen_post).  Cluster ids are compared as partitions (canonical numbering)."""
+    from oracle import post_oracle
+
+    z = load_golden("post_" + case)
+    n = int(z["ptr"][-1])
+    pred = post_oracle.decisions(z["logits"])
+    assert np.array_equal(pred, z["predictions"])
+    ids, k = post_oracle.clusters(n, pred, z["edge_index"])
+    assert k == int(z["n_raw"]) and np.array_equal(ids, post_oracle.canonical(z["ids_raw"]))
+    pruned = post_oracle.remove_edges_single_direction(pred, z["edge_index"])
+    assert np.array_equal(pruned, z["pruned"])
+    ids, k = post_oracle.clusters(n, pruned, z["edge_index"])
+    assert k == int(z["n_pruned"]) and np.array_equal(ids, post_oracle.canonical(z["ids_pruned"]))
+    ids, k = post_oracle.clusters(n, (z["labels"] == 1).astype(np.int64), z["edge_index"])
+    assert k == int(z["n_gt"]) and np.array_equal(ids, post_oracle.canonical(z["ids_gt"]))
