@@ -440,7 +440,8 @@ def main():
         _lib = gnncca._lib
         fp = engine.fast_path(model)
         stage_avg = {}
-        if fp is not None and args.math == "tf32":
+        small_frames = all(engine.frame_capacity(model, N, E, b.num_graphs, b.gnncca_caps) is not None for b in batches)
+        if fp is not None and args.math == "tf32" and small_frames:
             stream = torch.cuda.current_stream().cuda_stream
             l1, l2 = model.encoder.node_mlp.linear(0), model.encoder.node_mlp.linear(1)
             le = model.encoder.edge_mlp.linear(0)

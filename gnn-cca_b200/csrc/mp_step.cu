@@ -10,10 +10,14 @@
 //   logit[i] = w_c2 . relu(W_c1 e'[i] + b_c1) + b_c2
 // and nothing of width 70 / 38 is ever materialised: 64 B/edge of HBM traffic instead of ~2.3 KB.
 //
-// Mapping.  Edges are source-sorted.  A CTA owns tiles of 256 consecutive edges (persistent, tiles
-// strided over the grid).  Phase A is thread-per-edge (gather, edge update, classifier, write e' once,
-// stage e' in shared memory).  Phase B is lane-per-feature: warp w walks edges [32w, 32w+32) of the tile
-// and keeps the running aggregate of the current source segment in a register.  Segments are closed
+// Mapping.  Edges are source-sorted.  A CTA of 256 threads owns tiles of 512 consecutive edges (persistent, tiles
+// strided over the grid); edges travel as PAIRS (2p, 2p+1 of the global numbering) so that the arithmetic is packed
+// FFMA2 with the weights as broadcast scalars.  Phase A is thread-per-pair (gather P/Q rows, edge update, classifier,
+// e' written once and staged in shared memory as [pair][k][2]); the raw inputs of the NEXT tile are requested before
+// phase B starts, so their latency hides behind it.  Phase B is lane-per-feature: warp w walks edges [64w, 64w+64) of
+// the tile pair by pair (3 LDS.128 + 6 FFMA2 + 2 FMNMX + 1 FADD2 per pair) with the running aggregate of the current
+// source segment in registers (even / odd edges separately, folded at the end).  Segment boundaries come from one
+// ballot over the staged source ids, not from rowptr.  Segments are closed
 //   - inside a warp chunk: written directly;
 //   - across warps of the tile: chained in warp order through shared memory;
 //   - across tiles: each tile publishes its partial, bumps an integer counter keyed by the segment's first
@@ -24,8 +28,10 @@
 
 namespace gnncca {
 
-constexpr int TILE = 256;     // edges per tile == threads per CTA
-constexpr int NWARP = TILE / 32;
+constexpr int TILE = 512;     // edges per tile
+constexpr int THREADS = 256;  // one thread per edge pair
+constexpr int NWARP = THREADS / 32;
+constexpr int CHUNK = TILE / NWARP;   // edges per warp in phase B
 constexpr int FN = 32;        // latent node width handled by lane-per-feature phase B
 
 struct StepParams {
@@ -38,18 +44,46 @@ struct StepParams {
   int num_tiles;
   float* tile_part;      // [num_tiles][2][FN]  slot 0: continuation piece (started in an earlier tile), slot 1: open tail
   int32_t* counters;     // [num_tiles] arrival counters, zeroed by the host entry before the launch
-  int phase;             // position of local edge 0 inside a 256-edge tile of the GLOBAL edge numbering (edge-partitioned graphs)
+  int phase;             // position of local edge 0 inside a tile of the GLOBAL edge numbering (edge-partitioned graphs)
   const int32_t* guard;  // optional CSR flags (gnncca_csr_from_edge_index): the kernel is a no-op when any is set
 };
 
-__device__ __forceinline__ float agg_init(int agg) { return agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f; }
-__device__ __forceinline__ float agg_comb(int agg, float a, float b) { return agg == GNNCCA_AGG_MAX ? fmaxf(a, b) : a + b; }
-__device__ __forceinline__ void finalize_node(const StepParams& p, int node, float v, int deg, int lane) {
-  if (p.agg == GNNCCA_AGG_MEAN) v = v / (float)max(deg, 1);   // scatter_mean: sum / clamp(count, 1)
+namespace pk {   // packed fp32 pairs (FFMA2 / FADD2); a scalar operand is written bc(w) and costs no register
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t ra, rb, rc, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  uint64_t ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  float2 d;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+  return d;
+}
+__device__ __forceinline__ float2 bc(float w) { return make_float2(w, w); }
+__device__ __forceinline__ float2 relu2(float2 v) { return make_float2(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)); }
+}  // namespace pk
+
+__device__ __forceinline__ void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
+template <bool IS_MAX> __device__ __forceinline__ float comb(float a, float b) { return IS_MAX ? fmaxf(a, b) : a + b; }
+template <bool IS_MAX> __device__ __forceinline__ float2 comb2(float2 a, float2 b) {
+  return IS_MAX ? make_float2(fmaxf(a.x, b.x), fmaxf(a.y, b.y)) : pk::fadd2(a, b);
+}
+__device__ __forceinline__ void finalize_node(const StepParams& p, int node, float v, int lane) {
+  if (p.agg == GNNCCA_AGG_MEAN) v = v / (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);   // scatter_mean: sum / clamp(count, 1)
   p.h_out[(int64_t)node * FN + lane] = v;
 }
 
 // Cross-tile combination.  kind 0 = this tile continues a segment begun earlier, kind 1 = this tile opens one.
+template <bool IS_MAX>
 __device__ __forceinline__ void publish_partial(const StepParams& p, int tile, int kind, int node, float total, int lane) {
   const int rs = p.rowptr[node], re = p.rowptr[node + 1];
   const int t0 = (rs + p.phase) / TILE, t1 = (re - 1 + p.phase) / TILE;
@@ -62,151 +96,278 @@ __device__ __forceinline__ void publish_partial(const StepParams& p, int tile, i
   if (old == t1 - t0) {  // every tile of [t0, t1] has published: fold in tile order
     __threadfence();
     float tot = ld_cg_f(p.tile_part + ((int64_t)t0 * 2 + 1) * FN + lane);
-    for (int t = t0 + 1; t <= t1; ++t) tot = agg_comb(p.agg, tot, ld_cg_f(p.tile_part + ((int64_t)t * 2) * FN + lane));
-    finalize_node(p, node, tot, re - rs, lane);
+    for (int t = t0 + 1; t <= t1; ++t) tot = comb<IS_MAX>(tot, ld_cg_f(p.tile_part + ((int64_t)t * 2) * FN + lane));
+    finalize_node(p, node, tot, lane);
   }
 }
 
-template <int FE, int HC, bool REATT_E>
-__global__ void __launch_bounds__(TILE, 3) mp_step_fwd_kernel(const StepParams p) {
+template <int FE, bool REATT_E>
+struct RawPair {       // what phase A reads for one edge pair, requested one tile ahead
+  int sa, sb, da, db;
+  float2 ea[FE / 2], eb[FE / 2];
+  float2 xa[REATT_E ? FE / 2 : 1], xb[REATT_E ? FE / 2 : 1];
+};
+
+template <int FE, bool REATT_E>
+__device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPair<FE, REATT_E>& r) {
+  const bool va = i0 >= 0 && i0 < p.n_edges, vb = i0 + 1 >= 0 && i0 + 1 < p.n_edges;
+  r.sa = r.sb = r.da = r.db = -1;
+  if (va) {
+    r.sa = ld_stream_i32(p.src + i0); r.da = ld_stream_i32(p.dst + i0);
+#pragma unroll
+    for (int k = 0; k < FE / 2; ++k) r.ea[k] = ld_stream_f2(p.e_in + i0 * FE + 2 * k);
+    if (REATT_E) {
+#pragma unroll
+      for (int k = 0; k < FE / 2; ++k) r.xa[k] = ld_stream_f2(p.e0 + i0 * FE + 2 * k);
+    }
+  }
+  if (vb) {
+    r.sb = ld_stream_i32(p.src + i0 + 1); r.db = ld_stream_i32(p.dst + i0 + 1);
+#pragma unroll
+    for (int k = 0; k < FE / 2; ++k) r.eb[k] = ld_stream_f2(p.e_in + (i0 + 1) * FE + 2 * k);
+    if (REATT_E) {
+#pragma unroll
+      for (int k = 0; k < FE / 2; ++k) r.xb[k] = ld_stream_f2(p.e0 + (i0 + 1) * FE + 2 * k);
+    }
+  }
+}
+
+template <int FE, int HC, bool REATT_E, bool IS_MAX>
+__global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 1;
-  __shared__ float s_wee[FE][EIN];
+  static_assert(FE % 2 == 0 && (FE * EIN) % 4 == 0, "weights are read as float4");
+  __shared__ __align__(16) float s_wee[FE * EIN];
   __shared__ float s_wne[FE][FN];
-  __shared__ float s_c1[HCS][FE], s_b1[HCS], s_c2[HCS], s_b2;
-  __shared__ __align__(16) float s_e[TILE][FE];
-  __shared__ int s_src[TILE];
-  __shared__ float s_C[NWARP][FN], s_O[NWARP][FN];
-  __shared__ int s_Cnode[NWARP], s_Cclosed[NWARP], s_Onode[NWARP];
+  __shared__ __align__(16) float s_c1[HCS * FE];
+  __shared__ float s_b1[HCS], s_c2[HCS], s_b2;
+  __shared__ __align__(16) float s_e[TILE / 2][2 * FE];      // [pair][k][2]
+  __shared__ __align__(8) int s_src[TILE];
+  // pieces of segments that cross warp chunks; double-buffered by tile parity so that ONE barrier per tile is enough
+  __shared__ float s_C[2][NWARP][FN], s_O[2][NWARP][FN];
+  __shared__ int s_Cnode[2][NWARP], s_Cclosed[2][NWARP], s_Onode[2][NWARP];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = p.nf * FN;
   if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;   // CSR not valid (unsorted / out of range): uniform exit
+  const bool classify = HC > 0 && p.logits != nullptr;
   {  // stage weights (read from the live parameters at every launch)
     const int edge_row = 2 * K + EIN, node_row = K + FE;
-    for (int idx = tid; idx < FE * EIN; idx += TILE) s_wee[idx / EIN][idx % EIN] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
-    for (int idx = tid; idx < FE * FN; idx += TILE) s_wne[idx / FN][idx % FN] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
-    if (HC > 0 && p.logits != nullptr) {
-      for (int c = tid; c < HC; c += TILE) {
+    for (int idx = tid; idx < FE * EIN; idx += THREADS) s_wee[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
+    for (int idx = tid; idx < FE * FN; idx += THREADS) s_wne[idx / FN][idx % FN] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
+    if (classify) {
+      for (int c = tid; c < HC; c += THREADS) {
         float scale = 1.f, shift = 0.f;
         if (p.w.bn_weight) {  // BatchNorm1d (eval) folded into the hidden layer
           scale = p.w.bn_weight[c] / sqrtf(p.w.bn_var[c] + p.w.bn_eps);
           shift = p.w.bn_bias[c] - p.w.bn_mean[c] * scale;
         }
-        for (int k = 0; k < FE; ++k) s_c1[c][k] = p.w.w_c1[c * FE + k] * scale;
+        for (int k = 0; k < FE; ++k) s_c1[c * FE + k] = p.w.w_c1[c * FE + k] * scale;
         s_b1[c] = p.w.b_c1[c] * scale + shift;
         s_c2[c] = p.w.w_c2[c];
       }
       if (tid == 0) s_b2 = p.w.b_c2[0];
     }
   }
+  RawPair<FE, REATT_E> cur;
+  load_raw<FE, REATT_E>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
   __syncthreads();
   float wne[FE];
 #pragma unroll
   for (int k = 0; k < FE; ++k) wne[k] = s_wne[k][lane];
 
-  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+  int buf = 0;
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, buf ^= 1) {
     const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
-    const int64_t i = base + tid;
-    // ------------------------------ phase A: thread per edge ------------------------------
-    if (i >= 0 && i < p.n_edges) {
-      const int s = ld_stream_i32(p.src + i), d = ld_stream_i32(p.dst + i);
-      float ein[EIN];
+    const int64_t i0 = base + 2 * tid;
+    const bool va = cur.sa >= 0, vb = cur.sb >= 0;
+    // A warp stages and then reduces the SAME 64 edges, so phases A and B need no CTA barrier between them; the sources of
+    // the edges just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
+    const int lo = (int)max((int64_t)0, -base), hi = (int)min((int64_t)TILE, p.n_edges - base);   // valid tile-local edge range
+    const int c0 = warp * CHUNK;
+    const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
+    int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
+    if (p.h_out != nullptr && a < b) {
+      if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
+      if (lane == 1 && base + b < p.n_edges) nb = p.src[base + b];
+    }
+    // ------------------------------ phase A: thread per edge pair ------------------------------
+    {
+      float2 ein[EIN];
+      constexpr int OFF = REATT_E ? FE : 0;
       if (REATT_E) {  // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
 #pragma unroll
-        for (int k = 0; k < FE; k += 2) { float2 v = ld_stream_f2(p.e0 + i * FE + k); ein[k] = v.x; ein[k + 1] = v.y; }
+        for (int k = 0; k < FE / 2; ++k) {
+          ein[2 * k] = make_float2(cur.xa[k].x, cur.xb[k].x); ein[2 * k + 1] = make_float2(cur.xa[k].y, cur.xb[k].y);
+        }
       }
-      constexpr int OFF = REATT_E ? FE : 0;
 #pragma unroll
-      for (int k = 0; k < FE; k += 2) { float2 v = ld_stream_f2(p.e_in + i * FE + k); ein[OFF + k] = v.x; ein[OFF + k + 1] = v.y; }
-      const float4 p0 = *reinterpret_cast<const float4*>(p.P + (int64_t)s * 8), p1 = *reinterpret_cast<const float4*>(p.P + (int64_t)s * 8 + 4);
-      const float4 q0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)d * 8), q1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)d * 8 + 4);
-      const float pq[8] = {p0.x + q0.x, p0.y + q0.y, p0.z + q0.z, p0.w + q0.w, p1.x + q1.x, p1.y + q1.y, p1.z + q1.z, p1.w + q1.w};
-      float en[FE];
+      for (int k = 0; k < FE / 2; ++k) {
+        ein[OFF + 2 * k] = make_float2(cur.ea[k].x, cur.eb[k].x); ein[OFF + 2 * k + 1] = make_float2(cur.ea[k].y, cur.eb[k].y);
+      }
+      float2 en[8];
+      {
+        float4 pa0 = make_float4(0.f, 0.f, 0.f, 0.f), pa1 = pa0, qa0 = pa0, qa1 = pa0, pb0 = pa0, pb1 = pa0, qb0 = pa0, qb1 = pa0;
+        if (va) {
+          pa0 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sa * 8); pa1 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sa * 8 + 4);
+          qa0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.da * 8); qa1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.da * 8 + 4);
+        }
+        if (vb) {
+          pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8); pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8 + 4);
+          qb0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8); qb1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8 + 4);
+        }
+        en[0] = make_float2(pa0.x + qa0.x, pb0.x + qb0.x); en[1] = make_float2(pa0.y + qa0.y, pb0.y + qb0.y);
+        en[2] = make_float2(pa0.z + qa0.z, pb0.z + qb0.z); en[3] = make_float2(pa0.w + qa0.w, pb0.w + qb0.w);
+        en[4] = make_float2(pa1.x + qa1.x, pb1.x + qb1.x); en[5] = make_float2(pa1.y + qa1.y, pb1.y + qb1.y);
+        en[6] = make_float2(pa1.z + qa1.z, pb1.z + qb1.z); en[7] = make_float2(pa1.w + qa1.w, pb1.w + qb1.w);
+      }
 #pragma unroll
       for (int o = 0; o < FE; ++o) {
-        float acc = pq[o];
+        float2 acc = en[o];
 #pragma unroll
-        for (int k = 0; k < EIN; ++k) acc = fmaf(ein[k], s_wee[o][k], acc);
-        en[o] = fmaxf(acc, 0.f);
+        for (int k = 0; k < EIN; k += 2) {     // FE * EIN is a multiple of 4 and EIN is even: (o * EIN + k) is even
+          const float2 w2 = *reinterpret_cast<const float2*>(&s_wee[o * EIN + k]);
+          acc = pk::ffma2(ein[k], pk::bc(w2.x), acc);
+          acc = pk::ffma2(ein[k + 1], pk::bc(w2.y), acc);
+        }
+        en[o] = pk::relu2(acc);
+      }
+      if (va) {
+#pragma unroll
+        for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + i0 * FE + k, make_float2(en[k].x, en[k + 1].x));
+      }
+      if (vb) {
+#pragma unroll
+        for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + (i0 + 1) * FE + k, make_float2(en[k].y, en[k + 1].y));
       }
 #pragma unroll
-      for (int k = 0; k < FE; k += 2) {
-        st_stream_f2(p.e_out + i * FE + k, make_float2(en[k], en[k + 1]));
-        *reinterpret_cast<float2*>(&s_e[tid][k]) = make_float2(en[k], en[k + 1]);
-      }
-      s_src[tid] = s;
-      if (HC > 0 && p.logits != nullptr) {
-        float logit = s_b2;
+      for (int k = 0; k < FE; k += 2)
+        *reinterpret_cast<float4*>(&s_e[tid][2 * k]) = make_float4(en[k].x, en[k].y, en[k + 1].x, en[k + 1].y);
+      *reinterpret_cast<int2*>(&s_src[2 * tid]) = make_int2(cur.sa, cur.sb);
+      if (classify) {
+        float2 logit = pk::bc(s_b2);
 #pragma unroll
         for (int c = 0; c < HC; ++c) {
-          float hcv = s_b1[c];
+          float2 hcv = pk::bc(s_b1[c]);
 #pragma unroll
-          for (int k = 0; k < FE; ++k) hcv = fmaf(en[k], s_c1[c][k], hcv);
-          logit = fmaf(fmaxf(hcv, 0.f), s_c2[c], logit);
+          for (int k = 0; k < FE; k += 2) {
+            const float2 w2 = *reinterpret_cast<const float2*>(&s_c1[c * FE + k]);
+            hcv = pk::ffma2(en[k], pk::bc(w2.x), hcv);
+            hcv = pk::ffma2(en[k + 1], pk::bc(w2.y), hcv);
+          }
+          logit = pk::ffma2(pk::relu2(hcv), pk::bc(s_c2[c]), logit);
         }
-        st_stream_f1(p.logits + i, logit);
+        if (va) st_stream_f1(p.logits + i0, logit.x);
+        if (vb) st_stream_f1(p.logits + i0 + 1, logit.y);
       }
-    } else {
-      s_src[tid] = -1;
+    }
+    const int next_tile = tile + gridDim.x;
+    if (next_tile < p.num_tiles) load_raw<FE, REATT_E>(p, (int64_t)next_tile * TILE - p.phase + 2 * tid, cur);
+    {  // the tile after that: pull its lines into L2 now (one 128-byte line per thread), DRAM latency off the critical path
+      const int64_t far = (int64_t)next_tile + gridDim.x;
+      if (far < p.num_tiles) {
+        const int64_t fb = max(far * TILE - p.phase, (int64_t)0);
+        const float* pe = p.e_in + fb * FE + (int64_t)tid * 32;
+        if (tid < TILE * FE / 32 && pe < p.e_in + p.n_edges * FE) prefetch_l2(pe);
+        if (REATT_E) {
+          const float* p0 = p.e0 + fb * FE + (int64_t)tid * 32;
+          if (tid < TILE * FE / 32 && p0 < p.e0 + p.n_edges * FE) prefetch_l2(p0);
+        }
+        const int t2 = tid - (THREADS - 2 * TILE / 32);      // the last 32 threads: 16 lines of src, 16 of dst
+        if (t2 >= 0) {
+          const int32_t* pi = (t2 < TILE / 32 ? p.src : p.dst) + fb + (int64_t)(t2 & (TILE / 32 - 1)) * 32;
+          if (pi < (t2 < TILE / 32 ? p.src : p.dst) + p.n_edges) prefetch_l2(pi);
+        }
+      }
     }
     if (p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
-    __syncthreads();
+    __syncwarp();
     // ------------------------------ phase B: lane per feature ------------------------------
     {
-      const int64_t tile_end = min(base + TILE, p.n_edges);
-      const int64_t c0 = base + warp * 32;
-      const int64_t c1 = min(c0 + 32, tile_end);
       int Cnode = -1, Cclosed = 0, Onode = -1;
-      int64_t j0 = max(c0, (int64_t)0);
-      while (j0 < c1) {
-        const int s = s_src[j0 - base];
-        const int rs = p.rowptr[s], re = p.rowptr[s + 1];
-        const int64_t pe = min((int64_t)re, c1);
-        const float r = p.R[(int64_t)s * FN + lane];
-        float acc = agg_init(p.agg);
-        for (int64_t j = j0; j < pe; ++j) {
-          const float* ev = s_e[j - base];
-          float m = r;
+      if (a < b) {
+        const int nb_prev = __shfl_sync(0xffffffffu, nb, 0), nb_next = __shfl_sync(0xffffffffu, nb, 1);
+        const int ie = c0 + 2 * lane;
+        const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
+        const int prev = ie - 1 >= a ? s_src[max(ie - 1, 0)] : nb_prev;
+        const bool st_e = ie >= a && ie < b && (ie == a || my.x != prev);
+        const bool st_o = ie + 1 >= a && ie + 1 < b && (ie + 1 == a || my.y != my.x);
+        const unsigned bits = (st_e ? 1u : 0u) | (st_o ? 2u : 0u);
+        const unsigned m_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits << (2 * lane) : 0u);
+        const unsigned m_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits << (2 * lane - 32) : 0u);
+        unsigned long long mask = (unsigned long long)m_lo | ((unsigned long long)m_hi << 32);   // bit i: edge c0 + i opens a piece
+        const bool first_cont = nb_prev == s_src[a];
+        const bool last_cont = nb_next == s_src[b - 1];
+        while (mask) {
+          const int j0 = c0 + __ffsll((long long)mask) - 1;
+          mask &= mask - 1;
+          const int j1 = mask ? c0 + __ffsll((long long)mask) - 1 : b;
+          const int s = s_src[j0];
+          const float r = p.R[(int64_t)s * FN + lane];
+          float2 acc2 = pk::bc(IS_MAX ? -INFINITY : 0.f);
+          int j = j0;
+          if (j & 1) {
+            const float* ev = &s_e[j >> 1][1];
+            float m = r;
 #pragma unroll
-          for (int k = 0; k < FE; ++k) m = fmaf(ev[k], wne[k], m);
-          acc = agg_comb(p.agg, acc, fmaxf(m, 0.f));
+            for (int k = 0; k < FE; ++k) m = fmaf(ev[2 * k], wne[k], m);
+            acc2.y = comb<IS_MAX>(acc2.y, fmaxf(m, 0.f));
+            ++j;
+          }
+#pragma unroll 2
+          for (; j + 1 < j1; j += 2) {
+            const float4* ev = reinterpret_cast<const float4*>(&s_e[j >> 1][0]);
+            float2 m = pk::bc(r);
+#pragma unroll
+            for (int k = 0; k < FE / 2; ++k) {
+              const float4 v = ev[k];
+              m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
+              m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
+            }
+            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+          }
+          if (j < j1) {
+            const float* ev = &s_e[j >> 1][0];
+            float m = r;
+#pragma unroll
+            for (int k = 0; k < FE; ++k) m = fmaf(ev[2 * k], wne[k], m);
+            acc2.x = comb<IS_MAX>(acc2.x, fmaxf(m, 0.f));
+          }
+          const float acc = comb<IS_MAX>(acc2.x, acc2.y);
+          const bool starts = !(j0 == a && first_cont), ends = !(j1 == b && last_cont);
+          if (starts && ends) finalize_node(p, s, acc, lane);
+          else if (!starts) { s_C[buf][warp][lane] = acc; Cnode = s; Cclosed = ends ? 1 : 0; }
+          else { s_O[buf][warp][lane] = acc; Onode = s; }
         }
-        const bool starts = rs >= c0, ends = re <= c1;
-        if (starts && ends) finalize_node(p, s, acc, re - rs, lane);
-        else if (!starts) { s_C[warp][lane] = acc; Cnode = s; Cclosed = ends ? 1 : 0; }
-        else { s_O[warp][lane] = acc; Onode = s; }
-        j0 = pe;
       }
-      if (lane == 0) { s_Cnode[warp] = Cnode; s_Cclosed[warp] = Cclosed; s_Onode[warp] = Onode; }
+      if (lane == 0) { s_Cnode[buf][warp] = Cnode; s_Cclosed[buf][warp] = Cclosed; s_Onode[buf][warp] = Onode; }
     }
-    __syncthreads();
+    __syncthreads();   // the only CTA barrier of the tile (the piece buffers alternate, s_e / s_src are per-warp)
     // chain the pieces of segments that cross warp chunks, in warp order
-    if (s_Onode[warp] >= 0) {
-      const int s = s_Onode[warp];
-      float total = s_O[warp][lane];
+    if (s_Onode[buf][warp] >= 0) {
+      const int s = s_Onode[buf][warp];
+      float total = s_O[buf][warp][lane];
       bool closed = false;
       for (int w2 = warp + 1; w2 < NWARP; ++w2) {
-        if (s_Cnode[w2] != s) break;
-        total = agg_comb(p.agg, total, s_C[w2][lane]);
-        if (s_Cclosed[w2]) { closed = true; break; }
+        if (s_Cnode[buf][w2] != s) break;
+        total = comb<IS_MAX>(total, s_C[buf][w2][lane]);
+        if (s_Cclosed[buf][w2]) { closed = true; break; }
       }
-      if (closed) finalize_node(p, s, total, p.rowptr[s + 1] - p.rowptr[s], lane);
-      else publish_partial(p, tile, 1, s, total, lane);
+      if (closed) finalize_node(p, s, total, lane);
+      else publish_partial<IS_MAX>(p, tile, 1, s, total, lane);
     }
-    if (warp == 0 && s_Cnode[0] >= 0) {  // the tile begins inside a segment opened by an earlier tile
-      const int s = s_Cnode[0];
-      float total = s_C[0][lane];
-      if (!s_Cclosed[0]) {
+    if (warp == 0 && s_Cnode[buf][0] >= 0) {  // the tile begins inside a segment opened by an earlier tile
+      const int s = s_Cnode[buf][0];
+      float total = s_C[buf][0][lane];
+      if (!s_Cclosed[buf][0]) {
         for (int w2 = 1; w2 < NWARP; ++w2) {
-          if (s_Cnode[w2] != s) break;
-          total = agg_comb(p.agg, total, s_C[w2][lane]);
-          if (s_Cclosed[w2]) break;
+          if (s_Cnode[buf][w2] != s) break;
+          total = comb<IS_MAX>(total, s_C[buf][w2][lane]);
+          if (s_Cclosed[buf][w2]) break;
         }
       }
-      publish_partial(p, tile, 0, s, total, lane);
+      publish_partial<IS_MAX>(p, tile, 0, s, total, lane);
     }
-    __syncthreads();  // s_e / s_C / s_O are rewritten by the next tile
   }
 }
 
@@ -225,10 +386,18 @@ extern "C" int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int6
 template <int FE, int HC>
 static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
   const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * 3);
-  if (reatt_e) mp_step_fwd_kernel<FE, HC, true><<<grid, TILE, 0, st>>>(sp);
-  else mp_step_fwd_kernel<FE, HC, false><<<grid, TILE, 0, st>>>(sp);
+  const bool is_max = sp.agg == GNNCCA_AGG_MAX;
+  if (reatt_e) {
+    if (is_max) mp_step_fwd_kernel<FE, HC, true, true><<<grid, THREADS, 0, st>>>(sp);
+    else mp_step_fwd_kernel<FE, HC, true, false><<<grid, THREADS, 0, st>>>(sp);
+  } else {
+    if (is_max) mp_step_fwd_kernel<FE, HC, false, true><<<grid, THREADS, 0, st>>>(sp);
+    else mp_step_fwd_kernel<FE, HC, false, false><<<grid, THREADS, 0, st>>>(sp);
+  }
   return check_launch();
 }
+
+extern "C" int32_t gnncca_mp_step_tile(void) { return TILE; }
 
 extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
                                   const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,

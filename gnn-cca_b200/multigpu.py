@@ -151,7 +151,7 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     e = engine.small_mlp_rows(model.encoder.edge_mlp, edge_attr_local.contiguous())
     h0, e0 = h, e
     sb = engine.StepBinding(model, math)
-    sb.cfg.edge_phase = int(edge_base) % 256      # tile the local slice like the whole graph: bit-identical reductions
+    sb.cfg.edge_phase = int(edge_base) % int(_lib.load().gnncca_mp_step_tile())      # tile the local slice like the whole graph: bit-identical reductions
     L, k = model.num_enc_steps, model.num_class_steps
     first = L - k + 1
     outs: List[torch.Tensor] = []

@@ -111,7 +111,7 @@ typedef struct {
   int32_t reattach_nodes;  /* mpn.py:284-285                                                      */
   int32_t reattach_edges;  /* mpn.py:282-283                                                      */
   int32_t math;            /* GNNCCA_MATH_*: how the 6->32 message product is computed            */
-  int32_t edge_phase;      /* 0, or (global id of local edge 0) % 256 when the edges are one rank's slice of a larger
+  int32_t edge_phase;      /* 0, or (global id of local edge 0) % gnncca_mp_step_tile() when the edges are one rank's slice of a larger
                               source-major list: keeps the reduction tiling -- and so every bit -- of the whole graph */
 } gnncca_mp_cfg;
 
@@ -140,6 +140,8 @@ typedef struct {
 int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* h0, const float* h,
                         int64_t n_nodes, float* P, float* Q, float* R, void* stream);
 
+/* Edges per reduction tile of gnncca_mp_step_fwd (the modulus of gnncca_mp_cfg.edge_phase). */
+int32_t gnncca_mp_step_tile(void);
 int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes, int64_t n_edges);
 
 /* e_out[i]   = ReLU( P[src[i]] + Q[dst[i]] + W_edge[:, edge block] [e0[i],] e_in[i] )   (mpn.py:48,68-69)
