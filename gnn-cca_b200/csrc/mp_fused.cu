@@ -88,7 +88,7 @@ extern "C" int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_wei
   // of frames (1024 frames on 148 SMs: 7 groups x 1 round instead of 8 groups of which one idles)
   const int gt = cap_edges <= 512 ? 128 : 256;
   int gmax = (int)((budget - wbytes) / sbytes);
-  if (gmax > 1024 / gt) gmax = 1024 / gt;
+  if (gmax > 896 / gt) gmax = 896 / gt;       // __launch_bounds__(896, 1)
   const int64_t per_sm = ceil_div(n_graphs, kNumSMs);
   const int64_t rounds = ceil_div(per_sm, gmax);
   const int groups = (int)ceil_div(per_sm, rounds);

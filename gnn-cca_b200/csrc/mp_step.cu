@@ -187,9 +187,12 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
+    float r_next = 0.f;   // R row of the chunk's first segment, requested before phase A so that phase B does not wait for it
     if (p.h_out != nullptr && a < b) {
       if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
       if (lane == 1 && base + b < p.n_edges) nb = p.src[base + b];
+      const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
+      r_next = p.R[(int64_t)s_first * FN + lane];
     }
     // ------------------------------ phase A: thread per edge pair ------------------------------
     {
@@ -303,7 +306,8 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
           mask &= mask - 1;
           const int j1 = mask ? c0 + __ffsll((long long)mask) - 1 : b;
           const int s = s_src[j0];
-          const float r = p.R[(int64_t)s * FN + lane];
+          const float r = r_next;
+          if (mask) r_next = p.R[(int64_t)s_src[j1] * FN + lane];      // next segment's row: in flight during this one
           float2 acc2 = pk::bc(IS_MAX ? -INFINITY : 0.f);
           int j = j0;
           if (j & 1) {
@@ -314,17 +318,26 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
             acc2.y = comb<IS_MAX>(acc2.y, fmaxf(m, 0.f));
             ++j;
           }
-#pragma unroll 2
-          for (; j + 1 < j1; j += 2) {
-            const float4* ev = reinterpret_cast<const float4*>(&s_e[j >> 1][0]);
-            float2 m = pk::bc(r);
+          if (j + 1 < j1) {     // pairs, software-pipelined: the next pair's rows are loaded while this one is multiplied
+            float4 v[FE / 2];
 #pragma unroll
-            for (int k = 0; k < FE / 2; ++k) {
-              const float4 v = ev[k];
-              m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
-              m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
+            for (int k = 0; k < FE / 2; ++k) v[k] = reinterpret_cast<const float4*>(&s_e[j >> 1][0])[k];
+#pragma unroll 2
+            for (; j + 1 < j1; j += 2) {
+              float4 nv[FE / 2];
+              const int jn = j + 3 < j1 ? j + 2 : j;          // clamp: the last iteration reloads its own rows
+#pragma unroll
+              for (int k = 0; k < FE / 2; ++k) nv[k] = reinterpret_cast<const float4*>(&s_e[jn >> 1][0])[k];
+              float2 m = pk::bc(r);
+#pragma unroll
+              for (int k = 0; k < FE / 2; ++k) {
+                m = pk::ffma2(make_float2(v[k].x, v[k].y), pk::bc(wne[2 * k]), m);
+                m = pk::ffma2(make_float2(v[k].z, v[k].w), pk::bc(wne[2 * k + 1]), m);
+              }
+              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+#pragma unroll
+              for (int k = 0; k < FE / 2; ++k) v[k] = nv[k];
             }
-            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
           }
           if (j < j1) {
             const float* ev = &s_e[j >> 1][0];

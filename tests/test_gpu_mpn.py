@@ -277,6 +277,24 @@ def test_raw_edge_index_form_equals_csr_form_bit_for_bit(agg, cuda_device):
         assert close(o, r) <= FP32_RTOL
 
 
+def test_many_frames_of_the_wide_class_fill_the_cta_with_256_thread_groups(cuda_device):
+    """700 frames of 4 x 9 detections (> 512 edges per frame: 256-thread groups, several rounds per SM): the group count
+    must respect the kernel's 896-thread launch bound.  Fused result against the per-step kernels on the same batch."""
+    import gnncca
+    from importlib import import_module
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    torch.manual_seed(6)
+    model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50", math="fp32").to(cuda_device).eval()
+    b = _trusted_batch(cuda_device, cams=4, dets=9, frames=700, seed=21)
+    with torch.no_grad():
+        fused = model(b)["classified_edges"]
+        assert model.last_plan.last_path == "fused"
+        steps = model(D(b.x, b.edge_index, b.edge_attr))["classified_edges"]
+        assert model.last_plan.last_path == "steps"
+    for f, st in zip(fused, steps):
+        assert close(f, st) <= FP32_RTOL
+
+
 @pytest.mark.parametrize("violation", ["none", "unsorted", "leaves_frame", "bad_edge_ptr", "too_large"])
 def test_raw_form_verifies_the_frames_on_the_device(violation, cuda_device):
     """C-ABI level: the RAW form raises flags[2] for edges that are not source-major, leave their frame, for
