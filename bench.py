@@ -275,11 +275,18 @@ def run_training(args):
     N, E = batches[0].num_nodes, batches[0].num_edges
     in_bytes = sum(t.numel() * t.element_size() for t in (batches[0].x, batches[0].edge_index, batches[0].edge_attr, batches[0].edge_labels))
 
-    def step(b):
+    def step_eager(b):
         opt.zero_grad(set_to_none=True)
         out = model(b)["classified_edges"]
         loss = gnncca.loss_stats(out, b.edge_labels).loss      # train.py:80-97 in one pass (gnncca_bce_stats_fwd/bwd)
         loss.backward()
+        opt.step()
+        return loss
+
+    gstep = gnncca.GraphedTrainStep(model)     # forward + loss + backward captured once per batch shape, replayed afterwards
+
+    def step(b):
+        loss = gstep(b)                        # zeroes .grad, runs the same kernels as step_eager, out of one CUDA graph
         opt.step()
         return loss
 
@@ -288,20 +295,27 @@ def run_training(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(fn, n):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for i in range(n):
+            fn(batches[i % 8])
+        ev1.record()
+        barrier()
+        return ev0.elapsed_time(ev1)
+
+    for i in range(max(args.warmup, 3)):
+        step_eager(batches[i % 8])
+    ms_eager = timed(step_eager, args.steps)
     for i in range(max(args.warmup, 3)):
         step(batches[i % 8])
     barrier()
     sampler = ClockSampler(physical_gpu_index(local))
     sampler.start()
-    l0 = int(lib.gnncca_launch_count())
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for i in range(args.steps):
-        step(batches[i % 8])
-    ev1.record()
-    barrier()
-    launches = int(lib.gnncca_launch_count()) - l0
-    ms = ev0.elapsed_time(ev1)
+    l0 = int(lib.gnncca_launch_count()) + gstep.launches_replayed
+    ms = timed(step, args.steps)
+    launches = int(lib.gnncca_launch_count()) + gstep.launches_replayed - l0
     t_end = time.perf_counter() + 0.3
     while time.perf_counter() < t_end:
         step(batches[0])
@@ -312,11 +326,12 @@ def run_training(args):
     e2e_steps = max(3, min(args.steps, 20))
     barrier()
     t0 = time.perf_counter()
+    sb = gstep.static_batch(batches[0])          # the graph's own input buffers: host data is copied straight into them
     for i in range(e2e_steps):
         hx, hei, hea, hl = hosts[i & 1]
-        b = gnncca.Batch(x=hx.to(dev, non_blocking=True), edge_index=hei.to(dev, non_blocking=True), edge_attr=hea.to(dev, non_blocking=True),
-                         edge_labels=hl.to(dev, non_blocking=True))
-        float(step(b).item())
+        sb.x.copy_(hx, non_blocking=True); sb.edge_index.copy_(hei, non_blocking=True)
+        sb.edge_attr.copy_(hea, non_blocking=True); sb.edge_labels.copy_(hl, non_blocking=True)
+        float(step(sb).item())
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
@@ -336,10 +351,11 @@ def run_training(args):
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "%s: %s per GPU (N=%d, E=%d)" % (args.workload, wl["desc"], N, E), "l2": "8 batches rotate; a batch is 22 MB (fits L2: launch-bound regime)",
+                           "step": "forward + loss + backward replayed from one CUDA graph (GraphedTrainStep), then torch SGD; the same step launched eagerly: %.3f ms" % (ms_eager / args.steps),
                            "optimizer": "SGD lr 1e-3 momentum 0.9 wd 1e-4", "parallelism": "graph-sharded x%d, no gradient all-reduce (independent replicas)" % world},
                 "clocks": sampler.result(), "gpu_launches": launches,
                 "e2e": {"value": world * E * e2e_steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps,
-                        "api": "MOTMPNet.forward + loss_stats (summed BCE) + backward + SGD.step on a batch copied from pinned host memory"},
+                        "api": "GraphedTrainStep (MOTMPNet.forward + loss_stats + backward) + SGD.step, batch copied from pinned host memory into the graph's input buffers"},
                 "roofline": {"bound": "hbm", "kernel": "whole training step (launch-bound at this size)", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None, "algorithmic_bytes_per_launch": train_bytes}}
         if world == 1 and not args.no_cpu_baseline:

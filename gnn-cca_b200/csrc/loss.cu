@@ -6,7 +6,7 @@
 // Per sample and classified step s (torch.nn.BCEWithLogitsLoss, optional scalar pos_weight, main_training.py:263-268):
 //   l = (1 - y) x + (1 + (pw - 1) y) (log1p(exp(-|x|)) + max(-x, 0))
 // optional per-sample focal transform (libs/utils.py:264-293, reduction 'none'): b (1 - exp(-l))^gamma l.
-// Sums are accumulated per thread, reduced per block in a fixed tree and folded over blocks in block order in double:
+// Sums are accumulated per thread, reduced per block in a fixed tree and folded over blocks in a fixed order in double:
 // results are bit-reproducible.  HBM-bound: 4 B/edge/step read (+4 B/edge/step for the optional probabilities).
 #include "common.cuh"
 
@@ -84,10 +84,14 @@ __global__ void __launch_bounds__(THREADS) stats_kernel(const Ptrs p, int k, con
 __global__ void finalize_kernel(const double* __restrict__ partials, int blocks, int k, int64_t E, double* __restrict__ out) {
   const int width = PER * k + 4;
   __shared__ double sums[PER * MAX_STEPS + 4];
-  for (int i = threadIdx.x; i < width; i += blockDim.x) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int i = warp; i < width; i += nwarps) {       // a warp per column: lanes stride the blocks, then a fixed xor tree
     double v = 0.0;
-    for (int b = 0; b < blocks; ++b) v += partials[(size_t)b * width + i];
-    sums[i] = v;
+#pragma unroll 4
+    for (int b = lane; b < blocks; b += 32) v += partials[(size_t)b * width + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) sums[i] = v;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -133,7 +137,7 @@ extern "C" int gnncca_bce_stats_fwd(const float* const* host_logits, int32_t n_s
   const int blocks = gnncca_loss_blocks(n_edges);
   cudaStream_t st = (cudaStream_t)stream;
   loss::stats_kernel<<<blocks, loss::THREADS, 0, st>>>(p, n_steps, labels, n_edges, pos_weight, focal, focus, balance, probs, partials);
-  loss::finalize_kernel<<<1, 64, 0, st>>>(partials, blocks, n_steps, n_edges, out);
+  loss::finalize_kernel<<<1, 256, 0, st>>>(partials, blocks, n_steps, n_edges, out);
   return check_launch(2);
 }
 

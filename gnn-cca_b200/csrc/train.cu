@@ -448,18 +448,34 @@ __global__ void __launch_bounds__(TB) edge_enc_bwd_kernel(const float* edge_attr
 // G. dense layer backward (node encoder, mlp.py:14,18): gz = gy * [y > 0]; gb partials; gW = gz^T x (split over rows);
 //    gx = gz W.
 // ------------------------------------------------------------------------------------------------
-constexpr int RG_ROWS = 128;
-__global__ void __launch_bounds__(256) relu_grad_bias_kernel(const float* y, const float* gy, int relu, int64_t rows, int out_dim, float* gz,
-                                                             float* partial /* [chunks][out] */) {
+constexpr int RG_ROWS = 64;
+// 256 threads = (256 / out_dim) row lanes x out_dim columns: every lane sums its rows of the chunk in order, the lanes are
+// folded in lane order (fixed summation order).  out_dim > 256: one row lane, columns strided.
+__global__ void __launch_bounds__(256) relu_grad_bias_kernel(const float* __restrict__ y, const float* __restrict__ gy, int relu, int64_t rows,
+                                                             int out_dim, float* __restrict__ gz, float* __restrict__ partial /* [chunks][out] */) {
+  __shared__ float red[256];
   const int64_t r0 = (int64_t)blockIdx.x * RG_ROWS, r1 = min(r0 + RG_ROWS, rows);
-  for (int c = threadIdx.x; c < out_dim; c += blockDim.x) {
+  const int lanes = out_dim <= 256 ? 256 / out_dim : 1;
+  const int lr = threadIdx.x / out_dim, c0 = threadIdx.x - lr * out_dim;
+  for (int cb = 0; cb < out_dim; cb += 256) {
+    const int c = cb + c0;
     float acc = 0.f;
-    for (int64_t r = r0; r < r1; ++r) {
-      const float g = (!relu || y[r * out_dim + c] > 0.f) ? gy[r * out_dim + c] : 0.f;
-      gz[r * out_dim + c] = g;
-      acc += g;
+    if (lr < lanes && c < out_dim) {
+#pragma unroll 4
+      for (int64_t r = r0 + lr; r < r1; r += lanes) {
+        const float g = (!relu || y[r * out_dim + c] > 0.f) ? gy[r * out_dim + c] : 0.f;
+        gz[r * out_dim + c] = g;
+        acc += g;
+      }
     }
-    partial[(int64_t)blockIdx.x * out_dim + c] = acc;
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (lr == 0 && c < out_dim) {
+      float tot = red[c0];
+      for (int l = 1; l < lanes; ++l) tot += red[l * out_dim + c0];
+      partial[(int64_t)blockIdx.x * out_dim + c] = tot;
+    }
+    __syncthreads();
   }
 }
 
@@ -519,13 +535,35 @@ __global__ void __launch_bounds__(256) gz_times_w_kernel(const float* gz, const 
 //    where per-block partial sums meet, in a fixed order.  One block per table entry.
 // ------------------------------------------------------------------------------------------------
 struct FinTable { gnncca_fin_seg s[GNNCCA_MAX_FIN_SEGS]; int n; };
+constexpr int FIN_WARP_MODE_BLOCKS = 64;   // from this many partial rows on, a WARP folds one element (lanes stride the rows)
 __global__ void __launch_bounds__(256) finalize_kernel(const FinTable t) {
   const gnncca_fin_seg sg = t.s[blockIdx.x];
   const int total = sg.rows * sg.cols;
+  if (sg.n_blocks >= FIN_WARP_MODE_BLOCKS) {
+    // few elements, many partial rows (per-edge / per-node kernels): lane l sums rows l, l + 32, ... in order, then a fixed
+    // xor tree over the lanes.  The order is a function of n_blocks only.
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = blockIdx.y * 8 + warp; i < total; i += 8 * gridDim.y) {
+      const int r = i / sg.cols, c = i - r * sg.cols;
+      const float* src = sg.partial + sg.src_off + r * sg.src_stride + c;
+      float acc = 0.f;
+#pragma unroll 4
+      for (int b = lane; b < sg.n_blocks; b += 32) acc += __ldg(src + (int64_t)b * sg.width);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) {
+        float* d = sg.dst + (int64_t)r * sg.dst_stride + c;
+        *d = sg.accumulate ? *d + acc : acc;
+      }
+    }
+    return;
+  }
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < total; i += blockDim.x * gridDim.y) {
     const int r = i / sg.cols, c = i - r * sg.cols;
     float acc = 0.f;
-    for (int b = 0; b < sg.n_blocks; ++b) acc += sg.partial[(int64_t)b * sg.width + sg.src_off + r * sg.src_stride + c];
+    const float* src = sg.partial + sg.src_off + r * sg.src_stride + c;
+#pragma unroll 8
+    for (int b = 0; b < sg.n_blocks; ++b) acc += __ldg(src + (int64_t)b * sg.width);     // same order, 8 loads in flight
     float* d = sg.dst + (int64_t)r * sg.dst_stride + c;
     *d = sg.accumulate ? *d + acc : acc;
   }
@@ -686,7 +724,9 @@ extern "C" int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_
   for (int i = 0; i < n_segs; ++i) {
     t.s[i] = host_segs[i];
     if (!t.s[i].partial || !t.s[i].dst || t.s[i].rows < 0 || t.s[i].cols < 0 || t.s[i].n_blocks < 0) return GNNCCA_ERR_BAD_ARG;
-    if (t.s[i].rows * t.s[i].cols > max_elems) max_elems = t.s[i].rows * t.s[i].cols;
+    // blocks along y so that the largest entry gets ~4 elements per thread (thread mode) or per warp (warp mode)
+    const int elems = t.s[i].rows * t.s[i].cols * (t.s[i].n_blocks >= tr::FIN_WARP_MODE_BLOCKS ? 32 : 1);
+    if (elems > max_elems) max_elems = elems;
   }
   int gy = (int)ceil_div(max_elems, 256 * 4);
   if (gy > 64) gy = 64;

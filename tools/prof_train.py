@@ -16,13 +16,17 @@ batches = [gnncca.build_graph_batch(**syn.make_detections(4, 10, 64, seed=7 + s,
 def step(b):
     opt.zero_grad(set_to_none=True)
     out = model(b)["classified_edges"]
-    loss = sum(crit(r.view(-1), b.edge_labels) for r in out)
+    loss = gnncca.loss_stats(out, b.edge_labels).loss
     loss.backward()
     opt.step()
 
-for i in range(8):
+import sys
+NW = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+for i in range(NW):
     step(batches[i % 4])
 torch.cuda.synchronize()
+if len(sys.argv) > 2 and sys.argv[2] == "only":      # for an ncu launch list: NW steps and out
+    sys.exit(0)
 t0 = time.perf_counter()
 for i in range(40):
     step(batches[i % 4])
