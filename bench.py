@@ -269,7 +269,7 @@ def run_training(args):
     lib = gnncca._lib.load(build_if_missing=False)
     torch.manual_seed(0)
     model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50").to(dev).train()
-    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4)
+    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4, fused=True)
     batches = [gnncca.build_graph_batch(**syn.make_detections(wl["cams"], wl["dets"], wl["frames"], seed=wl["seed"] + 100 * rank + 7919 * s,
                                                                device=dev, max_dist=wl["max_dist"])) for s in range(8)]
     N, E = batches[0].num_nodes, batches[0].num_edges
@@ -349,10 +349,10 @@ def run_training(args):
         ach = train_bytes / (ms_max / args.steps * 1e-3) / 1e9
         line = {"metric": METRIC, "value": world * E * args.steps / (ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic",
+                "dtype": "tf32", "data": "synthetic",
                 "config": {"workload": "%s: %s per GPU (N=%d, E=%d)" % (args.workload, wl["desc"], N, E), "l2": "8 batches rotate; a batch is 22 MB (fits L2: launch-bound regime)",
                            "step": "forward + loss + backward replayed from one CUDA graph (GraphedTrainStep), then torch SGD; the same step launched eagerly: %.3f ms" % (ms_eager / args.steps),
-                           "optimizer": "SGD lr 1e-3 momentum 0.9 wd 1e-4", "parallelism": "graph-sharded x%d, no gradient all-reduce (independent replicas)" % world},
+                           "optimizer": "torch.optim.SGD(fused=True) lr 1e-3 momentum 0.9 wd 1e-4", "parallelism": "graph-sharded x%d, no gradient all-reduce (independent replicas)" % world},
                 "clocks": sampler.result(), "gpu_launches": launches,
                 "e2e": {"value": world * E * e2e_steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": 4, "steps": e2e_steps,
                         "api": "GraphedTrainStep (MOTMPNet.forward + loss_stats + backward) + SGD.step, batch copied from pinned host memory into the graph's input buffers"},

@@ -51,6 +51,7 @@ SIGNATURES = {
     "gnncca_permute_rows": (C.c_int, [vp, vp, vp, i64, i32, i32, vp]),
     "gnncca_linear": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp, C.c_float, i32, vp]),
     "gnncca_node_encoder": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, i32, vp]),
+    "gnncca_node_encoder_train": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, vp]),
     "gnncca_node_project": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp]),
     "gnncca_mp_step_tile": (i32, []),
     "gnncca_mp_step_workspace_bytes": (i64, [C.POINTER(MpCfg), i64, i64]),

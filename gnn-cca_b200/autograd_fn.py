@@ -85,22 +85,33 @@ class _MPNFunction(torch.autograd.Function):
             plan.tperm, plan.colptr = tperm, colptr
         tperm, colptr = plan.tperm, plan.colptr
 
-        # node encoder, layer by layer (FP32: the training path keeps every activation)
+        # node encoder: every activation is kept for the backward.  math='tf32' (the module's default): both layers in the
+        # tcgen05 kernel of the inference path, which also writes the hidden activations; math='fp32': layer by layer in FP32
         acts = [x.contiguous()]
-        for i, sp in enumerate(enc_n.layer_specs):
-            acts.append(engine.linear(acts[-1], enc_n.linear(i), sp.relu, None, _lib.MATH_FP32))
+        if model.math == "tf32" and engine.node_encoder_fused_ok(enc_n, acts[0]):
+            l1, l2 = enc_n.linear(0), enc_n.linear(1)
+            h1 = torch.empty((N, l1.out_features), dtype=torch.float32, device=dev)
+            h2 = torch.empty((N, l2.out_features), dtype=torch.float32, device=dev)
+            _lib.check(lib.gnncca_node_encoder_train(P(acts[0]), P(l1.weight), P(l1.bias), P(l2.weight), P(l2.bias), P(h1), P(h2), N,
+                                                     l1.in_features, l1.out_features, l2.out_features, _stream()), "node_encoder_train")
+            acts += [h1, h2]
+        else:
+            for i, sp in enumerate(enc_n.layer_specs):
+                acts.append(engine.linear(acts[-1], enc_n.linear(i), sp.relu, None, _lib.MATH_FP32))
         h0 = acts[-1]
         ea = plan.to_sorted(edge_attr.contiguous())
         e0 = engine.small_mlp_rows(enc_e, ea)
 
         hs, es, affs, outs = [h0], [e0], {}, []
-        Pn = torch.empty((N, 8), dtype=torch.float32, device=dev)
-        Qn = torch.empty((N, 8), dtype=torch.float32, device=dev)
-        Rn = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
+        # the per-node projections of every step are kept for the backward (48 floats per node and step: nothing next to the
+        # per-edge latents) instead of being recomputed there
+        pw = 16 + sb.f_node
+        proj = torch.empty((L, N * pw), dtype=torch.float32, device=dev)
         ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), N, E))
         wsp = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         be = _blocks(lib, E, _lib.BLOCKS_PER_EDGE)
         for step in range(1, L + 1):
+            Pn, Qn, Rn = proj[step - 1, :N * 8], proj[step - 1, N * 8:N * 16], proj[step - 1, N * 16:]
             _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), P(h0), P(hs[-1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
             e_out = torch.empty_like(e0)
             h_out = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev) if step < L else None
@@ -132,7 +143,7 @@ class _MPNFunction(torch.autograd.Function):
             if classify:
                 outs.append(plan.to_caller(logits))
         ctx.model, ctx.plan, ctx.sb = model, plan, sb
-        ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
+        ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, proj=proj, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
                          names=[n for n, _ in model.named_parameters_fast()])
         ctx.set_materialize_grads(False)
         model.__dict__["_gnncca_train_plan"] = plan
@@ -164,7 +175,7 @@ class _MPNFunction(torch.autograd.Function):
         be, bnw, bp = _blocks(lib, E, _lib.BLOCKS_PER_EDGE), _blocks(lib, N, _lib.BLOCKS_PER_NODE_WARP), _blocks(lib, N, _lib.BLOCKS_NODE_PROJECT)
         n_cls = L - first + 1
         shapes = [("pa_agg", (L, bnw, FN * FE)), ("pa_edge", (L, be, FE * EIN)), ("pa_proj", (L, bp, 44 * (K + 1))),
-                  ("pa_cls", (n_cls, be, _lib.CLS_ACC)), ("Pn", (N, 8)), ("Qn", (N, 8)), ("Rn", (N, FN)), ("gP", (N, 8)), ("gQ", (N, 8)),
+                  ("pa_cls", (n_cls, be, _lib.CLS_ACC)), ("gP", (N, 8)), ("gQ", (N, 8)),
                   ("gR", (N, FN)), ("gze", (E, 8)), ("gh_prev", (L, N, FN))]
         if bn_mode == "train":
             shapes.append(("pa_cls1", (n_cls, be, _lib.CLS_ACC)))
@@ -184,7 +195,8 @@ class _MPNFunction(torch.autograd.Function):
         zb = {name: zeros[o:o + c].view(shp) for name, (o, c, shp) in offs.items()}
         grads = {n: zb["grad/" + n] for n in named}
         pa_agg, pa_edge, pa_proj, pa_cls, pa_cls1 = zb["pa_agg"], zb["pa_edge"], zb["pa_proj"], zb["pa_cls"], zb.get("pa_cls1")
-        Pn, Qn, Rn, gP, gQ, gR, gze = zb["Pn"], zb["Qn"], zb["Rn"], zb["gP"], zb["gQ"], zb["gR"], zb["gze"]
+        gP, gQ, gR, gze = zb["gP"], zb["gQ"], zb["gR"], zb["gze"]
+        proj = sv["proj"]
         ge0_acc, gh0_acc, gh_prevs = zb.get("ge0_acc"), zb.get("gh0_acc"), zb["gh_prev"]
         gh, ge_next = None, None
         is_max = model.node_agg_name == "max"
@@ -202,7 +214,7 @@ class _MPNFunction(torch.autograd.Function):
                     _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 2, P(g), P(sums), P(ge_cls), P(pa_cls[ci]), _stream()), "cls_bwd pass 2")
                 else:
                     _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 0, P(g), 0, P(ge_cls), P(pa_cls[ci]), _stream()), "cls_bwd")
-            _lib.check(lib.gnncca_node_project(cfg, w, P(hs[0]), P(hs[t - 1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
+            Rn = proj[t - 1, N * 16:]            # R of step t, kept by the forward
             if gh is not None:
                 gh_eff = torch.empty_like(gh) if is_max else None
                 _lib.check(lib.gnncca_node_agg_bwd(cfg, w, P(plan.rowptr), N, P(Rn), P(es[t]), P(gh), P(hs[t]), P(gR), P(gh_eff), P(pa_agg[t - 1]),

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(256) edge_linear_kernel(const float* __restric
 
 using namespace gnncca;
 
-int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
                              int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream);   // encoder_tc.cu
 
 extern "C" int gnncca_linear(const float* x, const float* W, const float* b, float* y, int64_t rows, int32_t in_dim,
@@ -249,7 +249,15 @@ extern "C" int gnncca_node_encoder(const float* x, const float* W1, const float*
   if (rows == 0) return GNNCCA_OK;
   if (!x || !W1 || !b1 || !W2 || !b2 || !h) return GNNCCA_ERR_BAD_ARG;
   if (math != GNNCCA_MATH_TF32) return GNNCCA_ERR_UNSUPPORTED;   // FP32: two gnncca_linear calls
-  return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, h, rows, in_dim, hidden, out_dim, stream);
+  return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, nullptr, h, rows, in_dim, hidden, out_dim, stream);
+}
+
+extern "C" int gnncca_node_encoder_train(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1,
+                                         float* h, int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream) {
+  if (rows < 0 || in_dim <= 0 || hidden <= 0 || out_dim <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!x || !W1 || !b1 || !W2 || !b2 || !h || !h1) return GNNCCA_ERR_BAD_ARG;
+  return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, h1, h, rows, in_dim, hidden, out_dim, stream);
 }
 
 extern "C" int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* h0, const float* h,

@@ -23,6 +23,7 @@ constexpr int NUM_THREADS = 320;
 struct Params {
   const float* b1; const float* W2; const float* b2;
   float* h_out;
+  float* h1_out;             // optional [rows][H]: the hidden activations as layer 2 consumed them (training keeps them), else NULL
   int64_t rows;
   int K, H, stages;
   int rows_per_cta;          // multiple of 8: CTA c owns rows [c * rows_per_cta, (c+1) * rows_per_cta)
@@ -215,6 +216,12 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = tf32_rna(fmaxf(v[j] + b1s[c * 32 + j], 0.f));
           tmem_st32(lane_base + (uint32_t)(t * H + c * 32), v);
+          if (p.h1_out != nullptr && row_in_tile < valid) {            // saved for the backward (uniform branch: NULL in inference)
+            const int64_t row = row_begin + (int64_t)st * 2 * BLOCK_M + t * BLOCK_M + row_in_tile;
+            float4* d1 = reinterpret_cast<float4*>(p.h1_out + row * H + c * 32);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) d1[j4] = make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+          }
         }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
@@ -357,13 +364,13 @@ int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaS
 
 // Fused two-layer node encoder on the tensor cores (see the header of this file).  Requirements: in_dim % 32 == 0,
 // hidden in {64, 128}, out_dim == 32, x and W1 16-byte aligned.
-int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
+int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
                              int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream) {
   if (out_dim != enc::F_OUT || in_dim % enc::BLOCK_K != 0 || in_dim < enc::BLOCK_K) return GNNCCA_ERR_UNSUPPORTED;
-  if ((((uintptr_t)x | (uintptr_t)W1 | (uintptr_t)h) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
+  if ((((uintptr_t)x | (uintptr_t)W1 | (uintptr_t)h | (uintptr_t)h1) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
   if (rows >= ((int64_t)1 << 31)) return GNNCCA_ERR_BAD_ARG;
   enc::Params p{};
-  p.b1 = b1; p.W2 = W2; p.b2 = b2; p.h_out = h; p.rows = rows; p.K = in_dim; p.H = hidden;
+  p.b1 = b1; p.W2 = W2; p.b2 = b2; p.h_out = h; p.h1_out = h1; p.rows = rows; p.K = in_dim; p.H = hidden;
   cudaStream_t st = (cudaStream_t)stream;
   switch (hidden) {
     case 64: return launch_encoder<64>(x, W1, p, st);

@@ -3,14 +3,14 @@
 A training step on EPFL-sized batches is ~45 short kernels (forward, loss, backward): launch-bound.  ``GraphedTrainStep``
 captures forward + loss (``loss_stats``, train.py:80-97) + backward of ONE batch shape into a CUDA graph and replays it
 for every later batch with the same (nodes, edges, frames) signature; inputs are copied into the graph's static
-buffers, parameter gradients land in the parameters' ``.grad`` tensors (allocated once, zeroed inside the graph), so
+buffers, every replay leaves the parameters' ``.grad`` pointing at the graph's freshly written gradient tensors, so
 any ``torch.optim`` optimiser steps on them as usual.  Batches of another shape get their own graph (up to
 ``max_graphs``), after that they run eagerly.  The kernels are the same ones the eager path launches; nothing is traced or compiled.
 
     step = gnncca.GraphedTrainStep(mpn_model)                       # criteria of main_training.py:258-268 via kwargs
     for data_batch in loader:                                       # batches from gnncca.build_graph_batch
         loss = step(data_batch)                                     # replaces train.py:454-458 + loss.backward() (:493)
-        optimizer.step()                                            # no optimizer.zero_grad(): the graph zeroes .grad
+        optimizer.step()                                            # no optimizer.zero_grad(): .grad is overwritten, not accumulated
 """
 from __future__ import annotations
 
@@ -69,9 +69,6 @@ class GraphedTrainStep:
         if not model.training:
             raise RuntimeError("GraphedTrainStep is for model.train() (use model(data) for inference)")
         static = Batch(**{k: (v.clone() if torch.is_tensor(v) else v) for k, v in batch.__dict__.items()})
-        for p in model.parameters():
-            if p.requires_grad and p.grad is None:
-                p.grad = torch.zeros_like(p)
         # BatchNorm buffers (classifier of the BNcls configurations): the rehearsals below must not count as training steps
         bn_state = [(b, b.detach().clone()) for m in model.modules() if isinstance(m, torch.nn.modules.batchnorm._BatchNorm)
                     for b in m.buffers(recurse=False)]
@@ -93,13 +90,15 @@ class GraphedTrainStep:
         lib = _lib.load()
         n0 = int(lib.gnncca_launch_count())
         with torch.cuda.graph(g):
+            # .grad = None: autograd then ADOPTS the gradient tensors the backward produced (memory of the graph's own pool, so
+            # the same addresses at every replay) instead of zero-filling and adding into older ones: 2 launches less per parameter
             for p in model.parameters():
-                if p.grad is not None:
-                    p.grad.zero_()
+                p.grad = None
             st = self._forward_backward(static)
         for b, saved in bn_state:
             b.copy_(saved)
         cap = _Captured(g, static, st.loss.detach(), st, int(lib.gnncca_launch_count()) - n0)
+        cap.grads = [p.grad for p in model.parameters()]
         self.graphs[sig] = cap
         return cap
 
@@ -120,6 +119,8 @@ class GraphedTrainStep:
             if src.data_ptr() != dst.data_ptr():
                 dst.copy_(src, non_blocking=True)
         cap.graph.replay()
+        for p, g in zip(self.model.parameters(), cap.grads):       # this shape's gradient buffers (each graph owns a set)
+            p.grad = g
         self.replays += 1
         self.launches_replayed += cap.launches
         cap.stats._host = None          # counts of the previous replay

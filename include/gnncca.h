@@ -97,6 +97,11 @@ int gnncca_linear(const float* x, const float* W, const float* b, float* y, int6
  * x / W1 / h.  Anything else returns GNNCCA_ERR_UNSUPPORTED (the caller then uses two gnncca_linear calls). */
 int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h,
                         int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, int32_t math, void* stream);
+/* The same kernel for the TRAINING forward: additionally writes h1 [rows, hidden], the hidden activations
+ * ReLU(x W1^T + b1) exactly as the second layer consumed them (rounded to TF32), which the backward of mlp.py:12-23 needs
+ * (gnncca_linear_bwd).  Forward in TF32, backward in FP32. */
+int gnncca_node_encoder_train(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1,
+                              float* h, int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * One message-passing step, models/mpn.py:32-54 (MetaLayer) = EdgeModel :67-69 + NodeModel :97-101

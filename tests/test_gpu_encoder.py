@@ -58,3 +58,35 @@ def test_node_encoder_rejects_hidden_widths_without_a_kernel(cuda_device):
     """hidden = 256 does not fit one CTA's tensor memory next to the layer-2 accumulators: UNSUPPORTED, never a fallback."""
     with pytest.raises(NotImplementedError):
         _run(64, 64, 256, cuda_device)
+
+
+@pytest.mark.parametrize("rows,in_dim,hidden", [(2560, 2048, 128), (777, 512, 64), (70000, 64, 128)])
+def test_training_entry_also_writes_the_hidden_activations(rows, in_dim, hidden, cuda_device):
+    """gnncca_node_encoder_train: same output bits as gnncca_node_encoder, plus h1 = ReLU(x W1^T + b1) as layer 2 read it."""
+    lib_mod = importlib.import_module("gnn-cca_b200._lib")
+    lib = lib_mod.load()
+    g = torch.Generator().manual_seed(5)
+    x = torch.relu(torch.randn(rows, in_dim, generator=g))
+    torch.manual_seed(6)
+    l1, l2 = torch.nn.Linear(in_dim, hidden), torch.nn.Linear(hidden, 32)
+    with torch.no_grad():
+        ref1 = torch.relu(l1(x))
+    xd = x.to(cuda_device)
+    W1, b1, W2, b2 = (t.detach().to(cuda_device).contiguous() for t in (l1.weight, l1.bias, l2.weight, l2.bias))
+    h = torch.full((rows, 32), float("nan"), device=cuda_device)
+    h_t = torch.full((rows, 32), float("nan"), device=cuda_device)
+    h1 = torch.full((rows, hidden), float("nan"), device=cuda_device)
+    st = torch.cuda.current_stream().cuda_stream
+    lib_mod.check(lib.gnncca_node_encoder(xd.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(), h.data_ptr(), rows,
+                                          in_dim, hidden, 32, lib_mod.MATH_TF32, st), "node_encoder")
+    lib_mod.check(lib.gnncca_node_encoder_train(xd.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(), h1.data_ptr(),
+                                                h_t.data_ptr(), rows, in_dim, hidden, 32, st), "node_encoder_train")
+    torch.cuda.synchronize()
+    assert torch.equal(h, h_t)
+    got1 = h1.cpu()
+    assert torch.isfinite(got1).all()
+    assert ((got1 - ref1).abs() / (1 + ref1.abs())).max().item() <= TF32_TOL
+    # layer 2 recomputed in fp32 from the SAVED activations reproduces the kernel's output to TF32 rounding of W2 only
+    with torch.no_grad():
+        again = torch.relu(l2(got1))
+    assert ((h.cpu() - again).abs() / (1 + again.abs())).max().item() <= TF32_TOL

@@ -105,3 +105,26 @@ def test_cfg3_shape_gradients_match_oracle_autograd(cuda_device):
     sum(crit(r.view(-1), labels.to(cuda_device)) for r in out).backward()
     for name, p in model.named_parameters():
         assert close(p.grad, sd[name].grad) <= GRAD_TOL, name
+
+
+def test_default_tf32_training_step_stays_within_tf32_tolerance_of_the_reference(cuda_device):
+    """math='tf32' (the module default): the node encoder of the training forward runs on tcgen05 kind::tf32 and keeps its
+    hidden activations; the backward is FP32.  Loss and gradients against the reference's own (fp32) step."""
+    TF32_GRAD_TOL = 2e-2
+    z = load_golden("mpn_shipped_bdnet_train")
+    from test_gpu_mpn import build_model
+    model = build_model(z, cuda_device, math="tf32").train()
+    data = D(torch.from_numpy(z["x"]).to(cuda_device), torch.from_numpy(z["edge_index"]).to(cuda_device),
+             torch.from_numpy(z["edge_attr"]).to(cuda_device))
+    labels = torch.from_numpy(z["labels"]).to(cuda_device)
+    import gnncca
+    n0 = gnncca._lib.load().gnncca_launch_count()
+    out = model(data)["classified_edges"]
+    crit = torch.nn.BCEWithLogitsLoss()
+    loss = sum(crit(r.view(-1), labels) for r in out)
+    loss.backward()
+    assert abs(loss.item() - float(z["loss"])) <= 5e-3 * (1 + abs(float(z["loss"])))
+    for name, p in model.named_parameters():
+        ref = torch.from_numpy(z["grad/" + name]).double()
+        err = ((p.grad.cpu().double() - ref).abs() / (1 + ref.abs() + 0.01 * ref.abs().max())).max()
+        assert float(err) <= TF32_GRAD_TOL, (name, float(err))
