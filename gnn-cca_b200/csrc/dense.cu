@@ -85,16 +85,16 @@ __global__ void __launch_bounds__(256) linear_fp32_kernel(const float* __restric
 }
 
 // ------------------------------------------------------------------------------------------------
-// P/Q/R node projections.  One block = 64 nodes; weights staged in shared memory as [k][out].
+// P/Q/R node projections.  One block = 64 nodes (16 for small graphs: more blocks than SMs); weights staged in shared
+// memory as [k][out].
 // ------------------------------------------------------------------------------------------------
-template <int FN, int FE>
+template <int FN, int FE, int NODES>
 __global__ void __launch_bounds__(256) node_project_kernel(const float* __restrict__ w_edge, const float* __restrict__ b_edge,
                                                            const float* __restrict__ w_node, const float* __restrict__ b_node,
                                                            const float* __restrict__ h0, const float* __restrict__ h, int64_t n_nodes,
                                                            int nf, int ef, float* __restrict__ P, float* __restrict__ Q,
                                                            float* __restrict__ R) {
   constexpr int OUT = 2 * FE + FN;
-  constexpr int NODES = 64;
   const int K = nf * FN;                       // node input width (FN, or 2*FN when the encoder output is reattached)
   const int edge_in = 2 * K + ef * FE;         // row length of w_edge
   const int node_in = K + FE;                  // row length of w_node
@@ -269,14 +269,15 @@ extern "C" int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_wei
   if (cfg->f_node != 32 || cfg->f_edge != 6) return GNNCCA_ERR_UNSUPPORTED;
   const int nf = cfg->reattach_nodes ? 2 : 1, ef = cfg->reattach_edges ? 2 : 1;
   const int K = nf * 32, OUT = 2 * 6 + 32;
-  const size_t smem = sizeof(float) * (K * OUT + OUT + 64 * (K + 1));
-  auto kern = node_project_kernel<32, 6>;
+  const int nodes = n_nodes <= 64 * kNumSMs * 4 ? 16 : 64;      // small graphs: 4x the blocks, a quarter of the work each
+  const size_t smem = sizeof(float) * (K * OUT + OUT + nodes * (K + 1));
+  auto kern = nodes == 16 ? node_project_kernel<32, 6, 16> : node_project_kernel<32, 6, 64>;
   if (smem > 48 * 1024) {
     int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (rc) return rc;
   }
-  kern<<<(unsigned)ceil_div(n_nodes, 64), 256, smem, (cudaStream_t)stream>>>(w->w_edge, w->b_edge, w->w_node, w->b_node, h0, h,
-                                                                             n_nodes, nf, ef, P, Q, R);
+  kern<<<(unsigned)ceil_div(n_nodes, nodes), 256, smem, (cudaStream_t)stream>>>(w->w_edge, w->b_edge, w->w_node, w->b_node, h0, h,
+                                                                                n_nodes, nf, ef, P, Q, R);
   return check_launch();
 }
 

@@ -369,13 +369,16 @@ __global__ void __launch_bounds__(TB) pq_reduce_kernel(const int32_t* rowptr, co
 
 // ------------------------------------------------------------------------------------------------
 // E. backward of the per-node projections: gh_prev = gP W_s + gQ W_d + gR W_nx, weight-gradient partials.
-//    One block = 64 nodes.  partial [gridDim][44 * (K + 1)], index o * (K+1) + k; column K is the bias sum.
+//    One block = 64 (16) nodes.  partial [gridDim][44 * (K + 1)], index o * (K+1) + k; column K is the bias sum.
 // ------------------------------------------------------------------------------------------------
+// nodes per block of the projection backward (= rows of its `partial`): 16 for small graphs (more blocks than SMs)
+__host__ __device__ inline int proj_bwd_nodes(int64_t n_nodes) { return n_nodes <= 64 * 148 * 4 ? 16 : 64; }
+template <int NODES>
 __global__ void __launch_bounds__(TB) node_project_bwd_kernel(const float* w_edge, const float* w_node, int edge_row, int node_row, int K,
                                                               const float* gP, const float* gQ, const float* gR, const float* h0,
                                                               const float* h, int64_t n_nodes, float* gh_prev, float* gh0_acc,
                                                               float* partial) {
-  constexpr int OUT = 2 * FE + FN, NODES = 64;
+  constexpr int OUT = 2 * FE + FN;
   extern __shared__ float sm[];
   float* w = sm;                       // [OUT][K]
   float* g = w + OUT * K;              // [NODES][OUT + 1]
@@ -486,7 +489,7 @@ __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, c
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
   const int64_t r_begin = (int64_t)blockIdx.z * rows_per_split, r_end = min(r_begin + rows_per_split, rows);
-  float acc[4][4] = {};
+  float2 acc[4][2] = {};                              // 4 x 4 outputs as column pairs: packed FFMA2, b pairs straight from the float4
   const int lr = tid >> 4, lc = (tid & 15) * 4;       // 16 rows x 64 columns per load wave
   for (int64_t r0 = r_begin; r0 < r_end; r0 += 16) {
     const int64_t r = r0 + lr;
@@ -500,11 +503,13 @@ __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, c
     for (int k = 0; k < 16; ++k) {
       const float4 a = *reinterpret_cast<const float4*>(&as[k][ty * 4]);
       const float4 b = *reinterpret_cast<const float4*>(&bs[k][tx * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      for (int i = 0; i < 4; ++i) {
+        acc[i][0] = pk::ffma2(b01, pk::bc(av[i]), acc[i][0]);
+        acc[i][1] = pk::ffma2(b23, pk::bc(av[i]), acc[i][1]);
+      }
     }
     __syncthreads();
   }
@@ -514,7 +519,7 @@ __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, c
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
-      if (m < M && n < Nn) out[(int64_t)m * Nn + n] = acc[i][j];
+      if (m < M && n < Nn) out[(int64_t)m * Nn + n] = (j & 1) ? acc[i][j >> 1].y : acc[i][j >> 1].x;
     }
 }
 
@@ -585,7 +590,7 @@ extern "C" int32_t gnncca_train_blocks(int64_t n_items, int32_t kind) {
   switch (kind) {
     case GNNCCA_BLOCKS_PER_EDGE: return blocks_for(n_items, tr::TB);
     case GNNCCA_BLOCKS_PER_NODE_WARP: return blocks_for(n_items, tr::NW);
-    case GNNCCA_BLOCKS_NODE_PROJECT: return (int32_t)ceil_div(n_items > 0 ? n_items : 1, 64);
+    case GNNCCA_BLOCKS_NODE_PROJECT: return (int32_t)ceil_div(n_items > 0 ? n_items : 1, tr::proj_bwd_nodes(n_items));
     case GNNCCA_BLOCKS_ROW_CHUNKS: return (int32_t)ceil_div(n_items > 0 ? n_items : 1, tr::RG_ROWS);
     default: return -1;
   }
@@ -680,13 +685,14 @@ extern "C" int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp
   if (n_nodes == 0) return GNNCCA_OK;
   if (!w || !gP || !gQ || !gR || !h || !gh_prev || !partial || (cfg->reattach_nodes && (!h0 || !gh0_acc))) return GNNCCA_ERR_BAD_ARG;
   const int K = cfg->reattach_nodes ? 2 * tr::FN : tr::FN, EIN = cfg->reattach_edges ? 2 * tr::FE : tr::FE, OUT = 2 * tr::FE + tr::FN;
-  const size_t smem = sizeof(float) * (OUT * K + 64 * (OUT + 1) + 64 * (K + 1));
-  auto kern = tr::node_project_bwd_kernel;
+  const int nodes = tr::proj_bwd_nodes(n_nodes);
+  const size_t smem = sizeof(float) * (OUT * K + nodes * (OUT + 1) + nodes * (K + 1));
+  auto kern = nodes == 16 ? tr::node_project_bwd_kernel<16> : tr::node_project_bwd_kernel<64>;
   if (smem > 48 * 1024) {
     int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (rc) return rc;
   }
-  kern<<<(unsigned)ceil_div(n_nodes, 64), tr::TB, smem, (cudaStream_t)stream>>>(w->w_edge, w->w_node, 2 * K + EIN, K + tr::FE, K, gP, gQ, gR, h0,
+  kern<<<(unsigned)ceil_div(n_nodes, nodes), tr::TB, smem, (cudaStream_t)stream>>>(w->w_edge, w->w_node, 2 * K + EIN, K + tr::FE, K, gP, gQ, gR, h0,
                                                                                h, n_nodes, gh_prev, gh0_acc, partial);
   return check_launch();
 }
