@@ -295,26 +295,17 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
             acc2.y = comb<IS_MAX>(acc2.y, fmaxf(m, 0.f));
             ++j;
           }
-          if (j + 1 < j1) {     // pairs, software-pipelined: the next pair's rows are loaded while this one is multiplied
-            float4 v[FE / 2];
+#pragma unroll 4
+          for (; j + 1 < j1; j += 2) {
+            const float4* ev = reinterpret_cast<const float4*>(&s_e[j >> 1][0]);
+            float2 m = pk::bc(r);
 #pragma unroll
-            for (int k = 0; k < FE / 2; ++k) v[k] = reinterpret_cast<const float4*>(&s_e[j >> 1][0])[k];
-#pragma unroll 2
-            for (; j + 1 < j1; j += 2) {
-              float4 nv[FE / 2];
-              const int jn = j + 3 < j1 ? j + 2 : j;          // clamp: the last iteration reloads its own rows
-#pragma unroll
-              for (int k = 0; k < FE / 2; ++k) nv[k] = reinterpret_cast<const float4*>(&s_e[jn >> 1][0])[k];
-              float2 m = pk::bc(r);
-#pragma unroll
-              for (int k = 0; k < FE / 2; ++k) {
-                m = pk::ffma2(make_float2(v[k].x, v[k].y), pk::bc(wne[2 * k]), m);
-                m = pk::ffma2(make_float2(v[k].z, v[k].w), pk::bc(wne[2 * k + 1]), m);
-              }
-              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
-#pragma unroll
-              for (int k = 0; k < FE / 2; ++k) v[k] = nv[k];
+            for (int k = 0; k < FE / 2; ++k) {
+              const float4 v = ev[k];
+              m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
+              m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
             }
+            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
           }
           if (j < j1) {
             const float* ev = &s_e[j >> 1][0];
