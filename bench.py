@@ -587,6 +587,24 @@ def main():
         cpu = {"value": E / statistics.median(times), "unit": UNIT, "cores": cores, "kind": "port",
                "sample": "%d forwards of the full %s batch (E=%d) through oracle/mpn_oracle.py, torch CPU fp32, median" % (len(times), args.workload, E)}
 
+    # graph + edge-attribute construction (train.py:257-361,450 -> build_graph_batch), timed separately: the call
+    # includes both column normalisations, the edge count pass, the tiled build kernel and its one small read-back
+    det = syn.make_detections(wl["cams"], wl["dets"], wl["frames"], seed=wl["seed"] + 100 * rank + 31, device=dev, max_dist=wl["max_dist"])
+    for _ in range(2):
+        gnncca.build_graph_batch(**det)
+    torch.cuda.synchronize()
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        gnncca.build_graph_batch(**det)
+    torch.cuda.synchronize()
+    gb_s = (time.perf_counter() - t0) / reps
+    gb_bytes = N * (2048 + 256) * 4 * 3 + E * (16 + 16 + 4 + 2 * 256 * 4 / max(1, wl["dets"]))     # normalise (2 reads + 1 write), outputs, ReID rows per tile
+    graph_build = {"value": E / gb_s, "unit": "edges built/s", "ms": gb_s * 1e3,
+                   "what": "build_graph_batch: column normalisation of both embeddings + edge_index / edge_attr / labels / ptr of %d frames" % wl["frames"],
+                   "approx_bytes": int(gb_bytes), "approx_frac_of_hbm_peak": gb_bytes / gb_s / 1e9 / peak}
+    del det
+
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "tf32" if args.math == "tf32" else "f32", "data": "synthetic",
@@ -598,7 +616,7 @@ def main():
             "clocks": sampler.result(), "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes + 8 * (wl["frames"] + 1), "d2h_bytes_per_step": d2h_bytes,
                     "steps": e2e_steps, "api": "MOTMPNet.forward_host (pinned host x/edge_index/edge_attr -> pinned host logits)"},
-            "roofline": roofline}
+            "roofline": roofline, "graph_build": graph_build}
     if cpu is not None:
         line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)

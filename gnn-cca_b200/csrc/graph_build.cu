@@ -21,18 +21,77 @@ __global__ void __launch_bounds__(256) colnorm_partial_kernel(const float* __res
   for (int64_t r = r0; r < r1; ++r) { const float v = x[r * cols + c]; acc = fmaf(v, v, acc); }
   partial[(int64_t)blockIdx.y * cols + c] = acc;
 }
+// cols % 4 == 0 and 16-byte aligned rows: a thread owns 4 adjacent columns, 4 rows in flight (same per-column row order)
+__global__ void __launch_bounds__(256) colnorm_partial4_kernel(const float* __restrict__ x, int64_t rows, int cols, float* __restrict__ partial) {
+  const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.y * CN_ROWS_PER_CHUNK;
+  const int64_t r1 = min(r0 + CN_ROWS_PER_CHUNK, rows);
+  if (c4 * 4 >= cols) return;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* px = x + (int64_t)c4 * 4;
+  int64_t r = r0;
+  for (; r + 4 <= r1; r += 4) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_stream_f4(px + (r + u) * cols);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      acc.x = fmaf(v[u].x, v[u].x, acc.x); acc.y = fmaf(v[u].y, v[u].y, acc.y);
+      acc.z = fmaf(v[u].z, v[u].z, acc.z); acc.w = fmaf(v[u].w, v[u].w, acc.w);
+    }
+  }
+  for (; r < r1; ++r) {
+    const float4 v = ld_stream_f4(px + r * cols);
+    acc.x = fmaf(v.x, v.x, acc.x); acc.y = fmaf(v.y, v.y, acc.y); acc.z = fmaf(v.z, v.z, acc.z); acc.w = fmaf(v.w, v.w, acc.w);
+  }
+  *reinterpret_cast<float4*>(partial + (int64_t)blockIdx.y * cols + c4 * 4) = acc;
+}
+// 32 columns per block; warp w sums the chunks w, w + 8, ... of its lane's column, the 8 partial sums are folded in warp order
 __global__ void __launch_bounds__(256) colnorm_final_kernel(const float* __restrict__ partial, int chunks, int cols, float* __restrict__ norm) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+  __shared__ float s_part[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
   float acc = 0.f;
-  for (int k = 0; k < chunks; ++k) acc += partial[(int64_t)k * cols + c];   // fixed order
-  norm[c] = fmaxf(sqrtf(acc), 1e-12f);                                       // clamp_min(eps), eps = 1e-12
+  if (c < cols) {
+#pragma unroll 4
+    for (int k = warp; k < chunks; k += 8) acc += __ldg(partial + (int64_t)k * cols + c);
+  }
+  s_part[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < cols) {
+    float tot = s_part[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) tot += s_part[w][lane];
+    norm[c] = fmaxf(sqrtf(tot), 1e-12f);                                     // clamp_min(eps), eps = 1e-12
+  }
 }
 __global__ void __launch_bounds__(256) colnorm_apply_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t rows, int cols,
                                                             const float* __restrict__ norm) {
   const int64_t total = rows * cols;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) out[t] = x[t] / norm[t % cols];
+}
+constexpr int CN_APPLY_ROWS = 32;
+__global__ void __launch_bounds__(256) colnorm_apply4_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t rows, int cols,
+                                                             const float* __restrict__ norm) {
+  const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c4 * 4 >= cols) return;
+  const float4 nr = *reinterpret_cast<const float4*>(norm + c4 * 4);
+  const int64_t r0 = (int64_t)blockIdx.y * CN_APPLY_ROWS, r1 = min(r0 + CN_APPLY_ROWS, rows);
+  const float* px = x + (int64_t)c4 * 4;
+  float* po = out + (int64_t)c4 * 4;
+  int64_t r = r0;
+  for (; r + 4 <= r1; r += 4) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_stream_f4(px + (r + u) * cols);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) *reinterpret_cast<float4*>(po + (r + u) * cols) = make_float4(v[u].x / nr.x, v[u].y / nr.y, v[u].z / nr.z, v[u].w / nr.w);
+  }
+  for (; r < r1; ++r) {
+    const float4 v = ld_stream_f4(px + r * cols);
+    *reinterpret_cast<float4*>(po + r * cols) = make_float4(v.x / nr.x, v.y / nr.y, v.z / nr.z, v.w / nr.w);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -95,23 +154,47 @@ __global__ void __launch_bounds__(256) graph_prepare_kernel(const int64_t* __res
 }
 
 // exclusive scan of a short int64 array (B+1 outputs), single CTA
-__global__ void __launch_bounds__(1024) scan_i64_kernel(const int64_t* __restrict__ in, int64_t n, int64_t* __restrict__ out) {
-  __shared__ int64_t s_part[1024];
-  const int t = threadIdx.x;
+// Exclusive scans of the per-frame edge and tile counts in ONE launch (block 0: edges -> edge_ptr, block 1: tiles ->
+// tile_ptr) plus the four numbers the host needs to size the outputs, next to each other for a single read back:
+// totals = {n_tiles, n_edges, max nodes per frame, max edges per frame}.
+__global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __restrict__ graph_edges, const int64_t* __restrict__ graph_tiles,
+                                                           const int64_t* __restrict__ graph_ptr, int64_t n, int64_t* __restrict__ edge_ptr,
+                                                           int64_t* __restrict__ tile_ptr, int64_t* __restrict__ totals) {
+  __shared__ int64_t s_warp[32], s_max[32];
+  const int64_t* in = blockIdx.x == 0 ? graph_edges : graph_tiles;
+  int64_t* out = blockIdx.x == 0 ? edge_ptr : tile_ptr;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int64_t per = (n + blockDim.x - 1) / blockDim.x;
   const int64_t b = min((int64_t)t * per, n), e = min(b + per, n);
-  int64_t acc = 0;
-  for (int64_t i = b; i < e; ++i) acc += in[i];
-  s_part[t] = acc;
+  int64_t acc = 0, mx = 0;
+  for (int64_t i = b; i < e; ++i) {
+    const int64_t v = in[i];
+    acc += v;
+    mx = max(mx, blockIdx.x == 0 ? v : graph_ptr[i + 1] - graph_ptr[i]);     // block 0: max edges, block 1: max nodes per frame
+  }
+  int64_t incl = acc;                              // inclusive scan of the per-thread sums: warp shuffles, then the 32 warp totals
+  for (int o = 1; o < 32; o <<= 1) { const int64_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 31) s_warp[warp] = incl;
+  if (lane == 0) s_max[warp] = mx;
   __syncthreads();
-  if (t == 0) {
-    int64_t run = 0;
-    for (int k = 0; k < (int)blockDim.x; ++k) { const int64_t v = s_part[k]; s_part[k] = run; run += v; }
-    out[n] = run;
+  if (warp == 0) {
+    int64_t w = s_warp[lane];
+    for (int o = 1; o < 32; o <<= 1) { const int64_t v = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += v; }
+    s_warp[lane] = w;                              // inclusive over warps
+    int64_t m = s_max[lane];
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) s_max[0] = m;
   }
   __syncthreads();
-  int64_t run = s_part[t];
+  int64_t run = (warp > 0 ? s_warp[warp - 1] : 0) + incl - acc;
   for (int64_t i = b; i < e; ++i) { const int64_t v = in[i]; out[i] = run; run += v; }
+  if (t == 0) {
+    const int64_t total = s_warp[31];
+    out[n] = total;
+    totals[blockIdx.x == 0 ? 1 : 0] = total;       // [0] tiles, [1] edges
+    totals[blockIdx.x == 0 ? 3 : 2] = s_max[0];    // [2] max nodes, [3] max edges
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -141,37 +224,42 @@ __global__ void __launch_bounds__(256) build_graphs_kernel(const BuildParams p) 
   const int i0 = (local / nt) * GT, j0 = (local % nt) * GT;
   const bool need_app = p.attr_mode != GNNCCA_ATTR_ONLY_DIST;
 
-  __shared__ float s_a[GT][GCH + 1];
-  __shared__ float s_b[GT][GCH + 1];
+  // ReID rows of the tile, feature-major ([k][row], row stride 36 floats = 16-byte aligned quads): the 4 sources of a thread
+  // are one LDS.128 (the same address for the whole warp), the target is lane-consecutive; arithmetic on source PAIRS (FFMA2)
+  __shared__ __align__(16) float s_a[GCH][GT + 4];
+  __shared__ __align__(16) float s_b[GCH][GT + 4];
   const int tid = threadIdx.x;
   const int tj = tid & 31;        // target within tile
-  const int ti0 = tid >> 5;       // first source within tile; this thread owns sources ti0 + 8*q, q = 0..3
-  float d2[4] = {0, 0, 0, 0}, dot[4] = {0, 0, 0, 0}, na[4] = {0, 0, 0, 0}, nb = 0.f;
+  const int ti0 = (tid >> 5) * 4; // this thread owns sources ti0 .. ti0 + 3 of the tile
+  float2 d2a = make_float2(0.f, 0.f), d2b = d2a, dota = d2a, dotb = d2a, naa = d2a, nab = d2a;
+  float nb = 0.f;
   if (need_app) {
     for (int k0 = 0; k0 < p.reid_dim; k0 += GCH) {
       for (int idx = tid; idx < GT * GCH; idx += 256) {
         const int r = idx / GCH, k = idx % GCH;
         const bool kin = (k0 + k) < p.reid_dim;
-        s_a[r][k] = (i0 + r < n && kin) ? p.reid[(a + i0 + r) * p.reid_dim + k0 + k] : 0.f;
-        s_b[r][k] = (j0 + r < n && kin) ? p.reid[(a + j0 + r) * p.reid_dim + k0 + k] : 0.f;
+        s_a[k][r] = (i0 + r < n && kin) ? p.reid[(a + i0 + r) * p.reid_dim + k0 + k] : 0.f;
+        s_b[k][r] = (j0 + r < n && kin) ? p.reid[(a + j0 + r) * p.reid_dim + k0 + k] : 0.f;
       }
       __syncthreads();
       const int kmax = min(GCH, p.reid_dim - k0);
+#pragma unroll 4
       for (int k = 0; k < kmax; ++k) {
-        const float b = s_b[tj][k];
+        const float b = s_b[k][tj];
+        const float4 av = *reinterpret_cast<const float4*>(&s_a[k][ti0]);
+        const float2 a01 = make_float2(av.x, av.y), a23 = make_float2(av.z, av.w);
         nb = fmaf(b, b, nb);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float av = s_a[ti0 + 8 * q][k];
-          const float df = (av - b) + 1e-6f;          // F.pairwise_distance: ||a - b + eps||_2, eps = 1e-6
-          d2[q] = fmaf(df, df, d2[q]);
-          dot[q] = fmaf(av, b, dot[q]);
-          na[q] = fmaf(av, av, na[q]);
-        }
+        // F.pairwise_distance: ||a - b + eps||_2, eps = 1e-6 ((a - b) first, then + eps, as torch does)
+        const float2 df01 = pk::fadd2(pk::fadd2(a01, pk::bc(-b)), pk::bc(1e-6f));
+        const float2 df23 = pk::fadd2(pk::fadd2(a23, pk::bc(-b)), pk::bc(1e-6f));
+        d2a = pk::ffma2(df01, df01, d2a); d2b = pk::ffma2(df23, df23, d2b);
+        dota = pk::ffma2(a01, pk::bc(b), dota); dotb = pk::ffma2(a23, pk::bc(b), dotb);
+        naa = pk::ffma2(a01, a01, naa); nab = pk::ffma2(a23, a23, nab);
       }
       __syncthreads();
     }
   }
+  const float d2[4] = {d2a.x, d2a.y, d2b.x, d2b.y}, dot[4] = {dota.x, dota.y, dotb.x, dotb.y}, na[4] = {naa.x, naa.y, nab.x, nab.y};
   const int j = j0 + tj;
   if (j >= n) return;
   const int cj = p.id_cam[a + j];
@@ -182,7 +270,7 @@ __global__ void __launch_bounds__(256) build_graphs_kernel(const BuildParams p) 
   const int width = (p.attr_mode == GNNCCA_ATTR_FULL) ? 4 : 2;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const int i = i0 + ti0 + 8 * q;
+    const int i = i0 + ti0 + q;
     if (i >= n) continue;
     const int ci = p.id_cam[a + i];
     if (ci == cj) continue;
@@ -227,19 +315,30 @@ extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_
   const int chunks = (int)ceil_div(rows, CN_ROWS_PER_CHUNK);
   if (chunks > 65535) return GNNCCA_ERR_UNSUPPORTED;
   float* norm = scratch + (int64_t)chunks * cols;
-  dim3 g1((unsigned)ceil_div(cols, 256), (unsigned)chunks);
-  colnorm_partial_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
-  colnorm_final_kernel<<<(unsigned)ceil_div(cols, 256), 256, 0, st>>>(scratch, chunks, cols, norm);
-  colnorm_apply_kernel<<<grid_for(rows * cols, 256), 256, 0, st>>>(emb, out, rows, cols, norm);
+  const bool vec = cols % 4 == 0 && ((((uintptr_t)emb | (uintptr_t)out | (uintptr_t)scratch) & 15) == 0) && ceil_div(rows, CN_APPLY_ROWS) <= 65535;
+  if (vec) {
+    dim3 g1((unsigned)ceil_div(cols / 4, 256), (unsigned)chunks);
+    colnorm_partial4_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
+  } else {
+    dim3 g1((unsigned)ceil_div(cols, 256), (unsigned)chunks);
+    colnorm_partial_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
+  }
+  colnorm_final_kernel<<<(unsigned)ceil_div(cols, 32), 256, 0, st>>>(scratch, chunks, cols, norm);
+  if (vec) {
+    dim3 g3((unsigned)ceil_div(cols / 4, 256), (unsigned)ceil_div(rows, CN_APPLY_ROWS));
+    colnorm_apply4_kernel<<<g3, 256, 0, st>>>(emb, out, rows, cols, norm);
+  } else {
+    colnorm_apply_kernel<<<grid_for(rows * cols, 256), 256, 0, st>>>(emb, out, rows, cols, norm);
+  }
   return check_launch(3);
 }
 
 extern "C" int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes) {
   // cam_cnt, cam_first, order (int32 x N each) + src_off (int64 x N) + graph_edges, graph_tiles (int64 x B) + tile_ptr (B+1)
-  return (n_nodes + 8) * (3 * 4 + 8) + (3 * n_graphs + 4) * 8 + 1024;
+  return (n_nodes + 8) * (3 * 4 + 8) + (3 * n_graphs + 8) * 8 + 1024;
 }
 
-struct PrepLayout { int32_t* cam_cnt; int32_t* cam_first; int32_t* order; int64_t* src_off; int64_t* graph_edges; int64_t* graph_tiles; int64_t* tile_ptr; };
+struct PrepLayout { int32_t* cam_cnt; int32_t* cam_first; int32_t* order; int64_t* src_off; int64_t* graph_edges; int64_t* graph_tiles; int64_t* tile_ptr; int64_t* totals; };
 static PrepLayout prep_layout(void* scratch, int64_t n_graphs, int64_t n_nodes) {
   char* p = (char*)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
   PrepLayout L;
@@ -248,6 +347,7 @@ static PrepLayout prep_layout(void* scratch, int64_t n_graphs, int64_t n_nodes) 
   L.graph_edges = (int64_t*)p; p += 8 * (n_graphs + 1);
   L.graph_tiles = (int64_t*)p; p += 8 * (n_graphs + 1);
   L.tile_ptr = (int64_t*)p; p += 8 * (n_graphs + 2);
+  L.totals = (int64_t*)p; p += 8 * 4;
   L.cam_cnt = (int32_t*)p; p += 4 * n8;
   L.cam_first = (int32_t*)p; p += 4 * n8;
   L.order = (int32_t*)p;
@@ -265,9 +365,8 @@ extern "C" int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t*
   PrepLayout L = prep_layout(scratch, n_graphs, n_nodes);
   graph_prepare_kernel<<<(unsigned)n_graphs, 256, 0, st>>>(graph_ptr, id_cam, L.cam_cnt, L.cam_first, L.src_off, L.order,
                                                            L.graph_edges, L.graph_tiles, GT);
-  scan_i64_kernel<<<1, 1024, 0, st>>>(L.graph_edges, n_graphs, edge_ptr);
-  scan_i64_kernel<<<1, 1024, 0, st>>>(L.graph_tiles, n_graphs, L.tile_ptr);
-  return check_launch(3);
+  scan_counts_kernel<<<2, 1024, 0, st>>>(L.graph_edges, L.graph_tiles, graph_ptr, n_graphs, edge_ptr, L.tile_ptr, L.totals);
+  return check_launch(2);
 }
 
 extern "C" int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64_t n_graphs, int64_t n_nodes,
@@ -289,8 +388,9 @@ extern "C" int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge
   return check_launch();
 }
 
-// tile_ptr[B] (total number of 32x32 tiles) lives in the scratch; expose where so the host can read it with edge_ptr[B]
+// {n_tiles, n_edges, max nodes per frame, max edges per frame} of the last gnncca_graph_edge_counts live in the scratch, next to
+// each other: the host reads them with ONE copy to size step 2 (and the capacity class of the fused message-passing kernel)
 extern "C" const int64_t* gnncca_graph_tile_total_ptr(const void* scratch, int64_t n_graphs, int64_t n_nodes) {
   PrepLayout L = prep_layout(const_cast<void*>(scratch), n_graphs, n_nodes);
-  return L.tile_ptr + n_graphs;
+  return L.totals;
 }

@@ -24,6 +24,20 @@ class Batch:
             setattr(self, k, v)
 
     @property
+    def batch(self) -> torch.Tensor:
+        """PyG's ``Batch.batch`` (frame index of every node), built from ``ptr`` on first use: the MPN never reads it."""
+        b = self.__dict__.get("_batch_vec")
+        if b is None:
+            counts = self.ptr[1:] - self.ptr[:-1]
+            b = torch.repeat_interleave(torch.arange(counts.numel(), device=self.ptr.device), counts, output_size=int(self.x.size(0)))
+            self.__dict__["_batch_vec"] = b
+        return b
+
+    @batch.setter
+    def batch(self, value) -> None:
+        self.__dict__["_batch_vec"] = value
+
+    @property
     def num_nodes(self) -> int:
         return int(self.x.size(0))
 
@@ -80,15 +94,13 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     edge_ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
     _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
                                             _lib.ptr(scratch), nbytes, _stream()), "graph_edge_counts")
-    # the output size is data dependent: one 16-byte read back (the reference syncs several times per FRAME)
-    tile_total_addr = lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N)
-    off = (tile_total_addr - scratch.data_ptr()) // 8
-    counts = graph_ptr[1:] - graph_ptr[:-1]
-    ecounts = edge_ptr[1:] - edge_ptr[:-1]
-    zero = torch.zeros((), dtype=torch.int64, device=dev)
-    totals = torch.stack([edge_ptr[B], scratch[off], counts.max() if B > 0 else zero, ecounts.max() if B > 0 else zero]).cpu()
-    E, n_tiles = int(totals[0]), int(totals[1])
-    caps = (int(totals[2]), int(totals[3]))      # exact frame maxima: sizes the fused all-steps kernel without guessing
+    # the output size is data dependent: one 32-byte read back (the reference syncs several times per FRAME)
+    if B > 0:
+        off = (lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N) - scratch.data_ptr()) // 8
+        n_tiles, E, max_n, max_e = (int(v) for v in scratch[off:off + 4].tolist())
+    else:
+        n_tiles = E = max_n = max_e = 0
+    caps = (max_n, max_e)      # exact frame maxima: sizes the fused all-steps kernel without guessing
 
     width = 4 if mode == "full" else 2
     edge_index = torch.empty((2, E), dtype=torch.int64, device=dev)
@@ -98,6 +110,5 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
                                        _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
                                        int(reid.size(1)), attr_mode, _lib.ptr(scratch), _lib.ptr(edge_index),
                                        _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
-    batch_vec = torch.repeat_interleave(torch.arange(B, device=dev), counts, output_size=N)
-    return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64, batch=batch_vec,
+    return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64,
                  ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps, gnncca_trusted=True)

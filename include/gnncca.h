@@ -333,7 +333,8 @@ int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, flo
  * per detection (row order of the frame's table).  Writes edge_ptr[B+1] (int64 exclusive scan of the
  * per-frame directed edge counts n_g^2 - sum_c n_{g,c}^2) and fills `scratch`
  * (gnncca_graph_prepare_scratch_bytes) with the per-detection enumeration tables step 2 needs.
- * The caller reads edge_ptr[B] (= E) and *gnncca_graph_tile_total_ptr() (= n_tiles) to size step 2. */
+ * gnncca_graph_tile_total_ptr() points at four int64 inside the scratch: {n_tiles, E, max nodes per frame, max edges per
+ * frame}; the caller reads them with one copy to size step 2 (and the capacity class of gnncca_mp_fused_fwd). */
 int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes);
 int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t* id_cam, int64_t n_graphs, int64_t n_nodes,
                              int64_t* edge_ptr, void* scratch, int64_t scratch_bytes, void* stream);
