@@ -211,7 +211,7 @@ struct BuildParams {
   int64_t* edge_index; int64_t n_edges; float* edge_attr; float* edge_labels;
 };
 
-__global__ void __launch_bounds__(256) build_graphs_kernel(const BuildParams p) {
+__global__ void __launch_bounds__(256, 3) build_graphs_kernel(const BuildParams p) {
   // which frame does this tile belong to: binary search in tile_ptr
   const int64_t tb = blockIdx.x;
   int64_t lo = 0, hi = p.n_graphs;  // invariant: tile_ptr[lo] <= tb < tile_ptr[hi]
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(256) build_graphs_kernel(const BuildParams p) 
         s_b[k][r] = (j0 + r < n && kin) ? p.reid[(a + j0 + r) * p.reid_dim + k0 + k] : 0.f;
       }
       __syncthreads();
-      const int kmax = min(GCH, p.reid_dim - k0);
+      const int kmax = (i0 + ti0 < n) ? min(GCH, p.reid_dim - k0) : 0;     // a warp whose four sources lie beyond the frame only stages
 #pragma unroll 4
       for (int k = 0; k < kmax; ++k) {
         const float b = s_b[k][tj];
