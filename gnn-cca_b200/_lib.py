@@ -57,6 +57,8 @@ SIGNATURES = {
     "gnncca_mp_step_workspace_bytes": (i64, [C.POINTER(MpCfg), i64, i64]),
     "gnncca_mp_step_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, i64, i64, vp, vp, vp, vp, vp,
                                      vp, vp, vp, vp, vp, i64, vp]),
+    "gnncca_mp_step_fwd_attr": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, i64, i64, vp, vp, vp, vp, i32, vp, vp, vp, vp,
+                                          vp, vp, vp, vp, i64, vp]),
     "gnncca_mp_fused_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i32, vp, i64, vp, vp, vp, vp, vp, i64, i64,
                                       vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp]),
     "gnncca_mpn_forward_frames": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp,

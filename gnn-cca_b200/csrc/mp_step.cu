@@ -46,6 +46,9 @@ struct StepParams {
   int32_t* counters;     // [num_tiles] arrival counters, zeroed by the host entry before the launch
   int phase;             // position of local edge 0 inside a tile of the GLOBAL edge numbering (edge-partitioned graphs)
   const int32_t* guard;  // optional CSR flags (gnncca_csr_from_edge_index): the kernel is a no-op when any is set
+  // ATTR variants: the encoded edge features e0 = ReLU(W_enc attr + b_enc) (mpn.py:116-126, 4 -> FE) are computed here from
+  // the raw attributes (16 B/edge) instead of being written by one kernel and read back by this one (2 x 24 B/edge)
+  const float* attr; const float* w_enc; const float* b_enc;
 };
 
 
@@ -78,44 +81,56 @@ __device__ __forceinline__ void publish_partial(const StepParams& p, int tile, i
   }
 }
 
-template <int FE, bool REATT_E>
+constexpr int FA = 4;   // raw attribute width of the ATTR variants (one 16-byte load per edge)
+
+template <int FE, bool REATT_E, bool ATTR>
 struct RawPair {       // what phase A reads for one edge pair, requested one tile ahead
   int sa, sb, da, db;
-  float2 ea[FE / 2], eb[FE / 2];
-  float2 xa[REATT_E ? FE / 2 : 1], xb[REATT_E ? FE / 2 : 1];
+  float2 ea[FE / 2], eb[FE / 2];                                  // latent edge features (not read in step 1 of an ATTR variant)
+  float2 xa[(REATT_E && !ATTR) ? FE / 2 : 1], xb[(REATT_E && !ATTR) ? FE / 2 : 1];   // stored initial features
+  float4 ta[ATTR ? 1 : 1], tb[ATTR ? 1 : 1];                      // raw attributes
 };
 
-template <int FE, bool REATT_E>
-__device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPair<FE, REATT_E>& r) {
+template <int FE, bool REATT_E, bool ATTR>
+__device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPair<FE, REATT_E, ATTR>& r) {
   const bool va = i0 >= 0 && i0 < p.n_edges, vb = i0 + 1 >= 0 && i0 + 1 < p.n_edges;
+  const bool latent = !ATTR || p.e_in != nullptr;
   r.sa = r.sb = r.da = r.db = -1;
   if (va) {
     r.sa = ld_stream_i32(p.src + i0); r.da = ld_stream_i32(p.dst + i0);
+    if (latent) {
 #pragma unroll
-    for (int k = 0; k < FE / 2; ++k) r.ea[k] = ld_stream_f2(p.e_in + i0 * FE + 2 * k);
-    if (REATT_E) {
+      for (int k = 0; k < FE / 2; ++k) r.ea[k] = ld_stream_f2(p.e_in + i0 * FE + 2 * k);
+    }
+    if (REATT_E && !ATTR) {
 #pragma unroll
       for (int k = 0; k < FE / 2; ++k) r.xa[k] = ld_stream_f2(p.e0 + i0 * FE + 2 * k);
     }
+    if (ATTR) r.ta[0] = ld_stream_f4(p.attr + i0 * FA);
   }
   if (vb) {
     r.sb = ld_stream_i32(p.src + i0 + 1); r.db = ld_stream_i32(p.dst + i0 + 1);
+    if (latent) {
 #pragma unroll
-    for (int k = 0; k < FE / 2; ++k) r.eb[k] = ld_stream_f2(p.e_in + (i0 + 1) * FE + 2 * k);
-    if (REATT_E) {
+      for (int k = 0; k < FE / 2; ++k) r.eb[k] = ld_stream_f2(p.e_in + (i0 + 1) * FE + 2 * k);
+    }
+    if (REATT_E && !ATTR) {
 #pragma unroll
       for (int k = 0; k < FE / 2; ++k) r.xb[k] = ld_stream_f2(p.e0 + (i0 + 1) * FE + 2 * k);
     }
+    if (ATTR) r.tb[0] = ld_stream_f4(p.attr + (i0 + 1) * FA);
   }
 }
 
-template <int FE, int HC, bool REATT_E, bool IS_MAX>
+template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR>
 __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 1;
   static_assert(FE % 2 == 0 && (FE * EIN) % 4 == 0, "weights are read as float4");
   __shared__ __align__(16) float s_wee[FE * EIN];
   __shared__ float s_wne[FE][FN];
+  __shared__ __align__(16) float s_wenc[ATTR ? FE * FA : 4];
+  __shared__ float s_benc[ATTR ? FE : 1];
   __shared__ __align__(16) float s_c1[HCS * FE];
   __shared__ float s_b1[HCS], s_c2[HCS], s_b2;
   __shared__ __align__(16) float s_e[TILE / 2][2 * FE];      // [pair][k][2]
@@ -132,6 +147,10 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
     const int edge_row = 2 * K + EIN, node_row = K + FE;
     for (int idx = tid; idx < FE * EIN; idx += THREADS) s_wee[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
     for (int idx = tid; idx < FE * FN; idx += THREADS) s_wne[idx / FN][idx % FN] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
+    if (ATTR) {
+      for (int idx = tid; idx < FE * FA; idx += THREADS) s_wenc[idx] = p.w_enc[idx];
+      for (int idx = tid; idx < FE; idx += THREADS) s_benc[idx] = p.b_enc[idx];
+    }
     if (classify) {
       for (int c = tid; c < HC; c += THREADS) {
         float scale = 1.f, shift = 0.f;
@@ -146,8 +165,8 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
       if (tid == 0) s_b2 = p.w.b_c2[0];
     }
   }
-  RawPair<FE, REATT_E> cur;
-  load_raw<FE, REATT_E>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
+  RawPair<FE, REATT_E, ATTR> cur;
+  load_raw<FE, REATT_E, ATTR>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
   __syncthreads();
   float wne[FE];
 #pragma unroll
@@ -175,15 +194,38 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
     {
       float2 ein[EIN];
       constexpr int OFF = REATT_E ? FE : 0;
-      if (REATT_E) {  // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
+      float2 e0p[ATTR ? FE : 1];
+      if (ATTR) {     // e0 = ReLU(W_enc attr + b_enc) for both edges of the pair (the FMA order of the stand-alone encoder kernel)
+        const float2 t0 = make_float2(cur.ta[0].x, cur.tb[0].x), t1 = make_float2(cur.ta[0].y, cur.tb[0].y);
+        const float2 t2 = make_float2(cur.ta[0].z, cur.tb[0].z), t3 = make_float2(cur.ta[0].w, cur.tb[0].w);
 #pragma unroll
-        for (int k = 0; k < FE / 2; ++k) {
-          ein[2 * k] = make_float2(cur.xa[k].x, cur.xb[k].x); ein[2 * k + 1] = make_float2(cur.xa[k].y, cur.xb[k].y);
+        for (int o = 0; o < FE; ++o) {
+          const float4 w4 = *reinterpret_cast<const float4*>(&s_wenc[o * FA]);
+          float2 acc = pk::bc(s_benc[o]);
+          acc = pk::ffma2(t0, pk::bc(w4.x), acc); acc = pk::ffma2(t1, pk::bc(w4.y), acc);
+          acc = pk::ffma2(t2, pk::bc(w4.z), acc); acc = pk::ffma2(t3, pk::bc(w4.w), acc);
+          e0p[o] = pk::relu2(acc);
         }
       }
+      if (REATT_E) {  // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
+        if (ATTR) {
 #pragma unroll
-      for (int k = 0; k < FE / 2; ++k) {
-        ein[OFF + 2 * k] = make_float2(cur.ea[k].x, cur.eb[k].x); ein[OFF + 2 * k + 1] = make_float2(cur.ea[k].y, cur.eb[k].y);
+          for (int k = 0; k < FE; ++k) ein[k] = e0p[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < FE / 2; ++k) {
+            ein[2 * k] = make_float2(cur.xa[k].x, cur.xb[k].x); ein[2 * k + 1] = make_float2(cur.xa[k].y, cur.xb[k].y);
+          }
+        }
+      }
+      if (ATTR && p.e_in == nullptr) {   // step 1: the latent features are the encoded ones
+#pragma unroll
+        for (int k = 0; k < FE; ++k) ein[OFF + k] = e0p[k];
+      } else {
+#pragma unroll
+        for (int k = 0; k < FE / 2; ++k) {
+          ein[OFF + 2 * k] = make_float2(cur.ea[k].x, cur.eb[k].x); ein[OFF + 2 * k + 1] = make_float2(cur.ea[k].y, cur.eb[k].y);
+        }
       }
       float2 en[8];
       {
@@ -242,14 +284,15 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
       }
     }
     const int next_tile = tile + gridDim.x;
-    if (next_tile < p.num_tiles) load_raw<FE, REATT_E>(p, (int64_t)next_tile * TILE - p.phase + 2 * tid, cur);
+    if (next_tile < p.num_tiles) load_raw<FE, REATT_E, ATTR>(p, (int64_t)next_tile * TILE - p.phase + 2 * tid, cur);
     {  // the tile after that: pull its lines into L2 now (one 128-byte line per thread), DRAM latency off the critical path
       const int64_t far = (int64_t)next_tile + gridDim.x;
       if (far < p.num_tiles) {
         const int64_t fb = max(far * TILE - p.phase, (int64_t)0);
         const float* pe = p.e_in + fb * FE + (int64_t)tid * 32;
-        if (tid < TILE * FE / 32 && pe < p.e_in + p.n_edges * FE) prefetch_l2(pe);
-        if (REATT_E) {
+        if (p.e_in != nullptr && tid < TILE * FE / 32 && pe < p.e_in + p.n_edges * FE) prefetch_l2(pe);
+        if (ATTR && tid < TILE * FA / 32 && p.attr + fb * FA + (int64_t)tid * 32 < p.attr + p.n_edges * FA) prefetch_l2(p.attr + fb * FA + (int64_t)tid * 32);
+        if (REATT_E && !ATTR) {
           const float* p0 = p.e0 + fb * FE + (int64_t)tid * 32;
           if (tid < TILE * FE / 32 && p0 < p.e0 + p.n_edges * FE) prefetch_l2(p0);
         }
@@ -368,22 +411,26 @@ template <int FE, int HC>
 static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
   const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * 3);
   const bool is_max = sp.agg == GNNCCA_AGG_MAX;
+  const bool attr = sp.attr != nullptr;
+#define GNNCCA_STEP(R, M, A) mp_step_fwd_kernel<FE, HC, R, M, A><<<grid, THREADS, 0, st>>>(sp)
   if (reatt_e) {
-    if (is_max) mp_step_fwd_kernel<FE, HC, true, true><<<grid, THREADS, 0, st>>>(sp);
-    else mp_step_fwd_kernel<FE, HC, true, false><<<grid, THREADS, 0, st>>>(sp);
+    if (is_max) { if (attr) GNNCCA_STEP(true, true, true); else GNNCCA_STEP(true, true, false); }
+    else { if (attr) GNNCCA_STEP(true, false, true); else GNNCCA_STEP(true, false, false); }
   } else {
-    if (is_max) mp_step_fwd_kernel<FE, HC, false, true><<<grid, THREADS, 0, st>>>(sp);
-    else mp_step_fwd_kernel<FE, HC, false, false><<<grid, THREADS, 0, st>>>(sp);
+    if (is_max) { if (attr) GNNCCA_STEP(false, true, true); else GNNCCA_STEP(false, true, false); }
+    else { if (attr) GNNCCA_STEP(false, false, true); else GNNCCA_STEP(false, false, false); }
   }
+#undef GNNCCA_STEP
   return check_launch();
 }
 
 extern "C" int32_t gnncca_mp_step_tile(void) { return TILE; }
 
-extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
-                                  const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
-                                  const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
-                                  float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream) {
+static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
+                        const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
+                        const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
+                        float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream,
+                        const float* attr, const float* w_enc, const float* b_enc) {
   if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   if (h_out && n_nodes > 0) {  // nodes without out-edges aggregate to 0 (torch_scatter semantics)
@@ -391,12 +438,12 @@ extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weig
     if (rc) return rc;
   }
   if (n_edges == 0) return GNNCCA_OK;
-  if (!rowptr || !src || !dst || !P || !Q || !R || !e_in || !e_out || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
-  if (cfg->reattach_edges && !e0) return GNNCCA_ERR_BAD_ARG;
+  if (!rowptr || !src || !dst || !P || !Q || !R || !e_out || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
+  if (attr ? (!w_enc || !b_enc || (((uintptr_t)attr) & 15) != 0) : (!e_in || (cfg->reattach_edges && !e0))) return GNNCCA_ERR_BAD_ARG;
   if (logits && cfg->cls_hidden > 0 && (!w->w_c1 || !w->b_c1 || !w->w_c2 || !w->b_c2)) return GNNCCA_ERR_BAD_ARG;
   if (cfg->agg < GNNCCA_AGG_SUM || cfg->agg > GNNCCA_AGG_MAX) return GNNCCA_ERR_BAD_ARG;
   if (cfg->f_node != FN) return GNNCCA_ERR_UNSUPPORTED;
-  if (((uintptr_t)e_in | (uintptr_t)e_out | (uintptr_t)(e0 ? e0 : e_in)) & 7) return GNNCCA_ERR_BAD_ARG;
+  if (((uintptr_t)e_in | (uintptr_t)e_out | (uintptr_t)e0) & 7) return GNNCCA_ERR_BAD_ARG;
   if (((uintptr_t)P | (uintptr_t)Q) & 15) return GNNCCA_ERR_BAD_ARG;
   if (workspace_bytes < gnncca_mp_step_workspace_bytes(cfg, n_nodes, n_edges) || !workspace) return GNNCCA_ERR_WORKSPACE;
 
@@ -404,6 +451,7 @@ extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weig
   sp.rowptr = rowptr; sp.src = src; sp.dst = dst; sp.n_nodes = n_nodes; sp.n_edges = n_edges;
   sp.P = P; sp.Q = Q; sp.R = R; sp.e0 = e0; sp.e_in = e_in; sp.e_out = e_out; sp.h_out = h_out; sp.logits = logits;
   sp.guard = guard_flags;
+  sp.attr = attr; sp.w_enc = w_enc; sp.b_enc = b_enc;
   sp.w = *w; sp.agg = cfg->agg; sp.nf = cfg->reattach_nodes ? 2 : 1;
   if (cfg->edge_phase < 0 || cfg->edge_phase >= TILE) return GNNCCA_ERR_BAD_ARG;
   sp.phase = cfg->edge_phase;
@@ -418,4 +466,23 @@ extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weig
   const bool re = cfg->reattach_edges != 0;
   if (cfg->f_edge == 6 && cfg->cls_hidden == 4) return launch_step<6, 4>(sp, re, st);
   return GNNCCA_ERR_UNSUPPORTED;
+}
+
+extern "C" int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
+                                  const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
+                                  const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
+                                  float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream) {
+  return mp_step_impl(cfg, w, rowptr, src, dst, n_nodes, n_edges, P, Q, R, e0, e_in, e_out, h_out, logits, guard_flags, workspace, workspace_bytes,
+                      stream, nullptr, nullptr, nullptr);
+}
+
+extern "C" int gnncca_mp_step_fwd_attr(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr,
+                                       const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
+                                       const float* Q, const float* R, const float* edge_attr, int32_t edge_in_dim, const float* w_enc_edge,
+                                       const float* b_enc_edge, const float* e_in, float* e_out, float* h_out, float* logits,
+                                       const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream) {
+  if (edge_in_dim != FA) return GNNCCA_ERR_UNSUPPORTED;
+  if (!edge_attr && n_edges > 0) return GNNCCA_ERR_BAD_ARG;
+  return mp_step_impl(cfg, w, rowptr, src, dst, n_nodes, n_edges, P, Q, R, nullptr, e_in, e_out, h_out, logits, guard_flags, workspace,
+                      workspace_bytes, stream, edge_attr, w_enc_edge, b_enc_edge);
 }

@@ -276,7 +276,11 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
 
     # ------------------------------------------------------------------ general path: one fused launch per step
     guard = _lib.ptr(plan.flags) if optimistic else 0
-    e = small_mlp_rows(model.encoder.edge_mlp, ea_sorted)
+    enc_e = model.encoder.edge_mlp
+    # edge encoder folded into the step kernel (gnncca_mp_step_fwd_attr): Linear(4, f_edge) + ReLU, latents not requested
+    fold = (L > 0 and not return_latents and len(enc_e.layer_specs) == 1 and enc_e.layer_specs[0].relu and enc_e.layer_specs[0].bn is None
+            and int(ea_sorted.size(1)) == 4 and ea_sorted.is_contiguous() and ea_sorted.data_ptr() % 16 == 0)
+    e = None if fold else small_mlp_rows(enc_e, ea_sorted)
     if prof is not None:
         prof.mark("encoder_edge")
     h0, e0 = h, e
@@ -289,19 +293,27 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), N, E))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         keep = return_latents or model.reattach_initial_edges
+        le = enc_e.linear(0) if fold else None
         for step in range(1, L + 1):
             _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P),
                                                _lib.ptr(Q), _lib.ptr(R), _stream()), "node_project")
             last = step == L
             classify = step >= first_class_step
-            e_out = torch.empty_like(e) if (keep and (step == 1 or return_latents)) else e   # in place unless e0 must survive
             h_out = None if (last and not return_latents) else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
             logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if classify else None
-            _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
-                                              _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
-                                              _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e), _lib.ptr(e_out),
-                                              _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()),
-                       "mp_step_fwd")
+            if fold and (step == 1 or model.reattach_initial_edges):
+                e_out = torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e
+                _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
+                                                       _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea_sorted), 4,
+                                                       _lib.ptr(le.weight), _lib.ptr(le.bias), _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out),
+                                                       _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd_attr")
+            else:
+                e_out = torch.empty_like(e) if (keep and (step == 1 or return_latents)) else e   # in place unless e0 must survive
+                _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
+                                                  _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
+                                                  _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e), _lib.ptr(e_out),
+                                                  _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()),
+                           "mp_step_fwd")
             e = e_out
             if h_out is not None:
                 h = h_out

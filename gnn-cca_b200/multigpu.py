@@ -148,11 +148,18 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     if plan.perm is not None:
         raise ValueError("the local edge slice must be source-major")
     h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math)
-    e = engine.small_mlp_rows(model.encoder.edge_mlp, edge_attr_local.contiguous())
+    enc_e = model.encoder.edge_mlp
+    ea = edge_attr_local.contiguous()
+    L = model.num_enc_steps
+    # edge encoder folded into the step kernel when it is the shipped Linear(4, f_edge) + ReLU (gnncca_mp_step_fwd_attr)
+    fold = (L > 0 and len(enc_e.layer_specs) == 1 and enc_e.layer_specs[0].relu and enc_e.layer_specs[0].bn is None
+            and int(ea.size(1)) == 4 and ea.data_ptr() % 16 == 0)
+    e = None if fold else engine.small_mlp_rows(enc_e, ea)
+    le = enc_e.linear(0) if fold else None
     h0, e0 = h, e
     sb = engine.StepBinding(model, math)
     sb.cfg.edge_phase = int(edge_base) % int(_lib.load().gnncca_mp_step_tile())      # tile the local slice like the whole graph: bit-identical reductions
-    L, k = model.num_enc_steps, model.num_class_steps
+    k = model.num_class_steps
     first = L - k + 1
     outs: List[torch.Tensor] = []
     if L == 0:
@@ -166,12 +173,19 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
         _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
                                            _stream()), "node_project")
         last = step == L
-        e_out = torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e
         h_out = None if last else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
         logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if step >= first else None
-        _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
-                                          _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
-                                          _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+        if fold and (step == 1 or model.reattach_initial_edges):
+            e_out = torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e
+            _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
+                                                   _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
+                                                   _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes,
+                                                   _stream()), "mp_step_fwd_attr")
+        else:
+            e_out = torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e
+            _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
+                                              _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
+                                              _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
         e = e_out
         if logits is not None:
             outs.append(logits)

@@ -164,6 +164,16 @@ int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                        const float* e0, const float* e_in, float* e_out, float* h_out, float* logits,
                        const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* The same step with the EDGE ENCODER folded in (mpn.py:116-126, Linear(4, f_edge) + ReLU): the initial edge features
+ * e0 = ReLU(w_enc_edge edge_attr + b_enc_edge) are computed from the raw attributes [E, 4] (16-byte aligned) instead of being
+ * written by gnncca_edge_mlp and read back.  e_in == NULL: this is step 1 (the latent edge features are e0);
+ * reattach_edges: e0 is recomputed at every step from edge_attr.  edge_in_dim != 4: GNNCCA_ERR_UNSUPPORTED. */
+int gnncca_mp_step_fwd_attr(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, const int32_t* src,
+                            const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P, const float* Q, const float* R,
+                            const float* edge_attr, int32_t edge_in_dim, const float* w_enc_edge, const float* b_enc_edge,
+                            const float* e_in, float* e_out, float* h_out, float* logits, const int32_t* guard_flags,
+                            void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ALL message-passing steps for a batch of SMALL frame graphs in one launch (MOTMPNet.forward, mpn.py:270-299,
  * after the node encoder): edge encoder (Linear(edge_in_dim, f_edge)+ReLU), num_steps x (edge update, node
  * update), classifier at steps >= first_class_step.  One persistent CTA per SM runs up to 8 warp groups; a
