@@ -254,11 +254,11 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
         }
         en[o] = pk::relu2(acc);
       }
-      if (va) {
+      if (va && p.e_out != nullptr) {       // NULL in the last step of an inference forward: nothing reads e^L (mpn.py:288-299)
 #pragma unroll
         for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + i0 * FE + k, make_float2(en[k].x, en[k + 1].x));
       }
-      if (vb) {
+      if (vb && p.e_out != nullptr) {
 #pragma unroll
         for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + (i0 + 1) * FE + k, make_float2(en[k].y, en[k + 1].y));
       }
@@ -438,7 +438,8 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
     if (rc) return rc;
   }
   if (n_edges == 0) return GNNCCA_OK;
-  if (!rowptr || !src || !dst || !P || !Q || !R || !e_out || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
+  if (!rowptr || !src || !dst || !P || !Q || !R || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
+  if (!e_out && (h_out || !logits)) return GNNCCA_ERR_BAD_ARG;      // e_out may only be dropped when the step just classifies
   if (attr ? (!w_enc || !b_enc || (((uintptr_t)attr) & 15) != 0) : (!e_in || (cfg->reattach_edges && !e0))) return GNNCCA_ERR_BAD_ARG;
   if (logits && cfg->cls_hidden > 0 && (!w->w_c1 || !w->b_c1 || !w->w_c2 || !w->b_c2)) return GNNCCA_ERR_BAD_ARG;
   if (cfg->agg < GNNCCA_AGG_SUM || cfg->agg > GNNCCA_AGG_MAX) return GNNCCA_ERR_BAD_ARG;

@@ -175,14 +175,15 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
         last = step == L
         h_out = None if last else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
         logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if step >= first else None
+        dead_e = last and logits is not None                 # e^L is never read
         if fold and (step == 1 or model.reattach_initial_edges):
-            e_out = torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e
+            e_out = None if dead_e else (torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e)
             _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                                    _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
                                                    _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes,
                                                    _stream()), "mp_step_fwd_attr")
         else:
-            e_out = torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e
+            e_out = None if dead_e else (torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e)
             _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                               _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
                                               _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")

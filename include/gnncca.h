@@ -156,7 +156,8 @@ int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes
  * segments that span tiles are combined in tile order by the last tile to arrive.
  * e_out may alias e_in.  h_out may be NULL (last step: the node update is dead, mpn.py:288-299).
  * guard_flags (optional): the flags[] of gnncca_csr_from_edge_index; when any is set the launch is a
- * no-op, so a caller may enqueue the whole forward before reading the flags back. */
+ * no-op, so a caller may enqueue the whole forward before reading the flags back.  * e_out may be NULL in a step that only classifies (h_out == NULL and logits != NULL: the last step of an inference
+ * forward), whose updated edge features nobody reads. */
 int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                        const int32_t* rowptr, const int32_t* src, const int32_t* dst,
                        int64_t n_nodes, int64_t n_edges,
