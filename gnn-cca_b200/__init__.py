@@ -13,6 +13,7 @@ from . import multigpu
 from .loss import compute_loss_acc, loss_stats, LossStats
 from . import postprocess
 from .graphs import GraphedTrainStep
+from . import detections
 from .postprocess import decide_and_cluster, ground_truth_clusters, frame_clusters
 
 __all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer", "compute_loss_acc", "loss_stats", "LossStats", "decide_and_cluster", "ground_truth_clusters", "frame_clusters", "GraphedTrainStep"]

@@ -79,6 +79,8 @@ SIGNATURES = {
     "gnncca_bce_stats_fwd": (C.c_int, [C.POINTER(vp), i32, vp, i64, C.c_float, i32, C.c_float, C.c_float, vp, vp, vp, vp]),
     "gnncca_bce_stats_bwd": (C.c_int, [C.POINTER(vp), C.POINTER(vp), i32, vp, i64, C.c_float, vp, vp]),
     "gnncca_frame_clusters": (C.c_int, [vp, i32, vp, i64, vp, vp, i64, i64, i32, vp, vp, vp, vp, vp, vp]),
+    "gnncca_foot_to_world": (C.c_int, [vp, vp, vp, vp, vp, i32, i64, vp, vp, vp, vp]),
+    "gnncca_frame_valid": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),
     "gnncca_edge_mlp": (C.c_int, [vp, vp, i64, i32, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32), vp]),
     "gnncca_colnorm_scratch_bytes": (i64, [i64, i32]),
     "gnncca_colnorm": (C.c_int, [vp, vp, i64, i32, vp, vp]),

@@ -363,6 +363,21 @@ int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64
                         int32_t attr_mode, const void* scratch, int64_t* edge_index, float* edge_attr,
                         float* edge_labels, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Detection tables -> device tensors: libs/datasets.py:99-134, libs/utils.py:211-225.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Ground-plane coordinates of every detection: bottom-centre of the box (xmin + round(width / 2), ymax), width = xmax - xmin
+ * (datasets.py:95,101-102), through the image->world homography H[id_cam] ([n_cams][9] row-major float64):
+ * prj = H [x, y, 1]^T, xw = prj0 / prj2, yw = prj1 / prj2 (utils.py:211-225).  float64.  flags[0] |= 1: camera id out of range. */
+int gnncca_foot_to_world(const double* xmin, const double* xmax, const double* ymax, const int32_t* id_cam, const double* H,
+                         int32_t n_cams, int64_t n_dets, double* xw, double* yw, int32_t* flags, void* stream);
+
+/* valid[f] = 1 iff frame f (rows perm[frame_ptr[f] .. frame_ptr[f+1]) of the table) has detections from more than one camera
+ * and an identity that occurs more than once (datasets.py:126-134).  frame_ptr / perm: gnncca_csr_sort on the frame numbers. */
+int gnncca_frame_valid(const int32_t* frame_ptr, const int32_t* perm, const int32_t* id_cam, const int64_t* ids, int64_t n_frames,
+                       uint8_t* valid, void* stream);
+
 #pragma GCC visibility pop
 #ifdef __cplusplus
 }

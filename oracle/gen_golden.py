@@ -391,6 +391,48 @@ def gen_post():
             name, n_nodes, len(lab), int(predictions.sum()), int(pruned.sum()), n_raw, n_p, n_gt))
 
 
+# ----------------------------------------------------------------------------------------------
+# detection tables: homography function and valid-frame loop of the reference, from its own source
+# ----------------------------------------------------------------------------------------------
+def gen_dets():
+    """``dets_<sequence>.npz``: a window of the real EPFL ground truth parsed by the rules of datasets.py:89-98; world
+    coordinates by the reference's OWN ``apply_homography_image_to_world`` (utils.py:211-225, source compiled as is, called
+    per detection as :107 does for scalars) on the foot points of :101-102; valid frames by the reference's OWN loop
+    (datasets.py:126-134: the source lines executed against a stand-in ``self`` with the DataFrame, ``np.int`` mapped to
+    ``int`` because numpy 2 removed the alias)."""
+    import textwrap
+    import types
+    import pandas as pd
+
+    homog = ref_shim.reference_def("libs/utils.py", "apply_homography_image_to_world", {"np": np})
+    with open(os.path.join(REF, "libs", "datasets.py")) as f:
+        lines = f.read().splitlines()
+    loop_src = textwrap.dedent("\n".join(lines[123:134]))            # datasets.py:124-134
+    assert "frames_valid = []" in loop_src and "np.bincount" in loop_src, loop_src
+    npx = types.SimpleNamespace(**{k: getattr(np, k) for k in ("min", "max", "unique", "bincount")}, int=int)
+    for dataset, f_lo, f_hi in (("EPFL-Terrace", 0, 400), ("EPFL-Laboratory", 1000, 1300)):
+        det = parse_gt(dataset)
+        det = det[(det["frame"].values >= f_lo) & (det["frame"].values < f_hi)]
+        root = os.path.join(REF, "datasets", dataset)
+        cams = sorted(c for c in os.listdir(root) if c[0] != ".")
+        Hs = np.stack([np.asarray(pd.read_csv(os.path.join(root, c, "Homography.txt"), header=None, sep="\t"), np.float64) for c in cams])
+        bx = det["xmin"].values + np.round(det["width"].values / 2)
+        by = det["ymax"].values
+        xw = np.empty(len(det)); yw = np.empty(len(det))
+        for i, (x, y, c) in enumerate(zip(bx, by, det["id_cam"].values)):
+            xw[i], yw[i] = homog(float(x), float(y), Hs[int(c)])
+        ns = {"np": npx, "self": types.SimpleNamespace(data_det=det.copy())}
+        exec(loop_src, ns)
+        frames_valid = np.asarray(ns["frames_valid"], np.int64)
+        some = frames_valid[:: max(1, len(frames_valid) // 7)][:7]
+        rows = np.concatenate([np.nonzero(det["frame"].values == f)[0] for f in some])     # datasets.py:250-251
+        name = dataset.split("-")[1].lower()
+        np.savez_compressed(os.path.join(GOLDEN, "dets_%s.npz" % name),
+                            **{k: det[k].values.astype(np.int64) for k in ("id", "xmin", "ymin", "xmax", "ymax", "frame", "id_cam")},
+                            homographies=Hs, xw=xw, yw=yw, frames_valid=frames_valid, some_frames=some, some_rows=rows.astype(np.int64))
+        print("dets_%s: M=%d frames %d..%d valid=%d" % (name, len(det), f_lo, f_hi, len(frames_valid)))
+
+
 def main():
     if not ref_shim.reference_available():
         sys.exit("needs /root/reference (build container only)")
@@ -399,10 +441,13 @@ def main():
         return gen_loss()
     if "--post-only" in sys.argv:
         return gen_post()
+    if "--dets-only" in sys.argv:
+        return gen_dets()
     gen_mpn()
     gen_graph()
     gen_loss()
     gen_post()
+    gen_dets()
 
 
 if __name__ == "__main__":

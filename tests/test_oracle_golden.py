@@ -156,3 +156,17 @@ def test_post_oracle_matches_the_reference_functions(case):
     assert k == int(z["n_pruned"]) and np.array_equal(ids, post_oracle.canonical(z["ids_pruned"]))
     ids, k = post_oracle.clusters(n, (z["labels"] == 1).astype(np.int64), z["edge_index"])
     assert k == int(z["n_gt"]) and np.array_equal(ids, post_oracle.canonical(z["ids_gt"]))
+
+
+@pytest.mark.parametrize("case", golden_cases("dets_"))
+def test_detections_oracle_matches_the_reference_source(case):
+    """oracle/detections_oracle.py against the reference's own homography function and valid-frame loop on real EPFL ground truth."""
+    from oracle import detections_oracle
+
+    z = load_golden("dets_" + case)
+    xw, yw = detections_oracle.world_coordinates(z["xmin"], z["xmax"], z["ymax"], z["id_cam"], z["homographies"])
+    np.testing.assert_allclose(xw, z["xw"], rtol=1e-12, atol=0)
+    np.testing.assert_allclose(yw, z["yw"], rtol=1e-12, atol=0)
+    assert np.array_equal(detections_oracle.valid_frames(z["frame"], z["id_cam"], z["id"]), z["frames_valid"])
+    rows = np.concatenate([detections_oracle.frame_rows(z["frame"], f) for f in z["some_frames"]])
+    assert np.array_equal(rows, z["some_rows"])
