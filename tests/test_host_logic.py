@@ -2,6 +2,7 @@
 import copy
 import importlib
 import json
+import os
 
 import pytest
 import torch
@@ -84,3 +85,41 @@ def test_frame_capacity_classes():
     assert engine.frame_capacity(model, 24576, 442368, 1024) == (32, 1024)                # 1.25 x average -> class
     assert engine.frame_capacity(model, 2048, 917504, 4, (512, 229376)) is None           # cfg 4 frames: per-step kernels
     assert engine.frame_capacity(model, 10, 10, 0) is None
+
+
+def test_checkpoints_travel_both_ways_through_the_reference_functions(tmp_path):
+    """the checkpoint dict of main_training.py:422-433 written from the drop-in is read by the reference's own
+    load_pretrained_weights (utils.py:458-507) into the reference's MOTMPNet with every layer matched, and a reference checkpoint
+    (also with DataParallel's 'module.' prefix) loads into the drop-in.  Needs /root/reference (build container)."""
+    import collections
+    import os.path as osp
+    import shutil
+    import warnings
+    import yaml
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("/root/reference not present")
+    ns = {"torch": torch, "osp": osp, "warnings": warnings, "OrderedDict": collections.OrderedDict, "shutil": shutil, "yaml": yaml, "os": os}
+    ref_shim.reference_def("libs/utils.py", "load_checkpoint", ns)
+    load_pretrained = ref_shim.reference_def("libs/utils.py", "load_pretrained_weights", ns)
+    save_checkpoint = ref_shim.reference_def("libs/utils.py", "save_checkpoint", ns)
+    mpn = ref_shim.import_reference("models.mpn")
+    params = cfgmod.graph_net_params(classifier_batchnorm=True)
+    torch.manual_seed(11)
+    ours = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50")
+    torch.manual_seed(12)
+    ref = mpn.MOTMPNet(copy.deepcopy(params), None, "resnet50")
+    os.makedirs(tmp_path / "files")
+    opt = torch.optim.SGD(ours.parameters(), lr=0.1)
+    save_checkpoint({"epoch": 3, "model_state_dict": ours.state_dict(), "optimizer_state_dict": opt.state_dict(), "prec": 90.0, "prec1": [91.0],
+                     "prec0": [89.0], "best_loss": 0.5, "model_parameters": 0.268, "CONFIG": {"DATASET_TRAIN": {"NAME": ["EPFL-Terrace"]}}},
+                    False, str(tmp_path), "ours")                                                      # utils.py:406-407
+    load_pretrained(ref, str(tmp_path / "files" / "ours_latest.pth.tar"))
+    for (ka, va), (kb, vb) in zip(ours.state_dict().items(), ref.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)                                                         # nothing discarded
+    torch.manual_seed(13)
+    ref2 = mpn.MOTMPNet(copy.deepcopy(params), None, "resnet50")
+    torch.save({"model_state_dict": {"module." + k: v for k, v in ref2.state_dict().items()}}, tmp_path / "ref.pth.tar")
+    load_pretrained(ours, str(tmp_path / "ref.pth.tar"))
+    for (ka, va), (kb, vb) in zip(ref2.state_dict().items(), ours.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)
