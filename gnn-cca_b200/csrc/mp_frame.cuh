@@ -163,7 +163,7 @@ __device__ __forceinline__ float agg_comb(int agg, float a, float b) { return ag
 // the same arguments; returns after the group's last barrier (the state may be overwritten at once).
 template <bool REATT_E, int AGG>
 __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const Batch& bt, const float* sw, const WOff& wo,
-                                         float* ss, const SOff& so, int64_t g) {
+                                         float* ss, const SOff& so, int64_t g, bool dep_wait = false) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   int* const ssi = reinterpret_cast<int*>(ss);
   const int tid = gr.tid, NT = gr.size, lane = gr.lane;
@@ -186,15 +186,9 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
   }
   if (!fits || n > nt.cap_n) { if (tid == 0) atomicOr(bt.flags + 2, 1); return; }     // group-uniform
 
-  // ---- load the frame: encoded nodes, local CSR, edge encoder
+  // ---- load the frame: local CSR + edge encoder first (inputs of the forward), the encoded nodes last: when the kernel is a
+  //      programmatic dependent of the node encoder (dep_wait), everything before the wait overlaps the encoder's tail
   if (tid == 0) ssi[so.bad] = 0;
-  for (int idx = tid; idx < n * (FN / 4); idx += NT) {
-    const float4 v = __ldcg(reinterpret_cast<const float4*>(bt.h_enc + a * FN) + idx);
-    const int hoff = (idx >> 3) * HS + (idx & 7) * 4;
-    *reinterpret_cast<float4*>(ss + so.h + hoff) = v;
-    if (nt.reatt_n) *reinterpret_cast<float4*>(ss + so.h0 + hoff) = v;
-    if (bt.h_dump) *(reinterpret_cast<float4*>(bt.h_dump + a * FN) + idx) = v;
-  }
   if (!raw) for (int v = tid; v <= n; v += NT) ssi[so.rp + v] = bt.rowptr[a + v] - (int)eb;
   else if (ne == 0) for (int v = tid; v <= n; v += NT) ssi[so.rp + v] = 0;
   gr.sync();                                       // bad flag cleared before anyone raises it
@@ -273,6 +267,14 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
       }
     }
     if (bad) ssi[so.bad] = 1;
+  }
+  if (dep_wait) asm volatile("griddepcontrol.wait;" ::: "memory");      // the encoder's output is visible from here on
+  for (int idx = tid; idx < n * (FN / 4); idx += NT) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(bt.h_enc + a * FN) + idx);
+    const int hoff = (idx >> 3) * HS + (idx & 7) * 4;
+    *reinterpret_cast<float4*>(ss + so.h + hoff) = v;
+    if (nt.reatt_n) *reinterpret_cast<float4*>(ss + so.h0 + hoff) = v;
+    if (bt.h_dump) *(reinterpret_cast<float4*>(bt.h_dump + a * FN) + idx) = v;
   }
   gr.sync();
   if (ssi[so.bad]) {                                 // not a closed, source-major frame: group-uniform exit

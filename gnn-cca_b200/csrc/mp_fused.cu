@@ -26,18 +26,20 @@ __global__ void __launch_bounds__(896, 1) mp_fused_fwd_kernel(const __grid_const
   const mpf::WOff wo = mpf::weight_layout(K, EIN);
   const mpf::SOff so = mpf::state_layout(p.net.cap_n, p.net.cap_e, p.net.reatt_n != 0, REATT_E);
   mpf::load_weights(smem_f, wo, p.net, threadIdx.x, blockDim.x);
-  // launched as a programmatic dependent of the node encoder (gnncca_mpn_forward_frames): everything above overlapped
-  // the encoder's tail; its output is visible from here on.  A no-op for ordinary launches.
-  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
+  // Launched as a programmatic dependent of the node encoder (gnncca_mpn_forward_frames): the weights above AND the edge side
+  // of every group's first frame (edge list check, local CSR, edge encoder: inputs of the forward, not products of the
+  // encoder) overlap the encoder's tail; mp_frame waits for the encoder right before it reads the encoded nodes.
+  // griddepcontrol.wait is a no-op for ordinary launches.
   mpf::Group gr;
   const int gi = threadIdx.x / p.group_threads;
   gr.tid = threadIdx.x - gi * p.group_threads; gr.size = p.group_threads;
   gr.warp = gr.tid >> 5; gr.nwarps = gr.size >> 5; gr.lane = gr.tid & 31; gr.bar = 1 + gi;
   float* ss = smem_f + wo.total + gi * so.total;
   const int64_t stride = (int64_t)gridDim.x * p.groups;
-  for (int64_t g = (int64_t)gi * gridDim.x + blockIdx.x; g < p.batch.n_graphs; g += stride)
-    mpf::mp_frame<REATT_E, AGG>(gr, p.net, p.batch, smem_f, wo, ss, so, g);
+  bool first = true;
+  for (int64_t g = (int64_t)gi * gridDim.x + blockIdx.x; g < p.batch.n_graphs; g += stride, first = false)
+    mpf::mp_frame<REATT_E, AGG>(gr, p.net, p.batch, smem_f, wo, ss, so, g, first);
 }
 
 }  // namespace fused
