@@ -13,6 +13,7 @@
 //                              shared memory, + b2, ReLU, one 128 B store per node.  The hidden activations never
 //                              touch HBM.
 // Roofline: HBM.  Algorithmic bytes per launch = N * (4 K + 128) + weights.
+#include <cstdlib>
 #include "tc_helpers.cuh"
 
 namespace gnncca {
@@ -322,6 +323,10 @@ int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaS
 #endif
   // every SM gets the same number of rows (8-row granules); grids smaller than the machine only for tiny inputs
   int64_t rpc = (ceil_div(p.rows, kNumSMs) + 7) & ~(int64_t)7;
+  // small inputs: every CTA streams all of W1 (K x H floats from L2) whatever its row count, so below ~64 rows per CTA the W1
+  // re-reads are most of the traffic (N = 2560: 107 CTAs x 1 MB); fewer CTAs with 64 rows each move half the bytes
+  static const int64_t min_rows = [] { const char* e = getenv("GNNCCA_ENC_MIN_ROWS"); return e ? (int64_t)atoi(e) : (int64_t)64; }();
+  if (rpc < min_rows) rpc = p.rows < min_rows ? ((p.rows + 7) & ~(int64_t)7) : min_rows;
   if (rpc < 8) rpc = 8;
   p.rows_per_cta = (int)rpc;
   const int grid = (int)ceil_div(p.rows, rpc);
