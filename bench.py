@@ -523,11 +523,39 @@ def main():
         for i in range(e2e_steps):
             model.forward_host(*hosts[i & 1], out=outs_host, graph_ptr=ptrs[i & 1], caps=batches[i & 1].gnncca_caps)     # returns after the D2H copy of the logits
         torch.cuda.synchronize()
+        e2e_blocking_s = time.perf_counter() - t0
+        # the same stream of batches through HostPipeline: batch i+1 is copied in while batch i computes and its logits
+        # travel back; every step still moves its inputs host->device and its logits device->host, and every result is
+        # waited for (one step later) inside the timed region
+        pipe = gnncca.HostPipeline(model)
+        outs_pair = [outs_host, [torch.empty((E, 1), dtype=torch.float32).pin_memory() for _ in range(model.num_class_steps)]]
+        for i in range(2):
+            pipe.submit(*hosts[i & 1], out=outs_pair[i & 1], graph_ptr=ptrs[i & 1], caps=batches[i & 1].gnncca_caps).wait()
+        barrier()
+        t0 = time.perf_counter()
+        pending = None
+        for i in range(e2e_steps):
+            hd = pipe.submit(*hosts[i & 1], out=outs_pair[i & 1], graph_ptr=ptrs[i & 1], caps=batches[i & 1].gnncca_caps)
+            if pending is not None:
+                pending.wait()
+            pending = hd
+        pending.wait()
+        torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        # what the link alone allows: the step's input bytes, pinned host -> device, nothing else running
+        x_probe = torch.empty_like(batches[0].x)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(3):
+            x_probe.copy_(hosts[i & 1][0], non_blocking=True)
+        torch.cuda.synchronize()
+        h2d_gbs = 3 * x_probe.numel() * 4 / (time.perf_counter() - t0) / 1e9
+        del x_probe
+    t = torch.tensor([e2e_s, e2e_blocking_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * E * e2e_steps / float(t.item())
+    e2e_value = world * E * e2e_steps / float(t[0].item())
+    e2e_blocking = world * E * e2e_steps / float(t[1].item())
     d2h_bytes = model.num_class_steps * E * 4
 
     if rank != 0:
@@ -615,7 +643,9 @@ def main():
                        "graphs_per_s": world * wl["frames"] * args.steps / (ms_max * 1e-3)},
             "clocks": sampler.result(), "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": in_bytes + 8 * (wl["frames"] + 1), "d2h_bytes_per_step": d2h_bytes,
-                    "steps": e2e_steps, "api": "MOTMPNet.forward_host (pinned host x/edge_index/edge_attr -> pinned host logits)"},
+                    "steps": e2e_steps, "api": "gnncca.HostPipeline.submit / wait (pinned host x/edge_index/edge_attr -> pinned host logits, two batches in flight)",
+                    "h2d_link_gbs": h2d_gbs, "link_bound_value": world * E / ((in_bytes + 8 * (wl["frames"] + 1)) / (h2d_gbs * 1e9)),
+                    "blocking_call_value": e2e_blocking, "blocking_api": "MOTMPNet.forward_host (returns after the logits are on the host)"},
             "roofline": roofline, "graph_build": graph_build}
     if cpu is not None:
         line["cpu_baseline"] = cpu

@@ -8,7 +8,7 @@ from .mpn import MOTMPNet, MetaLayer, EdgeModel, NodeModel, MLPGraphIndependent
 from .plan import GraphPlan
 from .graph import Batch, build_graph_batch, column_normalize
 from . import _lib
-from .engine import forward_host, StageTimer
+from .engine import forward_host, StageTimer, HostPipeline
 from . import multigpu
 from .loss import compute_loss_acc, loss_stats, LossStats
 from . import postprocess
@@ -16,4 +16,4 @@ from .graphs import GraphedTrainStep
 from . import detections
 from .postprocess import decide_and_cluster, ground_truth_clusters, frame_clusters
 
-__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer", "compute_loss_acc", "loss_stats", "LossStats", "decide_and_cluster", "ground_truth_clusters", "frame_clusters", "GraphedTrainStep"]
+__all__ = ["MLP", "MOTMPNet", "MetaLayer", "EdgeModel", "NodeModel", "MLPGraphIndependent", "GraphPlan", "Batch", "build_graph_batch", "column_normalize", "forward_host", "StageTimer", "HostPipeline", "compute_loss_acc", "loss_stats", "LossStats", "decide_and_cluster", "ground_truth_clusters", "frame_clusters", "GraphedTrainStep"]

@@ -390,6 +390,89 @@ def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: to
     return out
 
 
+class HostPipeline:
+    """``forward_host`` for a STREAM of host batches: two sets of device input buffers used alternately, so that the
+    host->device copy of batch i+1 (side stream) runs while batch i is still computing and while its logits travel back
+    (PCIe is full duplex).  ``submit`` returns at once with a handle; ``handle.wait()`` returns the host logits.
+
+        pipe = gnncca.HostPipeline(model)
+        pending = None
+        for x, edge_index, edge_attr, ptr in batches:            # pinned host tensors
+            h = pipe.submit(x, edge_index, edge_attr, graph_ptr=ptr, out=out_bufs[i % 2])
+            if pending is not None:
+                logits = pending.wait()
+            pending = h
+    """
+
+    class Handle:
+        def __init__(self, out, event):
+            self.out, self.event = out, event
+
+        def wait(self):
+            self.event.synchronize()
+            return self.out
+
+    def __init__(self, model, n_chunks: int = 8, slots: int = 2):
+        check_supported(model)
+        self.model, self.n_chunks = model, n_chunks
+        self.dev = next(model.parameters()).device
+        if self.dev.type != "cuda":
+            raise RuntimeError("gnn-cca_b200: the model must live on a CUDA device (no CPU path)")
+        self.slots = [dict(key=None, free=None) for _ in range(slots)]
+        self.turn = 0
+        self.side = torch.cuda.Stream(device=self.dev)
+
+    def submit(self, x, edge_index, edge_attr, out=None, graph_ptr=None, caps=None) -> "HostPipeline.Handle":
+        if x.is_cuda or edge_index.is_cuda or edge_attr.is_cuda:
+            raise ValueError("HostPipeline takes host tensors; call the module itself for device tensors")
+        model, dev = self.model, self.dev
+        math = MATH_MODES[model.math]
+        N, E = int(x.size(0)), int(edge_index.size(1))
+        cur = torch.cuda.current_stream(dev)
+        slot = self.slots[self.turn % len(self.slots)]
+        self.turn += 1
+        key = (N, int(x.size(1)), E, int(edge_attr.size(1)))
+        enc = model.encoder.node_mlp
+        if slot["key"] != key:          # (re)allocate this slot's device buffers; ordered after whatever still uses the old ones
+            if slot["free"] is not None:
+                slot["free"].synchronize()
+            slot.update(key=key, x=torch.empty((N, key[1]), dtype=torch.float32, device=dev), ei=torch.empty((2, E), dtype=torch.int64, device=dev),
+                        ea=torch.empty((E, key[3]), dtype=torch.float32, device=dev),
+                        h=torch.empty((N, enc.layer_specs[-1].out_dim), dtype=torch.float32, device=dev))
+            self.side.wait_stream(cur)
+        side = self.side
+        if slot["free"] is not None:
+            side.wait_event(slot["free"])       # the forward that last read these buffers has finished
+        bounds = [N * i // self.n_chunks for i in range(self.n_chunks + 1)]
+        events = []
+        with torch.cuda.stream(side):
+            slot["ei"].copy_(edge_index, non_blocking=True)
+            slot["ea"].copy_(edge_attr, non_blocking=True)
+            gp = graph_ptr.to(dev, non_blocking=True) if (graph_ptr is not None and not graph_ptr.is_cuda) else graph_ptr
+            ev0 = torch.cuda.Event(); ev0.record(side)
+            for a, b in zip(bounds[:-1], bounds[1:]):
+                if b > a:
+                    slot["x"][a:b].copy_(x[a:b], non_blocking=True)
+                ev = torch.cuda.Event(); ev.record(side)
+                events.append(ev)
+        if gp is not None:
+            gp.record_stream(cur)
+        cur.wait_event(ev0)
+        plan = GraphPlan(slot["ei"], N)
+        for (a, b), ev in zip(zip(bounds[:-1], bounds[1:]), events):
+            cur.wait_event(ev)
+            if b > a:
+                mlp_forward_nograd(enc, slot["x"][a:b], math, out=slot["h"][a:b])
+        outs = forward_inference(model, slot["x"], slot["ei"], slot["ea"], plan, h_encoded=slot["h"], graph_ptr=gp, caps=caps)
+        if out is None:
+            out = [torch.empty((E, 1), dtype=torch.float32, pin_memory=True) for _ in outs]
+        for o, d in zip(out, outs):
+            o.copy_(d, non_blocking=True)
+        done = torch.cuda.Event(); done.record(cur)
+        slot["free"] = done
+        return HostPipeline.Handle(out, done)
+
+
 FAST_PLAN = TrustedPlan.__new__(TrustedPlan)     # what ``last_plan`` reports after the single-call path
 FAST_PLAN.last_path = "fused"
 FAST_PLAN.caps = None
