@@ -17,11 +17,12 @@
 // phase B starts, so their latency hides behind it.  Phase B is lane-per-feature: warp w walks edges [64w, 64w+64) of
 // the tile pair by pair (3 LDS.128 + 6 FFMA2 + 2 FMNMX + 1 FADD2 per pair) with the running aggregate of the current
 // source segment in registers (even / odd edges separately, folded at the end).  Segment boundaries come from one
-// ballot over the staged source ids, not from rowptr.  Segments are closed
-//   - inside a warp chunk: written directly;
-//   - across warps of the tile: chained in warp order through shared memory;
-//   - across tiles: each tile publishes its partial, bumps an integer counter keyed by the segment's first
-//     tile, and the LAST tile to arrive folds the partials in tile order.
+// ballot over the staged source ids, not from rowptr.  A warp stages and reduces the SAME 64 edges (a "chunk" of the global
+// edge numbering), so after the weights are staged the warps of a CTA never synchronise with each other:
+//   - a segment that lies inside one chunk is finished and written by its warp;
+//   - a segment that crosses chunks leaves one piece per chunk in the workspace (plain stores), and a second small
+//     kernel (warp per node) folds the pieces of each such node in chunk order; it also zero-fills the nodes without
+//     out-edges.  (A CTA barrier per tile plus fence / counter hand-over between tiles cost 0.17 of 0.57 ms at 8 x 64.)
 // No floating-point atomics anywhere: the summation order is a pure function of (E, rowptr), so results are
 // bit-identical run to run (the reference's torch_scatter atomicAdd path is not).
 #include "common.cuh"
@@ -33,6 +34,10 @@ constexpr int THREADS = 256;  // one thread per edge pair
 constexpr int NWARP = THREADS / 32;
 constexpr int CHUNK = TILE / NWARP;   // edges per warp in phase B
 constexpr int FN = 32;        // latent node width handled by lane-per-feature phase B
+#ifndef GNNCCA_STEP_MIN_CTAS
+#define GNNCCA_STEP_MIN_CTAS 3
+#endif
+constexpr int STEP_MIN_CTAS = GNNCCA_STEP_MIN_CTAS;   // resident CTAs per SM the register allocation is held to
 
 struct StepParams {
   const int32_t* rowptr; const int32_t* src; const int32_t* dst;
@@ -42,8 +47,7 @@ struct StepParams {
   gnncca_mp_weights w;
   int agg, nf;
   int num_tiles;
-  float* tile_part;      // [num_tiles][2][FN]  slot 0: continuation piece (started in an earlier tile), slot 1: open tail
-  int32_t* counters;     // [num_tiles] arrival counters, zeroed by the host entry before the launch
+  float* chunk_part;     // [num_tiles * NWARP][2][FN]  slot 0: piece of a segment begun in an earlier chunk, slot 1: open tail
   int phase;             // position of local edge 0 inside a tile of the GLOBAL edge numbering (edge-partitioned graphs)
   const int32_t* guard;  // optional CSR flags (gnncca_csr_from_edge_index): the kernel is a no-op when any is set
   // ATTR variants: the encoded edge features e0 = ReLU(W_enc attr + b_enc) (mpn.py:116-126, 4 -> FE) are computed here from
@@ -60,25 +64,6 @@ template <bool IS_MAX> __device__ __forceinline__ float2 comb2(float2 a, float2 
 __device__ __forceinline__ void finalize_node(const StepParams& p, int node, float v, int lane) {
   if (p.agg == GNNCCA_AGG_MEAN) v = v / (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);   // scatter_mean: sum / clamp(count, 1)
   p.h_out[(int64_t)node * FN + lane] = v;
-}
-
-// Cross-tile combination.  kind 0 = this tile continues a segment begun earlier, kind 1 = this tile opens one.
-template <bool IS_MAX>
-__device__ __forceinline__ void publish_partial(const StepParams& p, int tile, int kind, int node, float total, int lane) {
-  const int rs = p.rowptr[node], re = p.rowptr[node + 1];
-  const int t0 = (rs + p.phase) / TILE, t1 = (re - 1 + p.phase) / TILE;
-  p.tile_part[((int64_t)tile * 2 + kind) * FN + lane] = total;
-  __threadfence();
-  __syncwarp();
-  int old = 0;
-  if (lane == 0) old = atomicAdd(p.counters + t0, 1);
-  old = __shfl_sync(0xffffffffu, old, 0);
-  if (old == t1 - t0) {  // every tile of [t0, t1] has published: fold in tile order
-    __threadfence();
-    float tot = ld_cg_f(p.tile_part + ((int64_t)t0 * 2 + 1) * FN + lane);
-    for (int t = t0 + 1; t <= t1; ++t) tot = comb<IS_MAX>(tot, ld_cg_f(p.tile_part + ((int64_t)t * 2) * FN + lane));
-    finalize_node(p, node, tot, lane);
-  }
 }
 
 constexpr int FA = 4;   // raw attribute width of the ATTR variants (one 16-byte load per edge)
@@ -123,7 +108,7 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
 }
 
 template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR>
-__global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParams p) {
+__global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 1;
   static_assert(FE % 2 == 0 && (FE * EIN) % 4 == 0, "weights are read as float4");
@@ -135,9 +120,6 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
   __shared__ float s_b1[HCS], s_c2[HCS], s_b2;
   __shared__ __align__(16) float s_e[TILE / 2][2 * FE];      // [pair][k][2]
   __shared__ __align__(8) int s_src[TILE];
-  // pieces of segments that cross warp chunks; double-buffered by tile parity so that ONE barrier per tile is enough
-  __shared__ float s_C[2][NWARP][FN], s_O[2][NWARP][FN];
-  __shared__ int s_Cnode[2][NWARP], s_Cclosed[2][NWARP], s_Onode[2][NWARP];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = p.nf * FN;
@@ -172,13 +154,12 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
 #pragma unroll
   for (int k = 0; k < FE; ++k) wne[k] = s_wne[k][lane];
 
-  int buf = 0;
-  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, buf ^= 1) {
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
     const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
     const int64_t i0 = base + 2 * tid;
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
-    // A warp stages and then reduces the SAME 64 edges, so phases A and B need no CTA barrier between them; the sources of
-    // the edges just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
+    // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
+    // just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
     const int lo = (int)max((int64_t)0, -base), hi = (int)min((int64_t)TILE, p.n_edges - base);   // valid tile-local edge range
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
@@ -307,7 +288,6 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
     __syncwarp();
     // ------------------------------ phase B: lane per feature ------------------------------
     {
-      int Cnode = -1, Cclosed = 0, Onode = -1;
       if (a < b) {
         const int nb_prev = __shfl_sync(0xffffffffu, nb, 0), nb_next = __shfl_sync(0xffffffffu, nb, 1);
         const int ie = c0 + 2 * lane;
@@ -360,39 +340,44 @@ __global__ void __launch_bounds__(THREADS, 3) mp_step_fwd_kernel(const StepParam
           const float acc = comb<IS_MAX>(acc2.x, acc2.y);
           const bool starts = !(j0 == a && first_cont), ends = !(j1 == b && last_cont);
           if (starts && ends) finalize_node(p, s, acc, lane);
-          else if (!starts) { s_C[buf][warp][lane] = acc; Cnode = s; Cclosed = ends ? 1 : 0; }
-          else { s_O[buf][warp][lane] = acc; Onode = s; }
+          else p.chunk_part[(((int64_t)tile * NWARP + warp) * 2 + (starts ? 1 : 0)) * FN + lane] = acc;   // folded by mp_step_fold_kernel
         }
       }
-      if (lane == 0) { s_Cnode[buf][warp] = Cnode; s_Cclosed[buf][warp] = Cclosed; s_Onode[buf][warp] = Onode; }
     }
-    __syncthreads();   // the only CTA barrier of the tile (the piece buffers alternate, s_e / s_src are per-warp)
-    // chain the pieces of segments that cross warp chunks, in warp order
-    if (s_Onode[buf][warp] >= 0) {
-      const int s = s_Onode[buf][warp];
-      float total = s_O[buf][warp][lane];
-      bool closed = false;
-      for (int w2 = warp + 1; w2 < NWARP; ++w2) {
-        if (s_Cnode[buf][w2] != s) break;
-        total = comb<IS_MAX>(total, s_C[buf][w2][lane]);
-        if (s_Cclosed[buf][w2]) { closed = true; break; }
-      }
-      if (closed) finalize_node(p, s, total, lane);
-      else publish_partial<IS_MAX>(p, tile, 1, s, total, lane);
-    }
-    if (warp == 0 && s_Cnode[buf][0] >= 0) {  // the tile begins inside a segment opened by an earlier tile
-      const int s = s_Cnode[buf][0];
-      float total = s_C[buf][0][lane];
-      if (!s_Cclosed[buf][0]) {
-        for (int w2 = 1; w2 < NWARP; ++w2) {
-          if (s_Cnode[buf][w2] != s) break;
-          total = comb<IS_MAX>(total, s_C[buf][w2][lane]);
-          if (s_Cclosed[buf][w2]) break;
-        }
-      }
-      publish_partial<IS_MAX>(p, tile, 0, s, total, lane);
-    }
+    __syncwarp();      // the warp's rows of s_e / s_src are rewritten by its next phase A
   }
+}
+
+// Second kernel of a step: one warp per node.  Nodes without out-edges aggregate to 0 (torch_scatter semantics); a node whose
+// segment crosses chunk boundaries gets the fold of its pieces in chunk order (first chunk's open tail, then one piece per
+// later chunk); everything else was written by the step kernel.
+__global__ void __launch_bounds__(256) mp_step_fold_kernel(const StepParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t v = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (v >= p.n_nodes) return;
+  if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;
+  const int rs = p.rowptr[v], re = p.rowptr[v + 1];
+  if (re <= rs) { p.h_out[v * FN + lane] = 0.f; return; }
+  const int64_t c0 = ((int64_t)rs + p.phase) / CHUNK, c1 = ((int64_t)re - 1 + p.phase) / CHUNK;
+  if (c0 == c1) return;
+  const bool is_max = p.agg == GNNCCA_AGG_MAX;
+  // sums are carried in double across the pieces (a handful of adds per node): the rounding of a long segment is then that
+  // of its 64-edge chunks alone
+  double tot = p.chunk_part[(c0 * 2 + 1) * FN + lane];
+  int64_t c = c0 + 1;
+  for (; c + 3 <= c1; c += 4) {        // four loads in flight, folded in order
+    const float v0 = p.chunk_part[(c * 2) * FN + lane], v1 = p.chunk_part[((c + 1) * 2) * FN + lane];
+    const float v2 = p.chunk_part[((c + 2) * 2) * FN + lane], v3 = p.chunk_part[((c + 3) * 2) * FN + lane];
+    if (is_max) tot = fmax(fmax(fmax(fmax(tot, (double)v0), (double)v1), (double)v2), (double)v3);
+    else tot = (((tot + v0) + v1) + v2) + v3;
+  }
+  for (; c <= c1; ++c) {
+    const float v0 = p.chunk_part[(c * 2) * FN + lane];
+    tot = is_max ? fmax(tot, (double)v0) : tot + v0;
+  }
+  float out = (float)tot;
+  if (p.agg == GNNCCA_AGG_MEAN) out = out / (float)(re - rs);      // scatter_mean: sum / count, in fp32 like finalize_node
+  p.h_out[v * FN + lane] = out;
 }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -404,12 +389,12 @@ using namespace gnncca;
 extern "C" int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes, int64_t n_edges) {
   (void)cfg; (void)n_nodes;
   const int64_t tiles = ceil_div((n_edges > 0 ? n_edges : 1) + TILE, TILE);   // + one tile: the partition phase shifts the tiling
-  return (int64_t)(align256(sizeof(int32_t) * tiles) + align256(sizeof(float) * tiles * 2 * FN) + 256);
+  return (int64_t)(align256(sizeof(float) * tiles * NWARP * 2 * FN) + 256);
 }
 
 template <int FE, int HC>
 static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
-  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * 3);
+  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * STEP_MIN_CTAS);
   const bool is_max = sp.agg == GNNCCA_AGG_MAX;
   const bool attr = sp.attr != nullptr;
 #define GNNCCA_STEP(R, M, A) mp_step_fwd_kernel<FE, HC, R, M, A><<<grid, THREADS, 0, st>>>(sp)
@@ -421,7 +406,9 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
     else { if (attr) GNNCCA_STEP(false, false, true); else GNNCCA_STEP(false, false, false); }
   }
 #undef GNNCCA_STEP
-  return check_launch();
+  if (sp.h_out == nullptr) return check_launch();
+  mp_step_fold_kernel<<<(unsigned)ceil_div(sp.n_nodes, (int64_t)8), 256, 0, st>>>(sp);
+  return check_launch(2);
 }
 
 extern "C" int32_t gnncca_mp_step_tile(void) { return TILE; }
@@ -433,11 +420,10 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
                         const float* attr, const float* w_enc, const float* b_enc) {
   if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
-  if (h_out && n_nodes > 0) {  // nodes without out-edges aggregate to 0 (torch_scatter semantics)
-    int rc = check_cuda(cudaMemsetAsync(h_out, 0, sizeof(float) * n_nodes * FN, st));
-    if (rc) return rc;
+  if (n_edges == 0) {          // nodes without out-edges aggregate to 0 (torch_scatter semantics)
+    if (h_out && n_nodes > 0) return check_cuda(cudaMemsetAsync(h_out, 0, sizeof(float) * n_nodes * FN, st));
+    return GNNCCA_OK;
   }
-  if (n_edges == 0) return GNNCCA_OK;
   if (!rowptr || !src || !dst || !P || !Q || !R || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
   if (!e_out && (h_out || !logits)) return GNNCCA_ERR_BAD_ARG;      // e_out may only be dropped when the step just classifies
   if (attr ? (!w_enc || !b_enc || (((uintptr_t)attr) & 15) != 0) : (!e_in || (cfg->reattach_edges && !e0))) return GNNCCA_ERR_BAD_ARG;
@@ -458,12 +444,7 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
   sp.phase = cfg->edge_phase;
   sp.num_tiles = (int)ceil_div(n_edges + sp.phase, TILE);
   char* ws = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
-  sp.counters = (int32_t*)ws;
-  sp.tile_part = (float*)(ws + align256(sizeof(int32_t) * sp.num_tiles));
-  if (h_out) {
-    int rc = check_cuda(cudaMemsetAsync(sp.counters, 0, sizeof(int32_t) * sp.num_tiles, st));
-    if (rc) return rc;
-  }
+  sp.chunk_part = (float*)ws;
   const bool re = cfg->reattach_edges != 0;
   if (cfg->f_edge == 6 && cfg->cls_hidden == 4) return launch_step<6, 4>(sp, re, st);
   return GNNCCA_ERR_UNSUPPORTED;

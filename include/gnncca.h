@@ -153,10 +153,12 @@ int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int64_t n_nodes
  * h_out[v]   = agg_{i : src[i]==v} ReLU( R[v] + W_node[:, edge block] e_out[i] )        (mpn.py:97-99)
  * logits[i]  = classifier(e_out[i])  if logits != NULL                                  (mpn.py:290-293)
  * Edges must be source-sorted (rowptr consistent with src).  Deterministic: no floating-point atomics;
- * segments that span tiles are combined in tile order by the last tile to arrive.
+ * a segment that spans 64-edge chunks of the edge numbering leaves one piece per chunk in the workspace and a
+ * second launch (warp per node) folds the pieces in chunk order and zero-fills the nodes without out-edges.
  * e_out may alias e_in.  h_out may be NULL (last step: the node update is dead, mpn.py:288-299).
  * guard_flags (optional): the flags[] of gnncca_csr_from_edge_index; when any is set the launch is a
- * no-op, so a caller may enqueue the whole forward before reading the flags back.  * e_out may be NULL in a step that only classifies (h_out == NULL and logits != NULL: the last step of an inference
+ * no-op, so a caller may enqueue the whole forward before reading the flags back.
+ * e_out may be NULL in a step that only classifies (h_out == NULL and logits != NULL: the last step of an inference
  * forward), whose updated edge features nobody reads. */
 int gnncca_mp_step_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                        const int32_t* rowptr, const int32_t* src, const int32_t* dst,
