@@ -107,6 +107,37 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
   }
 }
 
+// The same for a pair that lies wholly inside the edge range at an even edge index with 16-byte aligned arrays (every pair of an
+// interior tile when the partition phase is even): the pair's 2 x FE floats are contiguous, so they travel as float4s and the two
+// ids as one 8-byte load; the pairing of the registers (k, k+1 of one edge) is the same as in load_raw.
+template <int FE, bool REATT_E, bool ATTR>
+__device__ __forceinline__ void load_raw_fast(const StepParams& p, int64_t i0, RawPair<FE, REATT_E, ATTR>& r) {
+  static_assert((2 * FE) % 4 == 0, "a pair's features are read as float4");
+  const int2 s2 = ld_stream_i2(p.src + i0), d2 = ld_stream_i2(p.dst + i0);
+  r.sa = s2.x; r.sb = s2.y; r.da = d2.x; r.db = d2.y;
+  if (!ATTR || p.e_in != nullptr) {
+    float t[2 * FE];
+#pragma unroll
+    for (int q = 0; q < 2 * FE / 4; ++q) {
+      const float4 v = ld_stream_f4(p.e_in + i0 * FE + 4 * q);
+      t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w;
+    }
+#pragma unroll
+    for (int k = 0; k < FE / 2; ++k) { r.ea[k] = make_float2(t[2 * k], t[2 * k + 1]); r.eb[k] = make_float2(t[FE + 2 * k], t[FE + 2 * k + 1]); }
+  }
+  if (REATT_E && !ATTR) {
+    float t[2 * FE];
+#pragma unroll
+    for (int q = 0; q < 2 * FE / 4; ++q) {
+      const float4 v = ld_stream_f4(p.e0 + i0 * FE + 4 * q);
+      t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w;
+    }
+#pragma unroll
+    for (int k = 0; k < FE / 2; ++k) { r.xa[k] = make_float2(t[2 * k], t[2 * k + 1]); r.xb[k] = make_float2(t[FE + 2 * k], t[FE + 2 * k + 1]); }
+  }
+  if (ATTR) { r.ta[0] = ld_stream_f4(p.attr + i0 * FA); r.tb[0] = ld_stream_f4(p.attr + (i0 + 1) * FA); }
+}
+
 template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR>
 __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
@@ -147,6 +178,9 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       if (tid == 0) s_b2 = p.w.b_c2[0];
     }
   }
+  // interior tiles of an even partition phase read their pairs as 16-byte vectors (uniform over the launch)
+  const bool vec_ok = (p.phase & 1) == 0 && (((uintptr_t)p.e_in | (uintptr_t)p.e0 | (uintptr_t)p.attr) & 15) == 0 &&
+                      (((uintptr_t)p.src | (uintptr_t)p.dst) & 7) == 0;
   RawPair<FE, REATT_E, ATTR> cur;
   load_raw<FE, REATT_E, ATTR>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
   __syncthreads();
@@ -265,23 +299,23 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       }
     }
     const int next_tile = tile + gridDim.x;
-    if (next_tile < p.num_tiles) load_raw<FE, REATT_E, ATTR>(p, (int64_t)next_tile * TILE - p.phase + 2 * tid, cur);
+    if (next_tile < p.num_tiles) {
+      const int64_t nbase = (int64_t)next_tile * TILE - p.phase;
+      if (vec_ok && nbase >= 0 && nbase + TILE <= p.n_edges) load_raw_fast<FE, REATT_E, ATTR>(p, nbase + 2 * tid, cur);
+      else load_raw<FE, REATT_E, ATTR>(p, nbase + 2 * tid, cur);
+    }
     {  // the tile after that: pull its lines into L2 now (one 128-byte line per thread), DRAM latency off the critical path
       const int64_t far = (int64_t)next_tile + gridDim.x;
       if (far < p.num_tiles) {
-        const int64_t fb = max(far * TILE - p.phase, (int64_t)0);
-        const float* pe = p.e_in + fb * FE + (int64_t)tid * 32;
-        if (p.e_in != nullptr && tid < TILE * FE / 32 && pe < p.e_in + p.n_edges * FE) prefetch_l2(pe);
-        if (ATTR && tid < TILE * FA / 32 && p.attr + fb * FA + (int64_t)tid * 32 < p.attr + p.n_edges * FA) prefetch_l2(p.attr + fb * FA + (int64_t)tid * 32);
-        if (REATT_E && !ATTR) {
-          const float* p0 = p.e0 + fb * FE + (int64_t)tid * 32;
-          if (tid < TILE * FE / 32 && p0 < p.e0 + p.n_edges * FE) prefetch_l2(p0);
-        }
-        const int t2 = tid - (THREADS - 2 * TILE / 32);      // the last 32 threads: 16 lines of src, 16 of dst
-        if (t2 >= 0) {
-          const int32_t* pi = (t2 < TILE / 32 ? p.src : p.dst) + fb + (int64_t)(t2 & (TILE / 32 - 1)) * 32;
-          if (pi < (t2 < TILE / 32 ? p.src : p.dst) + p.n_edges) prefetch_l2(pi);
-        }
+        const int64_t fb = far * TILE - p.phase;        // > 0: far >= 2
+        constexpr int LE = TILE * FE / 32, LI = TILE / 32, LA = TILE * FA / 32;      // lines of e_in (e0), of src / dst, of attr
+        const char* ptr = nullptr; const char* end = nullptr;
+        if (tid < LE) { if (p.e_in != nullptr) { ptr = (const char*)(p.e_in + fb * FE); end = (const char*)(p.e_in + p.n_edges * FE); } }
+        else if (tid < LE + LI) { ptr = (const char*)(p.src + fb) - LE * 128; end = (const char*)(p.src + p.n_edges); }
+        else if (tid < LE + 2 * LI) { ptr = (const char*)(p.dst + fb) - (LE + LI) * 128; end = (const char*)(p.dst + p.n_edges); }
+        else if (ATTR && tid < LE + 2 * LI + LA) { ptr = (const char*)(p.attr + fb * FA) - (LE + 2 * LI) * 128; end = (const char*)(p.attr + p.n_edges * FA); }
+        else if (REATT_E && !ATTR && tid < 2 * LE + 2 * LI) { ptr = (const char*)(p.e0 + fb * FE) - (LE + 2 * LI) * 128; end = (const char*)(p.e0 + p.n_edges * FE); }
+        if (ptr != nullptr) { ptr += (size_t)tid * 128; if (ptr < end) prefetch_l2(ptr); }
       }
     }
     if (p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
@@ -318,17 +352,21 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
             acc2.y = comb<IS_MAX>(acc2.y, fmaxf(m, 0.f));
             ++j;
           }
-#pragma unroll 4
-          for (; j + 1 < j1; j += 2) {
+          {   // whole pairs: one pointer walks the staged rows (3 x LDS.128 per pair at immediate offsets)
             const float4* ev = reinterpret_cast<const float4*>(&s_e[j >> 1][0]);
-            float2 m = pk::bc(r);
+            const int npairs = (j1 - j) >> 1;
+#pragma unroll 4
+            for (int q = 0; q < npairs; ++q, ev += FE / 2) {
+              float2 m = pk::bc(r);
 #pragma unroll
-            for (int k = 0; k < FE / 2; ++k) {
-              const float4 v = ev[k];
-              m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
-              m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
+              for (int k = 0; k < FE / 2; ++k) {
+                const float4 v = ev[k];
+                m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
+                m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
+              }
+              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
             }
-            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+            j += 2 * npairs;
           }
           if (j < j1) {
             const float* ev = &s_e[j >> 1][0];
