@@ -61,9 +61,13 @@ template <bool IS_MAX> __device__ __forceinline__ float comb(float a, float b) {
 template <bool IS_MAX> __device__ __forceinline__ float2 comb2(float2 a, float2 b) {
   return IS_MAX ? make_float2(fmaxf(a.x, b.x), fmaxf(a.y, b.y)) : pk::fadd2(a, b);
 }
-__device__ __forceinline__ void finalize_node(const StepParams& p, int node, float v, int lane) {
-  if (p.agg == GNNCCA_AGG_MEAN) v = v / (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);   // scatter_mean: sum / clamp(count, 1)
-  p.h_out[(int64_t)node * FN + lane] = v;
+// lanes 0..15 hold features (2 fl, 2 fl + 1) of the node's aggregate
+__device__ __forceinline__ void finalize_node(const StepParams& p, int node, float2 v, int fl) {
+  if (p.agg == GNNCCA_AGG_MEAN) {   // scatter_mean: sum / clamp(count, 1)
+    const float cnt = (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);
+    v.x = v.x / cnt; v.y = v.y / cnt;
+  }
+  *reinterpret_cast<float2*>(p.h_out + (int64_t)node * FN + 2 * fl) = v;
 }
 
 constexpr int FA = 4;   // raw attribute width of the ATTR variants (one 16-byte load per edge)
@@ -144,7 +148,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   constexpr int HCS = HC > 0 ? HC : 1;
   static_assert(FE % 2 == 0 && (FE * EIN) % 4 == 0, "weights are read as float4");
   __shared__ __align__(16) float s_wee[FE * EIN];
-  __shared__ float s_wne[FE][FN];
+  __shared__ __align__(8) float s_wne[FE][FN];
   __shared__ __align__(16) float s_wenc[ATTR ? FE * FA : 4];
   __shared__ float s_benc[ATTR ? FE : 1];
   __shared__ __align__(16) float s_c1[HCS * FE];
@@ -184,9 +188,11 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   RawPair<FE, REATT_E, ATTR> cur;
   load_raw<FE, REATT_E, ATTR>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
   __syncthreads();
-  float wne[FE];
+  // phase B: the two half-warps take alternate edge pairs, a lane owns features (2 fl, 2 fl + 1)
+  const int half = lane >> 4, fl = lane & 15;
+  float2 w2[FE];
 #pragma unroll
-  for (int k = 0; k < FE; ++k) wne[k] = s_wne[k][lane];
+  for (int k = 0; k < FE; ++k) w2[k] = *reinterpret_cast<const float2*>(&s_wne[k][2 * fl]);
 
   for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
     const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
@@ -198,12 +204,12 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
-    float r_next = 0.f;   // R row of the chunk's first segment, requested before phase A so that phase B does not wait for it
+    float2 r_next = make_float2(0.f, 0.f);   // R row of the chunk's first segment, requested before phase A so that phase B does not wait for it
     if (p.h_out != nullptr && a < b) {
       if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
       if (lane == 1 && base + b < p.n_edges) nb = p.src[base + b];
       const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
-      r_next = p.R[(int64_t)s_first * FN + lane];
+      r_next = *reinterpret_cast<const float2*>(p.R + (int64_t)s_first * FN + 2 * fl);
     }
     // ------------------------------ phase A: thread per edge pair ------------------------------
     {
@@ -340,45 +346,55 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           mask &= mask - 1;
           const int j1 = mask ? c0 + __ffsll((long long)mask) - 1 : b;
           const int s = s_src[j0];
-          const float r = r_next;
-          if (mask) r_next = p.R[(int64_t)s_src[j1] * FN + lane];      // next segment's row: in flight during this one
+          const float2 r = r_next;
+          if (mask) r_next = *reinterpret_cast<const float2*>(p.R + (int64_t)s_src[j1] * FN + 2 * fl);   // next segment's row: in flight during this one
           float2 acc2 = pk::bc(IS_MAX ? -INFINITY : 0.f);
           int j = j0;
-          if (j & 1) {
-            const float* ev = &s_e[j >> 1][1];
-            float m = r;
+          if (j & 1) {                      // a piece that begins on an odd edge: that edge goes to half 0, ahead of its pairs
+            if (half == 0) {
+              const float* ev = &s_e[j >> 1][1];
+              float2 m = r;
 #pragma unroll
-            for (int k = 0; k < FE; ++k) m = fmaf(ev[2 * k], wne[k], m);
-            acc2.y = comb<IS_MAX>(acc2.y, fmaxf(m, 0.f));
+              for (int k = 0; k < FE; ++k) m = pk::ffma2(w2[k], pk::bc(ev[2 * k]), m);
+              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+            }
             ++j;
           }
-          {   // whole pairs: one pointer walks the staged rows (3 x LDS.128 per pair at immediate offsets)
-            const float4* ev = reinterpret_cast<const float4*>(&s_e[j >> 1][0]);
+          {   // whole pairs, alternately to the two halves; one pointer walks the staged rows (3 x LDS.128 per pair, immediate offsets)
             const int npairs = (j1 - j) >> 1;
+            const int nq = (npairs - half + 1) >> 1;
+            const float4* ev = reinterpret_cast<const float4*>(&s_e[(j >> 1) + half][0]);
 #pragma unroll 4
-            for (int q = 0; q < npairs; ++q, ev += FE / 2) {
-              float2 m = pk::bc(r);
+            for (int q = 0; q < nq; ++q, ev += FE) {
+              float2 ma = r, mb = r;
 #pragma unroll
               for (int k = 0; k < FE / 2; ++k) {
                 const float4 v = ev[k];
-                m = pk::ffma2(make_float2(v.x, v.y), pk::bc(wne[2 * k]), m);
-                m = pk::ffma2(make_float2(v.z, v.w), pk::bc(wne[2 * k + 1]), m);
+                ma = pk::ffma2(w2[2 * k], pk::bc(v.x), ma);
+                mb = pk::ffma2(w2[2 * k], pk::bc(v.y), mb);
+                ma = pk::ffma2(w2[2 * k + 1], pk::bc(v.z), ma);
+                mb = pk::ffma2(w2[2 * k + 1], pk::bc(v.w), mb);
               }
-              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+              acc2 = comb2<IS_MAX>(acc2, pk::relu2(ma));
+              acc2 = comb2<IS_MAX>(acc2, pk::relu2(mb));
             }
             j += 2 * npairs;
           }
-          if (j < j1) {
+          if (j < j1 && half == 1) {         // a piece that ends on an even edge: that edge goes to half 1, after its pairs
             const float* ev = &s_e[j >> 1][0];
-            float m = r;
+            float2 m = r;
 #pragma unroll
-            for (int k = 0; k < FE; ++k) m = fmaf(ev[2 * k], wne[k], m);
-            acc2.x = comb<IS_MAX>(acc2.x, fmaxf(m, 0.f));
+            for (int k = 0; k < FE; ++k) m = pk::ffma2(w2[k], pk::bc(ev[2 * k]), m);
+            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
           }
-          const float acc = comb<IS_MAX>(acc2.x, acc2.y);
+          float2 other;
+          other.x = __shfl_xor_sync(0xffffffffu, acc2.x, 16); other.y = __shfl_xor_sync(0xffffffffu, acc2.y, 16);
+          const float2 acc = half == 0 ? comb2<IS_MAX>(acc2, other) : comb2<IS_MAX>(other, acc2);     // half 0's part first, on every lane
           const bool starts = !(j0 == a && first_cont), ends = !(j1 == b && last_cont);
-          if (starts && ends) finalize_node(p, s, acc, lane);
-          else p.chunk_part[(((int64_t)tile * NWARP + warp) * 2 + (starts ? 1 : 0)) * FN + lane] = acc;   // folded by mp_step_fold_kernel
+          if (half == 0) {
+            if (starts && ends) finalize_node(p, s, acc, fl);
+            else *reinterpret_cast<float2*>(p.chunk_part + (((int64_t)tile * NWARP + warp) * 2 + (starts ? 1 : 0)) * FN + 2 * fl) = acc;   // folded by mp_step_fold_kernel
+          }
         }
       }
     }
