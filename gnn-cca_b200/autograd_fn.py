@@ -216,16 +216,16 @@ class _MPNFunction(torch.autograd.Function):
                     _lib.check(lib.gnncca_cls_bwd(cfg, w, P(es[t]), E, P(aff), 0, P(g), 0, P(ge_cls), P(pa_cls[ci]), _stream()), "cls_bwd")
             Rn = proj[t - 1, N * 16:]            # R of step t, kept by the forward
             if gh is not None:
-                gh_eff = torch.empty_like(gh) if is_max else None
+                gh_eff = torch.empty((2, N, FN), dtype=torch.float32, device=dev) if is_max else None   # gh / ties | recomputed max
                 _lib.check(lib.gnncca_node_agg_bwd(cfg, w, P(plan.rowptr), N, P(Rn), P(es[t]), P(gh), P(hs[t]), P(gR), P(gh_eff), P(pa_agg[t - 1]),
                                                    _stream()), "node_agg_bwd")
                 if is_max:
-                    gh = gh_eff      # ties at the max share the gradient
+                    gh = gh_eff[0]      # ties at the max share the gradient
             else:
                 gR.zero_()
             ge_prev = torch.empty((E, FE), dtype=torch.float32, device=dev)
             _lib.check(lib.gnncca_edge_bwd(cfg, w, P(plan.rowptr), P(plan.src), E, P(Rn), P(es[t]), P(es[t - 1]), P(es[0]) if re else 0, P(gh),
-                                           P(hs[t]) if gh is not None else 0, P(ge_next), P(ge_cls), P(gze), P(ge_prev), P(ge0_acc),
+                                           (P(gh_eff[1]) if is_max else P(hs[t])) if gh is not None else 0, P(ge_next), P(ge_cls), P(gze), P(ge_prev), P(ge0_acc),
                                            P(pa_edge[t - 1]), _stream()), "edge_bwd")
             _lib.check(lib.gnncca_pq_reduce(P(plan.rowptr), P(sv["colptr"]), P(sv["tperm"]), P(gze), N, P(gP), P(gQ), _stream()), "pq_reduce")
             gh_prev = gh_prevs[t - 1]

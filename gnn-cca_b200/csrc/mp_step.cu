@@ -26,6 +26,7 @@
 // No floating-point atomics anywhere: the summation order is a pure function of (E, rowptr), so results are
 // bit-identical run to run (the reference's torch_scatter atomicAdd path is not).
 #include "common.cuh"
+#include "tc_helpers.cuh"
 
 namespace gnncca {
 
@@ -61,15 +62,6 @@ template <bool IS_MAX> __device__ __forceinline__ float comb(float a, float b) {
 template <bool IS_MAX> __device__ __forceinline__ float2 comb2(float2 a, float2 b) {
   return IS_MAX ? make_float2(fmaxf(a.x, b.x), fmaxf(a.y, b.y)) : pk::fadd2(a, b);
 }
-// lanes 0..15 hold features (2 fl, 2 fl + 1) of the node's aggregate
-__device__ __forceinline__ void finalize_node(const StepParams& p, int node, float2 v, int fl) {
-  if (p.agg == GNNCCA_AGG_MEAN) {   // scatter_mean: sum / clamp(count, 1)
-    const float cnt = (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);
-    v.x = v.x / cnt; v.y = v.y / cnt;
-  }
-  *reinterpret_cast<float2*>(p.h_out + (int64_t)node * FN + 2 * fl) = v;
-}
-
 constexpr int FA = 4;   // raw attribute width of the ATTR variants (one 16-byte load per edge)
 
 template <int FE, bool REATT_E, bool ATTR>
@@ -79,6 +71,22 @@ struct RawPair {       // what phase A reads for one edge pair, requested one ti
   float2 xa[(REATT_E && !ATTR) ? FE / 2 : 1], xb[(REATT_E && !ATTR) ? FE / 2 : 1];   // stored initial features
   float4 ta[ATTR ? 1 : 1], tb[ATTR ? 1 : 1];                      // raw attributes
 };
+
+
+// ---- per-warp input ring: the raw inputs of a warp's 64-edge chunk travel global -> shared memory as 1-D bulk copies (TMA engine,
+// completion on an mbarrier), two tiles ahead of their use.  No registers are held across phase B for them and nobody waits for DRAM.
+constexpr int NSTAGE = 2;
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(enc::smem_u32(dst)), "l"(src), "r"(bytes), "r"(enc::smem_u32(bar)) : "memory");
+}
+template <int FE, bool REATT_E, bool ATTR> struct Slot {
+  static constexpr int SRC = 0, DST = CHUNK * 4, E = 2 * CHUNK * 4, X = E + CHUNK * FE * 4;
+  static constexpr int BYTES = X + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
+};
+template <int FE, bool REATT_E, bool ATTR> constexpr int step_dyn_smem() {
+  return NWARP * NSTAGE * Slot<FE, REATT_E, ATTR>::BYTES + TILE * FE * 4 + TILE * 4 + NWARP * NSTAGE * 8;
+}
 
 template <int FE, bool REATT_E, bool ATTR>
 __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPair<FE, REATT_E, ATTR>& r) {
@@ -111,61 +119,134 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
   }
 }
 
-// The same for a pair that lies wholly inside the edge range at an even edge index with 16-byte aligned arrays (every pair of an
-// interior tile when the partition phase is even): the pair's 2 x FE floats are contiguous, so they travel as float4s and the two
-// ids as one 8-byte load; the pairing of the registers (k, k+1 of one edge) is the same as in load_raw.
+// Requests the raw inputs of the chunk [c0, c0 + CHUNK) of `tile` into `slot`.  Interior chunks of a 16-byte aligned layout go as bulk
+// copies (returns true: the consumer waits on `bar`); chunks that touch the ends of the edge range, or any chunk of a partition whose
+// phase breaks the alignment, are loaded through registers with the invalid edges marked src = -1 (returns false).
 template <int FE, bool REATT_E, bool ATTR>
-__device__ __forceinline__ void load_raw_fast(const StepParams& p, int64_t i0, RawPair<FE, REATT_E, ATTR>& r) {
+__device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok) {
+  using SL = Slot<FE, REATT_E, ATTR>;
+  const int64_t cb = tile * TILE - p.phase + c0;     // global index of the chunk's first edge
+  const bool latent = !ATTR || p.e_in != nullptr;
+  if (bulk_ok && cb >= 0 && cb + CHUNK <= p.n_edges) {
+    if (lane == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the slot was last touched through the generic proxy
+      const uint32_t bytes = 2 * CHUNK * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
+      enc::mbar_expect_tx(bar, bytes);
+      bulk_load(slot + SL::SRC, p.src + cb, CHUNK * 4, bar);
+      bulk_load(slot + SL::DST, p.dst + cb, CHUNK * 4, bar);
+      if (latent) bulk_load(slot + SL::E, p.e_in + cb * FE, CHUNK * FE * 4, bar);
+      if (ATTR) bulk_load(slot + SL::X, p.attr + cb * FA, CHUNK * FA * 4, bar);
+      else if (REATT_E) bulk_load(slot + SL::X, p.e0 + cb * FE, CHUNK * FE * 4, bar);
+    }
+    return true;
+  }
+  RawPair<FE, REATT_E, ATTR> r{};
+  load_raw<FE, REATT_E, ATTR>(p, cb + 2 * lane, r);
+  *reinterpret_cast<int2*>(slot + SL::SRC + 8 * lane) = make_int2(r.sa, r.sb);
+  *reinterpret_cast<int2*>(slot + SL::DST + 8 * lane) = make_int2(r.da, r.db);
+  float* e = reinterpret_cast<float*>(slot + SL::E) + 2 * FE * lane;
+#pragma unroll
+  for (int k = 0; k < FE / 2; ++k) {
+    *reinterpret_cast<float2*>(e + 2 * k) = r.ea[k];
+    *reinterpret_cast<float2*>(e + FE + 2 * k) = r.eb[k];
+  }
+  if (ATTR) {
+    float4* x = reinterpret_cast<float4*>(slot + SL::X) + 2 * lane;
+    x[0] = r.ta[0]; x[1] = r.tb[0];
+  } else if (REATT_E) {
+    float* x = reinterpret_cast<float*>(slot + SL::X) + 2 * FE * lane;
+#pragma unroll
+    for (int k = 0; k < FE / 2; ++k) {
+      *reinterpret_cast<float2*>(x + 2 * k) = r.xa[k];
+      *reinterpret_cast<float2*>(x + FE + 2 * k) = r.xb[k];
+    }
+  }
+  __syncwarp();
+  return false;
+}
+
+// A lane's edge pair out of the slot (the register naming of load_raw)
+template <int FE, bool REATT_E, bool ATTR>
+__device__ __forceinline__ void read_slot(const unsigned char* slot, int lane, bool latent, RawPair<FE, REATT_E, ATTR>& r) {
+  using SL = Slot<FE, REATT_E, ATTR>;
   static_assert((2 * FE) % 4 == 0, "a pair's features are read as float4");
-  const int2 s2 = ld_stream_i2(p.src + i0), d2 = ld_stream_i2(p.dst + i0);
+  const int2 s2 = *reinterpret_cast<const int2*>(slot + SL::SRC + 8 * lane), d2 = *reinterpret_cast<const int2*>(slot + SL::DST + 8 * lane);
   r.sa = s2.x; r.sb = s2.y; r.da = d2.x; r.db = d2.y;
-  if (!ATTR || p.e_in != nullptr) {
+  if (latent) {
     float t[2 * FE];
 #pragma unroll
     for (int q = 0; q < 2 * FE / 4; ++q) {
-      const float4 v = ld_stream_f4(p.e_in + i0 * FE + 4 * q);
+      const float4 v = *reinterpret_cast<const float4*>(slot + SL::E + (2 * FE * lane + 4 * q) * 4);
       t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w;
     }
 #pragma unroll
     for (int k = 0; k < FE / 2; ++k) { r.ea[k] = make_float2(t[2 * k], t[2 * k + 1]); r.eb[k] = make_float2(t[FE + 2 * k], t[FE + 2 * k + 1]); }
   }
-  if (REATT_E && !ATTR) {
+  if (ATTR) {
+    const float4* x = reinterpret_cast<const float4*>(slot + SL::X) + 2 * lane;
+    r.ta[0] = x[0]; r.tb[0] = x[1];
+  } else if (REATT_E) {
     float t[2 * FE];
 #pragma unroll
     for (int q = 0; q < 2 * FE / 4; ++q) {
-      const float4 v = ld_stream_f4(p.e0 + i0 * FE + 4 * q);
+      const float4 v = *reinterpret_cast<const float4*>(slot + SL::X + (2 * FE * lane + 4 * q) * 4);
       t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w;
     }
 #pragma unroll
     for (int k = 0; k < FE / 2; ++k) { r.xa[k] = make_float2(t[2 * k], t[2 * k + 1]); r.xb[k] = make_float2(t[FE + 2 * k], t[FE + 2 * k + 1]); }
   }
-  if (ATTR) { r.ta[0] = ld_stream_f4(p.attr + i0 * FA); r.tb[0] = ld_stream_f4(p.attr + (i0 + 1) * FA); }
+}
+
+// mma.sync m16n8k8 (tf32 operands, fp32 accumulate): d = a . b + c with separate d / c registers, and in place
+__device__ __forceinline__ void mma_tf32_dc(float (&d)[4], const float (&a)[4], float b0, float b1, float c0, float c1, float c2, float c3) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+               : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+               : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)), "f"(c0), "f"(c1), "f"(c2), "f"(c3));
+}
+__device__ __forceinline__ void mma_tf32_acc(float (&d)[4], const float (&a)[4], float b0, float b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+// the tf32 prefix of an fp32 value (what the tensor core reads of it); value - prefix is exact in fp32
+__device__ __forceinline__ float tf32_prefix(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
+
+// lane (g, t) = (lane >> 2, lane & 3) holds feature 8 t + g of a node's aggregate
+__device__ __forceinline__ void finalize_node_feat(const StepParams& p, int node, float v, int feat) {
+  if (p.agg == GNNCCA_AGG_MEAN) v = v / (float)max(p.rowptr[node + 1] - p.rowptr[node], 1);   // scatter_mean: sum / clamp(count, 1)
+  p.h_out[(int64_t)node * FN + feat] = v;
 }
 
 template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR>
 __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
-  constexpr int HCS = HC > 0 ? HC : 1;
-  static_assert(FE % 2 == 0 && (FE * EIN) % 4 == 0, "weights are read as float4");
-  __shared__ __align__(16) float s_wee[FE * EIN];
-  __shared__ __align__(8) float s_wne[FE][FN];
-  __shared__ __align__(16) float s_wenc[ATTR ? FE * FA : 4];
-  __shared__ float s_benc[ATTR ? FE : 1];
-  __shared__ __align__(16) float s_c1[HCS * FE];
-  __shared__ float s_b1[HCS], s_c2[HCS], s_b2;
-  __shared__ __align__(16) float s_e[TILE / 2][2 * FE];      // [pair][k][2]
-  __shared__ __align__(8) int s_src[TILE];
+  constexpr int HCS = HC > 0 ? HC : 2;
+  constexpr int FEP = (FE + 3) & ~3;      // row stride of the transposed weight tables (16-byte rows)
+  static_assert(FE % 2 == 0 && FE <= 8 && HCS % 2 == 0, "outputs are handled as (o, o + 1) pairs; an edge row is one k-step of the mma");
+  __shared__ __align__(16) float s_weeT[EIN][FEP];           // [k][o]: the pair (o, o + 1) is one FFMA2 operand
+  __shared__ __align__(16) float4 s_afrag[4][32];             // phase B: W_ne^T as mma A fragments, [tile i][hi | lo] per lane
+  __shared__ __align__(16) float s_wencT[ATTR ? FA : 1][FEP];
+  __shared__ __align__(8) float s_benc[ATTR ? FE : 2];
+  __shared__ __align__(16) float s_c1T[FE][HCS];             // [k][c]
+  __shared__ __align__(16) float s_b1[HCS], s_c2[HCS];
+  __shared__ float s_b2;
+  using SL = Slot<FE, REATT_E, ATTR>;
+  extern __shared__ __align__(128) unsigned char step_dyn[];
+  float (*s_e)[FE] = reinterpret_cast<float (*)[FE]>(step_dyn + NWARP * NSTAGE * SL::BYTES);      // e' of the tile, one row per edge (B operand of phase B)
+  int* s_src = reinterpret_cast<int*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4);
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4 + TILE * 4);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = p.nf * FN;
   if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;   // CSR not valid (unsorted / out of range): uniform exit
   const bool classify = HC > 0 && p.logits != nullptr;
   {  // stage weights (read from the live parameters at every launch)
-    const int edge_row = 2 * K + EIN, node_row = K + FE;
-    for (int idx = tid; idx < FE * EIN; idx += THREADS) s_wee[idx] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
-    for (int idx = tid; idx < FE * FN; idx += THREADS) s_wne[idx / FN][idx % FN] = p.w.w_node[(idx % FN) * node_row + K + idx / FN];
+    const int edge_row = 2 * K + EIN;
+    for (int idx = tid; idx < FE * EIN; idx += THREADS) s_weeT[idx % EIN][idx / EIN] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
     if (ATTR) {
-      for (int idx = tid; idx < FE * FA; idx += THREADS) s_wenc[idx] = p.w_enc[idx];
+      for (int idx = tid; idx < FE * FA; idx += THREADS) s_wencT[idx % FA][idx / FA] = p.w_enc[idx];
       for (int idx = tid; idx < FE; idx += THREADS) s_benc[idx] = p.b_enc[idx];
     }
     if (classify) {
@@ -175,28 +256,64 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           scale = p.w.bn_weight[c] / sqrtf(p.w.bn_var[c] + p.w.bn_eps);
           shift = p.w.bn_bias[c] - p.w.bn_mean[c] * scale;
         }
-        for (int k = 0; k < FE; ++k) s_c1[c * FE + k] = p.w.w_c1[c * FE + k] * scale;
+        for (int k = 0; k < FE; ++k) s_c1T[k][c] = p.w.w_c1[c * FE + k] * scale;
         s_b1[c] = p.w.b_c1[c] * scale + shift;
         s_c2[c] = p.w.w_c2[c];
       }
       if (tid == 0) s_b2 = p.w.b_c2[0];
     }
   }
-  // interior tiles of an even partition phase read their pairs as 16-byte vectors (uniform over the launch)
-  const bool vec_ok = (p.phase & 1) == 0 && (((uintptr_t)p.e_in | (uintptr_t)p.e0 | (uintptr_t)p.attr) & 15) == 0 &&
-                      (((uintptr_t)p.src | (uintptr_t)p.dst) & 7) == 0;
-  RawPair<FE, REATT_E, ATTR> cur;
-  load_raw<FE, REATT_E, ATTR>(p, (int64_t)blockIdx.x * TILE - p.phase + 2 * tid, cur);
-  __syncthreads();
-  // phase B: the two half-warps take alternate edge pairs, a lane owns features (2 fl, 2 fl + 1)
-  const int half = lane >> 4, fl = lane & 15;
-  float2 w2[FE];
+  // interior chunks of a 16-byte aligned layout arrive as bulk copies (uniform over the launch)
+  const bool bulk_ok = (p.phase & 3) == 0 && (((uintptr_t)p.e_in | (uintptr_t)p.e0 | (uintptr_t)p.attr | (uintptr_t)p.src | (uintptr_t)p.dst) & 15) == 0;
+  const bool vec_out = (p.phase & 1) == 0 && (((uintptr_t)p.e_out) & 15) == 0;
+  const bool latent = !ATTR || p.e_in != nullptr;
+  if (tid < NWARP * NSTAGE) enc::mbar_init(&s_bar[tid], 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  // phase B operands: the message GEMM runs transposed, m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges], as two
+  // m16n8k8 tiles.  k-slot t carries edge feature 2t and k-slot t + 4 feature 2t + 1 (a lane reads ONE float2 of the staged row); the
+  // slots beyond FE are zero.  3xTF32: operands split into their tf32 prefix and the exact rest, lo.hi + hi.lo + hi.hi.
+  // The 16 weight fragment registers of a lane are parked in shared memory ([4][32 lanes] float4: conflict-free LDS.128) and
+  // fetched at the start of each phase B, so that they are not live (and spilled) across phase A.
+  const int g = lane >> 2, t = lane & 3;
+  if (warp == 0) {
 #pragma unroll
-  for (int k = 0; k < FE; ++k) w2[k] = *reinterpret_cast<const float2*>(&s_wne[k][2 * fl]);
+    for (int i = 0; i < 2; ++i) {
+      float hi4[4], lo4[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int k = 2 * t + (q >> 1), feat = 16 * i + g + 8 * (q & 1);
+        const float w = k < FE ? p.w.w_node[feat * (K + FE) + K + k] : 0.f;
+        hi4[q] = tf32_prefix(w); lo4[q] = w - hi4[q];
+      }
+      s_afrag[2 * i][lane] = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
+      s_afrag[2 * i + 1][lane] = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
+    }
+  }
+  __syncthreads();
 
-  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+  unsigned char* ring = step_dyn + (size_t)warp * NSTAGE * SL::BYTES;      // this warp's slots
+  uint64_t* wbar = s_bar + warp * NSTAGE;
+  uint32_t parity = 0, isbulk = 0;      // bit per slot
+#pragma unroll
+  for (int st = 0; st < NSTAGE; ++st) {
+    const int64_t t0 = (int64_t)blockIdx.x + (int64_t)st * gridDim.x;
+    if (t0 < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok)) isbulk |= 1u << st;
+  }
+
+  int it = 0;
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
     const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
     const int64_t i0 = base + 2 * tid;
+    RawPair<FE, REATT_E, ATTR> cur;
+    {
+      const int sl = it & (NSTAGE - 1);
+      if ((isbulk >> sl) & 1u) { enc::mbar_wait(wbar + sl, (parity >> sl) & 1u); parity ^= 1u << sl; }
+      read_slot<FE, REATT_E, ATTR>(ring + sl * SL::BYTES, lane, latent, cur);
+      __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
+      const int64_t nt = (int64_t)tile + (int64_t)NSTAGE * gridDim.x;
+      isbulk &= ~(1u << sl);
+      if (nt < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok)) isbulk |= 1u << sl;
+    }
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
     // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
     // just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
@@ -204,51 +321,50 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
-    float2 r_next = make_float2(0.f, 0.f);   // R row of the chunk's first segment, requested before phase A so that phase B does not wait for it
+    float r_next[4] = {0.f, 0.f, 0.f, 0.f};   // R row of the chunk's first segment (features g + 8 q), requested before phase A
     if (p.h_out != nullptr && a < b) {
       if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
       if (lane == 1 && base + b < p.n_edges) nb = p.src[base + b];
       const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
-      r_next = *reinterpret_cast<const float2*>(p.R + (int64_t)s_first * FN + 2 * fl);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)s_first * FN + g + 8 * q];
     }
     // ------------------------------ phase A: thread per edge pair ------------------------------
+    // Packed arithmetic runs over OUTPUT pairs (o, o + 1) of one edge: the weight pair comes out of shared memory as an aligned
+    // register pair and the edge value is the broadcast scalar (pairing the two EDGES instead cost two register moves per FFMA2).
     {
-      float2 ein[EIN];
+      float xa[EIN], xb[EIN];
       constexpr int OFF = REATT_E ? FE : 0;
-      float2 e0p[ATTR ? FE : 1];
-      if (ATTR) {     // e0 = ReLU(W_enc attr + b_enc) for both edges of the pair (the FMA order of the stand-alone encoder kernel)
-        const float2 t0 = make_float2(cur.ta[0].x, cur.tb[0].x), t1 = make_float2(cur.ta[0].y, cur.tb[0].y);
-        const float2 t2 = make_float2(cur.ta[0].z, cur.tb[0].z), t3 = make_float2(cur.ta[0].w, cur.tb[0].w);
+      float2 e0a[ATTR ? FE / 2 : 1], e0b[ATTR ? FE / 2 : 1];
+      if (ATTR) {     // e0 = ReLU(W_enc attr + b_enc) (the FMA order of the stand-alone encoder kernel)
+        const float ta[FA] = {cur.ta[0].x, cur.ta[0].y, cur.ta[0].z, cur.ta[0].w}, tb[FA] = {cur.tb[0].x, cur.tb[0].y, cur.tb[0].z, cur.tb[0].w};
 #pragma unroll
-        for (int o = 0; o < FE; ++o) {
-          const float4 w4 = *reinterpret_cast<const float4*>(&s_wenc[o * FA]);
-          float2 acc = pk::bc(s_benc[o]);
-          acc = pk::ffma2(t0, pk::bc(w4.x), acc); acc = pk::ffma2(t1, pk::bc(w4.y), acc);
-          acc = pk::ffma2(t2, pk::bc(w4.z), acc); acc = pk::ffma2(t3, pk::bc(w4.w), acc);
-          e0p[o] = pk::relu2(acc);
+        for (int j = 0; j < FE / 2; ++j) {
+          float2 aa = *reinterpret_cast<const float2*>(&s_benc[2 * j]), ab = aa;
+#pragma unroll
+          for (int k = 0; k < FA; ++k) {
+            const float2 w = *reinterpret_cast<const float2*>(&s_wencT[k][2 * j]);
+            aa = pk::ffma2(w, pk::bc(ta[k]), aa); ab = pk::ffma2(w, pk::bc(tb[k]), ab);
+          }
+          e0a[j] = pk::relu2(aa); e0b[j] = pk::relu2(ab);
         }
       }
       if (REATT_E) {  // cat(initial_edge_feats, latent_edge_feats), mpn.py:283
-        if (ATTR) {
-#pragma unroll
-          for (int k = 0; k < FE; ++k) ein[k] = e0p[k];
-        } else {
-#pragma unroll
-          for (int k = 0; k < FE / 2; ++k) {
-            ein[2 * k] = make_float2(cur.xa[k].x, cur.xb[k].x); ein[2 * k + 1] = make_float2(cur.xa[k].y, cur.xb[k].y);
-          }
-        }
-      }
-      if (ATTR && p.e_in == nullptr) {   // step 1: the latent features are the encoded ones
-#pragma unroll
-        for (int k = 0; k < FE; ++k) ein[OFF + k] = e0p[k];
-      } else {
 #pragma unroll
         for (int k = 0; k < FE / 2; ++k) {
-          ein[OFF + 2 * k] = make_float2(cur.ea[k].x, cur.eb[k].x); ein[OFF + 2 * k + 1] = make_float2(cur.ea[k].y, cur.eb[k].y);
+          if (ATTR) { xa[2 * k] = e0a[k].x; xa[2 * k + 1] = e0a[k].y; xb[2 * k] = e0b[k].x; xb[2 * k + 1] = e0b[k].y; }
+          else { xa[2 * k] = cur.xa[k].x; xa[2 * k + 1] = cur.xa[k].y; xb[2 * k] = cur.xb[k].x; xb[2 * k + 1] = cur.xb[k].y; }
         }
       }
-      float2 en[8];
+#pragma unroll
+      for (int k = 0; k < FE / 2; ++k) {
+        if (ATTR && p.e_in == nullptr) {   // step 1: the latent features are the encoded ones
+          xa[OFF + 2 * k] = e0a[k].x; xa[OFF + 2 * k + 1] = e0a[k].y; xb[OFF + 2 * k] = e0b[k].x; xb[OFF + 2 * k + 1] = e0b[k].y;
+        } else {
+          xa[OFF + 2 * k] = cur.ea[k].x; xa[OFF + 2 * k + 1] = cur.ea[k].y; xb[OFF + 2 * k] = cur.eb[k].x; xb[OFF + 2 * k + 1] = cur.eb[k].y;
+        }
+      }
+      float2 ea[FE / 2], eb[FE / 2];
       {
         float4 pa0 = make_float4(0.f, 0.f, 0.f, 0.f), pa1 = pa0, qa0 = pa0, qa1 = pa0, pb0 = pa0, pb1 = pa0, qb0 = pa0, qb1 = pa0;
         if (va) {
@@ -259,76 +375,86 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8); pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8 + 4);
           qb0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8); qb1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8 + 4);
         }
-        en[0] = make_float2(pa0.x + qa0.x, pb0.x + qb0.x); en[1] = make_float2(pa0.y + qa0.y, pb0.y + qb0.y);
-        en[2] = make_float2(pa0.z + qa0.z, pb0.z + qb0.z); en[3] = make_float2(pa0.w + qa0.w, pb0.w + qb0.w);
-        en[4] = make_float2(pa1.x + qa1.x, pb1.x + qb1.x); en[5] = make_float2(pa1.y + qa1.y, pb1.y + qb1.y);
-        en[6] = make_float2(pa1.z + qa1.z, pb1.z + qb1.z); en[7] = make_float2(pa1.w + qa1.w, pb1.w + qb1.w);
+        const float2 pa[4] = {make_float2(pa0.x, pa0.y), make_float2(pa0.z, pa0.w), make_float2(pa1.x, pa1.y), make_float2(pa1.z, pa1.w)};
+        const float2 qa[4] = {make_float2(qa0.x, qa0.y), make_float2(qa0.z, qa0.w), make_float2(qa1.x, qa1.y), make_float2(qa1.z, qa1.w)};
+        const float2 pb[4] = {make_float2(pb0.x, pb0.y), make_float2(pb0.z, pb0.w), make_float2(pb1.x, pb1.y), make_float2(pb1.z, pb1.w)};
+        const float2 qb[4] = {make_float2(qb0.x, qb0.y), make_float2(qb0.z, qb0.w), make_float2(qb1.x, qb1.y), make_float2(qb1.z, qb1.w)};
+#pragma unroll
+        for (int j = 0; j < FE / 2; ++j) { ea[j] = pk::fadd2(pa[j], qa[j]); eb[j] = pk::fadd2(pb[j], qb[j]); }
       }
 #pragma unroll
-      for (int o = 0; o < FE; ++o) {
-        float2 acc = en[o];
+      for (int k = 0; k < EIN; ++k) {
 #pragma unroll
-        for (int k = 0; k < EIN; k += 2) {     // FE * EIN is a multiple of 4 and EIN is even: (o * EIN + k) is even
-          const float2 w2 = *reinterpret_cast<const float2*>(&s_wee[o * EIN + k]);
-          acc = pk::ffma2(ein[k], pk::bc(w2.x), acc);
-          acc = pk::ffma2(ein[k + 1], pk::bc(w2.y), acc);
+        for (int j = 0; j < FE / 2; ++j) {
+          const float2 w = *reinterpret_cast<const float2*>(&s_weeT[k][2 * j]);
+          ea[j] = pk::ffma2(w, pk::bc(xa[k]), ea[j]);
+          eb[j] = pk::ffma2(w, pk::bc(xb[k]), eb[j]);
         }
-        en[o] = pk::relu2(acc);
-      }
-      if (va && p.e_out != nullptr) {       // NULL in the last step of an inference forward: nothing reads e^L (mpn.py:288-299)
-#pragma unroll
-        for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + i0 * FE + k, make_float2(en[k].x, en[k + 1].x));
-      }
-      if (vb && p.e_out != nullptr) {
-#pragma unroll
-        for (int k = 0; k < FE; k += 2) st_stream_f2(p.e_out + (i0 + 1) * FE + k, make_float2(en[k].y, en[k + 1].y));
       }
 #pragma unroll
-      for (int k = 0; k < FE; k += 2)
-        *reinterpret_cast<float4*>(&s_e[tid][2 * k]) = make_float4(en[k].x, en[k].y, en[k + 1].x, en[k + 1].y);
+      for (int j = 0; j < FE / 2; ++j) { ea[j] = pk::relu2(ea[j]); eb[j] = pk::relu2(eb[j]); }
+      float row[2 * FE];          // the pair's two rows, contiguous in e_out and in s_e
+#pragma unroll
+      for (int j = 0; j < FE / 2; ++j) { row[2 * j] = ea[j].x; row[2 * j + 1] = ea[j].y; row[FE + 2 * j] = eb[j].x; row[FE + 2 * j + 1] = eb[j].y; }
+      if (p.e_out != nullptr) {       // NULL in the last step of an inference forward: nothing reads e^L (mpn.py:288-299)
+        if (vec_out && va && vb) {
+#pragma unroll
+          for (int q = 0; q < 2 * FE / 4; ++q) st_stream_f4(p.e_out + i0 * FE + 4 * q, make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]));
+        } else {
+          if (va) {
+#pragma unroll
+            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + i0 * FE + 2 * j, ea[j]);
+          }
+          if (vb) {
+#pragma unroll
+            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + (i0 + 1) * FE + 2 * j, eb[j]);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 2 * FE / 4; ++q)
+        *reinterpret_cast<float4*>(&s_e[2 * tid][0] + 4 * q) = make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]);
       *reinterpret_cast<int2*>(&s_src[2 * tid]) = make_int2(cur.sa, cur.sb);
       if (classify) {
-        float2 logit = pk::bc(s_b2);
+        float2 ha[HCS / 2], hb[HCS / 2];
 #pragma unroll
-        for (int c = 0; c < HC; ++c) {
-          float2 hcv = pk::bc(s_b1[c]);
+        for (int c = 0; c < HCS / 2; ++c) ha[c] = hb[c] = *reinterpret_cast<const float2*>(&s_b1[2 * c]);
 #pragma unroll
-          for (int k = 0; k < FE; k += 2) {
-            const float2 w2 = *reinterpret_cast<const float2*>(&s_c1[c * FE + k]);
-            hcv = pk::ffma2(en[k], pk::bc(w2.x), hcv);
-            hcv = pk::ffma2(en[k + 1], pk::bc(w2.y), hcv);
+        for (int k = 0; k < FE; ++k) {
+#pragma unroll
+          for (int c = 0; c < HCS / 2; ++c) {
+            const float2 w = *reinterpret_cast<const float2*>(&s_c1T[k][2 * c]);
+            ha[c] = pk::ffma2(w, pk::bc(row[k]), ha[c]);
+            hb[c] = pk::ffma2(w, pk::bc(row[FE + k]), hb[c]);
           }
-          logit = pk::ffma2(pk::relu2(hcv), pk::bc(s_c2[c]), logit);
         }
-        if (va) st_stream_f1(p.logits + i0, logit.x);
-        if (vb) st_stream_f1(p.logits + i0 + 1, logit.y);
-      }
-    }
-    const int next_tile = tile + gridDim.x;
-    if (next_tile < p.num_tiles) {
-      const int64_t nbase = (int64_t)next_tile * TILE - p.phase;
-      if (vec_ok && nbase >= 0 && nbase + TILE <= p.n_edges) load_raw_fast<FE, REATT_E, ATTR>(p, nbase + 2 * tid, cur);
-      else load_raw<FE, REATT_E, ATTR>(p, nbase + 2 * tid, cur);
-    }
-    {  // the tile after that: pull its lines into L2 now (one 128-byte line per thread), DRAM latency off the critical path
-      const int64_t far = (int64_t)next_tile + gridDim.x;
-      if (far < p.num_tiles) {
-        const int64_t fb = far * TILE - p.phase;        // > 0: far >= 2
-        constexpr int LE = TILE * FE / 32, LI = TILE / 32, LA = TILE * FA / 32;      // lines of e_in (e0), of src / dst, of attr
-        const char* ptr = nullptr; const char* end = nullptr;
-        if (tid < LE) { if (p.e_in != nullptr) { ptr = (const char*)(p.e_in + fb * FE); end = (const char*)(p.e_in + p.n_edges * FE); } }
-        else if (tid < LE + LI) { ptr = (const char*)(p.src + fb) - LE * 128; end = (const char*)(p.src + p.n_edges); }
-        else if (tid < LE + 2 * LI) { ptr = (const char*)(p.dst + fb) - (LE + LI) * 128; end = (const char*)(p.dst + p.n_edges); }
-        else if (ATTR && tid < LE + 2 * LI + LA) { ptr = (const char*)(p.attr + fb * FA) - (LE + 2 * LI) * 128; end = (const char*)(p.attr + p.n_edges * FA); }
-        else if (REATT_E && !ATTR && tid < 2 * LE + 2 * LI) { ptr = (const char*)(p.e0 + fb * FE) - (LE + 2 * LI) * 128; end = (const char*)(p.e0 + p.n_edges * FE); }
-        if (ptr != nullptr) { ptr += (size_t)tid * 128; if (ptr < end) prefetch_l2(ptr); }
+        float la = s_b2, lb = la;
+#pragma unroll
+        for (int c = 0; c < HCS / 2; ++c) {
+          const float2 w = *reinterpret_cast<const float2*>(&s_c2[2 * c]);
+          la = fmaf(fmaxf(ha[c].x, 0.f), w.x, la); la = fmaf(fmaxf(ha[c].y, 0.f), w.y, la);
+          lb = fmaf(fmaxf(hb[c].x, 0.f), w.x, lb); lb = fmaf(fmaxf(hb[c].y, 0.f), w.y, lb);
+        }
+        if (va) st_stream_f1(p.logits + i0, la);
+        if (vb) st_stream_f1(p.logits + i0 + 1, lb);
       }
     }
     if (p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
     __syncwarp();
-    // ------------------------------ phase B: lane per feature ------------------------------
+    // ------------------------------ phase B: messages of 8 edges per mma ------------------------------
+    // The chunk is cut into 8-edge blocks aligned to the global numbering.  A piece (edges of one source inside the chunk) walks
+    // its blocks; the accumulator tile starts as the R row of the source (C operand), ReLU and the running aggregate are applied
+    // to the D fragment (lane (g, t): features g + 8 q of edges 2t, 2t + 1), edges of a block outside the piece are zeroed (a
+    // ReLU output is >= 0, so 0 is neutral for sum and max alike).  Lanes are folded once per piece.
     {
       if (a < b) {
+        float a_hi[2][4], a_lo[2][4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const float4 h4 = s_afrag[2 * i][lane], l4 = s_afrag[2 * i + 1][lane];
+          a_hi[i][0] = h4.x; a_hi[i][1] = h4.y; a_hi[i][2] = h4.z; a_hi[i][3] = h4.w;
+          a_lo[i][0] = l4.x; a_lo[i][1] = l4.y; a_lo[i][2] = l4.z; a_lo[i][3] = l4.w;
+        }
         const int nb_prev = __shfl_sync(0xffffffffu, nb, 0), nb_next = __shfl_sync(0xffffffffu, nb, 1);
         const int ie = c0 + 2 * lane;
         const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
@@ -346,55 +472,65 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           mask &= mask - 1;
           const int j1 = mask ? c0 + __ffsll((long long)mask) - 1 : b;
           const int s = s_src[j0];
-          const float2 r = r_next;
-          if (mask) r_next = *reinterpret_cast<const float2*>(p.R + (int64_t)s_src[j1] * FN + 2 * fl);   // next segment's row: in flight during this one
-          float2 acc2 = pk::bc(IS_MAX ? -INFINITY : 0.f);
-          int j = j0;
-          if (j & 1) {                      // a piece that begins on an odd edge: that edge goes to half 0, ahead of its pairs
-            if (half == 0) {
-              const float* ev = &s_e[j >> 1][1];
-              float2 m = r;
+          float r[4];
 #pragma unroll
-              for (int k = 0; k < FE; ++k) m = pk::ffma2(w2[k], pk::bc(ev[2 * k]), m);
-              acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
-            }
-            ++j;
+          for (int q = 0; q < 4; ++q) r[q] = r_next[q];
+          if (mask) {   // next segment's row: in flight during this one
+            const int sn = s_src[j1];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)sn * FN + g + 8 * q];
           }
-          {   // whole pairs, alternately to the two halves; one pointer walks the staged rows (3 x LDS.128 per pair, immediate offsets)
-            const int npairs = (j1 - j) >> 1;
-            const int nq = (npairs - half + 1) >> 1;
-            const float4* ev = reinterpret_cast<const float4*>(&s_e[(j >> 1) + half][0]);
-#pragma unroll 4
-            for (int q = 0; q < nq; ++q, ev += FE) {
-              float2 ma = r, mb = r;
+          float acc[2][4];
 #pragma unroll
-              for (int k = 0; k < FE / 2; ++k) {
-                const float4 v = ev[k];
-                ma = pk::ffma2(w2[2 * k], pk::bc(v.x), ma);
-                mb = pk::ffma2(w2[2 * k], pk::bc(v.y), mb);
-                ma = pk::ffma2(w2[2 * k + 1], pk::bc(v.z), ma);
-                mb = pk::ffma2(w2[2 * k + 1], pk::bc(v.w), mb);
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][q] = 0.f;
+          const int e_lo = j0 - 2 * t, e_hi = j1 - 2 * t;     // edge kb + 2t + x is in the piece iff e_lo <= kb + x < e_hi
+#pragma unroll 2
+          for (int kb = j0 & ~7; kb < j1; kb += 8) {
+            float2 v = make_float2(0.f, 0.f);
+            if (2 * t < FE) v = *reinterpret_cast<const float2*>(&s_e[kb + g][2 * t]);
+            const float bh0 = tf32_prefix(v.x), bh1 = tf32_prefix(v.y);
+            const float bl0 = v.x - bh0, bl1 = v.y - bh1;
+            float d[2][4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              mma_tf32_dc(d[i], a_lo[i], bh0, bh1, r[2 * i], r[2 * i], r[2 * i + 1], r[2 * i + 1]);
+              mma_tf32_acc(d[i], a_hi[i], bl0, bl1);
+              mma_tf32_acc(d[i], a_hi[i], bh0, bh1);
+            }
+            if (kb < j0 || kb + 8 > j1) {        // a block that the piece covers in part (uniform over the warp)
+              const bool k0 = kb >= e_lo && kb < e_hi, k1 = kb + 1 >= e_lo && kb + 1 < e_hi;
+#pragma unroll
+              for (int i = 0; i < 2; ++i) {
+                d[i][0] = k0 ? d[i][0] : 0.f; d[i][2] = k0 ? d[i][2] : 0.f;
+                d[i][1] = k1 ? d[i][1] : 0.f; d[i][3] = k1 ? d[i][3] : 0.f;
               }
-              acc2 = comb2<IS_MAX>(acc2, pk::relu2(ma));
-              acc2 = comb2<IS_MAX>(acc2, pk::relu2(mb));
             }
-            j += 2 * npairs;
-          }
-          if (j < j1 && half == 1) {         // a piece that ends on an even edge: that edge goes to half 1, after its pairs
-            const float* ev = &s_e[j >> 1][0];
-            float2 m = r;
 #pragma unroll
-            for (int k = 0; k < FE; ++k) m = pk::ffma2(w2[k], pk::bc(ev[2 * k]), m);
-            acc2 = comb2<IS_MAX>(acc2, pk::relu2(m));
+            for (int i = 0; i < 2; ++i) {
+              if (IS_MAX) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[i][q] = fmaxf(acc[i][q], d[i][q]);    // max(acc, relu(d)) with acc >= 0
+              } else {
+                const float2 s01 = pk::fadd2(make_float2(acc[i][0], acc[i][1]), pk::relu2(make_float2(d[i][0], d[i][1])));
+                const float2 s23 = pk::fadd2(make_float2(acc[i][2], acc[i][3]), pk::relu2(make_float2(d[i][2], d[i][3])));
+                acc[i][0] = s01.x; acc[i][1] = s01.y; acc[i][2] = s23.x; acc[i][3] = s23.y;
+              }
+            }
           }
-          float2 other;
-          other.x = __shfl_xor_sync(0xffffffffu, acc2.x, 16); other.y = __shfl_xor_sync(0xffffffffu, acc2.y, 16);
-          const float2 acc = half == 0 ? comb2<IS_MAX>(acc2, other) : comb2<IS_MAX>(other, acc2);     // half 0's part first, on every lane
+          float v4[4];     // feature g + 8 q: even edges then odd edges, then the four t lanes by two exchanges
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float x = comb<IS_MAX>(acc[q >> 1][2 * (q & 1)], acc[q >> 1][2 * (q & 1) + 1]);
+            x = comb<IS_MAX>(x, __shfl_xor_sync(0xffffffffu, x, 1));
+            x = comb<IS_MAX>(x, __shfl_xor_sync(0xffffffffu, x, 2));
+            v4[q] = x;
+          }
+          const float mine = t == 0 ? v4[0] : t == 1 ? v4[1] : t == 2 ? v4[2] : v4[3];     // lane (g, t) writes feature g + 8 t
           const bool starts = !(j0 == a && first_cont), ends = !(j1 == b && last_cont);
-          if (half == 0) {
-            if (starts && ends) finalize_node(p, s, acc, fl);
-            else *reinterpret_cast<float2*>(p.chunk_part + (((int64_t)tile * NWARP + warp) * 2 + (starts ? 1 : 0)) * FN + 2 * fl) = acc;   // folded by mp_step_fold_kernel
-          }
+          if (starts && ends) finalize_node_feat(p, s, mine, g + 8 * t);
+          else p.chunk_part[(((int64_t)tile * NWARP + warp) * 2 + (starts ? 1 : 0)) * FN + g + 8 * t] = mine;   // folded by mp_step_fold_kernel
         }
       }
     }
@@ -451,7 +587,18 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
   const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * STEP_MIN_CTAS);
   const bool is_max = sp.agg == GNNCCA_AGG_MAX;
   const bool attr = sp.attr != nullptr;
-#define GNNCCA_STEP(R, M, A) mp_step_fwd_kernel<FE, HC, R, M, A><<<grid, THREADS, 0, st>>>(sp)
+#define GNNCCA_STEP(R, M, A)                                                                                              \
+  do {                                                                                                                    \
+    constexpr int smem = step_dyn_smem<FE, R, A>();                                                                       \
+    static bool optin[16] = {};          /* static + dynamic shared memory exceed 48 KB: opt in once per device */         \
+    int dev = 0; cudaGetDevice(&dev);                                                                                     \
+    if (!optin[dev & 15]) {                                                                                               \
+      const int rc = check_cuda(cudaFuncSetAttribute(mp_step_fwd_kernel<FE, HC, R, M, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+      if (rc) return rc;                                                                                                  \
+      optin[dev & 15] = true;                                                                                             \
+    }                                                                                                                     \
+    mp_step_fwd_kernel<FE, HC, R, M, A><<<grid, THREADS, smem, st>>>(sp);                                                 \
+  } while (0)
   if (reatt_e) {
     if (is_max) { if (attr) GNNCCA_STEP(true, true, true); else GNNCCA_STEP(true, true, false); }
     else { if (attr) GNNCCA_STEP(true, false, true); else GNNCCA_STEP(true, false, false); }

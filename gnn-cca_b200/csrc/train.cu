@@ -71,21 +71,25 @@ __global__ void __launch_bounds__(TB) node_agg_bwd_kernel(const NodeAggBwd p) {
   for (int64_t v = (int64_t)blockIdx.x * NW + warp; v < p.n_nodes; v += (int64_t)gridDim.x * NW) {
     const int j0 = p.rowptr[v], j1 = p.rowptr[v + 1];
     const float r = p.R[v * FN + lane], gh_in = p.gh[v * FN + lane];
-    const float hval = p.agg == GNNCCA_AGG_MAX ? p.h_out[v * FN + lane] : 0.f;
     const float inv_deg = j1 > j0 ? 1.f / (float)(j1 - j0) : 0.f;
-    float gh = gh_in;
+    float gh = gh_in, hval = 0.f;
     if (p.agg == GNNCCA_AGG_MAX) {
-      // Several edges can attain the max exactly (every edge whose updated feature row is all zero has z == R[v]);
-      // the gradient is shared between them (torch amax semantics; the total is what torch_scatter's argmax gives too).
+      // The attaining edges are found against the max of the messages as THIS pass recomputes them (one fmaf chain per message, the
+      // same chain in edge_bwd_kernel), not against the forward's h_out: the forward computes the messages on the tensor cores
+      // (3xTF32), whose last bits differ.  Several edges can attain the max exactly (every edge whose updated feature row is all
+      // zero has z == R[v]); the gradient is shared between them (torch amax semantics; the total is what torch_scatter's argmax
+      // gives too).  The recomputed max goes to the second half of gh_eff for gnncca_edge_bwd.
       int ties = 0;
       for (int j = j0; j < j1; ++j) {
         float z = r;
 #pragma unroll
         for (int k = 0; k < FE; ++k) z = fmaf(p.e[(int64_t)j * FE + k], wne[k], z);
-        ties += (z > 0.f && z == hval) ? 1 : 0;
+        if (z > hval) { hval = z; ties = 1; }
+        else if (z > 0.f && z == hval) ++ties;
       }
       gh = ties > 0 ? gh_in / (float)ties : 0.f;
       p.gh_eff[v * FN + lane] = gh;
+      p.gh_eff[(p.n_nodes + v) * FN + lane] = hval;
     }
     float acc = 0.f;
     for (int j = j0; j < j1; ++j) {

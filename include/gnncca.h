@@ -238,8 +238,9 @@ int32_t gnncca_train_blocks(int64_t n_items, int32_t kind);
 
 /* gR[v] = sum over out-edges of d(agg)/d(message) * [z_m > 0] (z_m recomputed from R and e); partial
  * [GNNCCA_BLOCKS_PER_NODE_WARP blocks][f_edge * f_node] holds gW_node[c][K + k] at index c * f_edge + k.
- * gh = gradient wrt h_out; h_out itself is only read for GNNCCA_AGG_MAX, where gh_eff[N][f_node] receives gh divided
- * by the number of edges attaining the max (ties share the gradient) -- pass THAT as gh to gnncca_edge_bwd. */
+ * gh = gradient wrt h_out.  GNNCCA_AGG_MAX: gh_eff[2][N][f_node] receives (0) gh divided by the number of edges attaining the
+ * max (ties share the gradient) and (1) the max of the messages as the backward recomputes them -- pass (0) as gh and (1) as
+ * h_out to gnncca_edge_bwd (h_out of the forward is not read: its last bits come from a different summation). */
 int gnncca_node_agg_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, int64_t n_nodes,
                         const float* R, const float* e, const float* gh, const float* h_out, float* gR, float* gh_eff,
                         float* partial, void* stream);
