@@ -125,23 +125,24 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
 template <int FE, bool REATT_E, bool ATTR>
 __device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok) {
   using SL = Slot<FE, REATT_E, ATTR>;
-  const int64_t cb = tile * TILE - p.phase + c0;     // global index of the chunk's first edge
+  const int cb = (int)tile * TILE - p.phase + c0;     // global index of the chunk's first edge (E < 2^31 - 2 TILE)
+  const int n_edges = (int)p.n_edges;
   const bool latent = !ATTR || p.e_in != nullptr;
-  if (bulk_ok && cb >= 0 && cb + CHUNK <= p.n_edges) {
+  if (bulk_ok && cb >= 0 && cb + CHUNK <= n_edges) {
     if (lane == 0) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the slot was last touched through the generic proxy
       const uint32_t bytes = 2 * CHUNK * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
       enc::mbar_expect_tx(bar, bytes);
       bulk_load(slot + SL::SRC, p.src + cb, CHUNK * 4, bar);
       bulk_load(slot + SL::DST, p.dst + cb, CHUNK * 4, bar);
-      if (latent) bulk_load(slot + SL::E, p.e_in + cb * FE, CHUNK * FE * 4, bar);
-      if (ATTR) bulk_load(slot + SL::X, p.attr + cb * FA, CHUNK * FA * 4, bar);
-      else if (REATT_E) bulk_load(slot + SL::X, p.e0 + cb * FE, CHUNK * FE * 4, bar);
+      if (latent) bulk_load(slot + SL::E, p.e_in + (int64_t)cb * FE, CHUNK * FE * 4, bar);
+      if (ATTR) bulk_load(slot + SL::X, p.attr + (int64_t)cb * FA, CHUNK * FA * 4, bar);
+      else if (REATT_E) bulk_load(slot + SL::X, p.e0 + (int64_t)cb * FE, CHUNK * FE * 4, bar);
     }
     return true;
   }
   RawPair<FE, REATT_E, ATTR> r{};
-  load_raw<FE, REATT_E, ATTR>(p, cb + 2 * lane, r);
+  load_raw<FE, REATT_E, ATTR>(p, (int64_t)cb + 2 * lane, r);
   *reinterpret_cast<int2*>(slot + SL::SRC + 8 * lane) = make_int2(r.sa, r.sb);
   *reinterpret_cast<int2*>(slot + SL::DST + 8 * lane) = make_int2(r.da, r.db);
   float* e = reinterpret_cast<float*>(slot + SL::E) + 2 * FE * lane;
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 2;
   constexpr int FEP = (FE + 3) & ~3;      // row stride of the transposed weight tables (16-byte rows)
-  static_assert(FE % 2 == 0 && FE <= 8 && HCS % 2 == 0, "outputs are handled as (o, o + 1) pairs; an edge row is one k-step of the mma");
+  static_assert(FE % 2 == 0 && FE <= 6 && HCS % 2 == 0, "outputs are handled as (o, o + 1) pairs; an edge row is one k-step of the mma");
   __shared__ __align__(16) float s_weeT[EIN][FEP];           // [k][o]: the pair (o, o + 1) is one FFMA2 operand
   __shared__ __align__(16) float4 s_afrag[4][32];             // phase B: W_ne^T as mma A fragments, [tile i][hi | lo] per lane
   __shared__ __align__(16) float s_wencT[ATTR ? FA : 1][FEP];
@@ -232,6 +233,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   __shared__ __align__(16) float s_c1T[FE][HCS];             // [k][c]
   __shared__ __align__(16) float s_b1[HCS], s_c2[HCS];
   __shared__ float s_b2;
+  __shared__ __align__(8) float s_one[2];                    // B operand of the k-slots that carry the R row
   using SL = Slot<FE, REATT_E, ATTR>;
   extern __shared__ __align__(128) unsigned char step_dyn[];
   float (*s_e)[FE] = reinterpret_cast<float (*)[FE]>(step_dyn + NWARP * NSTAGE * SL::BYTES);      // e' of the tile, one row per edge (B operand of phase B)
@@ -262,11 +264,13 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       }
       if (tid == 0) s_b2 = p.w.b_c2[0];
     }
+    if (tid < 2) s_one[tid] = 1.f;
   }
   // interior chunks of a 16-byte aligned layout arrive as bulk copies (uniform over the launch)
   const bool bulk_ok = (p.phase & 3) == 0 && (((uintptr_t)p.e_in | (uintptr_t)p.e0 | (uintptr_t)p.attr | (uintptr_t)p.src | (uintptr_t)p.dst) & 15) == 0;
   const bool vec_out = (p.phase & 1) == 0 && (((uintptr_t)p.e_out) & 15) == 0;
   const bool latent = !ATTR || p.e_in != nullptr;
+  const int n_edges = (int)p.n_edges;
   if (tid < NWARP * NSTAGE) enc::mbar_init(&s_bar[tid], 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   // phase B operands: the message GEMM runs transposed, m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges], as two
@@ -302,8 +306,8 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
 
   int it = 0;
   for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-    const int64_t base = (int64_t)tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition
-    const int64_t i0 = base + 2 * tid;
+    const int base = tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition (E < 2^31 - 2 TILE)
+    const int i0 = base + 2 * tid;
     RawPair<FE, REATT_E, ATTR> cur;
     {
       const int sl = it & (NSTAGE - 1);
@@ -317,14 +321,14 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
     // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
     // just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
-    const int lo = (int)max((int64_t)0, -base), hi = (int)min((int64_t)TILE, p.n_edges - base);   // valid tile-local edge range
+    const int lo = max(0, -base), hi = min(TILE, n_edges - base);   // valid tile-local edge range
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
     float r_next[4] = {0.f, 0.f, 0.f, 0.f};   // R row of the chunk's first segment (features g + 8 q), requested before phase A
     if (p.h_out != nullptr && a < b) {
       if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
-      if (lane == 1 && base + b < p.n_edges) nb = p.src[base + b];
+      if (lane == 1 && base + b < n_edges) nb = p.src[base + b];
       const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
 #pragma unroll
       for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)s_first * FN + g + 8 * q];
@@ -399,15 +403,15 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       if (p.e_out != nullptr) {       // NULL in the last step of an inference forward: nothing reads e^L (mpn.py:288-299)
         if (vec_out && va && vb) {
 #pragma unroll
-          for (int q = 0; q < 2 * FE / 4; ++q) st_stream_f4(p.e_out + i0 * FE + 4 * q, make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]));
+          for (int q = 0; q < 2 * FE / 4; ++q) st_stream_f4(p.e_out + (int64_t)i0 * FE + 4 * q, make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]));
         } else {
           if (va) {
 #pragma unroll
-            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + i0 * FE + 2 * j, ea[j]);
+            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + (int64_t)i0 * FE + 2 * j, ea[j]);
           }
           if (vb) {
 #pragma unroll
-            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + (i0 + 1) * FE + 2 * j, eb[j]);
+            for (int j = 0; j < FE / 2; ++j) st_stream_f2(p.e_out + (int64_t)(i0 + 1) * FE + 2 * j, eb[j]);
           }
         }
       }
@@ -485,27 +489,34 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           for (int i = 0; i < 2; ++i)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[i][q] = 0.f;
-          const int e_lo = j0 - 2 * t, e_hi = j1 - 2 * t;     // edge kb + 2t + x is in the piece iff e_lo <= kb + x < e_hi
+          // The R row of the source rides in the two k-slots the FE edge features leave free (k = 3 and 7, the t == 3 lanes): there the A
+          // fragment holds R split into tf32 prefix + rest and the B fragment holds 1.0, so hi.hi adds R_hi + R_lo; lo.hi sees a zero A,
+          // hi.lo a zero B (1 - prefix(1)).  An edge of the block outside the piece gets an all-zero B column (the 1.0 included): its
+          // messages come out as relu(0) = 0, neutral for sum and max.
+          if (t == 3) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float h = tf32_prefix(r[q]);
+              a_hi[q >> 1][q & 1] = h; a_hi[q >> 1][2 + (q & 1)] = r[q] - h;
+            }
+          }
+          const int kb0 = j0 & ~7;
+          const unsigned span = (unsigned)(j1 - j0);
+          unsigned x = (unsigned)(kb0 + g - j0);                 // edge kb + g is in the piece iff x < span (unsigned)
+          const float2* bp = 2 * t < FE ? reinterpret_cast<const float2*>(&s_e[kb0 + g][2 * t]) : reinterpret_cast<const float2*>(s_one);
+          const int bstep = 2 * t < FE ? 8 * FE / 2 : 0;         // float2 units per block
 #pragma unroll 2
-          for (int kb = j0 & ~7; kb < j1; kb += 8) {
+          for (int kb = kb0; kb < j1; kb += 8, x += 8, bp += bstep) {
             float2 v = make_float2(0.f, 0.f);
-            if (2 * t < FE) v = *reinterpret_cast<const float2*>(&s_e[kb + g][2 * t]);
+            if (x < span) v = *bp;
             const float bh0 = tf32_prefix(v.x), bh1 = tf32_prefix(v.y);
             const float bl0 = v.x - bh0, bl1 = v.y - bh1;
             float d[2][4];
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-              mma_tf32_dc(d[i], a_lo[i], bh0, bh1, r[2 * i], r[2 * i], r[2 * i + 1], r[2 * i + 1]);
+              mma_tf32_dc(d[i], a_lo[i], bh0, bh1, 0.f, 0.f, 0.f, 0.f);
               mma_tf32_acc(d[i], a_hi[i], bl0, bl1);
               mma_tf32_acc(d[i], a_hi[i], bh0, bh1);
-            }
-            if (kb < j0 || kb + 8 > j1) {        // a block that the piece covers in part (uniform over the warp)
-              const bool k0 = kb >= e_lo && kb < e_hi, k1 = kb + 1 >= e_lo && kb + 1 < e_hi;
-#pragma unroll
-              for (int i = 0; i < 2; ++i) {
-                d[i][0] = k0 ? d[i][0] : 0.f; d[i][2] = k0 ? d[i][2] : 0.f;
-                d[i][1] = k1 ? d[i][1] : 0.f; d[i][3] = k1 ? d[i][3] : 0.f;
-              }
             }
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
@@ -619,7 +630,7 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
                         const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
                         float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream,
                         const float* attr, const float* w_enc, const float* b_enc) {
-  if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX - 2 * TILE) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   if (n_edges == 0) {          // nodes without out-edges aggregate to 0 (torch_scatter semantics)
     if (h_out && n_nodes > 0) return check_cuda(cudaMemsetAsync(h_out, 0, sizeof(float) * n_nodes * FN, st));
