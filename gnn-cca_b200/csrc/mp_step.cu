@@ -240,7 +240,8 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   int* s_src = reinterpret_cast<int*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4);
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4 + TILE * 4);
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform by construction: per-warp bookkeeping runs on the uniform datapath
   const int K = p.nf * FN;
   if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;   // CSR not valid (unsorted / out of range): uniform exit
   const bool classify = HC > 0 && p.logits != nullptr;
@@ -370,15 +371,12 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       }
       float2 ea[FE / 2], eb[FE / 2];
       {
-        float4 pa0 = make_float4(0.f, 0.f, 0.f, 0.f), pa1 = pa0, qa0 = pa0, qa1 = pa0, pb0 = pa0, pb1 = pa0, qb0 = pa0, qb1 = pa0;
-        if (va) {
-          pa0 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sa * 8); pa1 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sa * 8 + 4);
-          qa0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.da * 8); qa1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.da * 8 + 4);
-        }
-        if (vb) {
-          pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8); pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)cur.sb * 8 + 4);
-          qb0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8); qb1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)cur.db * 8 + 4);
-        }
+        // invalid edges (src = -1, only in the chunks at the ends of the edge range) read node 0's rows: finite values, never stored
+        const int sa = max(cur.sa, 0), sb = max(cur.sb, 0), da = max(cur.da, 0), db = max(cur.db, 0);
+        const float4 pa0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8), pa1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8 + 4);
+        const float4 qa0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8), qa1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8 + 4);
+        const float4 pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8), pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8 + 4);
+        const float4 qb0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)db * 8), qb1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)db * 8 + 4);
         const float2 pa[4] = {make_float2(pa0.x, pa0.y), make_float2(pa0.z, pa0.w), make_float2(pa1.x, pa1.y), make_float2(pa1.z, pa1.w)};
         const float2 qa[4] = {make_float2(qa0.x, qa0.y), make_float2(qa0.z, qa0.w), make_float2(qa1.x, qa1.y), make_float2(qa1.z, qa1.w)};
         const float2 pb[4] = {make_float2(pb0.x, pb0.y), make_float2(pb0.z, pb0.w), make_float2(pb1.x, pb1.y), make_float2(pb1.z, pb1.w)};
@@ -460,15 +458,18 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           a_lo[i][0] = l4.x; a_lo[i][1] = l4.y; a_lo[i][2] = l4.z; a_lo[i][3] = l4.w;
         }
         const int nb_prev = __shfl_sync(0xffffffffu, nb, 0), nb_next = __shfl_sync(0xffffffffu, nb, 1);
-        const int ie = c0 + 2 * lane;
-        const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
-        const int prev = ie - 1 >= a ? s_src[max(ie - 1, 0)] : nb_prev;
-        const bool st_e = ie >= a && ie < b && (ie == a || my.x != prev);
-        const bool st_o = ie + 1 >= a && ie + 1 < b && (ie + 1 == a || my.y != my.x);
-        const unsigned bits = (st_e ? 1u : 0u) | (st_o ? 2u : 0u);
-        const unsigned m_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits << (2 * lane) : 0u);
-        const unsigned m_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits << (2 * lane - 32) : 0u);
-        unsigned long long mask = (unsigned long long)m_lo | ((unsigned long long)m_hi << 32);   // bit i: edge c0 + i opens a piece
+        unsigned long long mask = 1ull << (a - c0);      // bit i: edge c0 + i opens a piece; sorted sources: equal ends = one piece
+        if (s_src[a] != s_src[b - 1]) {
+          const int ie = c0 + 2 * lane;
+          const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
+          const int prev = ie - 1 >= a ? s_src[max(ie - 1, 0)] : nb_prev;
+          const bool st_e = ie >= a && ie < b && (ie == a || my.x != prev);
+          const bool st_o = ie + 1 >= a && ie + 1 < b && (ie + 1 == a || my.y != my.x);
+          const unsigned bits = (st_e ? 1u : 0u) | (st_o ? 2u : 0u);
+          const unsigned m_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits << (2 * lane) : 0u);
+          const unsigned m_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits << (2 * lane - 32) : 0u);
+          mask = (unsigned long long)m_lo | ((unsigned long long)m_hi << 32);
+        }
         const bool first_cont = nb_prev == s_src[a];
         const bool last_cont = nb_next == s_src[b - 1];
         while (mask) {
