@@ -81,8 +81,11 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t b
                ::"r"(enc::smem_u32(dst)), "l"(src), "r"(bytes), "r"(enc::smem_u32(bar)) : "memory");
 }
 template <int FE, bool REATT_E, bool ATTR> struct Slot {
-  static constexpr int SRC = 0, DST = CHUNK * 4, E = 2 * CHUNK * 4, X = E + CHUNK * FE * 4;
-  static constexpr int BYTES = X + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
+  // src carries a halo of 4 ids on either side (16-byte granules): the sources of the edges just outside the chunk tell whether its
+  // first / last piece belongs to a longer segment
+  static constexpr int HALO = 4;
+  static constexpr int SRC = 0, DST = (CHUNK + 2 * HALO) * 4, E = DST + CHUNK * 4, X = E + CHUNK * FE * 4;
+  static constexpr int BYTES = (X + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0)) + 127) & ~127;
 };
 template <int FE, bool REATT_E, bool ATTR> constexpr int step_dyn_smem() {
   return NWARP * NSTAGE * Slot<FE, REATT_E, ATTR>::BYTES + TILE * FE * 4 + TILE * 4 + NWARP * NSTAGE * 8;
@@ -128,12 +131,12 @@ __device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int
   const int cb = (int)tile * TILE - p.phase + c0;     // global index of the chunk's first edge (E < 2^31 - 2 TILE)
   const int n_edges = (int)p.n_edges;
   const bool latent = !ATTR || p.e_in != nullptr;
-  if (bulk_ok && cb >= 0 && cb + CHUNK <= n_edges) {
+  if (bulk_ok && cb >= SL::HALO && cb + CHUNK + SL::HALO <= n_edges) {
     if (lane == 0) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the slot was last touched through the generic proxy
-      const uint32_t bytes = 2 * CHUNK * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
+      const uint32_t bytes = 2 * (CHUNK + SL::HALO) * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
       enc::mbar_expect_tx(bar, bytes);
-      bulk_load(slot + SL::SRC, p.src + cb, CHUNK * 4, bar);
+      bulk_load(slot + SL::SRC, p.src + cb - SL::HALO, (CHUNK + 2 * SL::HALO) * 4, bar);
       bulk_load(slot + SL::DST, p.dst + cb, CHUNK * 4, bar);
       if (latent) bulk_load(slot + SL::E, p.e_in + (int64_t)cb * FE, CHUNK * FE * 4, bar);
       if (ATTR) bulk_load(slot + SL::X, p.attr + (int64_t)cb * FA, CHUNK * FA * 4, bar);
@@ -143,7 +146,11 @@ __device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int
   }
   RawPair<FE, REATT_E, ATTR> r{};
   load_raw<FE, REATT_E, ATTR>(p, (int64_t)cb + 2 * lane, r);
-  *reinterpret_cast<int2*>(slot + SL::SRC + 8 * lane) = make_int2(r.sa, r.sb);
+  *reinterpret_cast<int2*>(slot + SL::SRC + SL::HALO * 4 + 8 * lane) = make_int2(r.sa, r.sb);
+  if (lane < 2) {      // the two halo ids next to the chunk (-1: no such edge)
+    const int j = lane == 0 ? cb - 1 : cb + CHUNK;
+    *reinterpret_cast<int*>(slot + SL::SRC + (lane == 0 ? SL::HALO - 1 : SL::HALO + CHUNK) * 4) = (j >= 0 && j < n_edges) ? p.src[j] : -1;
+  }
   *reinterpret_cast<int2*>(slot + SL::DST + 8 * lane) = make_int2(r.da, r.db);
   float* e = reinterpret_cast<float*>(slot + SL::E) + 2 * FE * lane;
 #pragma unroll
@@ -171,7 +178,7 @@ template <int FE, bool REATT_E, bool ATTR>
 __device__ __forceinline__ void read_slot(const unsigned char* slot, int lane, bool latent, RawPair<FE, REATT_E, ATTR>& r) {
   using SL = Slot<FE, REATT_E, ATTR>;
   static_assert((2 * FE) % 4 == 0, "a pair's features are read as float4");
-  const int2 s2 = *reinterpret_cast<const int2*>(slot + SL::SRC + 8 * lane), d2 = *reinterpret_cast<const int2*>(slot + SL::DST + 8 * lane);
+  const int2 s2 = *reinterpret_cast<const int2*>(slot + SL::SRC + SL::HALO * 4 + 8 * lane), d2 = *reinterpret_cast<const int2*>(slot + SL::DST + 8 * lane);
   r.sa = s2.x; r.sb = s2.y; r.da = d2.x; r.db = d2.y;
   if (latent) {
     float t[2 * FE];
@@ -310,10 +317,13 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const int base = tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition (E < 2^31 - 2 TILE)
     const int i0 = base + 2 * tid;
     RawPair<FE, REATT_E, ATTR> cur;
+    int nb_prev, nb_next;      // sources of the edges just before / after the chunk (-1: none)
     {
       const int sl = it & (NSTAGE - 1);
       if ((isbulk >> sl) & 1u) { enc::mbar_wait(wbar + sl, (parity >> sl) & 1u); parity ^= 1u << sl; }
       read_slot<FE, REATT_E, ATTR>(ring + sl * SL::BYTES, lane, latent, cur);
+      nb_prev = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO - 1) * 4);
+      nb_next = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO + CHUNK) * 4);
       __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
       const int64_t nt = (int64_t)tile + (int64_t)NSTAGE * gridDim.x;
       isbulk &= ~(1u << sl);
@@ -325,11 +335,8 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const int lo = max(0, -base), hi = min(TILE, n_edges - base);   // valid tile-local edge range
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
-    int nb = -1;     // lane 0: source of the edge before the chunk, lane 1: of the edge after it (-1: none)
     float r_next[4] = {0.f, 0.f, 0.f, 0.f};   // R row of the chunk's first segment (features g + 8 q), requested before phase A
     if (p.h_out != nullptr && a < b) {
-      if (lane == 0 && base + a > 0) nb = p.src[base + a - 1];
-      if (lane == 1 && base + b < n_edges) nb = p.src[base + b];
       const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
 #pragma unroll
       for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)s_first * FN + g + 8 * q];
@@ -450,14 +457,12 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     // ReLU output is >= 0, so 0 is neutral for sum and max alike).  Lanes are folded once per piece.
     {
       if (a < b) {
-        float a_hi[2][4], a_lo[2][4];
+        float a_lo[2][4];
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-          const float4 h4 = s_afrag[2 * i][lane], l4 = s_afrag[2 * i + 1][lane];
-          a_hi[i][0] = h4.x; a_hi[i][1] = h4.y; a_hi[i][2] = h4.z; a_hi[i][3] = h4.w;
+          const float4 l4 = s_afrag[2 * i + 1][lane];
           a_lo[i][0] = l4.x; a_lo[i][1] = l4.y; a_lo[i][2] = l4.z; a_lo[i][3] = l4.w;
         }
-        const int nb_prev = __shfl_sync(0xffffffffu, nb, 0), nb_next = __shfl_sync(0xffffffffu, nb, 1);
         unsigned long long mask = 1ull << (a - c0);      // bit i: edge c0 + i opens a piece; sorted sources: equal ends = one piece
         if (s_src[a] != s_src[b - 1]) {
           const int ie = c0 + 2 * lane;
@@ -494,20 +499,22 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           // fragment holds R split into tf32 prefix + rest and the B fragment holds 1.0, so hi.hi adds R_hi + R_lo; lo.hi sees a zero A,
           // hi.lo a zero B (1 - prefix(1)).  An edge of the block outside the piece gets an all-zero B column (the 1.0 included): its
           // messages come out as relu(0) = 0, neutral for sum and max.
-          if (t == 3) {
+          float a_hi[2][4];          // whole fragments are selected per piece, so that each lives in one aligned register quad
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const float h = tf32_prefix(r[q]);
-              a_hi[q >> 1][q & 1] = h; a_hi[q >> 1][2 + (q & 1)] = r[q] - h;
-            }
+          for (int i = 0; i < 2; ++i) {
+            const float4 h4 = s_afrag[2 * i][lane];
+            const float h0 = tf32_prefix(r[2 * i]), h1 = tf32_prefix(r[2 * i + 1]);
+            a_hi[i][0] = t == 3 ? h0 : h4.x; a_hi[i][1] = t == 3 ? h1 : h4.y;
+            a_hi[i][2] = t == 3 ? r[2 * i] - h0 : h4.z; a_hi[i][3] = t == 3 ? r[2 * i + 1] - h1 : h4.w;
           }
           const int kb0 = j0 & ~7;
           const unsigned span = (unsigned)(j1 - j0);
           unsigned x = (unsigned)(kb0 + g - j0);                 // edge kb + g is in the piece iff x < span (unsigned)
           const float2* bp = 2 * t < FE ? reinterpret_cast<const float2*>(&s_e[kb0 + g][2 * t]) : reinterpret_cast<const float2*>(s_one);
-          const int bstep = 2 * t < FE ? 8 * FE / 2 : 0;         // float2 units per block
+          int bstep = 2 * t < FE ? 8 * FE * 4 : 0;               // bytes per block
+          asm volatile("" : "+r"(bstep));                        // a register stride: one add per block instead of a re-selected constant
 #pragma unroll 2
-          for (int kb = kb0; kb < j1; kb += 8, x += 8, bp += bstep) {
+          for (int kb = kb0; kb < j1; kb += 8, x += 8, bp = reinterpret_cast<const float2*>(reinterpret_cast<const char*>(bp) + bstep)) {
             float2 v = make_float2(0.f, 0.f);
             if (x < span) v = *bp;
             const float bh0 = tf32_prefix(v.x), bh1 = tf32_prefix(v.y);
