@@ -75,7 +75,10 @@ struct RawPair {       // what phase A reads for one edge pair, requested one ti
 
 // ---- per-warp input ring: the raw inputs of a warp's 64-edge chunk travel global -> shared memory as 1-D bulk copies (TMA engine,
 // completion on an mbarrier), two tiles ahead of their use.  No registers are held across phase B for them and nobody waits for DRAM.
-constexpr int NSTAGE = 2;
+#ifndef GNNCCA_STEP_STAGES
+#define GNNCCA_STEP_STAGES 2
+#endif
+constexpr int NSTAGE = GNNCCA_STEP_STAGES;
 __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(enc::smem_u32(dst)), "l"(src), "r"(bytes), "r"(enc::smem_u32(bar)) : "memory");
@@ -319,7 +322,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     RawPair<FE, REATT_E, ATTR> cur;
     int nb_prev, nb_next;      // sources of the edges just before / after the chunk (-1: none)
     {
-      const int sl = it & (NSTAGE - 1);
+      const int sl = it % NSTAGE;
       if ((isbulk >> sl) & 1u) { enc::mbar_wait(wbar + sl, (parity >> sl) & 1u); parity ^= 1u << sl; }
       read_slot<FE, REATT_E, ATTR>(ring + sl * SL::BYTES, lane, latent, cur);
       nb_prev = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO - 1) * 4);
