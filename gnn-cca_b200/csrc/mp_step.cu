@@ -129,14 +129,17 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
 // copies (returns true: the consumer waits on `bar`); chunks that touch the ends of the edge range, or any chunk of a partition whose
 // phase breaks the alignment, are loaded through registers with the invalid edges marked src = -1 (returns false).
 template <int FE, bool REATT_E, bool ATTR>
-__device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok) {
+__device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok,
+                                          bool written_by_threads) {
   using SL = Slot<FE, REATT_E, ATTR>;
   const int cb = (int)tile * TILE - p.phase + c0;     // global index of the chunk's first edge (E < 2^31 - 2 TILE)
   const int n_edges = (int)p.n_edges;
   const bool latent = !ATTR || p.e_in != nullptr;
   if (bulk_ok && cb >= SL::HALO && cb + CHUNK + SL::HALO <= n_edges) {
     if (lane == 0) {
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the slot was last touched through the generic proxy
+      // a slot that the threads themselves wrote (register path) is handed to the async proxy behind a proxy fence; one that was only
+      // read needs none (the reads completed before the __syncwarp that precedes this call)
+      if (written_by_threads) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       const uint32_t bytes = 2 * (CHUNK + SL::HALO) * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
       enc::mbar_expect_tx(bar, bytes);
       bulk_load(slot + SL::SRC, p.src + cb - SL::HALO, (CHUNK + 2 * SL::HALO) * 4, bar);
@@ -312,7 +315,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
 #pragma unroll
   for (int st = 0; st < NSTAGE; ++st) {
     const int64_t t0 = (int64_t)blockIdx.x + (int64_t)st * gridDim.x;
-    if (t0 < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok)) isbulk |= 1u << st;
+    if (t0 < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok, false)) isbulk |= 1u << st;
   }
 
   int it = 0;
@@ -329,8 +332,9 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       nb_next = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO + CHUNK) * 4);
       __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
       const int64_t nt = (int64_t)tile + (int64_t)NSTAGE * gridDim.x;
+      const bool by_threads = ((isbulk >> sl) & 1u) == 0;
       isbulk &= ~(1u << sl);
-      if (nt < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok)) isbulk |= 1u << sl;
+      if (nt < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok, by_threads)) isbulk |= 1u << sl;
     }
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
     // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
