@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   constexpr int HCS = HC > 0 ? HC : 2;
   constexpr int FEP = (FE + 3) & ~3;      // row stride of the transposed weight tables (16-byte rows)
   static_assert(FE % 2 == 0 && FE <= 6 && HCS % 2 == 0, "outputs are handled as (o, o + 1) pairs; an edge row is one k-step of the mma");
-  __shared__ __align__(16) float s_weeT[EIN][FEP];           // [k][o]: the pair (o, o + 1) is one FFMA2 operand
+  __shared__ __align__(16) float s_weeT[EIN * FE];           // [k][o] flat (read as float4 chunks): the pair (o, o + 1) is one FFMA2 operand
   __shared__ __align__(16) float4 s_afrag[4][32];             // phase B: W_ne^T as mma A fragments, [tile i][hi | lo] per lane
   __shared__ __align__(16) float s_wencT[ATTR ? FA : 1][FEP];
   __shared__ __align__(8) float s_benc[ATTR ? FE : 2];
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   const bool classify = HC > 0 && p.logits != nullptr;
   {  // stage weights (read from the live parameters at every launch)
     const int edge_row = 2 * K + EIN;
-    for (int idx = tid; idx < FE * EIN; idx += THREADS) s_weeT[idx % EIN][idx / EIN] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
+    for (int idx = tid; idx < FE * EIN; idx += THREADS) s_weeT[(idx % EIN) * FE + idx / EIN] = p.w.w_edge[(idx / EIN) * edge_row + 2 * K + idx % EIN];
     if (ATTR) {
       for (int idx = tid; idx < FE * FA; idx += THREADS) s_wencT[idx % FA][idx / FA] = p.w_enc[idx];
       for (int idx = tid; idx < FE; idx += THREADS) s_benc[idx] = p.b_enc[idx];
@@ -309,17 +309,21 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   }
   __syncthreads();
 
+  // A CTA takes a CONTIGUOUS run of tiles: consecutive tiles gather from the same few hundred Q / P / R rows (one frame's nodes, or the
+  // neighbourhood of consecutive sources), which then answer from L1 instead of L2
+  const int t_per = p.num_tiles / (int)gridDim.x, t_rem = p.num_tiles % (int)gridDim.x;
+  const int t_begin = (int)blockIdx.x * t_per + min((int)blockIdx.x, t_rem), t_end = t_begin + t_per + ((int)blockIdx.x < t_rem ? 1 : 0);
   unsigned char* ring = step_dyn + (size_t)warp * NSTAGE * SL::BYTES;      // this warp's slots
   uint64_t* wbar = s_bar + warp * NSTAGE;
   uint32_t parity = 0, isbulk = 0;      // bit per slot
 #pragma unroll
   for (int st = 0; st < NSTAGE; ++st) {
-    const int64_t t0 = (int64_t)blockIdx.x + (int64_t)st * gridDim.x;
-    if (t0 < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok, false)) isbulk |= 1u << st;
+    const int64_t t0 = (int64_t)t_begin + st;
+    if (t0 < t_end && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok, false)) isbulk |= 1u << st;
   }
 
   int it = 0;
-  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+  for (int tile = t_begin; tile < t_end; ++tile, ++it) {
     const int base = tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition (E < 2^31 - 2 TILE)
     const int i0 = base + 2 * tid;
     RawPair<FE, REATT_E, ATTR> cur;
@@ -331,10 +335,10 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
       nb_prev = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO - 1) * 4);
       nb_next = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO + CHUNK) * 4);
       __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
-      const int64_t nt = (int64_t)tile + (int64_t)NSTAGE * gridDim.x;
+      const int64_t nt = (int64_t)tile + NSTAGE;
       const bool by_threads = ((isbulk >> sl) & 1u) == 0;
       isbulk &= ~(1u << sl);
-      if (nt < p.num_tiles && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok, by_threads)) isbulk |= 1u << sl;
+      if (nt < t_end && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok, by_threads)) isbulk |= 1u << sl;
     }
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
     // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
@@ -389,7 +393,8 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
         const int sa = max(cur.sa, 0), sb = max(cur.sb, 0), da = max(cur.da, 0), db = max(cur.db, 0);
         const float4 pa0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8), pa1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8 + 4);
         const float4 qa0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8), qa1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8 + 4);
-        const float4 pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8), pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8 + 4);
+        float4 pb0 = pa0, pb1 = pa1;      // the pair shares its source except across a segment boundary
+        if (sb != sa) { pb0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8); pb1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sb * 8 + 4); }
         const float4 qb0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)db * 8), qb1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)db * 8 + 4);
         const float2 pa[4] = {make_float2(pa0.x, pa0.y), make_float2(pa0.z, pa0.w), make_float2(pa1.x, pa1.y), make_float2(pa1.z, pa1.w)};
         const float2 qa[4] = {make_float2(qa0.x, qa0.y), make_float2(qa0.z, qa0.w), make_float2(qa1.x, qa1.y), make_float2(qa1.z, qa1.w)};
@@ -398,13 +403,23 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
 #pragma unroll
         for (int j = 0; j < FE / 2; ++j) { ea[j] = pk::fadd2(pa[j], qa[j]); eb[j] = pk::fadd2(pb[j], qb[j]); }
       }
+      static_assert((EIN * FE) % 4 == 0, "the weight table is read as float4");
 #pragma unroll
-      for (int k = 0; k < EIN; ++k) {
+      for (int k2 = 0; k2 < EIN; k2 += 2) {          // two k rows = 2 FE floats = whole float4 chunks
+        float wr[2 * FE];
 #pragma unroll
-        for (int j = 0; j < FE / 2; ++j) {
-          const float2 w = *reinterpret_cast<const float2*>(&s_weeT[k][2 * j]);
-          ea[j] = pk::ffma2(w, pk::bc(xa[k]), ea[j]);
-          eb[j] = pk::ffma2(w, pk::bc(xb[k]), eb[j]);
+        for (int q = 0; q < 2 * FE / 4; ++q) {
+          const float4 v = *reinterpret_cast<const float4*>(&s_weeT[k2 * FE + 4 * q]);
+          wr[4 * q] = v.x; wr[4 * q + 1] = v.y; wr[4 * q + 2] = v.z; wr[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+#pragma unroll
+          for (int j = 0; j < FE / 2; ++j) {
+            const float2 w = make_float2(wr[kk * FE + 2 * j], wr[kk * FE + 2 * j + 1]);
+            ea[j] = pk::ffma2(w, pk::bc(xa[k2 + kk]), ea[j]);
+            eb[j] = pk::ffma2(w, pk::bc(xb[k2 + kk]), eb[j]);
+          }
         }
       }
 #pragma unroll
@@ -451,8 +466,11 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           la = fmaf(fmaxf(ha[c].x, 0.f), w.x, la); la = fmaf(fmaxf(ha[c].y, 0.f), w.y, la);
           lb = fmaf(fmaxf(hb[c].x, 0.f), w.x, lb); lb = fmaf(fmaxf(hb[c].y, 0.f), w.y, lb);
         }
-        if (va) st_stream_f1(p.logits + i0, la);
-        if (vb) st_stream_f1(p.logits + i0 + 1, lb);
+        if (vec_out && va && vb && (((uintptr_t)p.logits) & 7) == 0) st_stream_f2(p.logits + i0, make_float2(la, lb));
+        else {
+          if (va) st_stream_f1(p.logits + i0, la);
+          if (vb) st_stream_f1(p.logits + i0 + 1, lb);
+        }
       }
     }
     if (p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
