@@ -90,8 +90,8 @@ template <int FE, bool REATT_E, bool ATTR> struct Slot {
   static constexpr int SRC = 0, DST = (CHUNK + 2 * HALO) * 4, E = DST + CHUNK * 4, X = E + CHUNK * FE * 4;
   static constexpr int BYTES = (X + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0)) + 127) & ~127;
 };
-template <int FE, bool REATT_E, bool ATTR> constexpr int step_dyn_smem() {
-  return NWARP * NSTAGE * Slot<FE, REATT_E, ATTR>::BYTES + TILE * FE * 4 + TILE * 4 + NWARP * NSTAGE * 8;
+template <int FE, bool REATT_E, bool ATTR, bool NODE> constexpr int step_dyn_smem() {      // ring | e' rows and sources of the tile (NODE) | mbarriers
+  return NWARP * NSTAGE * Slot<FE, REATT_E, ATTR>::BYTES + (NODE ? TILE * FE * 4 + TILE * 4 : 0) + NWARP * NSTAGE * 8;
 }
 
 template <int FE, bool REATT_E, bool ATTR>
@@ -233,8 +233,10 @@ __device__ __forceinline__ void finalize_node_feat(const StepParams& p, int node
   p.h_out[(int64_t)node * FN + feat] = v;
 }
 
-template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR>
-__global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(const StepParams p) {
+// NODE = false: the step only updates and classifies the edges (last step of an inference forward, h_out == NULL): no phase B, so
+// the register allocation is held to one more resident CTA per SM (this variant is bound by memory-instruction latency)
+template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR, bool NODE>
+__global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS + 1) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 2;
   constexpr int FEP = (FE + 3) & ~3;      // row stride of the transposed weight tables (16-byte rows)
@@ -251,7 +253,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   extern __shared__ __align__(128) unsigned char step_dyn[];
   float (*s_e)[FE] = reinterpret_cast<float (*)[FE]>(step_dyn + NWARP * NSTAGE * SL::BYTES);      // e' of the tile, one row per edge (B operand of phase B)
   int* s_src = reinterpret_cast<int*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4);
-  uint64_t* s_bar = reinterpret_cast<uint64_t*>(step_dyn + NWARP * NSTAGE * SL::BYTES + TILE * FE * 4 + TILE * 4);
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(step_dyn + NWARP * NSTAGE * SL::BYTES + (NODE ? TILE * FE * 4 + TILE * 4 : 0));
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform by construction: per-warp bookkeeping runs on the uniform datapath
@@ -293,7 +295,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
   // The 16 weight fragment registers of a lane are parked in shared memory ([4][32 lanes] float4: conflict-free LDS.128) and
   // fetched at the start of each phase B, so that they are not live (and spilled) across phase A.
   const int g = lane >> 2, t = lane & 3;
-  if (warp == 0) {
+  if (NODE && warp == 0) {
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
       float hi4[4], lo4[4];
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     float r_next[4] = {0.f, 0.f, 0.f, 0.f};   // R row of the chunk's first segment (features g + 8 q), requested before phase A
-    if (p.h_out != nullptr && a < b) {
+    if (NODE && p.h_out != nullptr && a < b) {
       const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
 #pragma unroll
       for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)s_first * FN + g + 8 * q];
@@ -442,10 +444,12 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
           }
         }
       }
+      if (NODE) {
 #pragma unroll
-      for (int q = 0; q < 2 * FE / 4; ++q)
-        *reinterpret_cast<float4*>(&s_e[2 * tid][0] + 4 * q) = make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]);
-      *reinterpret_cast<int2*>(&s_src[2 * tid]) = make_int2(cur.sa, cur.sb);
+        for (int q = 0; q < 2 * FE / 4; ++q)
+          *reinterpret_cast<float4*>(&s_e[2 * tid][0] + 4 * q) = make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]);
+        *reinterpret_cast<int2*>(&s_src[2 * tid]) = make_int2(cur.sa, cur.sb);
+      }
       if (classify) {
         float2 ha[HCS / 2], hb[HCS / 2];
 #pragma unroll
@@ -473,7 +477,7 @@ __global__ void __launch_bounds__(THREADS, STEP_MIN_CTAS) mp_step_fwd_kernel(con
         }
       }
     }
-    if (p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
+    if (!NODE || p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
     __syncwarp();
     // ------------------------------ phase B: messages of 8 edges per mma ------------------------------
     // The chunk is cut into 8-edge blocks aligned to the global numbering.  A piece (edges of one source inside the chunk) walks
@@ -628,22 +632,27 @@ extern "C" int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int6
 
 template <int FE, int HC>
 static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
-  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * STEP_MIN_CTAS);
+  const bool node = sp.h_out != nullptr;
+  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * (node ? STEP_MIN_CTAS : STEP_MIN_CTAS + 1));
   const bool is_max = sp.agg == GNNCCA_AGG_MAX;
   const bool attr = sp.attr != nullptr;
-#define GNNCCA_STEP(R, M, A)                                                                                              \
+#define GNNCCA_STEP(R, M, A) GNNCCA_STEP_N(R, M, A, true)
+#define GNNCCA_STEP_N(R, M, A, N)                                                                                           \
   do {                                                                                                                    \
-    constexpr int smem = step_dyn_smem<FE, R, A>();                                                                       \
+    constexpr int smem = step_dyn_smem<FE, R, A, N>();                                                                     \
     static bool optin[16] = {};          /* static + dynamic shared memory exceed 48 KB: opt in once per device */         \
     int dev = 0; cudaGetDevice(&dev);                                                                                     \
     if (!optin[dev & 15]) {                                                                                               \
-      const int rc = check_cuda(cudaFuncSetAttribute(mp_step_fwd_kernel<FE, HC, R, M, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+      const int rc = check_cuda(cudaFuncSetAttribute(mp_step_fwd_kernel<FE, HC, R, M, A, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
       if (rc) return rc;                                                                                                  \
       optin[dev & 15] = true;                                                                                             \
     }                                                                                                                     \
-    mp_step_fwd_kernel<FE, HC, R, M, A><<<grid, THREADS, smem, st>>>(sp);                                                 \
+    mp_step_fwd_kernel<FE, HC, R, M, A, N><<<grid, THREADS, smem, st>>>(sp);                                              \
   } while (0)
-  if (reatt_e) {
+  if (!node) {        // the aggregation kind is irrelevant
+    if (reatt_e) { if (attr) GNNCCA_STEP_N(true, false, true, false); else GNNCCA_STEP_N(true, false, false, false); }
+    else { if (attr) GNNCCA_STEP_N(false, false, true, false); else GNNCCA_STEP_N(false, false, false, false); }
+  } else if (reatt_e) {
     if (is_max) { if (attr) GNNCCA_STEP(true, true, true); else GNNCCA_STEP(true, true, false); }
     else { if (attr) GNNCCA_STEP(true, false, true); else GNNCCA_STEP(true, false, false); }
   } else {
@@ -651,6 +660,7 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
     else { if (attr) GNNCCA_STEP(false, false, true); else GNNCCA_STEP(false, false, false); }
   }
 #undef GNNCCA_STEP
+#undef GNNCCA_STEP_N
   if (sp.h_out == nullptr) return check_launch();
   mp_step_fold_kernel<<<(unsigned)ceil_div(sp.n_nodes, (int64_t)8), 256, 0, st>>>(sp);
   return check_launch(2);
