@@ -603,15 +603,14 @@ __global__ void __launch_bounds__(256) mp_step_fold_kernel(const StepParams p) {
   // of its 64-edge chunks alone
   double tot = p.chunk_part[(c0 * 2 + 1) * FN + lane];
   int64_t c = c0 + 1;
-  for (; c + 3 <= c1; c += 4) {        // four loads in flight, folded in order
-    const float v0 = p.chunk_part[(c * 2) * FN + lane], v1 = p.chunk_part[((c + 1) * 2) * FN + lane];
-    const float v2 = p.chunk_part[((c + 2) * 2) * FN + lane], v3 = p.chunk_part[((c + 3) * 2) * FN + lane];
-    if (is_max) tot = fmax(fmax(fmax(fmax(tot, (double)v0), (double)v1), (double)v2), (double)v3);
-    else tot = (((tot + v0) + v1) + v2) + v3;
-  }
-  for (; c <= c1; ++c) {
-    const float v0 = p.chunk_part[(c * 2) * FN + lane];
-    tot = is_max ? fmax(tot, (double)v0) : tot + v0;
+  for (; c <= c1; c += 8) {            // up to eight loads in flight, folded in order
+    float pv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) pv[u] = c + u <= c1 ? p.chunk_part[((c + u) * 2) * FN + lane] : (is_max ? -INFINITY : 0.f);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (c + u <= c1) tot = is_max ? fmax(tot, (double)pv[u]) : tot + pv[u];
+    }
   }
   float out = (float)tot;
   if (p.agg == GNNCCA_AGG_MEAN) out = out / (float)(re - rs);      // scatter_mean: sum / count, in fp32 like finalize_node
