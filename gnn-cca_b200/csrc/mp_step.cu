@@ -10,21 +10,24 @@
 //   logit[i] = w_c2 . relu(W_c1 e'[i] + b_c1) + b_c2
 // and nothing of width 70 / 38 is ever materialised: 64 B/edge of HBM traffic instead of ~2.3 KB.
 //
-// Mapping.  Edges are source-sorted.  A CTA of 256 threads owns tiles of 512 consecutive edges (persistent, tiles
-// strided over the grid); edges travel as PAIRS (2p, 2p+1 of the global numbering) so that the arithmetic is packed
-// FFMA2 with the weights as broadcast scalars.  Phase A is thread-per-pair (gather P/Q rows, edge update, classifier,
-// e' written once and staged in shared memory as [pair][k][2]); the raw inputs of the NEXT tile are requested before
-// phase B starts, so their latency hides behind it.  Phase B is lane-per-feature: warp w walks edges [64w, 64w+64) of
-// the tile pair by pair (3 LDS.128 + 6 FFMA2 + 2 FMNMX + 1 FADD2 per pair) with the running aggregate of the current
-// source segment in registers (even / odd edges separately, folded at the end).  Segment boundaries come from one
-// ballot over the staged source ids, not from rowptr.  A warp stages and reduces the SAME 64 edges (a "chunk" of the global
-// edge numbering), so after the weights are staged the warps of a CTA never synchronise with each other:
+// Mapping.  Edges are source-sorted.  Persistent CTAs of 256 threads take contiguous runs of 512-edge tiles; warp w owns the 64-edge
+// "chunk" w of every tile (a chunk of the GLOBAL edge numbering) and never synchronises with the other warps after the set-up.
+//   inputs   the chunk's src (+ a halo of 4 ids on either side), dst, e (and edge_attr / e0) arrive in a per-warp shared-memory ring as
+//            1-D bulk copies (cp.async.bulk + mbarrier complete_tx, lane 0, two tiles ahead); chunks at the ends of the edge range, or on
+//            a partition whose phase breaks the 16-byte alignment, are loaded through registers.
+//   phase A  thread per edge pair: gathers of the P[src] / Q[dst] rows, edge update and classifier with packed FFMA2 over OUTPUT pairs
+//            (weight pair = aligned LDS result, edge value = broadcast scalar), e' written once (STG.128) and staged row-major.
+//   phase B  messages on the tensor cores: m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges] as two mma.sync m16n8k8 (tf32
+//            operands split 3xTF32: fp32-level accuracy); the two k-slots the FE = 6 edge features leave free carry the R[src] row; ReLU and
+//            the running sum / max are applied to the D fragment, lanes folded once per piece (a piece = the edges of one source inside
+//            the chunk; boundaries from one ballot over the staged source ids, skipped when the chunk has a single source).
 //   - a segment that lies inside one chunk is finished and written by its warp;
 //   - a segment that crosses chunks leaves one piece per chunk in the workspace (plain stores), and a second small
 //     kernel (warp per node) folds the pieces of each such node in chunk order; it also zero-fills the nodes without
 //     out-edges.  (A CTA barrier per tile plus fence / counter hand-over between tiles cost 0.17 of 0.57 ms at 8 x 64.)
-// No floating-point atomics anywhere: the summation order is a pure function of (E, rowptr), so results are
-// bit-identical run to run (the reference's torch_scatter atomicAdd path is not).
+// A step without node update (h_out == NULL: the last step of an inference forward) runs a variant without phase B (NODE = false).
+// No floating-point atomics anywhere: the summation order is a pure function of (E, rowptr, phase), so results are
+// bit-identical run to run and between a partition and the whole graph (the reference's torch_scatter atomicAdd path is not).
 #include "common.cuh"
 #include "tc_helpers.cuh"
 
@@ -129,17 +132,17 @@ __device__ __forceinline__ void load_raw(const StepParams& p, int64_t i0, RawPai
 // copies (returns true: the consumer waits on `bar`); chunks that touch the ends of the edge range, or any chunk of a partition whose
 // phase breaks the alignment, are loaded through registers with the invalid edges marked src = -1 (returns false).
 template <int FE, bool REATT_E, bool ATTR>
-__device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok,
-                                          bool written_by_threads) {
+__device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int c0, int lane, unsigned char* slot, uint64_t* bar, bool bulk_ok) {
   using SL = Slot<FE, REATT_E, ATTR>;
   const int cb = (int)tile * TILE - p.phase + c0;     // global index of the chunk's first edge (E < 2^31 - 2 TILE)
   const int n_edges = (int)p.n_edges;
   const bool latent = !ATTR || p.e_in != nullptr;
   if (bulk_ok && cb >= SL::HALO && cb + CHUNK + SL::HALO <= n_edges) {
     if (lane == 0) {
-      // a slot that the threads themselves wrote (register path) is handed to the async proxy behind a proxy fence; one that was only
-      // read needs none (the reads completed before the __syncwarp that precedes this call)
-      if (written_by_threads) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      // the lanes' reads (and, on the register path, writes) of the slot went through the generic proxy and are ordered before this
+      // point by the __syncwarp that precedes the call: the proxy fence orders them before the bulk engine's writes.  (Without it the
+      // refill overtook the reads when the data came from L2: run-to-run differences on a 1 M-edge graph.)
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       const uint32_t bytes = 2 * (CHUNK + SL::HALO) * 4 + (latent ? CHUNK * FE * 4 : 0) + (ATTR ? CHUNK * FA * 4 : (REATT_E ? CHUNK * FE * 4 : 0));
       enc::mbar_expect_tx(bar, bytes);
       bulk_load(slot + SL::SRC, p.src + cb - SL::HALO, (CHUNK + 2 * SL::HALO) * 4, bar);
@@ -321,7 +324,7 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
 #pragma unroll
   for (int st = 0; st < NSTAGE; ++st) {
     const int64_t t0 = (int64_t)t_begin + st;
-    if (t0 < t_end && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok, false)) isbulk |= 1u << st;
+    if (t0 < t_end && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok)) isbulk |= 1u << st;
   }
 
   int it = 0;
@@ -338,9 +341,8 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
       nb_next = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO + CHUNK) * 4);
       __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
       const int64_t nt = (int64_t)tile + NSTAGE;
-      const bool by_threads = ((isbulk >> sl) & 1u) == 0;
       isbulk &= ~(1u << sl);
-      if (nt < t_end && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok, by_threads)) isbulk |= 1u << sl;
+      if (nt < t_end && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok)) isbulk |= 1u << sl;
     }
     const bool va = cur.sa >= 0, vb = cur.sb >= 0;
     // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges

@@ -36,12 +36,12 @@ def test_frame_shards_equal_the_single_gpu_result(cuda_device):
                 assert torch.equal(torch.cat([p[k] for p in parts]), full[k])
 
 
-@pytest.mark.parametrize("shape", [(6, 40), (4, 37)])
+@pytest.mark.parametrize("shape", [(6, 40), (4, 37), (16, 64)])
 @pytest.mark.parametrize("agg", ["sum", "max"])
 def test_edge_partitioned_giant_graph_equals_unpartitioned(agg, shape, cuda_device):
     """(6, 40): 240 nodes, degree 200: segments span tiles and rank boundaries fall mid-tile, on 16-byte aligned edge offsets (the
     chunks of a partition arrive as bulk copies).  (4, 37): degree 111, odd edge offsets: every chunk of a partition takes the
-    register path of the step kernel and the pair stores are unaligned."""
+    register path of the step kernel and the pair stores are unaligned.  (16, 64): degree 960, ~1 M edges, several tiles per CTA."""
     mg = importlib.import_module("gnn-cca_b200.multigpu")
     engine = importlib.import_module("gnn-cca_b200.engine")
     model = _model(cuda_device, agg)
