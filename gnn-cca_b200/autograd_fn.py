@@ -56,8 +56,16 @@ class _MPNFunction(torch.autograd.Function):
         N, E = int(x.size(0)), int(edge_index.size(1))
         if plan is None:
             plan = GraphPlan(edge_index, N)
+        elif getattr(plan, "_deferred", False):
+            plan.check_deferred()          # the flags an earlier forward asked for, if they have arrived (never blocks)
+        guard = 0
         if trusted and not plan.resolved:
-            plan._resolved = True          # build_graph_batch output: source-major and in range by construction, nothing to read back
+            # build_graph_batch output: source-major and in range by construction, so nothing is waited for.  The CSR flags still
+            # guard every step launch (no-ops on an invalid CSR) and travel back asynchronously for check_deferred().
+            plan._resolved = True
+            plan._deferred = True
+        if getattr(plan, "_deferred", False):
+            guard = P(plan.flags)
         plan.resolve()
         enc_n, enc_e = model.encoder.node_mlp, model.encoder.edge_mlp
         if len(enc_e.layer_specs) != 1:
@@ -120,7 +128,7 @@ class _MPNFunction(torch.autograd.Function):
             logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if classify else None
             _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(Pn), P(Qn), P(Rn),
                                               P(e0) if model.reattach_initial_edges else 0, P(es[-1]), P(e_out), P(h_out),
-                                              P(logits) if inline else 0, 0, P(wsp), ws_bytes, _stream()), "mp_step_fwd")
+                                              P(logits) if inline else 0, guard, P(wsp), ws_bytes, _stream()), "mp_step_fwd")
             es.append(e_out)
             hs.append(h_out)
             if classify and bn_mode == "train":       # BatchNorm1d with batch statistics over all E edges (mlp.py:16)
@@ -142,6 +150,8 @@ class _MPNFunction(torch.autograd.Function):
                 affs[step] = torch.cat([scale, bn.bias.detach() - bn.running_mean * scale, bn.running_mean.detach(), invstd]).contiguous()
             if classify:
                 outs.append(plan.to_caller(logits))
+        if guard and not plan._requested and not torch.cuda.is_current_stream_capturing():
+            plan.request_flags()
         ctx.model, ctx.plan, ctx.sb = model, plan, sb
         ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, proj=proj, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
                          names=[n for n, _ in model.named_parameters_fast()])

@@ -9,14 +9,17 @@ namespace gnncca {
 // One pass over edge_index: narrow to int32, range check, order check and -- valid only when the rows
 // turn out to be non-decreasing -- rowptr by boundary detection (edge i opens every row in
 // (src[i-1], src[i]]; the last edge closes the rows after it).
-__global__ void __launch_bounds__(256) csr_narrow_kernel(const int64_t* __restrict__ ei, int64_t n_nodes, int64_t n_edges,
+// `row` / `col` are the two rows of the caller's edge_index (or a column range of them: a block of whole frames of a larger
+// batch); `node_base` is subtracted from every id, so that a block's CSR is local to its own node range.
+__global__ void __launch_bounds__(256) csr_narrow_kernel(const int64_t* __restrict__ row, const int64_t* __restrict__ col, int64_t node_base,
+                                                         int64_t n_nodes, int64_t n_edges,
                                                          int32_t* __restrict__ src, int32_t* __restrict__ dst,
                                                          int32_t* __restrict__ rowptr, int32_t* __restrict__ flags) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   bool unsorted = false, bad = false;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_edges; i += stride) {
-    const int64_t r = ei[i], c = ei[n_edges + i];
-    const int64_t prev = (i == 0) ? -1 : ei[i - 1];
+    const int64_t r = row[i] - node_base, c = col[i] - node_base;
+    const int64_t prev = (i == 0) ? -1 : row[i - 1] - node_base;
     const bool ok = (r >= 0) & (r < n_nodes) & (c >= 0) & (c < n_nodes);
     src[i] = ok ? (int32_t)r : 0;   // out-of-range entries are reported through flags[1]; never let them index memory
     dst[i] = ok ? (int32_t)c : 0;
@@ -88,7 +91,19 @@ extern "C" int gnncca_csr_from_edge_index(const int64_t* edge_index, int64_t n_n
   int rc = check_cuda(cudaMemsetAsync(flags, 0, sizeof(int32_t) * GNNCCA_CSR_NFLAGS, st));
   if (rc) return rc;
   if (n_edges == 0) return check_cuda(cudaMemsetAsync(rowptr, 0, sizeof(int32_t) * (n_nodes + 1), st));
-  csr_narrow_kernel<<<grid_for(n_edges, 256), 256, 0, st>>>(edge_index, n_nodes, n_edges, src, dst, rowptr, flags);
+  csr_narrow_kernel<<<grid_for(n_edges, 256), 256, 0, st>>>(edge_index, edge_index + n_edges, 0, n_nodes, n_edges, src, dst, rowptr, flags);
+  return check_launch();
+}
+
+extern "C" int gnncca_csr_from_edge_rows(const int64_t* row, const int64_t* col, int64_t node_base, int64_t n_nodes, int64_t n_edges,
+                                         int32_t* src, int32_t* dst, int32_t* rowptr, int32_t* flags, void* stream) {
+  if (n_nodes < 0 || n_edges < 0 || n_nodes >= INT32_MAX || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (!rowptr || !flags || (n_edges > 0 && (!row || !col || !src || !dst))) return GNNCCA_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = check_cuda(cudaMemsetAsync(flags, 0, sizeof(int32_t) * GNNCCA_CSR_NFLAGS, st));
+  if (rc) return rc;
+  if (n_edges == 0) return check_cuda(cudaMemsetAsync(rowptr, 0, sizeof(int32_t) * (n_nodes + 1), st));
+  csr_narrow_kernel<<<grid_for(n_edges, 256), 256, 0, st>>>(row, col, node_base, n_nodes, n_edges, src, dst, rowptr, flags);
   return check_launch();
 }
 

@@ -105,7 +105,8 @@ __global__ void __launch_bounds__(256) colnorm_apply4_kernel(const float* __rest
 __global__ void __launch_bounds__(256) graph_prepare_kernel(const int64_t* __restrict__ graph_ptr, const int32_t* __restrict__ id_cam,
                                                             int32_t* __restrict__ cam_cnt, int32_t* __restrict__ cam_first,
                                                             int64_t* __restrict__ src_off, int32_t* __restrict__ order,
-                                                            int64_t* __restrict__ graph_edges, int64_t* __restrict__ graph_tiles, int tile) {
+                                                            int64_t* __restrict__ graph_edges, int64_t* __restrict__ graph_tiles,
+                                                            int64_t* __restrict__ graph_unsorted, int tile) {
   const int g = blockIdx.x;
   const int64_t a = graph_ptr[g];
   const int n = (int)(graph_ptr[g + 1] - a);
@@ -114,8 +115,10 @@ __global__ void __launch_bounds__(256) graph_prepare_kernel(const int64_t* __res
   if (threadIdx.x == 0) s_total = 0ull;
   __syncthreads();
   unsigned long long mine = 0;
+  bool cam_desc = false;       // a row whose camera id is below its predecessor's: the enumeration (camera-major) is then NOT source-major
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const int ci = cam[i];
+    cam_desc |= i > 0 && ci < cam[i - 1];
     int cnt = 0, rank = 0, lower = 0;
     for (int j = 0; j < n; ++j) {
       const int cj = cam[j];
@@ -129,7 +132,7 @@ __global__ void __launch_bounds__(256) graph_prepare_kernel(const int64_t* __res
     mine += (unsigned long long)(n - cnt);
   }
   atomicAdd(&s_total, mine);   // integer: order-independent
-  __syncthreads();
+  const int any_desc = __syncthreads_or(cam_desc);
   // src_off needs sum over lower cameras of their degrees: second O(n^2) sweep (degrees are per-camera constants)
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const int ci = cam[i];
@@ -150,14 +153,16 @@ __global__ void __launch_bounds__(256) graph_prepare_kernel(const int64_t* __res
     graph_edges[g] = (int64_t)s_total;
     const int64_t t = (n + tile - 1) / tile;
     graph_tiles[g] = t * t;
+    graph_unsorted[g] = any_desc ? 1 : 0;
   }
 }
 
 // exclusive scan of a short int64 array (B+1 outputs), single CTA
 // Exclusive scans of the per-frame edge and tile counts in ONE launch (block 0: edges -> edge_ptr, block 1: tiles ->
 // tile_ptr) plus the four numbers the host needs to size the outputs, next to each other for a single read back:
-// totals = {n_tiles, n_edges, max nodes per frame, max edges per frame}.
+// totals = {n_tiles, n_edges, max nodes per frame, max edges per frame, #frames whose rows are not camera-ascending}.
 __global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __restrict__ graph_edges, const int64_t* __restrict__ graph_tiles,
+                                                           const int64_t* __restrict__ graph_unsorted,
                                                            const int64_t* __restrict__ graph_ptr, int64_t n, int64_t* __restrict__ edge_ptr,
                                                            int64_t* __restrict__ tile_ptr, int64_t* __restrict__ totals) {
   __shared__ int64_t s_warp[32], s_max[32];
@@ -167,11 +172,14 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __rest
   const int64_t per = (n + blockDim.x - 1) / blockDim.x;
   const int64_t b = min((int64_t)t * per, n), e = min(b + per, n);
   int64_t acc = 0, mx = 0;
+  int uns = 0;
   for (int64_t i = b; i < e; ++i) {
     const int64_t v = in[i];
     acc += v;
+    uns += (int)graph_unsorted[i];
     mx = max(mx, blockIdx.x == 0 ? v : graph_ptr[i + 1] - graph_ptr[i]);     // block 0: max edges, block 1: max nodes per frame
   }
+  const int n_uns = __syncthreads_count(uns != 0);   // threads (not frames) that saw one: only "== 0" matters
   int64_t incl = acc;                              // inclusive scan of the per-thread sums: warp shuffles, then the 32 warp totals
   for (int o = 1; o < 32; o <<= 1) { const int64_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
   for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -194,6 +202,7 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(const int64_t* __rest
     out[n] = total;
     totals[blockIdx.x == 0 ? 1 : 0] = total;       // [0] tiles, [1] edges
     totals[blockIdx.x == 0 ? 3 : 2] = s_max[0];    // [2] max nodes, [3] max edges
+    if (blockIdx.x == 0) totals[4] = n_uns;        // [4] != 0: some frame's rows are not camera-ascending
   }
 }
 
@@ -335,10 +344,10 @@ extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_
 
 extern "C" int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes) {
   // cam_cnt, cam_first, order (int32 x N each) + src_off (int64 x N) + graph_edges, graph_tiles (int64 x B) + tile_ptr (B+1)
-  return (n_nodes + 8) * (3 * 4 + 8) + (3 * n_graphs + 8) * 8 + 1024;
+  return (n_nodes + 8) * (3 * 4 + 8) + (4 * n_graphs + 16) * 8 + 1024;
 }
 
-struct PrepLayout { int32_t* cam_cnt; int32_t* cam_first; int32_t* order; int64_t* src_off; int64_t* graph_edges; int64_t* graph_tiles; int64_t* tile_ptr; int64_t* totals; };
+struct PrepLayout { int32_t* cam_cnt; int32_t* cam_first; int32_t* order; int64_t* src_off; int64_t* graph_edges; int64_t* graph_tiles; int64_t* graph_unsorted; int64_t* tile_ptr; int64_t* totals; };
 static PrepLayout prep_layout(void* scratch, int64_t n_graphs, int64_t n_nodes) {
   char* p = (char*)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
   PrepLayout L;
@@ -346,8 +355,9 @@ static PrepLayout prep_layout(void* scratch, int64_t n_graphs, int64_t n_nodes) 
   L.src_off = (int64_t*)p; p += 8 * n8;
   L.graph_edges = (int64_t*)p; p += 8 * (n_graphs + 1);
   L.graph_tiles = (int64_t*)p; p += 8 * (n_graphs + 1);
+  L.graph_unsorted = (int64_t*)p; p += 8 * (n_graphs + 1);
   L.tile_ptr = (int64_t*)p; p += 8 * (n_graphs + 2);
-  L.totals = (int64_t*)p; p += 8 * 4;
+  L.totals = (int64_t*)p; p += 8 * 8;
   L.cam_cnt = (int32_t*)p; p += 4 * n8;
   L.cam_first = (int32_t*)p; p += 4 * n8;
   L.order = (int32_t*)p;
@@ -364,8 +374,8 @@ extern "C" int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t*
   if (n_graphs > INT32_MAX) return GNNCCA_ERR_BAD_ARG;
   PrepLayout L = prep_layout(scratch, n_graphs, n_nodes);
   graph_prepare_kernel<<<(unsigned)n_graphs, 256, 0, st>>>(graph_ptr, id_cam, L.cam_cnt, L.cam_first, L.src_off, L.order,
-                                                           L.graph_edges, L.graph_tiles, GT);
-  scan_counts_kernel<<<2, 1024, 0, st>>>(L.graph_edges, L.graph_tiles, graph_ptr, n_graphs, edge_ptr, L.tile_ptr, L.totals);
+                                                           L.graph_edges, L.graph_tiles, L.graph_unsorted, GT);
+  scan_counts_kernel<<<2, 1024, 0, st>>>(L.graph_edges, L.graph_tiles, L.graph_unsorted, graph_ptr, n_graphs, edge_ptr, L.tile_ptr, L.totals);
   return check_launch(2);
 }
 
@@ -388,8 +398,10 @@ extern "C" int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge
   return check_launch();
 }
 
-// {n_tiles, n_edges, max nodes per frame, max edges per frame} of the last gnncca_graph_edge_counts live in the scratch, next to
-// each other: the host reads them with ONE copy to size step 2 (and the capacity class of the fused message-passing kernel)
+// {n_tiles, n_edges, max nodes per frame, max edges per frame, camera-order flag} of the last gnncca_graph_edge_counts live in the
+// scratch, next to each other (5 x int64): the host reads them with ONE copy to size step 2 (and the capacity class of the fused
+// message-passing kernel).  [4] != 0 when some frame's rows are not in ascending camera order: the enumeration of train.py:292-299
+// (camera by camera) is then not source-major, and the batch must take the checked (sorting) path of the forward.
 extern "C" const int64_t* gnncca_graph_tile_total_ptr(const void* scratch, int64_t n_graphs, int64_t n_nodes) {
   PrepLayout L = prep_layout(const_cast<void*>(scratch), n_graphs, n_nodes);
   return L.totals;

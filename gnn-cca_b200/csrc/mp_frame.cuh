@@ -159,6 +159,16 @@ __device__ inline void load_weights(float* sw, const WOff& wo, const Net& nt, in
 __device__ __forceinline__ float agg_init(int agg) { return agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f; }
 __device__ __forceinline__ float agg_comb(int agg, float a, float b) { return agg == GNNCCA_AGG_MAX ? fmaxf(a, b) : a + b; }
 
+// A frame that breaks the contract of its batch (larger than the capacity class, an edge leaving the frame, sources not
+// ascending) is skipped with flags[2] raised; its logits are filled with NaN so that nobody mistakes uninitialised memory for a
+// result (the host re-runs such a batch on the checked path, or raises: engine.FastPath.verify).
+__device__ __forceinline__ void poison_frame_logits(const Group& gr, const Net& nt, const Batch& bt, int64_t e0, int64_t e1) {
+  if (!nt.has_cls || bt.logits == nullptr || e0 < 0 || e1 > bt.n_edges || e1 <= e0) return;
+  const float qnan = __int_as_float(0x7fc00000);
+  for (int s = 0; s <= nt.L - nt.first_cls; ++s)
+    for (int64_t j = e0 + gr.tid; j < e1; j += gr.size) bt.logits[(int64_t)s * bt.n_edges + j] = qnan;
+}
+
 // One frame, all steps.  sw: the CTA's weights; ss: this group's state.  Every thread of the group calls it with
 // the same arguments; returns after the group's last barrier (the state may be overwritten at once).
 template <bool REATT_E, int AGG>
@@ -174,17 +184,24 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
   bool fits = !(a < 0 || b < a || b > bt.n_nodes);
   const int n = fits ? (int)min(b - a, (int64_t)INT32_MAX) : 0;
   int64_t eb = 0; int ne = 0;
+  int64_t pe0 = -1, pe1 = -1;      // the frame's edge range as far as it can be trusted (for the NaN fill of a skipped frame)
   if (fits) {
     if (raw) {
       const int64_t e0 = bt.edge_ptr[g], e1 = bt.edge_ptr[g + 1];
+      if (e0 >= 0 && e1 >= e0 && e1 <= bt.n_edges) { pe0 = e0; pe1 = e1; }
       fits = e0 >= 0 && e1 >= e0 && e1 <= bt.n_edges && e1 - e0 <= nt.cap_e;
       eb = e0; ne = fits ? (int)(e1 - e0) : 0;
     } else {
       eb = bt.rowptr[a]; ne = bt.rowptr[b] - (int)eb;
+      if (ne >= 0) { pe0 = eb; pe1 = eb + ne; }
       fits = ne >= 0 && ne <= nt.cap_e;
     }
   }
-  if (!fits || n > nt.cap_n) { if (tid == 0) atomicOr(bt.flags + 2, 1); return; }     // group-uniform
+  if (!fits || n > nt.cap_n) {     // group-uniform
+    if (tid == 0) atomicOr(bt.flags + 2, 1);
+    poison_frame_logits(gr, nt, bt, pe0, pe1);
+    return;
+  }
 
   // ---- load the frame: local CSR + edge encoder first (inputs of the forward), the encoded nodes last: when the kernel is a
   //      programmatic dependent of the node encoder (dep_wait), everything before the wait overlaps the encoder's tail
@@ -279,6 +296,7 @@ __device__ __forceinline__ void mp_frame(const Group& gr, const Net& nt, const B
   gr.sync();
   if (ssi[so.bad]) {                                 // not a closed, source-major frame: group-uniform exit
     if (tid == 0) atomicOr(bt.flags + 2, 1);
+    poison_frame_logits(gr, nt, bt, pe0, pe1);
     gr.sync();
     return;
   }

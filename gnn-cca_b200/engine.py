@@ -3,6 +3,7 @@ PyTorch is used for device memory (caching allocator) and streams only; all arit
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -184,7 +185,7 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
                       plan: Optional[GraphPlan] = None, return_latents: bool = False, prof: Optional[StageTimer] = None,
                       h_encoded: Optional[torch.Tensor] = None, graph_ptr: Optional[torch.Tensor] = None, caps=None,
                       allow_fused: bool = True, return_plan: bool = False, trusted: bool = False,
-                      edge_ptr: Optional[torch.Tensor] = None):
+                      edge_ptr: Optional[torch.Tensor] = None, _no_block: bool = False, cache_on=None):
     """``MOTMPNet.forward`` (models/mpn.py:250-299), no autograd graph.  Returns the list of per-step logits
     [E,1] in the caller's edge order.
 
@@ -212,6 +213,11 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     B = int(graph_ptr.numel()) - 1 if graph_ptr is not None else 0
     fused_ok = allow_fused and graph_ptr is not None and L >= 1 and E > 0 and edge_attr.size(1) <= 8 and first_class_step >= 1
     cap = frame_capacity(model, N, E, B, caps) if fused_ok else None
+    if (cap is None and plan is None and graph_ptr is not None and not _no_block and not return_latents and h_encoded is None
+            and E >= BLOCKED_MIN_EDGES and L >= 1 and first_class_step >= 1 and B > 1 and int(edge_attr.size(1)) == 4):
+        # a batch of large frames whose per-edge buffers should not all be resident: blocks of whole frames (see forward_blocked)
+        outs = forward_blocked(model, x, edge_index, edge_attr, graph_ptr, edge_ptr, trusted=trusted, cache_on=cache_on, prof=prof)
+        return (outs, BLOCKED_PLAN) if return_plan else outs
     raw = plan is None and trusted and cap is not None and edge_ptr is not None and not return_latents
     if raw:
         plan = TrustedPlan(edge_index, N, edge_ptr)
@@ -335,6 +341,178 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
     if return_latents:
         return outs, latents, plan
     return (outs, plan) if return_plan else outs
+
+
+# ------------------------------------------------------------------------------------------------------------
+# frame-blocked execution of very large batches (BASELINE config 4: 4096 frames of 8 x 64 detections, 939.5 M edges)
+# ------------------------------------------------------------------------------------------------------------
+BLOCK_EDGES = int(os.environ.get("GNNCCA_BLOCK_EDGES", str(16 << 20)))     # target edges per block of frames
+BLOCKED_MIN_EDGES = int(os.environ.get("GNNCCA_BLOCKED_MIN_EDGES", str(24 << 20)))   # batches above this run blocked
+
+
+def frame_blocks(graph_ptr_host, edge_ptr_host, target_edges: int):
+    """Cut the frames [0, B) into contiguous blocks of about ``target_edges`` edges each (whole frames; sizes as even as
+    the frames allow).  Returns [(g0, g1, n0, n1, e0, e1)].  Pure host arithmetic on the two offset vectors."""
+    B = len(graph_ptr_host) - 1
+    E = int(edge_ptr_host[B]) - int(edge_ptr_host[0])
+    if B <= 0:
+        return []
+    nb = max(1, min(B, -(-E // max(1, target_edges))))
+    blocks, g0 = [], 0
+    for b in range(1, nb + 1):
+        if b == nb:
+            g1 = B
+        else:
+            goal = int(edge_ptr_host[0]) + (E * b) // nb
+            lo, hi = g0 + 1, B - (nb - b)         # leave at least one frame for every later block
+            while lo < hi:                        # first frame boundary at or beyond the goal
+                mid = (lo + hi) // 2
+                if int(edge_ptr_host[mid]) < goal:
+                    lo = mid + 1
+                else:
+                    hi = mid
+            g1 = lo
+        blocks.append((g0, g1, int(graph_ptr_host[g0]), int(graph_ptr_host[g1]), int(edge_ptr_host[g0]), int(edge_ptr_host[g1])))
+        g0 = g1
+    return blocks
+
+
+class BlockWorkspace:
+    """Per-edge / per-node work buffers of ONE block of frames, allocated once for the largest block and reused by every
+    block of every forward on that batch shape (the caching allocator would hand the same memory back anyway; keeping
+    them removes ~15 allocator calls per block from the host path)."""
+
+    def __init__(self, lib, sb, max_nodes: int, max_edges: int, n_blocks: int, dev, f_node: int, f_edge: int, reattach_e: bool):
+        i32, f32 = torch.int32, torch.float32
+        self.max_nodes, self.max_edges, self.n_blocks = max_nodes, max_edges, n_blocks
+        self.src = torch.empty(max_edges, dtype=i32, device=dev)
+        self.dst = torch.empty(max_edges, dtype=i32, device=dev)
+        self.rowptr = torch.empty(max_nodes + 1, dtype=i32, device=dev)
+        self.flags = torch.zeros((n_blocks, _lib.CSR_NFLAGS), dtype=i32, device=dev)
+        self.h = [torch.empty((max_nodes, f_node), dtype=f32, device=dev) for _ in range(3)]
+        self.P = torch.empty((max_nodes, 8), dtype=f32, device=dev)
+        self.Q = torch.empty((max_nodes, 8), dtype=f32, device=dev)
+        self.R = torch.empty((max_nodes, f_node), dtype=f32, device=dev)
+        self.e = torch.empty((max_edges, f_edge), dtype=f32, device=dev)
+        self.ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), max_nodes, max_edges))
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=dev)
+
+    def fits(self, max_nodes, max_edges, n_blocks):
+        return max_nodes <= self.max_nodes and max_edges <= self.max_edges and n_blocks <= self.n_blocks
+
+
+def forward_blocked(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor, graph_ptr: torch.Tensor,
+                    edge_ptr: Optional[torch.Tensor] = None, trusted: bool = False, target_edges: Optional[int] = None,
+                    cache_on=None, prof=None):
+    """``MOTMPNet.forward`` (models/mpn.py:250-299) for a batch whose per-edge work buffers should not (or cannot: the step
+    kernel indexes edges with int32) be resident for all E edges at once.  A PyG ``Batch`` is a disjoint union of frames
+    (train.py:450) and nothing in the eval-mode forward mixes frames, so blocks of whole frames run one after the other
+    through the per-step pipeline (CSR narrowing -> node encoder -> L x [node_project, mp_step, fold]) on ONE reused
+    workspace; each block's logits land in its slice of the batch-wide outputs.  Results are bit-identical to the
+    unblocked per-step forward: a block is tiled like the whole batch (``edge_phase`` = position of its first edge inside
+    a reduction tile of the batch-wide edge numbering), so every segment is summed in the same order
+    (tests/test_gpu_blocked.py).
+
+    ``graph_ptr`` [B+1] node offsets (Batch.ptr); ``edge_ptr`` [B+1] edge offsets when known (``build_graph_batch``),
+    otherwise found by a binary search in ``edge_index[0]`` (valid for source-major input, which each block verifies).
+    One small read back (the two offset vectors) the first time a batch is seen; untrusted input costs one more 16-byte
+    flag read per forward after the last launch."""
+    lib = _lib.load()
+    _require_cuda(x, "data.x")
+    _require_cuda(edge_attr, "data.edge_attr")
+    check_supported(model)
+    if edge_index.dim() != 2 or edge_index.size(0) != 2 or edge_index.dtype != torch.int64 or not edge_index.is_cuda:
+        raise ValueError("edge_index must be a CUDA int64 tensor of shape [2, E]")
+    math = MATH_MODES[model.math]
+    dev = x.device
+    x, edge_index, edge_attr = x.contiguous(), edge_index.contiguous(), edge_attr.contiguous()
+    N, E = int(x.size(0)), int(edge_index.size(1))
+    L, k = model.num_enc_steps, model.num_class_steps
+    first = L - k + 1
+    if L < 1 or first < 1:
+        raise NotImplementedError("blocked forward needs num_enc_steps >= 1 and num_class_steps <= num_enc_steps")
+    enc_e = model.encoder.edge_mlp
+    if not (len(enc_e.layer_specs) == 1 and enc_e.layer_specs[0].relu and enc_e.layer_specs[0].bn is None and int(edge_attr.size(1)) == 4):
+        raise NotImplementedError("blocked forward: the edge encoder must be the single Linear(4, f_edge) + ReLU")
+    target = int(target_edges) if target_edges else BLOCK_EDGES
+
+    cached = getattr(cache_on, "_gnncca_blocks", None) if cache_on is not None else None
+    key = (graph_ptr.data_ptr(), graph_ptr._version, edge_index.data_ptr(), edge_index._version, N, E, target)
+    if cached is not None and cached[0] == key:
+        blocks = cached[1]
+    else:
+        gp = graph_ptr.to(device=dev, dtype=torch.int64)
+        if edge_ptr is None:
+            edge_ptr = torch.searchsorted(edge_index[0].contiguous(), gp)      # first edge whose source is >= the frame's first node
+        host = torch.stack([gp, edge_ptr.to(device=dev, dtype=torch.int64)]).cpu()
+        gph, eph = host[0].tolist(), host[1].tolist()
+        if gph[0] != 0 or gph[-1] != N or eph[0] != 0 or eph[-1] != E or any(b < a for a, b in zip(gph, gph[1:])):
+            raise ValueError("data.ptr / edge offsets do not cover the batch (ptr must run from 0 to num_nodes, non-decreasing)")
+        blocks = frame_blocks(gph, eph, target)
+        if cache_on is not None:
+            try:
+                cache_on._gnncca_blocks = (key, blocks)
+            except AttributeError:
+                pass
+    max_n = max((b[3] - b[2]) for b in blocks)
+    max_e = max((b[5] - b[4]) for b in blocks)
+    if max_e >= (1 << 31) - 4096:
+        raise NotImplementedError("a single frame block of %d edges exceeds the step kernel's int32 edge index" % max_e)
+    sb = StepBinding(model, math)
+    wsp = model.__dict__.get("_gnncca_block_ws")
+    if wsp is None or not wsp.fits(max_n, max_e, len(blocks)) or wsp.ws.device != dev:
+        wsp = BlockWorkspace(lib, sb, max_n, max_e, len(blocks), dev, sb.f_node, sb.f_edge, bool(model.reattach_initial_edges))
+        model.__dict__["_gnncca_block_ws"] = wsp
+    logits = torch.empty((k, E), dtype=torch.float32, device=dev)
+    le = enc_e.linear(0)
+    row0, col0 = edge_index.data_ptr(), edge_index.data_ptr() + 8 * E
+    st = _stream()
+    cfg, w = C.byref(sb.cfg), C.byref(sb.w)
+    enc_n = model.encoder.node_mlp
+    tile = int(lib.gnncca_mp_step_tile())
+    if not trusted:
+        wsp.flags.zero_()
+    for bi, (g0, g1, n0, n1, e0, e1) in enumerate(blocks):
+        nn_, ne_ = n1 - n0, e1 - e0
+        if ne_ == 0 or nn_ == 0:
+            continue                # frames without cross-camera edges: no logits to write
+        sb.cfg.edge_phase = e0 % tile
+        flags_b = wsp.flags[bi]
+        guard = 0 if trusted else flags_b.data_ptr()
+        _lib.check(lib.gnncca_csr_from_edge_rows(row0 + 8 * e0, col0 + 8 * e0, n0, nn_, ne_, _lib.ptr(wsp.src), _lib.ptr(wsp.dst),
+                                                 _lib.ptr(wsp.rowptr), flags_b.data_ptr(), st), "csr_from_edge_rows")
+        h = mlp_forward_nograd(enc_n, x[n0:n1], math, out=wsp.h[0][:nn_])
+        h0 = h
+        ea = edge_attr[e0:e1]
+        hbuf = 1
+        for step in range(1, L + 1):
+            _lib.check(lib.gnncca_node_project(cfg, w, h0.data_ptr(), h.data_ptr(), nn_, _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), st), "node_project")
+            last = step == L
+            h_out = None if last else wsp.h[hbuf][:nn_]
+            lg = logits[step - first][e0:e1] if step >= first else None
+            dead_e = last and lg is not None
+            if step == 1 or model.reattach_initial_edges:
+                e_in = None if step == 1 else wsp.e
+                _lib.check(lib.gnncca_mp_step_fwd_attr(cfg, w, _lib.ptr(wsp.rowptr), _lib.ptr(wsp.src), _lib.ptr(wsp.dst), nn_, ne_,
+                                                       _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), ea.data_ptr(), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
+                                                       _lib.ptr(e_in), 0 if dead_e else _lib.ptr(wsp.e), _lib.ptr(h_out), _lib.ptr(lg), guard,
+                                                       _lib.ptr(wsp.ws), wsp.ws_bytes, st), "mp_step_fwd_attr")
+            else:
+                _lib.check(lib.gnncca_mp_step_fwd(cfg, w, _lib.ptr(wsp.rowptr), _lib.ptr(wsp.src), _lib.ptr(wsp.dst), nn_, ne_,
+                                                  _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), 0, _lib.ptr(wsp.e), 0 if dead_e else _lib.ptr(wsp.e),
+                                                  _lib.ptr(h_out), _lib.ptr(lg), guard, _lib.ptr(wsp.ws), wsp.ws_bytes, st), "mp_step_fwd")
+            if h_out is not None:
+                h = h_out
+                hbuf = 2 if hbuf == 1 else 1
+    if not trusted:      # one read back for all blocks, after the last launch
+        bad = wsp.flags[:len(blocks)].amax(dim=0).cpu().tolist()
+        if bad[1]:
+            raise IndexError("edge_index has entries outside their frame block's node range (frames must be closed; ptr must match)")
+        if bad[0]:
+            if E < (1 << 31) - 4096:
+                return forward_inference(model, x, edge_index, edge_attr, None, graph_ptr=graph_ptr, allow_fused=False, _no_block=True)
+            raise NotImplementedError("edge_index is not source-major and the batch is too large for the sorting path")
+    return [logits[i].view(E, 1) for i in range(k)]
 
 
 def forward_host(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor, out: Optional[List[torch.Tensor]] = None,
@@ -476,6 +654,9 @@ class HostPipeline:
 FAST_PLAN = TrustedPlan.__new__(TrustedPlan)     # what ``last_plan`` reports after the single-call path
 FAST_PLAN.last_path = "fused"
 FAST_PLAN.caps = None
+BLOCKED_PLAN = TrustedPlan.__new__(TrustedPlan)  # ... and after the frame-blocked path (no batch-wide CSR exists)
+BLOCKED_PLAN.last_path = "blocked"
+BLOCKED_PLAN.caps = None
 
 _SIDE_STREAMS = {}
 
@@ -557,7 +738,12 @@ class FastPath:
         self.in_dim = l1.in_features
         self.device = l1.weight.device
         self.fn = _lib.load().gnncca_mpn_forward_frames
-        self.flags = torch.zeros(_lib.CSR_NFLAGS, dtype=torch.int32, device=self.device)   # write-only scratch (never read back)
+        # The kernel raises flags[2] when a frame breaks the trust contract (not closed / not source-major / larger than caps) and
+        # leaves that frame's logits as NaN.  The flags live in PINNED HOST memory that the device writes through its mapped
+        # address: the normal case costs nothing (the word is never touched), and the host sees a violation of any earlier,
+        # completed forward by reading one int at the start of the next call -- no copy, no synchronisation.
+        self.flags = torch.zeros(_lib.CSR_NFLAGS, dtype=torch.int32).pin_memory()
+        self.flags_np = self.flags.numpy()
         self.training = model.training
 
     def valid(self, model) -> bool:
@@ -579,6 +765,7 @@ class FastPath:
         cap = frame_capacity(model, N, E, B, caps)
         if cap is None or edge_ptr.numel() != B + 1:
             return None
+        self.verify()
         h = torch.empty((N, 32), dtype=torch.float32, device=self.device)
         logits = torch.empty((self.n_cls, E), dtype=torch.float32, device=self.device)
         rc = self.fn(*self.prefix, x.data_ptr(), edge_index.data_ptr(), edge_attr.data_ptr(), graph_ptr.data_ptr(), edge_ptr.data_ptr(),
@@ -586,6 +773,22 @@ class FastPath:
         if rc:
             _lib.check(rc, "mpn_forward_frames")
         return [logits[i].view(E, 1) for i in range(self.n_cls)]
+
+
+def _fast_verify(self, wait: bool = False) -> None:
+    """Raise if a forward launched through this binding found a frame that breaks the contract of a trusted batch (edges
+    leaving their frame, sources not ascending, a frame larger than ``gnncca_caps``): its logits for that frame are NaN.
+    ``wait``: synchronise the device first (otherwise only forwards that have already completed are covered)."""
+    if wait:
+        torch.cuda.synchronize(self.device)
+    if self.flags_np[2]:
+        self.flags_np[2] = 0
+        raise RuntimeError("gnn-cca_b200: an earlier forward on a batch marked gnncca_trusted met a frame that is not a closed, "
+                           "source-major frame within gnncca_caps (edge_index / ptr / edge_ptr edited after build_graph_batch?); the "
+                           "logits of that frame were left as NaN.  Clear data.gnncca_trusted to use the checked path.")
+
+
+FastPath.verify = _fast_verify
 
 
 def fast_path(model):

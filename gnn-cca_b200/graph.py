@@ -97,9 +97,9 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     # the output size is data dependent: one 32-byte read back (the reference syncs several times per FRAME)
     if B > 0:
         off = (lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N) - scratch.data_ptr()) // 8
-        n_tiles, E, max_n, max_e = (int(v) for v in scratch[off:off + 4].tolist())
+        n_tiles, E, max_n, max_e, cam_unsorted = (int(v) for v in scratch[off:off + 5].tolist())
     else:
-        n_tiles = E = max_n = max_e = 0
+        n_tiles = E = max_n = max_e = cam_unsorted = 0
     caps = (max_n, max_e)      # exact frame maxima: sizes the fused all-steps kernel without guessing
 
     width = 4 if mode == "full" else 2
@@ -110,5 +110,8 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
                                        _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
                                        int(reid.size(1)), attr_mode, _lib.ptr(scratch), _lib.ptr(edge_index),
                                        _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
+    # "trusted" = source-major by construction: true only when every frame's rows are in ascending camera order (the reference
+    # enumerates camera by camera, train.py:292-299, so interleaved cameras give an edge_index[0] that is NOT non-decreasing);
+    # otherwise the forward takes its checked path (order flags read back, stable sort + permutation)
     return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64,
-                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps, gnncca_trusted=True)
+                 ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps, gnncca_trusted=cam_unsorted == 0)

@@ -145,9 +145,11 @@ class MOTMPNet(nn.Module):
         caps = getattr(data, "gnncca_caps", None)
         trusted = bool(getattr(data, "gnncca_trusted", False))
         plan = getattr(data, "gnncca_plan", None)          # CSR verified by an earlier forward on this very object
+        ptr_key = (graph_ptr.data_ptr(), graph_ptr._version) if torch.is_tensor(graph_ptr) else None
         if plan is not None and (not engine.CACHE_PLANS or plan.key() != (edge_index.data_ptr(), tuple(edge_index.shape),
-                                                                          edge_index._version, int(x.size(0)))):
-            plan = None
+                                                                          edge_index._version, int(x.size(0)))
+                                 or getattr(plan, "ptr_key", None) != ptr_key):
+            plan = None       # edge_index or ptr were replaced / edited in place since the plan was verified
         allow_fused = True
         if plan is not None and plan.last_path is not None:      # verified before: nothing left to check
             trusted, allow_fused = True, plan.last_path == "fused"
@@ -165,16 +167,19 @@ class MOTMPNet(nn.Module):
             outs, plan = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan, trusted=trusted, return_plan=True)
             if engine.CACHE_PLANS and plan is not None:
                 try:                    # the CSR (and its transpose for the backward) is reused while edge_index is unchanged
+                    plan.ptr_key = ptr_key
                     data.gnncca_plan = plan
                 except AttributeError:
                     pass
         else:
             edge_ptr = getattr(data, "edge_ptr", None) if getattr(data, "gnncca_trusted", False) else None
             outs, plan = engine.forward_inference(self, x, edge_index, edge_attr, plan, graph_ptr=graph_ptr, caps=caps,
-                                                  return_plan=True, trusted=trusted, allow_fused=allow_fused, edge_ptr=edge_ptr)
+                                                  return_plan=True, trusted=trusted, allow_fused=allow_fused, edge_ptr=edge_ptr,
+                                                  cache_on=data)
             self.last_plan = plan       # introspection only (which device pipeline ran, the CSR)
-            if engine.CACHE_PLANS and not getattr(data, "gnncca_trusted", False):
+            if engine.CACHE_PLANS and not getattr(data, "gnncca_trusted", False) and plan is not engine.BLOCKED_PLAN:
                 try:                    # a verified CSR is reused by later forwards on the same, unmodified Batch
+                    plan.ptr_key = ptr_key
                     data.gnncca_plan = plan
                     if caps is None and getattr(plan, "caps", None) is not None and plan.last_path == "fused":
                         data.gnncca_caps = plan.caps

@@ -111,19 +111,47 @@ def exchange_node_rows(h_partial: torch.Tensor, ranges: Sequence[Tuple[int, int]
 
 
 def forward_edge_partitioned(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor,
-                             ranges: Sequence[Tuple[int, int]], group=None, edge_base: int = 0) -> List[torch.Tensor]:
+                             ranges: Sequence[Tuple[int, int]], group=None, edge_base: int = 0, prof=None) -> List[torch.Tensor]:
     """Drive ``edge_partitioned_steps`` with the NCCL exchange of ``exchange_node_rows`` (see there).  ``edge_base``:
-    global id of this rank's first edge (the sum of the lower ranks' edge counts)."""
-    gen = edge_partitioned_steps(model, x, edge_index_local, edge_attr_local, edge_base)
+    global id of this rank's first edge (the sum of the lower ranks' edge counts).  ``prof``: an ``engine.StageTimer``
+    that receives a CUDA-event mark after every stage (csr, encoder, project / step of each step, exchange)."""
+    gen = edge_partitioned_steps(model, x, edge_index_local, edge_attr_local, edge_base, prof=prof)
     try:
         h_partial = next(gen)
         while True:
-            h_partial = gen.send(exchange_node_rows(h_partial, ranges, group))
+            h_full = exchange_node_rows(h_partial, ranges, group)
+            if prof is not None:
+                prof.mark("exchange")
+            h_partial = gen.send(h_full)
     except StopIteration as done:
         return done.value
 
 
-def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0):
+def forward_edge_partitioned_host(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor,
+                                  ranges: Sequence[Tuple[int, int]], out: Optional[List[torch.Tensor]] = None, group=None,
+                                  edge_base: int = 0, device: Optional[torch.device] = None) -> List[torch.Tensor]:
+    """``forward_edge_partitioned`` for HOST buffers (pinned memory recommended): this rank's node matrix, edge slice and
+    attributes are copied to the device, the partitioned forward runs, and the rank's logits are copied back into ``out``
+    (host tensors [E_r, 1]; allocated pinned when None).  Returns after the copies have completed."""
+    if x.is_cuda or edge_index_local.is_cuda or edge_attr_local.is_cuda:
+        raise ValueError("forward_edge_partitioned_host takes host tensors")
+    dev = device if device is not None else next(model.parameters()).device
+    if dev.type != "cuda":
+        raise RuntimeError("gnn-cca_b200: the model must live on a CUDA device (no CPU path)")
+    x_d = x.to(dev, non_blocking=True)
+    ei_d = edge_index_local.to(dev, non_blocking=True)
+    ea_d = edge_attr_local.to(dev, non_blocking=True)
+    outs = forward_edge_partitioned(model, x_d, ei_d, ea_d, ranges, group, edge_base)
+    if out is None:
+        out = [torch.empty(o.shape, dtype=torch.float32, pin_memory=True) for o in outs]
+    for o, d in zip(out, outs):
+        o.copy_(d, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    return out
+
+
+def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0,
+                           prof=None):
     """Generator form of the edge-partitioned forward: yields this rank's partial node matrix ([N, F], rows of
     nodes it does not own are zero) at every exchange point and expects the assembled matrix back through
     ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
@@ -144,10 +172,18 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     dev = x.device
     N, E = int(x.size(0)), int(edge_index_local.size(1))
     math = engine.MATH_MODES[model.math]
-    plan = GraphPlan(edge_index_local, N).resolve()      # rowptr spans all N nodes; segments outside the owned range are empty
-    if plan.perm is not None:
-        raise ValueError("the local edge slice must be source-major")
+    if prof is not None:
+        prof.mark("begin")
+    # rowptr spans all N nodes; segments outside the owned range are empty.  The order / range flags are NOT read back here (no
+    # host synchronisation on the data path): the step kernels take them as their guard and are no-ops on an invalid CSR, and
+    # ``check_partition_flags(plan)`` reads them whenever the caller wants the verdict.
+    plan = GraphPlan(edge_index_local, N)
+    guard = _lib.ptr(plan.flags)
+    if prof is not None:
+        prof.mark("csr")
     h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math)
+    if prof is not None:
+        prof.mark("encoder_node")
     enc_e = model.encoder.edge_mlp
     ea = edge_attr_local.contiguous()
     L = model.num_enc_steps
@@ -172,6 +208,8 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     for step in range(1, L + 1):
         _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
                                            _stream()), "node_project")
+        if prof is not None:
+            prof.mark("project%d" % step)
         last = step == L
         h_out = None if last else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
         logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if step >= first else None
@@ -180,19 +218,33 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
             e_out = None if dead_e else (torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e)
             _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                                    _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
-                                                   _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes,
+                                                   _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes,
                                                    _stream()), "mp_step_fwd_attr")
         else:
             e_out = None if dead_e else (torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e)
             _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                               _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
-                                              _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), 0, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+                                              _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+        if prof is not None:
+            prof.mark("step%d" % step)
         e = e_out
         if logits is not None:
             outs.append(logits)
         if h_out is not None:
             h = yield h_out                                  # the one exchange of the step: N x 32 fp32 over NVLink
+    model.__dict__["_gnncca_partition_plan"] = plan        # for check_partition_flags
     return outs
+
+
+def check_partition_flags(model) -> None:
+    """Read back the CSR flags of the model's last edge-partitioned forward (one 16-byte copy, synchronising) and raise when
+    the local edge slice was not source-major or held ids outside [0, N): in that case every step kernel of that forward was
+    a no-op and its outputs are undefined."""
+    plan = model.__dict__.get("_gnncca_partition_plan")
+    if plan is None:
+        return
+    if not plan.source_major():
+        raise ValueError("the local edge slice must be source-major")
 
 
 def complete_multipartite_slice(n_cams: int, n_dets: int, node_range: Tuple[int, int], device) -> torch.Tensor:

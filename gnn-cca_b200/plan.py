@@ -56,6 +56,20 @@ class GraphPlan:
         self._event.record()
         self._requested = True
 
+    def check_deferred(self) -> None:
+        """For plans used WITHOUT waiting for their flags (batches trusted by construction; the step kernels take the flags as
+        their guard and are no-ops on an invalid CSR): if a read back requested by an earlier forward has completed, look at
+        it now and raise when the trust was misplaced.  Never blocks."""
+        if not self._requested or self._event is None or not self._event.query():
+            return
+        self._requested = False
+        if int(self._flags_host[1]):
+            raise IndexError("edge_index has entries outside [0, num_nodes=%d) (found after a forward on a batch marked trusted: "
+                             "its outputs are invalid)" % self.N)
+        if int(self._flags_host[0]):
+            raise RuntimeError("a batch marked gnncca_trusted is not source-major: the forward that used it was a no-op and its "
+                               "outputs are invalid; clear data.gnncca_trusted so that the checked path sorts the edges")
+
     def frames_overflowed(self) -> bool:
         """flags[2]: raised by gnncca_mp_fused_fwd when a frame did not fit its capacity class (valid after
         ``source_major()``)."""

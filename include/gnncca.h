@@ -64,6 +64,13 @@ int64_t gnncca_launch_count(void);
 int gnncca_csr_from_edge_index(const int64_t* edge_index, int64_t n_nodes, int64_t n_edges,
                                int32_t* src, int32_t* dst, int32_t* rowptr, int32_t* flags, void* stream);
 
+/* The same for a BLOCK of whole frames of a larger batch (Batch.from_data_list is a disjoint union, train.py:450, and no
+ * operation of MOTMPNet.forward mixes frames in eval mode): row / col point at the block's first edge inside the two rows
+ * of the caller's edge_index, node_base is the block's first node and is subtracted from every id, n_nodes / n_edges are
+ * the block's sizes.  flags[1] is raised when an edge leaves the block's node range (a frame that is not closed). */
+int gnncca_csr_from_edge_rows(const int64_t* row, const int64_t* col, int64_t node_base, int64_t n_nodes, int64_t n_edges,
+                              int32_t* src, int32_t* dst, int32_t* rowptr, int32_t* flags, void* stream);
+
 /* Bytes of scratch gnncca_csr_sort needs. */
 int64_t gnncca_csr_sort_workspace_bytes(int64_t n_nodes, int64_t n_edges);
 
@@ -347,8 +354,10 @@ int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, flo
  * per detection (row order of the frame's table).  Writes edge_ptr[B+1] (int64 exclusive scan of the
  * per-frame directed edge counts n_g^2 - sum_c n_{g,c}^2) and fills `scratch`
  * (gnncca_graph_prepare_scratch_bytes) with the per-detection enumeration tables step 2 needs.
- * gnncca_graph_tile_total_ptr() points at four int64 inside the scratch: {n_tiles, E, max nodes per frame, max edges per
- * frame}; the caller reads them with one copy to size step 2 (and the capacity class of gnncca_mp_fused_fwd). */
+ * gnncca_graph_tile_total_ptr() points at five int64 inside the scratch: {n_tiles, E, max nodes per frame, max edges per
+ * frame, camera-order flag}; the caller reads them with one copy to size step 2 (and the capacity class of
+ * gnncca_mp_fused_fwd).  The flag is non-zero when some frame's rows are not in ascending camera order: the reference's
+ * camera-by-camera enumeration (train.py:292-299) is then not source-major and the MPN must take its checked path. */
 int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes);
 int gnncca_graph_edge_counts(const int64_t* graph_ptr, const int32_t* id_cam, int64_t n_graphs, int64_t n_nodes,
                              int64_t* edge_ptr, void* scratch, int64_t scratch_bytes, void* stream);

@@ -7,7 +7,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-TF32_TOL = 5e-3   # |got - ref| <= 5e-3 * (1 + |ref|): TF32 operands (10-bit mantissa), fp32 accumulate
+TF32_TOL = 1e-3   # |got - ref| <= 1e-3 * (1 + |ref|): TF32 operands (10-bit mantissa), fp32 accumulate; ~10x the measured error (1e-4)
 
 
 def _run(rows, in_dim, hidden, dev, seed=0, scale=1.0, keep=None):

@@ -234,7 +234,7 @@ def test_fused_pipeline_rejects_a_ptr_that_cuts_through_edges(cuda_device):
 def test_default_tf32_pipeline_matches_reference_vectors_within_tf32_tolerance(cuda_device):
     """The default math mode runs the node encoder on tcgen05 kind::tf32: logits stay within the TF32 tolerance of the
     reference's own outputs and agree on every decision that is not within tolerance of the threshold."""
-    TF32_TOL = 5e-3
+    TF32_TOL = 1e-3      # ~10x the measured worst case (1e-4); the decision mask uses the same margin
     z = load_golden("mpn_shipped_resnet50_eval")
     model = build_model(z, cuda_device, math="tf32").eval()
     import gnncca
