@@ -319,9 +319,19 @@ def timed_windows(ctx: Ctx, step, steps: int, warmup: int, budget_s: float, extr
                         "first_ms": per_window[0]}}
 
 
+ERR_FORMULA = "max |got - ref| / (1 + |ref| + 0.01 max|ref|)  (the last term is the fp32 reassociation floor: 1e-6 of the tensor's largest magnitude at tol 1e-4)"
+
+
 def rel_err(out, ref):
-    """max |out - ref| / (1 + |ref|) over a list of tensors (CPU)."""
-    return max(float(((o.double() - r.double()).abs() / (1 + r.double().abs())).max()) for o, r in zip(out, ref)) if out else 0.0
+    """The normalised error of tests/test_gpu_mpn.py::close over a list of tensors (CPU): max |out - ref| / (1 + |ref| + 0.01 max|ref|).
+    With sum aggregation and random weights the latents reach 1e13 at degree 7680; an element that is a cancelling sum of such terms
+    cannot be reproduced relative to its own size by ANY other fp32 summation order (the reference's atomicAdd path included)."""
+    worst = 0.0
+    for o, r in zip(out, ref):
+        if r.numel():
+            r = r.double()
+            worst = max(worst, float(((o.double() - r).abs() / (1 + r.abs() + 0.01 * r.abs().max())).max()))
+    return worst
 
 
 def decisions_equal(out, ref, margin: float):
@@ -522,7 +532,7 @@ def frames_parity(ctx: Ctx, model, batch, outs, ref_full=None, sample_frames=Non
         got = [o.detach().cpu() for o in outs]
         err = rel_err(got, ref_full)
         ok, near, n = decisions_equal(got, ref_full, margin=tol * (1 + max(float(r.abs().max()) for r in ref_full)))
-        return {"against": "oracle/mpn_oracle.py (CPU fp32) on the whole batch of the timed path", "max_rel_err": err, "tolerance": tol,
+        return {"against": "oracle/mpn_oracle.py (CPU fp32) on the whole batch of the timed path", "max_rel_err": err, "err_is": ERR_FORMULA, "tolerance": tol,
                 "within_tolerance": err <= tol, "decisions_equal": ok, "edges_checked": n, "edges_inside_margin": near}
     spec = mpn_oracle.MPNSpec(ctx.params, "resnet50")
     sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
@@ -539,7 +549,7 @@ def frames_parity(ctx: Ctx, model, batch, outs, ref_full=None, sample_frames=Non
             ok, near, n = decisions_equal(got, ref, margin=tol * (1 + max(float(r.abs().max()) for r in ref)))
             ok_all, n_all, near_all = ok_all and ok, n_all + n, near_all + near
     return {"against": "oracle/mpn_oracle.py (CPU fp32) on frames %s of this rank's batch, each evaluated alone" % sample_frames,
-            "max_rel_err": worst, "tolerance": tol, "within_tolerance": worst <= tol, "decisions_equal": ok_all, "edges_checked": n_all,
+            "max_rel_err": worst, "err_is": ERR_FORMULA, "tolerance": tol, "within_tolerance": worst <= tol, "decisions_equal": ok_all, "edges_checked": n_all,
             "edges_inside_margin": near_all}
 
 
@@ -854,6 +864,7 @@ def giant_parity(ctx: Ctx, model, wl, x, outs_local, n0, n1, sample_rows: int = 
         L, first = model.num_enc_steps, model.num_enc_steps - model.num_class_steps + 1
         tol = 1e-3 if model.math == "tf32" else 1e-4
         worst = {"encoder": 0.0, "edge_latents": 0.0, "node_latents": 0.0, "logits": 0.0}
+        per_step = {}
         with torch.no_grad():
             # encoders (all nodes; sampled edges)
             h_ref = mpn_oracle.mlp_forward(sd64, "encoder.node_mlp", spec.enc_node, x.cpu().double())
@@ -867,18 +878,19 @@ def giant_parity(ctx: Ctx, model, wl, x, outs_local, n0, n1, sample_rows: int = 
                 h_prev = latents[t - 1][0].cpu().double()
                 e_prev = latents[t - 1][1][sel_d].cpu().double()
                 e_new, h_new, lg = moc.motmpnet_step(spec, sd64, h_prev, h0, e_prev, e0, row, col, rows, classify=t >= first)
-                worst["edge_latents"] = max(worst["edge_latents"], rel_err([latents[t][1][sel_d].cpu()], [e_new]))
-                if t < L or latents[t][0] is not latents[t - 1][0]:
-                    worst["node_latents"] = max(worst["node_latents"], rel_err([latents[t][0][rows.to(ctx.dev)].cpu()], [h_new]))
+                ee, he = rel_err([latents[t][1][sel_d].cpu()], [e_new]), rel_err([latents[t][0][rows.to(ctx.dev)].cpu()], [h_new])
+                per_step["step%d" % t] = {"edge_latents": ee, "node_latents": he, "max_abs_node_latent": float(h_new.abs().max())}
+                worst["edge_latents"], worst["node_latents"] = max(worst["edge_latents"], ee), max(worst["node_latents"], he)
                 if lg is not None:
                     got = full[t - first][sel_d].cpu()
-                    worst["logits"] = max(worst["logits"], rel_err([got], [lg]))
+                    per_step["step%d" % t]["logits"] = rel_err([got], [lg])
+                    worst["logits"] = max(worst["logits"], per_step["step%d" % t]["logits"])
                     ok, nr, nn = decisions_equal([got], [lg], margin=tol * (1 + float(lg.abs().max())))
                     dec_ok, near, n_dec = dec_ok and ok, near + nr, n_dec + nn
         err = max(worst.values())
         out.update({"against": "oracle/mpn_oracle_chunked.motmpnet_step (CPU float64), every step of the forward on %d sampled source rows "
                                "(%d edges, degree %d); inputs of step t = device outputs of step t-1" % (sample_rows, sel.numel(), deg),
-                    "max_rel_err": err, "per_quantity": worst, "tolerance": tol, "within_tolerance": err <= tol, "decisions_equal": dec_ok,
+                    "max_rel_err": err, "err_is": ERR_FORMULA, "per_quantity": worst, "per_step": per_step, "tolerance": tol, "within_tolerance": err <= tol, "decisions_equal": dec_ok,
                     "edges_checked": n_dec, "edges_inside_margin": near})
         del latents, res
     del ei_f, ea_f, full

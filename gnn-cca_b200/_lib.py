@@ -47,6 +47,7 @@ SIGNATURES = {
     "gnncca_launch_count": (i64, []),
     "gnncca_csr_from_edge_index": (C.c_int, [vp, i64, i64, vp, vp, vp, vp, vp]),
     "gnncca_csr_from_edge_rows": (C.c_int, [vp, vp, i64, i64, i64, vp, vp, vp, vp, vp]),
+    "gnncca_segment_agg": (C.c_int, [vp, vp, i64, i32, i32, vp, vp]),
     "gnncca_csr_sort_workspace_bytes": (i64, [i64, i64]),
     "gnncca_csr_sort": (C.c_int, [i64, i64, vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_permute_rows": (C.c_int, [vp, vp, vp, i64, i32, i32, vp]),

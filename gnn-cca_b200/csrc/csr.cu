@@ -72,6 +72,27 @@ __global__ void __launch_bounds__(256) permute_rows_kernel(const float* __restri
   }
 }
 
+// torch_scatter scatter_add / scatter_mean / scatter_max(...)[0] over source-sorted rows (models/mpn.py:196-202, dim 0): one warp per
+// segment, lane = feature (two passes when width > 32), rows folded in edge order -- no atomics, bit-reproducible.  Empty segments give
+// 0; mean divides by max(count, 1).
+__global__ void __launch_bounds__(256) segment_agg_kernel(const float* __restrict__ rows, const int32_t* __restrict__ rowptr, int64_t n_nodes,
+                                                          int width, int agg, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t v = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (v >= n_nodes) return;
+  const int j0 = rowptr[v], j1 = rowptr[v + 1];
+  for (int c = lane; c < width; c += 32) {
+    float acc = agg == GNNCCA_AGG_MAX ? -INFINITY : 0.f;
+    for (int j = j0; j < j1; ++j) {
+      const float m = rows[(int64_t)j * width + c];
+      acc = agg == GNNCCA_AGG_MAX ? fmaxf(acc, m) : acc + m;
+    }
+    if (j1 <= j0) acc = 0.f;
+    else if (agg == GNNCCA_AGG_MEAN) acc = acc / (float)(j1 - j0);
+    out[v * width + c] = acc;
+  }
+}
+
 static int key_bits(int64_t n_nodes) {
   int b = 1;
   while (((int64_t)1 << b) < n_nodes && b < 31) ++b;
@@ -148,6 +169,15 @@ extern "C" int gnncca_csr_sort(int64_t n_nodes, int64_t n_edges, int32_t* src, i
   if (rc) return rc;
   rowptr_from_sorted_kernel<<<g, 256, 0, st>>>(src, n_nodes, n_edges, rowptr);
   return check_launch(3);
+}
+
+extern "C" int gnncca_segment_agg(const float* rows, const int32_t* rowptr, int64_t n_nodes, int32_t width, int32_t agg, float* out,
+                                  void* stream) {
+  if (n_nodes < 0 || width <= 0 || agg < GNNCCA_AGG_SUM || agg > GNNCCA_AGG_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (n_nodes == 0) return GNNCCA_OK;
+  if (!rowptr || !out) return GNNCCA_ERR_BAD_ARG;
+  segment_agg_kernel<<<(unsigned)ceil_div(n_nodes, (int64_t)8), 256, 0, (cudaStream_t)stream>>>(rows, rowptr, n_nodes, width, agg, out);
+  return check_launch();
 }
 
 extern "C" int gnncca_permute_rows(const float* in, float* out, const int32_t* perm, int64_t n_rows, int32_t width,

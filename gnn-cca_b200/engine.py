@@ -344,6 +344,86 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
 
 
 # ------------------------------------------------------------------------------------------------------------
+# stand-alone MetaLayer / NodeModel forwards (models/mpn.py:32-54, 97-101) on caller-supplied tensors
+# ------------------------------------------------------------------------------------------------------------
+def _inference_only(module, what: str) -> None:
+    if torch.is_grad_enabled() and any(p.requires_grad for p in module.parameters()):
+        raise NotImplementedError("stand-alone %s.forward is inference-only (use torch.no_grad()); training runs through MOTMPNet.forward" % what)
+
+
+def _agg_name(node_model) -> str:
+    name = node_model.node_agg_fn
+    if not isinstance(name, str) or name not in _lib.AGG:
+        raise NotImplementedError("NodeModel.node_agg_fn must be 'sum', 'mean' or 'max' (the reference passes a lambda over torch_scatter; "
+                                  "gnn-cca_b200 takes the name, models/mpn.py:192-202)")
+    return name
+
+
+def meta_layer_forward(meta, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor):
+    """``MetaLayer.forward`` (mpn.py:32-54): edge model on the old nodes, node model on the new edges, aggregation by ``row``."""
+    lib = _lib.load()
+    _require_cuda(x, "x")
+    _require_cuda(edge_attr, "edge_attr")
+    _inference_only(meta, "MetaLayer")
+    em, nm = meta.edge_model.edge_mlp, meta.node_model.node_mlp
+    if len(em.layer_specs) != 1 or len(nm.layer_specs) != 1 or not em.layer_specs[0].relu or not nm.layer_specs[0].relu \
+            or em.layer_specs[0].bn is not None or nm.layer_specs[0].bn is not None:
+        raise NotImplementedError("fused step: edge_model / node_model must be one Linear + ReLU each")
+    f_edge, f_node = em.layer_specs[0].out_dim, nm.layer_specs[0].out_dim
+    K, EIN = int(x.size(1)), int(edge_attr.size(1))
+    if (f_node, f_edge) != (32, 6) or K not in (32, 64) or EIN not in (6, 12):
+        raise NotImplementedError("fused step kernels are built for node / edge latent widths 32 / 6 (x: 32 or 64 columns, edge_attr: 6 or 12)")
+    if em.layer_specs[0].in_dim != 2 * K + EIN or nm.layer_specs[0].in_dim != K + f_edge:
+        raise ValueError("input widths do not match the update MLPs: x %d, edge_attr %d vs edge_mlp in %d, node_mlp in %d"
+                         % (K, EIN, em.layer_specs[0].in_dim, nm.layer_specs[0].in_dim))
+    N, E = int(x.size(0)), int(edge_index.size(1))
+    if int(edge_attr.size(0)) != E:
+        raise ValueError("edge_attr has %d rows but edge_index has %d edges" % (edge_attr.size(0), E))
+    dev = x.device
+    rn, re = K == 64, EIN == 12
+    cfg = _lib.MpCfg(f_node=32, f_edge=6, cls_hidden=4, agg=_lib.AGG[_agg_name(meta.node_model)], reattach_nodes=int(rn), reattach_edges=int(re),
+                     math=_lib.MATH_FP32, edge_phase=0)
+    w = _lib.MpWeights(w_edge=em.linear(0).weight.data_ptr(), b_edge=em.linear(0).bias.data_ptr(), w_node=nm.linear(0).weight.data_ptr(),
+                       b_node=nm.linear(0).bias.data_ptr(), w_c1=0, b_c1=0, bn_weight=0, bn_bias=0, bn_mean=0, bn_var=0, w_c2=0, b_c2=0, bn_eps=0.0, pad_=0)
+    plan = GraphPlan(edge_index, N).resolve()
+    h0 = x[:, :32].contiguous() if rn else None
+    h = x[:, 32:].contiguous() if rn else x.contiguous()
+    ea = plan.to_sorted(edge_attr.contiguous())
+    e0 = ea[:, :6].contiguous() if re else None
+    e = ea[:, 6:].contiguous() if re else ea
+    P = torch.empty((N, 8), dtype=torch.float32, device=dev)
+    Q = torch.empty((N, 8), dtype=torch.float32, device=dev)
+    R = torch.empty((N, 32), dtype=torch.float32, device=dev)
+    e_out = torch.empty((E, 6), dtype=torch.float32, device=dev)
+    h_out = torch.empty((N, 32), dtype=torch.float32, device=dev)
+    if N > 0:
+        _lib.check(lib.gnncca_node_project(C.byref(cfg), C.byref(w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _stream()),
+                   "node_project")
+    ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(cfg), N, E))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    _lib.check(lib.gnncca_mp_step_fwd(C.byref(cfg), C.byref(w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E, _lib.ptr(P),
+                                      _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0), _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), 0, 0, _lib.ptr(ws),
+                                      ws_bytes, _stream()), "mp_step_fwd")
+    return h_out, plan.to_caller(e_out)
+
+
+def node_model_forward(node_model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor) -> torch.Tensor:
+    """``NodeModel.forward`` (mpn.py:97-101)."""
+    lib = _lib.load()
+    _require_cuda(x, "x")
+    _require_cuda(edge_attr, "edge_attr")
+    _inference_only(node_model, "NodeModel")
+    agg = _lib.AGG[_agg_name(node_model)]
+    N = int(x.size(0))
+    plan = GraphPlan(edge_index, N).resolve()
+    row = plan.src.long()                                     # sorted sources
+    msgs = mlp_forward(node_model.node_mlp, torch.cat([x.index_select(0, row), plan.to_sorted(edge_attr.contiguous())], dim=1))
+    out = torch.empty((N, msgs.size(1)), dtype=torch.float32, device=x.device)
+    _lib.check(lib.gnncca_segment_agg(_lib.ptr(msgs), _lib.ptr(plan.rowptr), N, int(msgs.size(1)), agg, _lib.ptr(out), _stream()), "segment_agg")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
 # frame-blocked execution of very large batches (BASELINE config 4: 4096 frames of 8 x 64 detections, 939.5 M edges)
 # ------------------------------------------------------------------------------------------------------------
 BLOCK_EDGES = int(os.environ.get("GNNCCA_BLOCK_EDGES", str(16 << 20)))     # target edges per block of frames

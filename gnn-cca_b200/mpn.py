@@ -30,8 +30,12 @@ class MetaLayer(nn.Module):
                 item.reset_parameters()
 
     def forward(self, x, edge_index, edge_attr):
-        raise NotImplementedError("gnn-cca_b200 runs MetaLayer only fused inside MOTMPNet.forward "
-                                  "(edge update + node update + classifier are one kernel)")
+        """One message-passing step on caller-supplied tensors (mpn.py:32-54): ``x`` [N, 32 | 64] (64 = cat(initial, current),
+        mpn.py:285), ``edge_attr`` [E, 6 | 12], ``edge_index`` [2, E] int64 in any order.  Returns (x', edge_attr') like the
+        reference.  Runs the same fused kernels as ``MOTMPNet.forward`` (gnncca_node_project + gnncca_mp_step_fwd);
+        inference only -- training goes through ``MOTMPNet.forward``."""
+        from . import engine
+        return engine.meta_layer_forward(self, x, edge_index, edge_attr)
 
     def __repr__(self):
         return '{}(edge_model={}, node_model={})'.format(self.__class__.__name__, self.edge_model, self.node_model)
@@ -45,7 +49,11 @@ class EdgeModel(nn.Module):
         self.edge_mlp = edge_mlp
 
     def forward(self, source, target, edge_attr):
-        raise NotImplementedError("EdgeModel is fused into gnncca_mp_step_fwd; call MOTMPNet.forward")
+        """``edge_mlp(cat[source, target, edge_attr])`` (mpn.py:67-69) on caller-supplied per-edge rows, through the dense FP32
+        kernels (inference only; inside ``MOTMPNet.forward`` this is phase A of the fused step kernel and nothing of width 70
+        exists)."""
+        from . import engine
+        return engine.mlp_forward(self.edge_mlp, torch.cat([source, target, edge_attr], dim=1))
 
 
 class NodeModel(nn.Module):
@@ -57,7 +65,10 @@ class NodeModel(nn.Module):
         self.node_agg_fn = node_agg_fn
 
     def forward(self, x, edge_index, edge_attr):
-        raise NotImplementedError("NodeModel is fused into gnncca_mp_step_fwd; call MOTMPNet.forward")
+        """``agg_row(node_mlp(cat[x[row], edge_attr]))`` (mpn.py:97-101) on caller-supplied tensors: the MLP through the dense FP32
+        kernels, the aggregation through gnncca_segment_agg on the source-sorted rows (deterministic; inference only)."""
+        from . import engine
+        return engine.node_model_forward(self, x, edge_index, edge_attr)
 
 
 class MLPGraphIndependent(nn.Module):

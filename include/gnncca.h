@@ -71,6 +71,13 @@ int gnncca_csr_from_edge_index(const int64_t* edge_index, int64_t n_nodes, int64
 int gnncca_csr_from_edge_rows(const int64_t* row, const int64_t* col, int64_t node_base, int64_t n_nodes, int64_t n_edges,
                               int32_t* src, int32_t* dst, int32_t* rowptr, int32_t* flags, void* stream);
 
+/* torch_scatter's scatter_add / scatter_mean / scatter_max(...)[0] along dim 0 (models/mpn.py:196-202; third-party,
+ * 2.0.8) for SOURCE-SORTED rows: out[v][c] = agg over rows[rowptr[v] .. rowptr[v+1]) of column c, folded in row order
+ * (deterministic, no atomics).  Empty segments give 0; mean divides by max(count, 1).  agg = GNNCCA_AGG_*.
+ * The fused step kernel does this inside its phase B; this entry is the stand-alone NodeModel.forward path. */
+int gnncca_segment_agg(const float* rows, const int32_t* rowptr, int64_t n_nodes, int32_t width, int32_t agg, float* out,
+                       void* stream);
+
 /* Bytes of scratch gnncca_csr_sort needs. */
 int64_t gnncca_csr_sort_workspace_bytes(int64_t n_nodes, int64_t n_edges);
 
