@@ -7,7 +7,7 @@ import os
 import threading
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libgnncca.so")
+LIB_PATH = os.environ.get("GNNCCA_LIB") or os.path.join(PKG, "libgnncca.so")     # GNNCCA_LIB: an experimental build (tools/variant.sh)
 
 OK, ERR_BAD_ARG, ERR_UNSUPPORTED, ERR_LAUNCH, ERR_WORKSPACE = 0, -1, -2, -3, -4
 AGG = {"sum": 0, "mean": 1, "max": 2}
@@ -61,6 +61,8 @@ SIGNATURES = {
                                      vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_mp_step_fwd_attr": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, i64, i64, vp, vp, vp, vp, i32, vp, vp, vp, vp,
                                           vp, vp, vp, vp, i64, vp]),
+    "gnncca_mp_step_fwd_next": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, i64, i64, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp,
+                                          vp, vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_mp_fused_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i32, vp, i64, vp, vp, vp, vp, vp, i64, i64,
                                       vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp]),
     "gnncca_mpn_forward_frames": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp,

@@ -17,8 +17,10 @@
 //            a partition whose phase breaks the 16-byte alignment, are loaded through registers.
 //   phase A  thread per edge pair: gathers of the P[src] / Q[dst] rows, edge update and classifier with packed FFMA2 over OUTPUT pairs
 //            (weight pair = aligned LDS result, edge value = broadcast scalar), e' written once (STG.128) and staged row-major.
-//   phase B  messages on the tensor cores: m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges] as two mma.sync m16n8k8 (tf32
-//            operands split 3xTF32: fp32-level accuracy); the two k-slots the FE = 6 edge features leave free carry the R[src] row; ReLU and
+//   phase B  messages on the tensor cores: m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges], two m-tiles.  Operands are
+//            split into tf32 prefix + exact rest; hi.hi runs as mma.sync m16n8k8 tf32, the two cross terms hi.lo + lo.hi share ONE
+//            m16n8k16 bf16 mma (their factors of size 2^-11 need 8 bits: fp32-level accuracy at 4 instead of 6 tensor instructions
+//            per 8 edges -- the loop is bound by the mma.sync issue rate); the two k-slots the FE = 6 edge features leave free carry the R[src] row; ReLU and
 //            the running sum / max are applied to the D fragment, lanes folded once per piece (a piece = the edges of one source inside
 //            the chunk; boundaries from one ballot over the staged source ids, skipped when the chunk has a single source).
 //   - a segment that lies inside one chunk is finished and written by its warp;
@@ -50,6 +52,7 @@ struct StepParams {
   const float* e0; const float* e_in; float* e_out; float* h_out; float* logits;
   gnncca_mp_weights w;
   int agg, nf;
+  int edge_row;          // row length of w_edge: 2 K + EIN
   int num_tiles;
   float* chunk_part;     // [num_tiles * NWARP][2][FN]  slot 0: piece of a segment begun in an earlier chunk, slot 1: open tail
   int phase;             // position of local edge 0 inside a tile of the GLOBAL edge numbering (edge-partitioned graphs)
@@ -57,6 +60,9 @@ struct StepParams {
   // ATTR variants: the encoded edge features e0 = ReLU(W_enc attr + b_enc) (mpn.py:116-126, 4 -> FE) are computed here from
   // the raw attributes (16 B/edge) instead of being written by one kernel and read back by this one (2 x 24 B/edge)
   const float* attr; const float* w_enc; const float* b_enc;
+  // projections of the NEXT step (gnncca_mp_step_fwd_next): the fold kernel, which visits every node once the step kernel is done, also
+  // computes P | Q | R of the updated latents -- the stand-alone node_project launch between two steps disappears.  May alias P, Q, R.
+  float* Pn; float* Qn; float* Rn; const float* h0;
 };
 
 
@@ -227,6 +233,18 @@ __device__ __forceinline__ void mma_tf32_acc(float (&d)[4], const float (&a)[4],
                : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
                  "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
 }
+// mma.sync m16n8k16 (bf16 operands, fp32 accumulate), zero C: d = a . b
+__device__ __forceinline__ void mma_bf16_d(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+               : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.f));
+}
+// two fp32 values rounded to bf16 and packed: `lo` in bits 0..15 (the lower k index of an mma fragment register)
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 // the tf32 prefix of an fp32 value (what the tensor core reads of it); value - prefix is exact in fp32
 __device__ __forceinline__ float tf32_prefix(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
 
@@ -294,7 +312,7 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   // phase B operands: the message GEMM runs transposed, m^T [32 features x 8 edges] = W_ne^T [32 x 8] . e'^T [8 x 8 edges], as two
   // m16n8k8 tiles.  k-slot t carries edge feature 2t and k-slot t + 4 feature 2t + 1 (a lane reads ONE float2 of the staged row); the
-  // slots beyond FE are zero.  3xTF32: operands split into their tf32 prefix and the exact rest, lo.hi + hi.lo + hi.hi.
+  // slots beyond FE are zero.  Operands are split into their tf32 prefix and the exact rest: hi.hi in tf32, lo.hi + hi.lo in one bf16 mma.
   // The 16 weight fragment registers of a lane are parked in shared memory ([4][32 lanes] float4: conflict-free LDS.128) and
   // fetched at the start of each phase B, so that they are not live (and spilled) across phase A.
   const int g = lane >> 2, t = lane & 3;
@@ -309,7 +327,10 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
         hi4[q] = tf32_prefix(w); lo4[q] = w - hi4[q];
       }
       s_afrag[2 * i][lane] = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
-      s_afrag[2 * i + 1][lane] = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
+      // correction operand (bf16 m16n8k16): k-slots 0..7 hold W_hi (paired with the rests e'_lo), 8..15 hold W_lo (paired with e'_hi);
+      // a register = (k = 2t, 2t + 1) of one row: q = 0, 2 are row g, q = 1, 3 row g + 8
+      s_afrag[2 * i + 1][lane] = make_float4(__uint_as_float(pack_bf16(hi4[0], hi4[2])), __uint_as_float(pack_bf16(hi4[1], hi4[3])),
+                                             __uint_as_float(pack_bf16(lo4[0], lo4[2])), __uint_as_float(pack_bf16(lo4[1], lo4[3])));
     }
   }
   __syncthreads();
@@ -327,6 +348,9 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
     if (t0 < t_end && fill_slot<FE, REATT_E, ATTR>(p, t0, warp * CHUNK, lane, ring + st * SL::BYTES, wbar + st, bulk_ok)) isbulk |= 1u << st;
   }
 
+#ifdef GNNCCA_EXP_STAGGER   // timing experiment: spread the warps of an SM over one tile period instead of starting them in step
+  __nanosleep((((blockIdx.x / 148) % 3) * 8 + warp) * GNNCCA_EXP_STAGGER);
+#endif
   int it = 0;
   for (int tile = t_begin; tile < t_end; ++tile, ++it) {
     const int base = tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition (E < 2^31 - 2 TILE)
@@ -394,7 +418,11 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
       float2 ea[FE / 2], eb[FE / 2];
       {
         // invalid edges (src = -1, only in the chunks at the ends of the edge range) read node 0's rows: finite values, never stored
+#ifdef GNNCCA_EXP_NOGATHER      // timing experiment (tools/variant.sh): every gather hits one row
+        const int sa = 0, sb = 0, da = 0, db = 0;
+#else
         const int sa = max(cur.sa, 0), sb = max(cur.sb, 0), da = max(cur.da, 0), db = max(cur.db, 0);
+#endif
         const float4 pa0 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8), pa1 = *reinterpret_cast<const float4*>(p.P + (int64_t)sa * 8 + 4);
         const float4 qa0 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8), qa1 = *reinterpret_cast<const float4*>(p.Q + (int64_t)da * 8 + 4);
         float4 pb0 = pa0, pb1 = pa1;      // the pair shares its source except across a segment boundary
@@ -480,6 +508,9 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
       }
     }
     if (!NODE || p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
+#ifdef GNNCCA_EXP_NOB
+    continue;
+#endif
     __syncwarp();
     // ------------------------------ phase B: messages of 8 edges per mma ------------------------------
     // The chunk is cut into 8-edge blocks aligned to the global numbering.  A piece (edges of one source inside the chunk) walks
@@ -488,11 +519,11 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
     // ReLU output is >= 0, so 0 is neutral for sum and max alike).  Lanes are folded once per piece.
     {
       if (a < b) {
-        float a_lo[2][4];
+        uint32_t a_c[2][4];      // correction fragments (bf16 pairs)
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
           const float4 l4 = s_afrag[2 * i + 1][lane];
-          a_lo[i][0] = l4.x; a_lo[i][1] = l4.y; a_lo[i][2] = l4.z; a_lo[i][3] = l4.w;
+          a_c[i][0] = __float_as_uint(l4.x); a_c[i][1] = __float_as_uint(l4.y); a_c[i][2] = __float_as_uint(l4.z); a_c[i][3] = __float_as_uint(l4.w);
         }
         unsigned long long mask = 1ull << (a - c0);      // bit i: edge c0 + i opens a piece; sorted sources: equal ends = one piece
         if (s_src[a] != s_src[b - 1]) {
@@ -545,17 +576,23 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
           int bstep = 2 * t < FE ? 8 * FE * 4 : 0;               // bytes per block
           asm volatile("" : "+r"(bstep));                        // a register stride: one add per block instead of a re-selected constant
 #pragma unroll 2
+#ifdef GNNCCA_EXP_NOMSG
+          if (false)
+#endif
           for (int kb = kb0; kb < j1; kb += 8, x += 8, bp = reinterpret_cast<const float2*>(reinterpret_cast<const char*>(bp) + bstep)) {
             float2 v = make_float2(0.f, 0.f);
             if (x < span) v = *bp;
             const float bh0 = tf32_prefix(v.x), bh1 = tf32_prefix(v.y);
-            const float bl0 = v.x - bh0, bl1 = v.y - bh1;
+            const uint32_t cb0 = pack_bf16(v.x - bh0, v.y - bh1), cb1 = pack_bf16(bh0, bh1);      // (e'_lo pair | e'_hi pair) of features 2t, 2t + 1
             float d[2][4];
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-              mma_tf32_dc(d[i], a_lo[i], bh0, bh1, 0.f, 0.f, 0.f, 0.f);
-              mma_tf32_acc(d[i], a_hi[i], bl0, bl1);
-              mma_tf32_acc(d[i], a_hi[i], bh0, bh1);
+#ifdef GNNCCA_EXP_1MMA
+              mma_tf32_dc(d[i], a_hi[i], bh0, bh1, __uint_as_float(cb0), __uint_as_float(cb1), 0.f, 0.f);
+#else
+              mma_bf16_d(d[i], a_c[i], cb0, cb1);              // W_hi . e'_lo + W_lo . e'_hi
+              mma_tf32_acc(d[i], a_hi[i], bh0, bh1);           // + W_hi . e'_hi (+ the R row)
+#endif
             }
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
@@ -563,8 +600,15 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[i][q] = fmaxf(acc[i][q], d[i][q]);    // max(acc, relu(d)) with acc >= 0
               } else {
+#ifdef GNNCCA_RELU_FMNMX
                 const float2 s01 = pk::fadd2(make_float2(acc[i][0], acc[i][1]), pk::relu2(make_float2(d[i][0], d[i][1])));
                 const float2 s23 = pk::fadd2(make_float2(acc[i][2], acc[i][3]), pk::relu2(make_float2(d[i][2], d[i][3])));
+#else
+                // ReLU on the FMA pipe: d + |d| = 2 relu(d) exactly (FADD with an |.| operand; FMNMX issues on the half-rate ALU pipe, which
+                // bounds this loop).  The running sums are therefore 2 x the aggregate; the factor is removed (exactly) when the piece is folded.
+                const float2 s01 = pk::fadd2(make_float2(acc[i][0], acc[i][1]), make_float2(d[i][0] + fabsf(d[i][0]), d[i][1] + fabsf(d[i][1])));
+                const float2 s23 = pk::fadd2(make_float2(acc[i][2], acc[i][3]), make_float2(d[i][2] + fabsf(d[i][2]), d[i][3] + fabsf(d[i][3])));
+#endif
                 acc[i][0] = s01.x; acc[i][1] = s01.y; acc[i][2] = s23.x; acc[i][3] = s23.y;
               }
             }
@@ -575,6 +619,9 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
             float x = comb<IS_MAX>(acc[q >> 1][2 * (q & 1)], acc[q >> 1][2 * (q & 1) + 1]);
             x = comb<IS_MAX>(x, __shfl_xor_sync(0xffffffffu, x, 1));
             x = comb<IS_MAX>(x, __shfl_xor_sync(0xffffffffu, x, 2));
+#ifndef GNNCCA_RELU_FMNMX
+            if (!IS_MAX) x *= 0.5f;
+#endif
             v4[q] = x;
           }
           const float mine = t == 0 ? v4[0] : t == 1 ? v4[1] : t == 2 ? v4[2] : v4[3];     // lane (g, t) writes feature g + 8 t
@@ -591,32 +638,74 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
 // Second kernel of a step: one warp per node.  Nodes without out-edges aggregate to 0 (torch_scatter semantics); a node whose
 // segment crosses chunk boundaries gets the fold of its pieces in chunk order (first chunk's open tail, then one piece per
 // later chunk); everything else was written by the step kernel.
+// PROJECT: the warp then computes the per-node projections of the next step from the node's final latents (same arithmetic and FMA
+// order as node_project_kernel: acc = bias, k ascending): lane o produces output o and, for o < 12, output 32 + o of P (6) | Q (6) | R (32).
+template <bool PROJECT>
 __global__ void __launch_bounds__(256) mp_step_fold_kernel(const StepParams p) {
+  constexpr int FE = 6, OUT = 2 * FE + FN;
+  extern __shared__ float fold_smem[];           // PROJECT: wt [K][OUT] | bias [OUT]
   const int lane = threadIdx.x & 31;
-  const int64_t v = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (v >= p.n_nodes) return;
   if (p.guard != nullptr && (p.guard[0] | p.guard[1]) != 0) return;
-  const int rs = p.rowptr[v], re = p.rowptr[v + 1];
-  if (re <= rs) { p.h_out[v * FN + lane] = 0.f; return; }
-  const int64_t c0 = ((int64_t)rs + p.phase) / CHUNK, c1 = ((int64_t)re - 1 + p.phase) / CHUNK;
-  if (c0 == c1) return;
+  const int K = p.nf * FN;
+  float* wt = fold_smem;
+  float* bias = fold_smem + K * OUT;
+  if (PROJECT) {
+    const int edge_row = p.edge_row, node_row = K + FE;
+    for (int idx = threadIdx.x; idx < K * OUT; idx += blockDim.x) {
+      const int k = idx / OUT, o = idx - k * OUT;
+      float v;
+      if (o < FE) v = p.w.w_edge[o * edge_row + k];                       // source block
+      else if (o < 2 * FE) v = p.w.w_edge[(o - FE) * edge_row + K + k];   // target block
+      else v = p.w.w_node[(o - 2 * FE) * node_row + k];                   // node block of the node model
+      wt[idx] = v;
+    }
+    for (int o = threadIdx.x; o < OUT; o += blockDim.x) bias[o] = (o < FE) ? p.w.b_edge[o] : (o < 2 * FE ? 0.f : p.w.b_node[o - 2 * FE]);
+    __syncthreads();
+  }
   const bool is_max = p.agg == GNNCCA_AGG_MAX;
-  // sums are carried in double across the pieces (a handful of adds per node): the rounding of a long segment is then that
-  // of its 64-edge chunks alone
-  double tot = p.chunk_part[(c0 * 2 + 1) * FN + lane];
-  int64_t c = c0 + 1;
-  for (; c <= c1; c += 8) {            // up to eight loads in flight, folded in order
-    float pv[8];
+  const int64_t wstride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t v = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); v < p.n_nodes; v += wstride) {
+    const int rs = p.rowptr[v], re = p.rowptr[v + 1];
+    float out;
+    bool written = false;       // does h_out[v] already hold the value (written by the step kernel)?
+    if (re <= rs) out = 0.f;
+    else {
+      const int64_t c0 = ((int64_t)rs + p.phase) / CHUNK, c1 = ((int64_t)re - 1 + p.phase) / CHUNK;
+      if (c0 == c1) { written = true; out = PROJECT ? p.h_out[v * FN + lane] : 0.f; }
+      else {
+        // sums are carried in double across the pieces (a handful of adds per node): the rounding of a long segment is then that
+        // of its 64-edge chunks alone
+        double tot = p.chunk_part[(c0 * 2 + 1) * FN + lane];
+        for (int64_t c = c0 + 1; c <= c1; c += 8) {            // up to eight loads in flight, folded in order
+          float pv[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) pv[u] = c + u <= c1 ? p.chunk_part[((c + u) * 2) * FN + lane] : (is_max ? -INFINITY : 0.f);
+          for (int u = 0; u < 8; ++u) pv[u] = c + u <= c1 ? p.chunk_part[((c + u) * 2) * FN + lane] : (is_max ? -INFINITY : 0.f);
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      if (c + u <= c1) tot = is_max ? fmax(tot, (double)pv[u]) : tot + pv[u];
+          for (int u = 0; u < 8; ++u) {
+            if (c + u <= c1) tot = is_max ? fmax(tot, (double)pv[u]) : tot + pv[u];
+          }
+        }
+        out = (float)tot;
+        if (p.agg == GNNCCA_AGG_MEAN) out = out / (float)(re - rs);      // scatter_mean: sum / count, in fp32 like finalize_node
+      }
+    }
+    if (!written) p.h_out[v * FN + lane] = out;
+    if (PROJECT) {
+      const float h0v = p.nf == 2 ? p.h0[v * FN + lane] : 0.f;           // cat(initial, current), mpn.py:285
+      float acc0 = bias[lane], acc1 = lane < OUT - 32 ? bias[32 + lane] : 0.f;
+      for (int k = 0; k < K; ++k) {
+        const float hk = (p.nf == 2 && k < FN) ? __shfl_sync(0xffffffffu, h0v, k) : __shfl_sync(0xffffffffu, out, k & (FN - 1));
+        acc0 = fmaf(hk, wt[k * OUT + lane], acc0);
+        if (lane < OUT - 32) acc1 = fmaf(hk, wt[k * OUT + 32 + lane], acc1);
+      }
+      // outputs 0..5 P, 6..11 Q, 12..43 R; the two padding lanes of the 8-float P / Q rows are zeroed
+      if (lane < FE) p.Pn[v * 8 + lane] = acc0;
+      else if (lane < 2 * FE) p.Qn[v * 8 + lane - FE] = acc0;
+      else p.Rn[v * FN + lane - 2 * FE] = acc0;
+      if (lane < OUT - 32) p.Rn[v * FN + 32 - 2 * FE + lane] = acc1;
+      if (lane >= 30) { p.Pn[v * 8 + lane - 24] = 0.f; p.Qn[v * 8 + lane - 24] = 0.f; }
     }
   }
-  float out = (float)tot;
-  if (p.agg == GNNCCA_AGG_MEAN) out = out / (float)(re - rs);      // scatter_mean: sum / count, in fp32 like finalize_node
-  p.h_out[v * FN + lane] = out;
 }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -663,7 +752,14 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
 #undef GNNCCA_STEP
 #undef GNNCCA_STEP_N
   if (sp.h_out == nullptr) return check_launch();
-  mp_step_fold_kernel<<<(unsigned)ceil_div(sp.n_nodes, (int64_t)8), 256, 0, st>>>(sp);
+  if (sp.Pn != nullptr) {     // fold + the next step's projections: weights staged once per block, blocks loop over the nodes
+    const int K = sp.nf * FN;
+    const size_t smem = sizeof(float) * (K * (2 * FE + FN) + (2 * FE + FN));
+    const unsigned blocks = (unsigned)min(ceil_div(sp.n_nodes, (int64_t)8), (int64_t)kNumSMs * 8);
+    mp_step_fold_kernel<true><<<blocks, 256, smem, st>>>(sp);
+  } else {
+    mp_step_fold_kernel<false><<<(unsigned)ceil_div(sp.n_nodes, (int64_t)8), 256, 0, st>>>(sp);
+  }
   return check_launch(2);
 }
 
@@ -673,11 +769,18 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
                         const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P,
                         const float* Q, const float* R, const float* e0, const float* e_in, float* e_out,
                         float* h_out, float* logits, const int32_t* guard_flags, void* workspace, int64_t workspace_bytes, void* stream,
-                        const float* attr, const float* w_enc, const float* b_enc) {
+                        const float* attr, const float* w_enc, const float* b_enc,
+                        const float* h0 = nullptr, float* Pn = nullptr, float* Qn = nullptr, float* Rn = nullptr) {
   if (!cfg || !w || n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX - 2 * TILE) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
+  const bool next = Pn != nullptr || Qn != nullptr || Rn != nullptr;
+  if (next && (!Pn || !Qn || !Rn || !h_out || (cfg->reattach_nodes && !h0) || ((((uintptr_t)Pn | (uintptr_t)Qn) & 15) != 0))) return GNNCCA_ERR_BAD_ARG;
   if (n_edges == 0) {          // nodes without out-edges aggregate to 0 (torch_scatter semantics)
-    if (h_out && n_nodes > 0) return check_cuda(cudaMemsetAsync(h_out, 0, sizeof(float) * n_nodes * FN, st));
+    if (h_out && n_nodes > 0) {
+      const int rc = check_cuda(cudaMemsetAsync(h_out, 0, sizeof(float) * n_nodes * FN, st));
+      if (rc || !next) return rc;
+      return gnncca_node_project(cfg, w, h0, h_out, n_nodes, Pn, Qn, Rn, stream);
+    }
     return GNNCCA_OK;
   }
   if (!rowptr || !src || !dst || !P || !Q || !R || !w->w_edge || !w->w_node) return GNNCCA_ERR_BAD_ARG;
@@ -695,7 +798,9 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
   sp.P = P; sp.Q = Q; sp.R = R; sp.e0 = e0; sp.e_in = e_in; sp.e_out = e_out; sp.h_out = h_out; sp.logits = logits;
   sp.guard = guard_flags;
   sp.attr = attr; sp.w_enc = w_enc; sp.b_enc = b_enc;
+  sp.Pn = Pn; sp.Qn = Qn; sp.Rn = Rn; sp.h0 = h0;
   sp.w = *w; sp.agg = cfg->agg; sp.nf = cfg->reattach_nodes ? 2 : 1;
+  sp.edge_row = 2 * sp.nf * FN + (cfg->reattach_edges ? 2 : 1) * cfg->f_edge;
   if (cfg->edge_phase < 0 || cfg->edge_phase >= TILE) return GNNCCA_ERR_BAD_ARG;
   sp.phase = cfg->edge_phase;
   sp.num_tiles = (int)ceil_div(n_edges + sp.phase, TILE);
@@ -723,4 +828,16 @@ extern "C" int gnncca_mp_step_fwd_attr(const gnncca_mp_cfg* cfg, const gnncca_mp
   if (!edge_attr && n_edges > 0) return GNNCCA_ERR_BAD_ARG;
   return mp_step_impl(cfg, w, rowptr, src, dst, n_nodes, n_edges, P, Q, R, nullptr, e_in, e_out, h_out, logits, guard_flags, workspace,
                       workspace_bytes, stream, edge_attr, w_enc_edge, b_enc_edge);
+}
+
+extern "C" int gnncca_mp_step_fwd_next(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, const int32_t* src,
+                                       const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P, const float* Q, const float* R,
+                                       const float* edge_attr, int32_t edge_in_dim, const float* w_enc_edge, const float* b_enc_edge,
+                                       const float* e0, const float* e_in, float* e_out, float* h_out, float* logits, const float* h0,
+                                       float* P_next, float* Q_next, float* R_next, const int32_t* guard_flags, void* workspace,
+                                       int64_t workspace_bytes, void* stream) {
+  if (edge_attr != nullptr && edge_in_dim != FA) return GNNCCA_ERR_UNSUPPORTED;
+  if (!h_out || !P_next || !Q_next || !R_next) return GNNCCA_ERR_BAD_ARG;
+  return mp_step_impl(cfg, w, rowptr, src, dst, n_nodes, n_edges, P, Q, R, edge_attr ? nullptr : e0, e_in, e_out, h_out, logits, guard_flags,
+                      workspace, workspace_bytes, stream, edge_attr, w_enc_edge, b_enc_edge, h0, P_next, Q_next, R_next);
 }

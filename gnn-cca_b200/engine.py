@@ -301,21 +301,32 @@ def forward_inference(model, x: torch.Tensor, edge_index: torch.Tensor, edge_att
         keep = return_latents or model.reattach_initial_edges
         le = enc_e.linear(0) if fold else None
         for step in range(1, L + 1):
-            _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P),
-                                               _lib.ptr(Q), _lib.ptr(R), _stream()), "node_project")
+            if step == 1:      # later steps: the previous step's fold launch has already projected its output (gnncca_mp_step_fwd_next)
+                _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P),
+                                                   _lib.ptr(Q), _lib.ptr(R), _stream()), "node_project")
             last = step == L
             classify = step >= first_class_step
             h_out = None if (last and not return_latents) else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
             logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if classify else None
             dead_e = last and h_out is None and logits is not None       # e^L of an inference forward is never read
-            if fold and (step == 1 or model.reattach_initial_edges):
+            use_attr = fold and (step == 1 or model.reattach_initial_edges)
+            if use_attr:
                 e_out = None if dead_e else (torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e)
+            else:
+                e_out = None if dead_e else (torch.empty_like(e) if (keep and (step == 1 or return_latents)) else e)   # in place unless e0 must survive
+            if not last:       # the step + the projections of step + 1, in place over P / Q / R
+                _lib.check(lib.gnncca_mp_step_fwd_next(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
+                                                       _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea_sorted) if use_attr else 0, 4,
+                                                       _lib.ptr(le.weight) if use_attr else 0, _lib.ptr(le.bias) if use_attr else 0,
+                                                       _lib.ptr(e0) if (model.reattach_initial_edges and not use_attr) else 0, _lib.ptr(e), _lib.ptr(e_out),
+                                                       _lib.ptr(h_out), _lib.ptr(logits), _lib.ptr(h0), _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), guard,
+                                                       _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd_next")
+            elif use_attr:
                 _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
                                                        _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea_sorted), 4,
                                                        _lib.ptr(le.weight), _lib.ptr(le.bias), _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out),
                                                        _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd_attr")
             else:
-                e_out = None if dead_e else (torch.empty_like(e) if (keep and (step == 1 or return_latents)) else e)   # in place unless e0 must survive
                 _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src),
                                                   _lib.ptr(plan.dst), N, E, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
                                                   _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e), _lib.ptr(e_out),
@@ -565,14 +576,22 @@ def forward_blocked(model, x: torch.Tensor, edge_index: torch.Tensor, edge_attr:
         h0 = h
         ea = edge_attr[e0:e1]
         hbuf = 1
+        _lib.check(lib.gnncca_node_project(cfg, w, h0.data_ptr(), h.data_ptr(), nn_, _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), st), "node_project")
         for step in range(1, L + 1):
-            _lib.check(lib.gnncca_node_project(cfg, w, h0.data_ptr(), h.data_ptr(), nn_, _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), st), "node_project")
             last = step == L
             h_out = None if last else wsp.h[hbuf][:nn_]
             lg = logits[step - first][e0:e1] if step >= first else None
             dead_e = last and lg is not None
-            if step == 1 or model.reattach_initial_edges:
-                e_in = None if step == 1 else wsp.e
+            use_attr = step == 1 or model.reattach_initial_edges
+            e_in = None if step == 1 else wsp.e
+            if not last:      # the step + (in its fold launch) the projections of step + 1, in place over P / Q / R
+                _lib.check(lib.gnncca_mp_step_fwd_next(cfg, w, _lib.ptr(wsp.rowptr), _lib.ptr(wsp.src), _lib.ptr(wsp.dst), nn_, ne_,
+                                                       _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), ea.data_ptr() if use_attr else 0, 4,
+                                                       _lib.ptr(le.weight) if use_attr else 0, _lib.ptr(le.bias) if use_attr else 0, 0,
+                                                       _lib.ptr(e_in), _lib.ptr(wsp.e), _lib.ptr(h_out), _lib.ptr(lg), h0.data_ptr(),
+                                                       _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), guard, _lib.ptr(wsp.ws), wsp.ws_bytes, st),
+                           "mp_step_fwd_next")
+            elif use_attr:
                 _lib.check(lib.gnncca_mp_step_fwd_attr(cfg, w, _lib.ptr(wsp.rowptr), _lib.ptr(wsp.src), _lib.ptr(wsp.dst), nn_, ne_,
                                                        _lib.ptr(wsp.P), _lib.ptr(wsp.Q), _lib.ptr(wsp.R), ea.data_ptr(), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
                                                        _lib.ptr(e_in), 0 if dead_e else _lib.ptr(wsp.e), _lib.ptr(h_out), _lib.ptr(lg), guard,

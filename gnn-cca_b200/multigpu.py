@@ -17,6 +17,7 @@ structure of ``MOTMPNet.forward`` (models/mpn.py:250-299):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -114,17 +115,25 @@ def forward_edge_partitioned(model, x: torch.Tensor, edge_index_local: torch.Ten
                              ranges: Sequence[Tuple[int, int]], group=None, edge_base: int = 0, prof=None) -> List[torch.Tensor]:
     """Drive ``edge_partitioned_steps`` with the NCCL exchange of ``exchange_node_rows`` (see there).  ``edge_base``:
     global id of this rank's first edge (the sum of the lower ranks' edge counts).  ``prof``: an ``engine.StageTimer``
-    that receives a CUDA-event mark after every stage (csr, encoder, project / step of each step, exchange)."""
-    gen = edge_partitioned_steps(model, x, edge_index_local, edge_attr_local, edge_base, prof=prof)
+    that receives a CUDA-event mark after every stage (csr, encoder, project, step of each step, exchange)."""
+    gen = edge_partitioned_steps(model, x, edge_index_local, edge_attr_local, edge_base, prof=prof, owned=ranges[_rank(group)] if _live(group) else None)
     try:
-        h_partial = next(gen)
+        q_partial = next(gen)
         while True:
-            h_full = exchange_node_rows(h_partial, ranges, group)
+            q_full = exchange_node_rows(q_partial, ranges, group)
             if prof is not None:
                 prof.mark("exchange")
-            h_partial = gen.send(h_full)
+            q_partial = gen.send(q_full)
     except StopIteration as done:
         return done.value
+
+
+def _live(group=None) -> bool:
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+
+def _rank(group=None) -> int:
+    return dist.get_rank(group)
 
 
 def forward_edge_partitioned_host(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor,
@@ -151,16 +160,22 @@ def forward_edge_partitioned_host(model, x: torch.Tensor, edge_index_local: torc
 
 
 def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0,
-                           prof=None):
-    """Generator form of the edge-partitioned forward: yields this rank's partial node matrix ([N, F], rows of
-    nodes it does not own are zero) at every exchange point and expects the assembled matrix back through
-    ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
+                           prof=None, owned: Optional[Tuple[int, int]] = None, buffers: Optional[dict] = None):
+    """Generator form of the edge-partitioned forward: yields this rank's partial TARGET-PROJECTION matrix ``Q`` ([N, 8]: the
+    rows of the nodes it owns are valid, all others zero) at every exchange point and expects the assembled matrix back
+    through ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
 
     ``MOTMPNet.forward`` for ONE graph whose edges are partitioned by source-node range across the ranks of
     ``group``.  ``x`` [N, F] is the full node-feature matrix (replicated: the encoder is cheap next to E),
-    ``edge_index_local`` [2, E_r] holds GLOBAL node ids of the edges whose source lies in ``ranges[rank]``
+    ``edge_index_local`` [2, E_r] holds GLOBAL node ids of the edges whose source lies in the rank's range
     (source-major), ``edge_attr_local`` their attributes.  Returns this rank's slice of every classified step's
-    logits ([E_r, 1] each), identical to the corresponding rows of the single-GPU result."""
+    logits ([E_r, 1] each), identical to the corresponding rows of the single-GPU result.
+
+    What crosses the link.  The edge update of step t+1 reads, of the OTHER ranks' nodes, only ``Q[dst] = W_e[:, dst block] h[dst]``
+    (6 floats, padded to 8); ``P[src]`` and ``R[src]`` are needed for the rank's own sources alone.  The fold launch of step t projects
+    the freshly aggregated rows of the owned nodes (gnncca_mp_step_fwd_next), so the exchange carries N x 8 floats per step instead
+    of the N x 32 node latents, and no projection launch runs between the steps.  ``owned``: this rank's node range; needed (to
+    zero the other rows of Q) only with reattach_initial_nodes, where a non-owned row projects the replicated initial latents."""
     from . import engine
     from .plan import GraphPlan, _stream
     lib = _lib.load()
@@ -176,12 +191,22 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
         prof.mark("begin")
     # rowptr spans all N nodes; segments outside the owned range are empty.  The order / range flags are NOT read back here (no
     # host synchronisation on the data path): the step kernels take them as their guard and are no-ops on an invalid CSR, and
-    # ``check_partition_flags(plan)`` reads them whenever the caller wants the verdict.
+    # ``check_partition_flags(model)`` reads them whenever the caller wants the verdict.
     plan = GraphPlan(edge_index_local, N)
     guard = _lib.ptr(plan.flags)
     if prof is not None:
         prof.mark("csr")
-    h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math)
+    buf = buffers if buffers is not None else {}
+
+    def get(name, shape):
+        t = buf.get(name)
+        if t is None or tuple(t.shape) != tuple(shape):
+            t = torch.empty(shape, dtype=torch.float32, device=dev)
+            if buffers is not None:
+                buffers[name] = t
+        return t
+
+    h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math, out=get("h0", (N, 32)))
     if prof is not None:
         prof.mark("encoder_node")
     enc_e = model.encoder.edge_mlp
@@ -194,44 +219,62 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     le = enc_e.linear(0) if fold else None
     h0, e0 = h, e
     sb = engine.StepBinding(model, math)
-    sb.cfg.edge_phase = int(edge_base) % int(_lib.load().gnncca_mp_step_tile())      # tile the local slice like the whole graph: bit-identical reductions
+    sb.cfg.edge_phase = int(edge_base) % int(lib.gnncca_mp_step_tile())      # tile the local slice like the whole graph: bit-identical reductions
     k = model.num_class_steps
     first = L - k + 1
     outs: List[torch.Tensor] = []
     if L == 0:
         return [engine.small_mlp_rows_cls(model, e)]
-    P = torch.empty((N, 8), dtype=torch.float32, device=dev)
-    Q = torch.empty((N, 8), dtype=torch.float32, device=dev)
-    R = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
+    P, Q, R = get("P", (N, 8)), get("Q", (N, 8)), get("R", (N, sb.f_node))
     ws_bytes = int(lib.gnncca_mp_step_workspace_bytes(C.byref(sb.cfg), N, E))
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    ws = buf.get("ws")
+    if ws is None or ws.numel() < ws_bytes:
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        if buffers is not None:
+            buffers["ws"] = ws
+    h_out = get("h_out", (N, sb.f_node))
+    _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
+                                       _stream()), "node_project")
+    if prof is not None:
+        prof.mark("project1")
     for step in range(1, L + 1):
-        _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
-                                           _stream()), "node_project")
-        if prof is not None:
-            prof.mark("project%d" % step)
         last = step == L
-        h_out = None if last else torch.empty((N, sb.f_node), dtype=torch.float32, device=dev)
-        logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if step >= first else None
+        logits = get("logits%d" % step, (E, 1)) if step >= first else None
         dead_e = last and logits is not None                 # e^L is never read
-        if fold and (step == 1 or model.reattach_initial_edges):
-            e_out = None if dead_e else (torch.empty((E, sb.f_edge), dtype=torch.float32, device=dev) if step == 1 else e)
+        use_attr = fold and (step == 1 or model.reattach_initial_edges)
+        if use_attr:
+            e_out = None if dead_e else (get("e", (E, sb.f_edge)) if step == 1 else e)
+        else:
+            e_out = None if dead_e else (get("e", (E, sb.f_edge)) if (model.reattach_initial_edges and step == 1) else e)
+        if not last:
+            _lib.check(lib.gnncca_mp_step_fwd_next(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
+                                                   _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea) if use_attr else 0, 4,
+                                                   _lib.ptr(le.weight) if use_attr else 0, _lib.ptr(le.bias) if use_attr else 0,
+                                                   _lib.ptr(e0) if (model.reattach_initial_edges and not use_attr) else 0, _lib.ptr(e), _lib.ptr(e_out),
+                                                   _lib.ptr(h_out), _lib.ptr(logits), _lib.ptr(h0), _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), guard,
+                                                   _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd_next")
+        elif use_attr:
             _lib.check(lib.gnncca_mp_step_fwd_attr(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                                    _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(ea), 4, _lib.ptr(le.weight), _lib.ptr(le.bias),
-                                                   _lib.ptr(e), _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes,
+                                                   _lib.ptr(e), _lib.ptr(e_out), 0, _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes,
                                                    _stream()), "mp_step_fwd_attr")
         else:
-            e_out = None if dead_e else (torch.empty_like(e) if (model.reattach_initial_edges and step == 1) else e)
             _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E,
                                               _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R), _lib.ptr(e0) if model.reattach_initial_edges else 0, _lib.ptr(e),
-                                              _lib.ptr(e_out), _lib.ptr(h_out), _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
+                                              _lib.ptr(e_out), 0, _lib.ptr(logits), guard, _lib.ptr(ws), ws_bytes, _stream()), "mp_step_fwd")
         if prof is not None:
             prof.mark("step%d" % step)
         e = e_out
         if logits is not None:
             outs.append(logits)
-        if h_out is not None:
-            h = yield h_out                                  # the one exchange of the step: N x 32 fp32 over NVLink
+        if not last:
+            if model.reattach_initial_nodes and owned is not None:      # non-owned rows project the replicated h0: not this rank's to contribute
+                a, b = owned
+                Q[:a].zero_()
+                Q[b:].zero_()
+            q_full = yield Q                                 # the one exchange of the step: N x 8 fp32 over NVLink
+            if q_full.data_ptr() != Q.data_ptr():
+                Q.copy_(q_full)
     model.__dict__["_gnncca_partition_plan"] = plan        # for check_partition_flags
     return outs
 
@@ -245,6 +288,78 @@ def check_partition_flags(model) -> None:
         return
     if not plan.source_major():
         raise ValueError("the local edge slice must be source-major")
+
+
+class PartitionedForward:
+    """The edge-partitioned forward of ONE rank as a replayable object: all work buffers are allocated once, the launches of one
+    forward -- CSR narrowing, node encoder, L steps, and the NCCL all-gathers of the projected rows between them -- are captured
+    into ONE CUDA graph on the first call and replayed afterwards (the eager path costs ~20 Python-driven launches and
+    allocations per forward, which at 8 GPUs is a third of a 0.8 ms forward).  Inputs are read from the tensors given at
+    construction (write new values into them in place); the returned logits are the graph's own buffers, valid until the next call.
+
+        runner = PartitionedForward(model, x, edge_index_local, edge_attr_local, ranges, edge_base=first_edge)
+        logits = runner()            # list of [E_r, 1]
+    """
+
+    def __init__(self, model, x, edge_index_local, edge_attr_local, ranges, group=None, edge_base: int = 0, use_graph: Optional[bool] = None):
+        self.model, self.x, self.ei, self.ea = model, x, edge_index_local, edge_attr_local
+        self.ranges, self.group, self.edge_base = list(ranges), group, edge_base
+        self.live = _live(group)
+        self.rank = _rank(group) if self.live else 0
+        sizes = {b - a for a, b in self.ranges}
+        self.equal = len(sizes) == 1 and self.ranges[0][0] == 0 and all(self.ranges[i][1] == self.ranges[i + 1][0] for i in range(len(self.ranges) - 1))
+        self.buffers: dict = {}
+        self.graph = None
+        self.outs = None
+        self.launches_replayed = 0
+        self._launches_per_graph = 0
+        if use_graph is None:
+            use_graph = os.environ.get("GNNCCA_PARTITION_GRAPH", "1") != "0"
+        self.use_graph = use_graph
+        self.graphed = False
+        self._calls = 0
+
+    def _exchange(self, q: torch.Tensor) -> torch.Tensor:
+        if not self.live:
+            return q
+        a, b = self.ranges[self.rank]
+        if self.equal:      # in place: every rank's rows land at their own offset of the same [N, 8] matrix
+            dist.all_gather_into_tensor(q, q[a:b], group=self.group)
+            return q
+        zero = self.buffers.get("qz")
+        if zero is None or zero.shape != q.shape:
+            zero = self.buffers["qz"] = torch.empty_like(q)
+        zero.zero_()
+        zero[a:b].copy_(q[a:b])
+        dist.all_reduce(zero, op=dist.ReduceOp.SUM, group=self.group)       # x + 0 is exact: the same bits as a gather
+        return zero
+
+    def _run(self):
+        gen = edge_partitioned_steps(self.model, self.x, self.ei, self.ea, self.edge_base, owned=self.ranges[self.rank], buffers=self.buffers)
+        try:
+            q = next(gen)
+            while True:
+                q = gen.send(self._exchange(q))
+        except StopIteration as done:
+            return done.value
+
+    def __call__(self) -> List[torch.Tensor]:
+        self._calls += 1
+        if not self.use_graph or self._calls <= 2:      # two eager calls first: buffers allocated, NCCL communicators warmed up
+            self.outs = self._run()
+            return self.outs
+        if self.graph is None:
+            lib = _lib.load()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = int(lib.gnncca_launch_count())
+            with torch.cuda.graph(g):
+                self.outs = self._run()
+            self._launches_per_graph = int(lib.gnncca_launch_count()) - n0
+            self.graph, self.graphed = g, True
+        self.graph.replay()
+        self.launches_replayed += self._launches_per_graph
+        return self.outs
 
 
 def complete_multipartite_slice(n_cams: int, n_dets: int, node_range: Tuple[int, int], device) -> torch.Tensor:

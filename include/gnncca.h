@@ -191,6 +191,19 @@ int gnncca_mp_step_fwd_attr(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w
                             const float* e_in, float* e_out, float* h_out, float* logits, const int32_t* guard_flags,
                             void* workspace, int64_t workspace_bytes, void* stream);
 
+/* The step (either form above: edge_attr != NULL selects the folded edge encoder) PLUS the per-node projections of the NEXT
+ * step: the second launch of the step, which visits every node once the reduction is complete, also computes
+ *   P_next | Q_next | R_next = gnncca_node_project([h0,] h_out)
+ * with the arithmetic of gnncca_node_project, so that no stand-alone projection launch runs between two steps (MOTMPNet.forward,
+ * mpn.py:279-293: the same MetaLayer is applied at every step).  P_next / Q_next / R_next may alias P / Q / R (the step kernel
+ * has finished reading them).  h0: the encoder's node output, read only with reattach_nodes.  h_out must not be NULL. */
+int gnncca_mp_step_fwd_next(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int32_t* rowptr, const int32_t* src,
+                            const int32_t* dst, int64_t n_nodes, int64_t n_edges, const float* P, const float* Q, const float* R,
+                            const float* edge_attr, int32_t edge_in_dim, const float* w_enc_edge, const float* b_enc_edge,
+                            const float* e0, const float* e_in, float* e_out, float* h_out, float* logits, const float* h0,
+                            float* P_next, float* Q_next, float* R_next, const int32_t* guard_flags, void* workspace,
+                            int64_t workspace_bytes, void* stream);
+
 /* ALL message-passing steps for a batch of SMALL frame graphs in one launch (MOTMPNet.forward, mpn.py:270-299,
  * after the node encoder): edge encoder (Linear(edge_in_dim, f_edge)+ReLU), num_steps x (edge update, node
  * update), classifier at steps >= first_class_step.  One persistent CTA per SM runs up to 8 warp groups; a
