@@ -322,6 +322,19 @@ def timed_windows(ctx: Ctx, step, steps: int, warmup: int, budget_s: float, extr
 ERR_FORMULA = "max |got - ref| / (1 + |ref| + 0.01 max|ref|)  (the last term is the fp32 reassociation floor: 1e-6 of the tensor's largest magnitude at tol 1e-4)"
 
 
+def x_in(b):
+    """The node-feature matrix a forward on ``b`` will read: the raw embeddings of a lazily normalised batch (graph.Batch.x), else x.
+    (Reading ``b.x`` would materialise the normalised copy and change what the timed forward does.)"""
+    raw = b.raw_x() if hasattr(b, "raw_x") else None
+    return raw[0] if raw is not None else b.x
+
+
+def x_rows(b, n0, n1):
+    """Rows [n0, n1) of the NORMALISED node features (what the reference's MPN is given), without materialising the whole matrix."""
+    raw = b.raw_x() if hasattr(b, "raw_x") else None
+    return (raw[0][n0:n1] / raw[1]) if raw is not None else b.x[n0:n1]
+
+
 def rel_err(out, ref):
     """The normalised error of tests/test_gpu_mpn.py::close over a list of tensors (CPU): max |out - ref| / (1 + |ref| + 0.01 max|ref|).
     With sum aggregation and random weights the latents reach 1e13 at degree 7680; an element that is a cancelling sum of such terms
@@ -543,7 +556,7 @@ def frames_parity(ctx: Ctx, model, batch, outs, ref_full=None, sample_frames=Non
     with torch.no_grad():
         for i in range(S):
             n0, n1, e0, e1 = ptr[i], ptr[S + i], eptr[i], eptr[S + i]
-            ref = mpn_oracle.motmpnet_forward(spec, sd, batch.x[n0:n1].cpu(), (batch.edge_index[:, e0:e1] - n0).cpu(), batch.edge_attr[e0:e1].cpu())["classified_edges"]
+            ref = mpn_oracle.motmpnet_forward(spec, sd, x_rows(batch, n0, n1).cpu(), (batch.edge_index[:, e0:e1] - n0).cpu(), batch.edge_attr[e0:e1].cpu())["classified_edges"]
             got = [o[e0:e1].detach().cpu() for o in outs]
             worst = max(worst, rel_err(got, ref))
             ok, near, n = decisions_equal(got, ref, margin=tol * (1 + max(float(r.abs().max()) for r in ref)))
@@ -567,10 +580,10 @@ def run_frames(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
     one_batch_bytes = (g1 - g0) * (n_per * 8192 + e_per * 32)
     n_batches = 1 if one_batch_bytes > (512 << 20) else max(2, min(16, -(-(300 << 20) // one_batch_bytes)))
     batches = [make_frame_batch(ctx, wl, g0, g1, variant=v) for v in range(n_batches)]
-    N, E, F = batches[0].num_nodes, batches[0].num_edges, int(batches[0].x.size(1))
+    N, E, F = batches[0].num_nodes, batches[0].num_edges, int(x_in(batches[0]).size(1))
     E_total = E * ctx.world if not strong else wl["frames"] * e_per
     N_total = N * ctx.world if not strong else wl["frames"] * n_per
-    in_bytes = batches[0].x.numel() * 4 + batches[0].edge_index.numel() * 8 + batches[0].edge_attr.numel() * 4
+    in_bytes = N * F * 4 + batches[0].edge_index.numel() * 8 + batches[0].edge_attr.numel() * 4
     keep = {}
 
     def step(i):
@@ -607,12 +620,12 @@ def run_frames(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
             if path == "blocked":
                 blocks = kb._gnncca_blocks[1]
                 gb0, gb1, n0, n1, e0, e1 = blocks[0]
-                kb = gnncca.Batch(x=kb.x[n0:n1], edge_index=(kb.edge_index[:, e0:e1] - n0).contiguous(), edge_attr=kb.edge_attr[e0:e1],
+                kb = gnncca.Batch(x=x_in(kb)[n0:n1], edge_index=(kb.edge_index[:, e0:e1] - n0).contiguous(), edge_attr=kb.edge_attr[e0:e1],
                                   ptr=(kb.ptr[gb0:gb1 + 1] - n0).contiguous(), num_graphs=gb1 - gb0)
             profs = []
             for i in range(min(steps, 10) + 2):
                 pr = engine.StageTimer()
-                engine.forward_inference(model, kb.x, kb.edge_index, kb.edge_attr, prof=pr, graph_ptr=kb.ptr, trusted=True, _no_block=True)
+                engine.forward_inference(model, x_in(kb), kb.edge_index, kb.edge_attr, prof=pr, graph_ptr=kb.ptr, trusted=True, _no_block=True)
                 pr.mark("end")
                 profs.append(pr)
             torch.cuda.synchronize()
@@ -716,7 +729,7 @@ def fused_kernel_times(ctx: Ctx, model, batches, steps: int):
 
     def enc(i):
         b = batches[i % nb]
-        _lib.check(lib.gnncca_node_encoder(b.x.data_ptr(), l1.weight.data_ptr(), l1.bias.data_ptr(), l2.weight.data_ptr(), l2.bias.data_ptr(),
+        _lib.check(lib.gnncca_node_encoder(x_in(b).data_ptr(), l1.weight.data_ptr(), l1.bias.data_ptr(), l2.weight.data_ptr(), l2.bias.data_ptr(),
                                            hs[i % nb].data_ptr(), N, l1.in_features, l1.out_features, 32, _lib.MATH_TF32, stream), "node_encoder")
 
     def mp(i):
@@ -777,7 +790,7 @@ def frames_e2e(ctx: Ctx, model, batches, wl, E, e2e_steps, strong, E_total):
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
         # what the link alone allows: the step's x bytes, pinned host -> device, nothing else running
-        x_probe = torch.empty_like(batches[0].x)
+        x_probe = torch.empty_like(x_in(batches[0]))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for i in range(3):
@@ -786,7 +799,7 @@ def frames_e2e(ctx: Ctx, model, batches, wl, E, e2e_steps, strong, E_total):
         h2d_gbs = 3 * x_probe.numel() * 4 / (time.perf_counter() - t0) / 1e9
         del x_probe, hosts
     e2e_max, blocking_max = ctx.max_over_ranks([e2e_s, blocking_s])
-    in_bytes = batches[0].x.numel() * 4 + batches[0].edge_index.numel() * 8 + batches[0].edge_attr.numel() * 4 + 8 * (batches[0].num_graphs + 1)
+    in_bytes = x_in(batches[0]).numel() * 4 + batches[0].edge_index.numel() * 8 + batches[0].edge_attr.numel() * 4 + 8 * (batches[0].num_graphs + 1)
     return {"value": E_total * e2e_steps / e2e_max, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": model.num_class_steps * E * 4,
             "steps": e2e_steps, "api": "gnncca.HostPipeline.submit / wait (pinned host x/edge_index/edge_attr -> pinned host logits, two batches in flight)",
             "h2d_link_gbs": h2d_gbs, "link_bound_value": E_total / (in_bytes / (h2d_gbs * 1e9)),
@@ -813,7 +826,10 @@ def graph_build_entry(ctx: Ctx, wl):
     gb_s = statistics.median(times)
     # exact bytes of the construction as built: norms pass over both embeddings (read), normalised copies written and re-read where
     # materialised, detection table, outputs (edge_index 16, edge_attr 16, labels 4 B/edge)
-    gb_bytes = int(getattr(b, "gnncca_build_bytes", N * (2048 + 256) * 4 * 3 + N * 40 + E * (16 + 16 + 4)))
+    lazy = b.raw_x() is not None
+    # bytes the construction really moves: node embeddings read once for the norms (+ the normalised copy written and re-read when it
+    # is materialised), ReID embeddings read for the norms, normalised copy written and read by the tile kernel, detection table, outputs
+    gb_bytes = N * 2048 * 4 * (1 if lazy else 3) + N * 256 * 4 * 4 + N * 40 + E * (16 + 16 + 4)
     out = {"value": E / gb_s, "unit": "edges built/s", "ms": gb_s * 1e3, "ms_min": min(times) * 1e3,
            "what": "build_graph_batch: column normalisation of both embeddings + edge_index / edge_attr / labels / ptr of %d frames (wall clock incl. its one read-back)" % wl["frames"],
            "roofline": {"bound": "hbm", "bytes": gb_bytes, "achieved": gb_bytes / gb_s / 1e9, "peak": ctx.peak, "frac": gb_bytes / gb_s / 1e9 / ctx.peak, "unit": "GB/s"}}
@@ -965,8 +981,8 @@ def run_giant(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
     roofline = {"bound": "hbm", "kernel": dom, "peak": ctx.peak, "unit": "GB/s", "peak_source": ctx.peak_src,
                 "kernel_selection": "largest share of the step's device time", "kernels": per_kernel,
                 "stages_ms_max_over_ranks": {k: round(v, 5) for k, v in stage_max.items()},
-                "exchange": {"ms_per_forward": exch_ms, "bytes_per_rank_per_exchange": (n1 - n0) * 128, "exchanges_per_forward": model.num_enc_steps - 1,
-                             "collective": "NCCL all_gather_into_tensor of the owned node rows (N x 32 fp32 assembled on every rank)" if ctx.world > 1 else "none (1 GPU)"},
+                "exchange": {"ms_per_forward": exch_ms, "bytes_per_rank_per_exchange": (n1 - n0) * 32, "exchanges_per_forward": model.num_enc_steps - 1,
+                             "collective": "NCCL all_gather_into_tensor (in place) of the owned rows of the target projection Q (N x 8 fp32 assembled on every rank; the node latents themselves never travel)" if ctx.world > 1 else "none (1 GPU)"},
                 "host_enqueue_ms_per_forward": statistics.median(host_s) * 1e3,
                 "forward": {"contract_bytes": forward_bytes(N, E), "contract_frac": min(forward_bytes(N, E) / (ms_step * 1e-3) / 1e9 / (ctx.peak * ctx.world), 1.0),
                             "note": "SURVEY 8d B_fwd of the whole graph over the forward time and the AGGREGATE peak of the %d GPUs" % ctx.world}}

@@ -88,6 +88,9 @@ SIGNATURES = {
     "gnncca_edge_mlp": (C.c_int, [vp, vp, i64, i32, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32), vp]),
     "gnncca_colnorm_scratch_bytes": (i64, [i64, i32]),
     "gnncca_colnorm": (C.c_int, [vp, vp, i64, i32, vp, vp]),
+    "gnncca_colnorm_norms": (C.c_int, [vp, i64, i32, vp, vp, vp]),
+    "gnncca_colnorm_apply": (C.c_int, [vp, vp, i64, i32, vp, vp]),
+    "gnncca_scale_columns": (C.c_int, [vp, vp, i64, i32, vp, vp]),
     "gnncca_graph_prepare_scratch_bytes": (i64, [i64, i64]),
     "gnncca_graph_edge_counts": (C.c_int, [vp, vp, i64, i64, vp, vp, i64, vp]),
     "gnncca_graph_tile_total_ptr": (vp, [vp, i64, i64]),

@@ -74,10 +74,10 @@ __global__ void __launch_bounds__(256) colnorm_apply_kernel(const float* __restr
 constexpr int CN_APPLY_ROWS = 32;
 __global__ void __launch_bounds__(256) colnorm_apply4_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t rows, int cols,
                                                              const float* __restrict__ norm) {
-  const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c4 = blockIdx.y * blockDim.x + threadIdx.x;
   if (c4 * 4 >= cols) return;
   const float4 nr = *reinterpret_cast<const float4*>(norm + c4 * 4);
-  const int64_t r0 = (int64_t)blockIdx.y * CN_APPLY_ROWS, r1 = min(r0 + CN_APPLY_ROWS, rows);
+  const int64_t r0 = (int64_t)blockIdx.x * CN_APPLY_ROWS, r1 = min(r0 + CN_APPLY_ROWS, rows);
   const float* px = x + (int64_t)c4 * 4;
   float* po = out + (int64_t)c4 * 4;
   int64_t r = r0;
@@ -316,16 +316,18 @@ extern "C" int64_t gnncca_colnorm_scratch_bytes(int64_t rows, int32_t cols) {
   return (int64_t)sizeof(float) * (ceil_div(rows > 0 ? rows : 1, CN_ROWS_PER_CHUNK) + 1) * cols;
 }
 
-extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, float* scratch, void* stream) {
+static bool colnorm_vec_ok(const float* emb, const float* out, const float* scratch, int64_t rows, int32_t cols) {
+  return cols % 4 == 0 && ((((uintptr_t)emb | (uintptr_t)out | (uintptr_t)scratch) & 15) == 0);
+}
+
+extern "C" int gnncca_colnorm_norms(const float* emb, int64_t rows, int32_t cols, float* scratch, float* norm, void* stream) {
   if (rows < 0 || cols <= 0) return GNNCCA_ERR_BAD_ARG;
   if (rows == 0) return GNNCCA_OK;
-  if (!emb || !out || !scratch) return GNNCCA_ERR_BAD_ARG;
+  if (!emb || !scratch || !norm) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const int chunks = (int)ceil_div(rows, CN_ROWS_PER_CHUNK);
   if (chunks > 65535) return GNNCCA_ERR_UNSUPPORTED;
-  float* norm = scratch + (int64_t)chunks * cols;
-  const bool vec = cols % 4 == 0 && ((((uintptr_t)emb | (uintptr_t)out | (uintptr_t)scratch) & 15) == 0) && ceil_div(rows, CN_APPLY_ROWS) <= 65535;
-  if (vec) {
+  if (colnorm_vec_ok(emb, emb, scratch, rows, cols)) {
     dim3 g1((unsigned)ceil_div(cols / 4, 256), (unsigned)chunks);
     colnorm_partial4_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
   } else {
@@ -333,13 +335,49 @@ extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_
     colnorm_partial_kernel<<<g1, 256, 0, st>>>(emb, rows, cols, scratch);
   }
   colnorm_final_kernel<<<(unsigned)ceil_div(cols, 32), 256, 0, st>>>(scratch, chunks, cols, norm);
-  if (vec) {
-    dim3 g3((unsigned)ceil_div(cols / 4, 256), (unsigned)ceil_div(rows, CN_APPLY_ROWS));
+  return check_launch(2);
+}
+
+extern "C" int gnncca_colnorm_apply(const float* emb, float* out, int64_t rows, int32_t cols, const float* norm, void* stream) {
+  if (rows < 0 || cols <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!emb || !out || !norm) return GNNCCA_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  // (rows of 32) x (columns of 1024) blocks; the row blocks ride on grid.x (2^31 - 1 of them), so any batch size takes the vector path
+  if (colnorm_vec_ok(emb, out, norm, rows, cols) && ceil_div(cols / 4, 256) <= 65535) {
+    dim3 g3((unsigned)ceil_div(rows, CN_APPLY_ROWS), (unsigned)ceil_div(cols / 4, 256));
     colnorm_apply4_kernel<<<g3, 256, 0, st>>>(emb, out, rows, cols, norm);
   } else {
     colnorm_apply_kernel<<<grid_for(rows * cols, 256), 256, 0, st>>>(emb, out, rows, cols, norm);
   }
-  return check_launch(3);
+  return check_launch();
+}
+
+extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, float* scratch, void* stream) {
+  if (rows < 0 || cols <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!emb || !out || !scratch) return GNNCCA_ERR_BAD_ARG;
+  const int chunks = (int)ceil_div(rows, CN_ROWS_PER_CHUNK);
+  float* norm = scratch + (int64_t)chunks * cols;
+  int rc = gnncca_colnorm_norms(emb, rows, cols, scratch, norm, stream);
+  if (rc) return rc;
+  return gnncca_colnorm_apply(emb, out, rows, cols, norm, stream);
+}
+
+// out[r][c] = W[r][c] / norm[c]: the column scaling of F.normalize(x, dim=0) moved onto the weights of the Linear that reads x
+// (x_normalised W^T = x (W diag(1 / norm))^T), so that a 200 MB activation matrix is never rewritten for the sake of 2048 scalars
+__global__ void __launch_bounds__(256) scale_columns_kernel(const float* __restrict__ W, float* __restrict__ out, int64_t total, int cols,
+                                                            const float* __restrict__ norm) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) out[t] = W[t] / norm[t % cols];
+}
+
+extern "C" int gnncca_scale_columns(const float* W, float* out, int64_t rows, int32_t cols, const float* norm, void* stream) {
+  if (rows < 0 || cols <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!W || !out || !norm) return GNNCCA_ERR_BAD_ARG;
+  scale_columns_kernel<<<grid_for(rows * cols, 256, 4), 256, 0, (cudaStream_t)stream>>>(W, out, rows * cols, cols, norm);
+  return check_launch();
 }
 
 extern "C" int64_t gnncca_graph_prepare_scratch_bytes(int64_t n_graphs, int64_t n_nodes) {

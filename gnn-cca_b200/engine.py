@@ -22,7 +22,7 @@ def _require_cuda(t: torch.Tensor, name: str) -> None:
 
 
 def linear(x: torch.Tensor, lin: torch.nn.Linear, relu: bool, bn: Optional[torch.nn.BatchNorm1d] = None,
-           math: int = _lib.MATH_FP32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+           math: int = _lib.MATH_FP32, out: Optional[torch.Tensor] = None, weight: Optional[torch.Tensor] = None) -> torch.Tensor:
     """models/mlp.py:14-19 for one fc_dims entry: Linear [+ BatchNorm1d(eval)] [+ ReLU]."""
     lib = _lib.load()
     x = x.contiguous()
@@ -33,7 +33,7 @@ def linear(x: torch.Tensor, lin: torch.nn.Linear, relu: bool, bn: Optional[torch
     eps = 0.0
     if bn is not None:
         bnw, bnb, bnm, bnv, eps = bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps
-    _lib.check(lib.gnncca_linear(_lib.ptr(x), _lib.ptr(lin.weight), _lib.ptr(lin.bias), _lib.ptr(y), rows, in_dim,
+    _lib.check(lib.gnncca_linear(_lib.ptr(x), _lib.ptr(lin.weight if weight is None else weight), _lib.ptr(lin.bias), _lib.ptr(y), rows, in_dim,
                                  lin.out_features, int(relu), _lib.ptr(bnw), _lib.ptr(bnb), _lib.ptr(bnm), _lib.ptr(bnv),
                                  float(eps), math, _stream()), "linear")
     return y
@@ -779,6 +779,7 @@ def node_encoder_fused_ok(mlp, inp) -> bool:
 
 
 def mlp_forward_nograd(mlp, inp, math, out=None):
+    w0 = mlp.__dict__.get("_gnncca_w0")      # first-layer weight with the input's column normalisation folded in (MOTMPNet.forward)
     if math == _lib.MATH_TF32 and node_encoder_fused_ok(mlp, inp):
         lib = _lib.load()
         inp = inp.contiguous()
@@ -786,7 +787,7 @@ def mlp_forward_nograd(mlp, inp, math, out=None):
         l1, l2 = mlp.linear(0), mlp.linear(1)
         y = torch.empty((rows, l2.out_features), dtype=torch.float32, device=inp.device) if out is None else out
         assert y.is_contiguous() and y.shape == (rows, l2.out_features)
-        _lib.check(lib.gnncca_node_encoder(_lib.ptr(inp), _lib.ptr(l1.weight), _lib.ptr(l1.bias), _lib.ptr(l2.weight), _lib.ptr(l2.bias),
+        _lib.check(lib.gnncca_node_encoder(_lib.ptr(inp), _lib.ptr(l1.weight if w0 is None else w0), _lib.ptr(l1.bias), _lib.ptr(l2.weight), _lib.ptr(l2.bias),
                                            _lib.ptr(y), rows, l1.in_features, l1.out_features, l2.out_features, _lib.MATH_TF32,
                                            _stream()), "node_encoder")
         return y
@@ -796,7 +797,7 @@ def mlp_forward_nograd(mlp, inp, math, out=None):
     for i, sp in enumerate(mlp.layer_specs):
         ok_tc = sp.in_dim % 32 == 0 and sp.out_dim % 16 == 0 and sp.out_dim <= 256 and sp.bn is None
         cur = linear(cur, mlp.linear(i), sp.relu, mlp.batchnorm(i), math if ok_tc else _lib.MATH_FP32,
-                     out=out if i == n - 1 else None)
+                     out=out if i == n - 1 else None, weight=w0 if i == 0 else None)
     return cur
 
 
@@ -867,7 +868,9 @@ class FastPath:
         self.verify()
         h = torch.empty((N, 32), dtype=torch.float32, device=self.device)
         logits = torch.empty((self.n_cls, E), dtype=torch.float32, device=self.device)
-        rc = self.fn(*self.prefix, x.data_ptr(), edge_index.data_ptr(), edge_attr.data_ptr(), graph_ptr.data_ptr(), edge_ptr.data_ptr(),
+        w0 = model.encoder.node_mlp.__dict__.get("_gnncca_w0")
+        prefix = self.prefix if w0 is None else self.prefix[:2] + (w0.data_ptr(),) + self.prefix[3:]
+        rc = self.fn(*prefix, x.data_ptr(), edge_index.data_ptr(), edge_attr.data_ptr(), graph_ptr.data_ptr(), edge_ptr.data_ptr(),
                      N, E, B, self.L, self.first, cap[0], cap[1], h.data_ptr(), logits.data_ptr(), self.flags.data_ptr(), _stream())
         if rc:
             _lib.check(rc, "mpn_forward_frames")

@@ -23,13 +23,43 @@ class Batch:
         for k, v in kw.items():
             setattr(self, k, v)
 
+    # ``x``: the (column-normalised) node embeddings the reference hands to the MPN (train.py:257-259, 357).  A batch from
+    # ``build_graph_batch`` keeps the caller's RAW embeddings and the 2048 column norms instead (``x_raw``, ``x_norm``); ``x`` is
+    # materialised -- by the same kernel, bit for bit -- the first time somebody reads it.  ``MOTMPNet.forward`` does not: it feeds
+    # ``x_raw`` to the node encoder and divides the weight columns of its first Linear by the norms (1 MB instead of a 200 MB rewrite).
+    @property
+    def x(self) -> torch.Tensor:
+        xv = self.__dict__.get("_x")
+        if xv is None:
+            raw, norm = self.__dict__.get("x_raw"), self.__dict__.get("x_norm")
+            if raw is None:
+                raise AttributeError("x")
+            lib = _lib.load()
+            xv = torch.empty_like(raw)
+            _lib.check(lib.gnncca_colnorm_apply(_lib.ptr(raw), _lib.ptr(xv), raw.size(0), raw.size(1), _lib.ptr(norm), _stream()), "colnorm_apply")
+            self.__dict__["_x"] = xv
+        return xv
+
+    @x.setter
+    def x(self, value) -> None:
+        self.__dict__["_x"] = value
+        self.__dict__.pop("x_raw", None)
+        self.__dict__.pop("x_norm", None)
+
+    def raw_x(self):
+        """(x_raw, x_norm) when the normalised ``x`` has not been materialised or replaced, else None."""
+        d = self.__dict__
+        if d.get("_x") is None and d.get("x_raw") is not None:
+            return d["x_raw"], d["x_norm"]
+        return None
+
     @property
     def batch(self) -> torch.Tensor:
         """PyG's ``Batch.batch`` (frame index of every node), built from ``ptr`` on first use: the MPN never reads it."""
         b = self.__dict__.get("_batch_vec")
         if b is None:
             counts = self.ptr[1:] - self.ptr[:-1]
-            b = torch.repeat_interleave(torch.arange(counts.numel(), device=self.ptr.device), counts, output_size=int(self.x.size(0)))
+            b = torch.repeat_interleave(torch.arange(counts.numel(), device=self.ptr.device), counts, output_size=self.num_nodes)
             self.__dict__["_batch_vec"] = b
         return b
 
@@ -39,14 +69,30 @@ class Batch:
 
     @property
     def num_nodes(self) -> int:
-        return int(self.x.size(0))
+        d = self.__dict__
+        return int((d["_x"] if d.get("_x") is not None else d["x_raw"]).size(0))
 
     @property
     def num_edges(self) -> int:
         return int(self.edge_index.size(1))
 
     def to(self, device):
-        return Batch(**{k: (v.to(device) if torch.is_tensor(v) else v) for k, v in self.__dict__.items()})
+        kw = {("x" if k == "_x" else k): (v.to(device) if torch.is_tensor(v) else v) for k, v in self.__dict__.items() if not k.startswith("_gnncca")}
+        if kw.get("x") is not None:
+            kw.pop("x_raw", None); kw.pop("x_norm", None)
+        return Batch(**kw)
+
+
+def column_norms(emb: torch.Tensor) -> torch.Tensor:
+    """max(||emb[:, c]||_2, 1e-12) per column: the denominators of ``F.normalize(emb, p=2, dim=0)`` (train.py:257-259)."""
+    lib = _lib.load()
+    if not emb.is_cuda or emb.dtype != torch.float32 or emb.dim() != 2 or not emb.is_contiguous():
+        raise ValueError("column_norms expects a contiguous 2-D float32 CUDA tensor")
+    rows, cols = emb.shape
+    scratch = torch.empty(int(lib.gnncca_colnorm_scratch_bytes(rows, cols)) // 4 + 1, dtype=torch.float32, device=emb.device)
+    norm = torch.empty(cols, dtype=torch.float32, device=emb.device)
+    _lib.check(lib.gnncca_colnorm_norms(_lib.ptr(emb), rows, cols, _lib.ptr(scratch), _lib.ptr(norm), _stream()), "colnorm_norms")
+    return norm
 
 
 def column_normalize(emb: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -65,11 +111,13 @@ def column_normalize(emb: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
 
 def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.Tensor, xw: torch.Tensor, yw: torch.Tensor,
                       max_dist: torch.Tensor, reid_embeds: torch.Tensor, node_embeds: torch.Tensor, mode: str = "full",
-                      l2norm: bool = True) -> Batch:
+                      l2norm: bool = True, lazy_x: bool = True) -> Batch:
     """graph_ptr [B+1] int64 (detections of frame g are rows graph_ptr[g]:graph_ptr[g+1], in the row order of
     the frame's table), id_cam [N] int, ids [N] int, xw/yw [N] float64 ground-plane coordinates, max_dist [B]
     float64 (CONV_TO_M of the frame's dataset), reid_embeds [N,R] / node_embeds [N,F] float32 CNN outputs.
-    ``mode``: 'full' | 'only_appearance' | 'only_dist' (train.py:335-344); ``l2norm`` = CNN_MODEL.L2norm."""
+    ``mode``: 'full' | 'only_appearance' | 'only_dist' (train.py:335-344); ``l2norm`` = CNN_MODEL.L2norm.
+    ``lazy_x``: keep ``node_embeds`` as given plus its column norms and materialise the normalised ``Batch.x`` only when it is
+    read (see ``Batch.x``); False writes it here."""
     lib = _lib.load()
     dev = node_embeds.device
     if dev.type != "cuda":
@@ -82,11 +130,16 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     xw = xw.to(device=dev, dtype=torch.float64).contiguous()
     yw = yw.to(device=dev, dtype=torch.float64).contiguous()
     max_dist = max_dist.to(device=dev, dtype=torch.float64).contiguous()
+    x_kw = {}
     if l2norm:
         reid = column_normalize(reid_embeds)
-        x = column_normalize(node_embeds)
+        if lazy_x:
+            raw = node_embeds.contiguous()
+            x_kw = dict(x_raw=raw, x_norm=column_norms(raw))
+        else:
+            x_kw = dict(x=column_normalize(node_embeds))
     else:
-        reid, x = reid_embeds.contiguous(), node_embeds.contiguous()
+        reid, x_kw = reid_embeds.contiguous(), dict(x=node_embeds.contiguous())
 
     nbytes = int(lib.gnncca_graph_prepare_scratch_bytes(B, N))
     scratch = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
@@ -113,5 +166,5 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     # "trusted" = source-major by construction: true only when every frame's rows are in ascending camera order (the reference
     # enumerates camera by camera, train.py:292-299, so interleaved cameras give an edge_index[0] that is NOT non-decreasing);
     # otherwise the forward takes its checked path (order flags read back, stable sort + permutation)
-    return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64,
+    return Batch(edge_index=edge_index, edge_attr=edge_attr, edge_labels=edge_labels, y=ids64, **x_kw,
                  ptr=graph_ptr, edge_ptr=edge_ptr, num_graphs=B, gnncca_caps=caps, gnncca_trusted=cam_unsorted == 0)

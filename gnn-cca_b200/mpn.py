@@ -151,7 +151,42 @@ class MOTMPNet(nn.Module):
 
     def forward(self, data):
         from . import autograd_fn, engine
-        x, edge_index, edge_attr = data.x, data.edge_index, data.edge_attr
+        edge_index, edge_attr = data.edge_index, data.edge_attr
+        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for _, p in self.named_parameters_fast())
+        train_path = needs_grad or (self.training and self._has_batchnorm())
+        # A batch from build_graph_batch carries the RAW node embeddings + their column norms (graph.Batch.x): inference feeds the raw
+        # matrix to the encoder and scales the weight columns of its first Linear instead of materialising the normalised copy
+        raw_fn = getattr(data, "raw_x", None)
+        raw = raw_fn() if (callable(raw_fn) and not train_path) else None
+        if raw is not None:
+            x = raw[0]
+            enc = self.encoder.node_mlp
+            enc.__dict__["_gnncca_w0"] = self._scaled_first_weight(data, raw[1])
+            try:
+                return self._forward(data, x, edge_index, edge_attr, needs_grad, train_path)
+            finally:
+                enc.__dict__.pop("_gnncca_w0", None)
+        return self._forward(data, data.x, edge_index, edge_attr, needs_grad, train_path)
+
+    def _scaled_first_weight(self, data, norm):
+        """W1 / norm (column-wise) of the node encoder's first Linear, cached on the batch while neither changes."""
+        from . import _lib
+        from .plan import _stream
+        w = self.encoder.node_mlp.linear(0).weight
+        key = (w.data_ptr(), w._version, norm.data_ptr(), norm._version)
+        hit = data.__dict__.get("_gnncca_w1s") if hasattr(data, "__dict__") else None
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        out = torch.empty_like(w)
+        _lib.check(_lib.load().gnncca_scale_columns(w.data_ptr(), out.data_ptr(), w.size(0), w.size(1), norm.data_ptr(), _stream()), "scale_columns")
+        try:
+            data.__dict__["_gnncca_w1s"] = (key, out)
+        except AttributeError:
+            pass
+        return out
+
+    def _forward(self, data, x, edge_index, edge_attr, needs_grad, train_path):
+        from . import autograd_fn, engine
         graph_ptr = getattr(data, "ptr", None)             # PyG Batch.ptr / our Batch.ptr: frame boundaries, when known
         caps = getattr(data, "gnncca_caps", None)
         trusted = bool(getattr(data, "gnncca_trusted", False))
@@ -165,7 +200,6 @@ class MOTMPNet(nn.Module):
         if plan is not None and plan.last_path is not None:      # verified before: nothing left to check
             trusted, allow_fused = True, plan.last_path == "fused"
             caps = getattr(plan, "caps", caps) if allow_fused else caps
-        needs_grad = torch.is_grad_enabled() and any(p.requires_grad for _, p in self.named_parameters_fast())
         if (not needs_grad and not self.training and caps is not None and getattr(data, "gnncca_trusted", False)
                 and getattr(data, "edge_ptr", None) is not None and graph_ptr is not None):
             # batches from build_graph_batch in eval mode: one library call, two launches, nothing read back
@@ -174,7 +208,7 @@ class MOTMPNet(nn.Module):
             if outs is not None:
                 self.last_plan = engine.FAST_PLAN
                 return {'classified_edges': outs}
-        if needs_grad or (self.training and self._has_batchnorm()):
+        if train_path:
             outs, plan = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan, trusted=trusted, return_plan=True)
             if engine.CACHE_PLANS and plan is not None:
                 try:                    # the CSR (and its transpose for the backward) is reused while edge_index is unchanged

@@ -55,8 +55,12 @@ def shard_batch(batch: Batch, rank: int, world: int) -> Batch:
         row = batch.edge_index[0].contiguous()
         b = torch.searchsorted(row, torch.tensor([n0, n1], device=row.device, dtype=row.dtype))
         e0, e1 = int(b[0]), int(b[1])
-    kw = dict(x=batch.x[n0:n1], edge_index=batch.edge_index[:, e0:e1] - n0, edge_attr=batch.edge_attr[e0:e1], ptr=sub_ptr - n0,
-              num_graphs=g1 - g0)
+    raw = batch.raw_x() if hasattr(batch, "raw_x") else None
+    kw = dict(edge_index=batch.edge_index[:, e0:e1] - n0, edge_attr=batch.edge_attr[e0:e1], ptr=sub_ptr - n0, num_graphs=g1 - g0)
+    if raw is not None:      # lazily normalised batch: the shard keeps the raw rows and the norms of the WHOLE batch (train.py:257-259)
+        kw.update(x_raw=raw[0][n0:n1], x_norm=raw[1])
+    else:
+        kw["x"] = batch.x[n0:n1]
     for name in ("edge_labels",):
         if getattr(batch, name, None) is not None:
             kw[name] = getattr(batch, name)[e0:e1]

@@ -369,6 +369,13 @@ int gnncca_frame_clusters(const void* decision, int32_t kind, const int64_t* edg
  * Deterministic two-pass reduction; scratch of gnncca_colnorm_scratch_bytes(). In place allowed. */
 int64_t gnncca_colnorm_scratch_bytes(int64_t rows, int32_t cols);
 int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, float* scratch, void* stream);
+/* The two halves of gnncca_colnorm: norm[c] = max(||emb[:, c]||_2, 1e-12) (same scratch), and out = emb / norm.  A caller that
+ * feeds emb to a Linear may skip the second half and scale that layer's weight columns instead (gnncca_scale_columns):
+ * (emb / norm) W^T = emb (W / norm)^T, so the [rows, cols] matrix is read once for the norms and never rewritten. */
+int gnncca_colnorm_norms(const float* emb, int64_t rows, int32_t cols, float* scratch, float* norm, void* stream);
+int gnncca_colnorm_apply(const float* emb, float* out, int64_t rows, int32_t cols, const float* norm, void* stream);
+/* out[r][c] = W[r][c] / norm[c]  (W: nn.Linear weight [out_features = rows, in_features = cols]). */
+int gnncca_scale_columns(const float* W, float* out, int64_t rows, int32_t cols, const float* norm, void* stream);
 
 /* Step 1 of graph construction.  graph_ptr[B+1] int64 node offsets of the frames, id_cam[N] int32 camera id
  * per detection (row order of the frame's table).  Writes edge_ptr[B+1] (int64 exclusive scan of the

@@ -256,7 +256,40 @@ def _trusted_batch(cuda_device, cams=4, dets=6, frames=37, seed=11):
     from importlib import import_module
     syn = import_module("gnn-cca_b200.synthetic")
     det = syn.make_detections(cams, dets, frames, seed=seed, device=cuda_device)
-    return gnncca.build_graph_batch(**det)
+    b = gnncca.build_graph_batch(**det)
+    b.x       # materialise the normalised node features: these tests compare device paths bit for bit on the SAME x
+    return b
+
+
+def test_lazily_normalised_batch_matches_the_materialised_one_and_the_oracle(cuda_device):
+    """build_graph_batch keeps the raw node embeddings + column norms; MOTMPNet.forward scales the first encoder weight instead of
+    normalising 8 KB per node (x_n W^T = x (W / norm)^T).  Same logits as on the materialised x up to fp32 rounding, for the single-call
+    path (tf32), the fused path and the per-step path (fp32), and against the oracle on the normalised x."""
+    import gnncca
+    from importlib import import_module
+    syn = import_module("gnn-cca_b200.synthetic")
+    engine = import_module("gnn-cca_b200.engine")
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    for math, tol in (("fp32", 1e-5), ("tf32", 1e-3)):
+        torch.manual_seed(4)
+        model = gnncca.MOTMPNet(copy.deepcopy(params), None, "resnet50", math=math).to(cuda_device).eval()
+        lazy = gnncca.build_graph_batch(**syn.make_detections(4, 6, 37, seed=11, device=cuda_device))
+        assert lazy.raw_x() is not None
+        with torch.no_grad():
+            out_lazy = model(lazy)["classified_edges"]
+            assert lazy.raw_x() is not None                      # the forward did not materialise x
+            w = model.encoder.node_mlp.linear(0).weight
+            assert "_gnncca_w0" not in model.encoder.node_mlp.__dict__ and lazy._gnncca_w1s[1].shape == w.shape
+            eager = gnncca.build_graph_batch(**syn.make_detections(4, 6, 37, seed=11, device=cuda_device), lazy_x=False)
+            assert eager.raw_x() is None and torch.equal(eager.x, lazy.x)     # the same kernel materialises the same bits on demand
+            assert lazy.raw_x() is None
+            out_eager = model(eager)["classified_edges"]
+            steps = engine.forward_inference(model, eager.x, eager.edge_index, eager.edge_attr)
+            spec = mpn_oracle.MPNSpec(params, "resnet50")
+            sd = {k: v.cpu() for k, v in model.state_dict().items()}
+            ref = mpn_oracle.motmpnet_forward(spec, sd, eager.x.cpu(), eager.edge_index.cpu(), eager.edge_attr.cpu())["classified_edges"]
+        for a, c, s, r in zip(out_lazy, out_eager, steps, ref):
+            assert close(a, c, tol) <= tol and close(a, r, max(tol, FP32_RTOL)) <= max(tol, FP32_RTOL) and close(s, r) <= max(tol, FP32_RTOL)
 
 
 @pytest.mark.parametrize("agg", ["sum", "max"])
