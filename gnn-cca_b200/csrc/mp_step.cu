@@ -35,15 +35,26 @@
 
 namespace gnncca {
 
-constexpr int TILE = 512;     // edges per tile
-constexpr int THREADS = 256;  // one thread per edge pair
-constexpr int NWARP = THREADS / 32;
-constexpr int CHUNK = TILE / NWARP;   // edges per warp in phase B
-constexpr int FN = 32;        // latent node width handled by lane-per-feature phase B
-#ifndef GNNCCA_STEP_MIN_CTAS
-#define GNNCCA_STEP_MIN_CTAS 3
+constexpr int TILE = 512;     // edges per tile (the modulus of edge_phase: the reduction tiling of the GLOBAL edge numbering)
+#ifndef GNNCCA_STEP_CHUNK
+#define GNNCCA_STEP_CHUNK 64
 #endif
-constexpr int STEP_MIN_CTAS = GNNCCA_STEP_MIN_CTAS;   // resident CTAs per SM the register allocation is held to
+constexpr int CHUNK = GNNCCA_STEP_CHUNK;   // edges a warp stages and reduces per tile.  64 (8 warps per CTA) measured faster than 128 (4 warps, half
+                                           // the per-chunk bookkeeping per edge): 275 vs 312 us per step at cfg 4 (profiles/r02_step_experiments.md)
+#ifndef GNNCCA_STEP_UNROLL_SUB
+#define GNNCCA_STEP_UNROLL_SUB 1
+#endif
+constexpr int kUnrollSub = GNNCCA_STEP_UNROLL_SUB;
+constexpr int SUB = CHUNK / 64;            // phase A walks a chunk in sub-chunks of 64 edges (a lane's pair per sub-chunk)
+constexpr int NWARP = TILE / CHUNK;
+constexpr int THREADS = NWARP * 32;
+static_assert(CHUNK % 64 == 0 && TILE % CHUNK == 0, "a chunk is a whole number of 64-edge sub-chunks");
+constexpr int FN = 32;        // latent node width handled by lane-per-feature phase B
+#ifndef GNNCCA_STEP_WARPS_PER_SM
+#define GNNCCA_STEP_WARPS_PER_SM 24
+#endif
+constexpr int STEP_MIN_CTAS = GNNCCA_STEP_WARPS_PER_SM / NWARP;   // resident CTAs per SM the register allocation is held to (24 warps: 85 registers)
+constexpr int STEP_MIN_CTAS_EDGE = (GNNCCA_STEP_WARPS_PER_SM + 8) / NWARP;   // the variant without node update: 32 warps (64 registers)
 
 struct StepParams {
   const int32_t* rowptr; const int32_t* src; const int32_t* dst;
@@ -159,29 +170,33 @@ __device__ __forceinline__ bool fill_slot(const StepParams& p, int64_t tile, int
     }
     return true;
   }
-  RawPair<FE, REATT_E, ATTR> r{};
-  load_raw<FE, REATT_E, ATTR>(p, (int64_t)cb + 2 * lane, r);
-  *reinterpret_cast<int2*>(slot + SL::SRC + SL::HALO * 4 + 8 * lane) = make_int2(r.sa, r.sb);
   if (lane < 2) {      // the two halo ids next to the chunk (-1: no such edge)
     const int j = lane == 0 ? cb - 1 : cb + CHUNK;
     *reinterpret_cast<int*>(slot + SL::SRC + (lane == 0 ? SL::HALO - 1 : SL::HALO + CHUNK) * 4) = (j >= 0 && j < n_edges) ? p.src[j] : -1;
   }
-  *reinterpret_cast<int2*>(slot + SL::DST + 8 * lane) = make_int2(r.da, r.db);
-  float* e = reinterpret_cast<float*>(slot + SL::E) + 2 * FE * lane;
-#pragma unroll
-  for (int k = 0; k < FE / 2; ++k) {
-    *reinterpret_cast<float2*>(e + 2 * k) = r.ea[k];
-    *reinterpret_cast<float2*>(e + FE + 2 * k) = r.eb[k];
-  }
-  if (ATTR) {
-    float4* x = reinterpret_cast<float4*>(slot + SL::X) + 2 * lane;
-    x[0] = r.ta[0]; x[1] = r.tb[0];
-  } else if (REATT_E) {
-    float* x = reinterpret_cast<float*>(slot + SL::X) + 2 * FE * lane;
+#pragma unroll 1
+  for (int h = 0; h < SUB; ++h) {
+    const int pl = 32 * h + lane;      // this lane's pair of the sub-chunk
+    RawPair<FE, REATT_E, ATTR> r{};
+    load_raw<FE, REATT_E, ATTR>(p, (int64_t)cb + 2 * pl, r);
+    *reinterpret_cast<int2*>(slot + SL::SRC + SL::HALO * 4 + 8 * pl) = make_int2(r.sa, r.sb);
+    *reinterpret_cast<int2*>(slot + SL::DST + 8 * pl) = make_int2(r.da, r.db);
+    float* e = reinterpret_cast<float*>(slot + SL::E) + 2 * FE * pl;
 #pragma unroll
     for (int k = 0; k < FE / 2; ++k) {
-      *reinterpret_cast<float2*>(x + 2 * k) = r.xa[k];
-      *reinterpret_cast<float2*>(x + FE + 2 * k) = r.xb[k];
+      *reinterpret_cast<float2*>(e + 2 * k) = r.ea[k];
+      *reinterpret_cast<float2*>(e + FE + 2 * k) = r.eb[k];
+    }
+    if (ATTR) {
+      float4* x = reinterpret_cast<float4*>(slot + SL::X) + 2 * pl;
+      x[0] = r.ta[0]; x[1] = r.tb[0];
+    } else if (REATT_E) {
+      float* x = reinterpret_cast<float*>(slot + SL::X) + 2 * FE * pl;
+#pragma unroll
+      for (int k = 0; k < FE / 2; ++k) {
+        *reinterpret_cast<float2*>(x + 2 * k) = r.xa[k];
+        *reinterpret_cast<float2*>(x + FE + 2 * k) = r.xb[k];
+      }
     }
   }
   __syncwarp();
@@ -257,7 +272,7 @@ __device__ __forceinline__ void finalize_node_feat(const StepParams& p, int node
 // NODE = false: the step only updates and classifies the edges (last step of an inference forward, h_out == NULL): no phase B, so
 // the register allocation is held to one more resident CTA per SM (this variant is bound by memory-instruction latency)
 template <int FE, int HC, bool REATT_E, bool IS_MAX, bool ATTR, bool NODE>
-__global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS + 1) mp_step_fwd_kernel(const StepParams p) {
+__global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS_EDGE) mp_step_fwd_kernel(const StepParams p) {
   constexpr int EIN = REATT_E ? 2 * FE : FE;
   constexpr int HCS = HC > 0 ? HC : 2;
   constexpr int FEP = (FE + 3) & ~3;      // row stride of the transposed weight tables (16-byte rows)
@@ -354,36 +369,33 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
   int it = 0;
   for (int tile = t_begin; tile < t_end; ++tile, ++it) {
     const int base = tile * TILE - p.phase;   // tiles follow the global numbering: same chunking, same bits, on any partition (E < 2^31 - 2 TILE)
-    const int i0 = base + 2 * tid;
-    RawPair<FE, REATT_E, ATTR> cur;
-    int nb_prev, nb_next;      // sources of the edges just before / after the chunk (-1: none)
-    {
-      const int sl = it % NSTAGE;
-      if ((isbulk >> sl) & 1u) { enc::mbar_wait(wbar + sl, (parity >> sl) & 1u); parity ^= 1u << sl; }
-      read_slot<FE, REATT_E, ATTR>(ring + sl * SL::BYTES, lane, latent, cur);
-      nb_prev = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO - 1) * 4);
-      nb_next = *reinterpret_cast<const int*>(ring + sl * SL::BYTES + SL::SRC + (SL::HALO + CHUNK) * 4);
-      __syncwarp();        // every lane has its pair: the slot goes to the tile two rounds ahead
-      const int64_t nt = (int64_t)tile + NSTAGE;
-      isbulk &= ~(1u << sl);
-      if (nt < t_end && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok)) isbulk |= 1u << sl;
-    }
-    const bool va = cur.sa >= 0, vb = cur.sb >= 0;
-    // A warp stages and then reduces the SAME 64 edges, so the warps never wait for each other; the sources of the edges
-    // just outside the chunk (is its first / last piece part of a longer segment?) come from global memory.
+    const int sl = it % NSTAGE;
+    const unsigned char* slot = ring + sl * SL::BYTES;
+    if ((isbulk >> sl) & 1u) { enc::mbar_wait(wbar + sl, (parity >> sl) & 1u); parity ^= 1u << sl; }
+    // sources of the edges just before / after the chunk (-1: none): is its first / last piece part of a longer segment?
+    const int nb_prev = *reinterpret_cast<const int*>(slot + SL::SRC + (SL::HALO - 1) * 4);
+    const int nb_next = *reinterpret_cast<const int*>(slot + SL::SRC + (SL::HALO + CHUNK) * 4);
+    // A warp stages and then reduces the SAME edges (its chunk of the tile), so the warps never wait for each other
     const int lo = max(0, -base), hi = min(TILE, n_edges - base);   // valid tile-local edge range
     const int c0 = warp * CHUNK;
     const int a = max(c0, lo), b = min(c0 + CHUNK, hi);
     float r_next[4] = {0.f, 0.f, 0.f, 0.f};   // R row of the chunk's first segment (features g + 8 q), requested before phase A
     if (NODE && p.h_out != nullptr && a < b) {
-      const int s_first = __shfl_sync(0xffffffffu, (a & 1) ? cur.sb : cur.sa, (a - c0) >> 1);
+      const int s_first = *reinterpret_cast<const int*>(slot + SL::SRC + (SL::HALO + a - c0) * 4);
 #pragma unroll
       for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)s_first * FN + g + 8 * q];
     }
-    // ------------------------------ phase A: thread per edge pair ------------------------------
+    // ------------------------------ phase A: thread per edge pair, one 64-edge sub-chunk after the other ------------------------------
     // Packed arithmetic runs over OUTPUT pairs (o, o + 1) of one edge: the weight pair comes out of shared memory as an aligned
     // register pair and the edge value is the broadcast scalar (pairing the two EDGES instead cost two register moves per FFMA2).
-    {
+#pragma unroll kUnrollSub
+    for (int h = 0; h < SUB; ++h) {
+      const int pl = 32 * h + lane;          // this lane's pair of the chunk
+      const int te = c0 + 2 * pl;            // its first edge, tile-local
+      const int i0 = base + te;
+      RawPair<FE, REATT_E, ATTR> cur;
+      read_slot<FE, REATT_E, ATTR>(slot, pl, latent, cur);
+      const bool va = cur.sa >= 0, vb = cur.sb >= 0;
       float xa[EIN], xb[EIN];
       constexpr int OFF = REATT_E ? FE : 0;
       float2 e0a[ATTR ? FE / 2 : 1], e0b[ATTR ? FE / 2 : 1];
@@ -477,8 +489,8 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
       if (NODE) {
 #pragma unroll
         for (int q = 0; q < 2 * FE / 4; ++q)
-          *reinterpret_cast<float4*>(&s_e[2 * tid][0] + 4 * q) = make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]);
-        *reinterpret_cast<int2*>(&s_src[2 * tid]) = make_int2(cur.sa, cur.sb);
+          *reinterpret_cast<float4*>(&s_e[te][0] + 4 * q) = make_float4(row[4 * q], row[4 * q + 1], row[4 * q + 2], row[4 * q + 3]);
+        *reinterpret_cast<int2*>(&s_src[te]) = make_int2(cur.sa, cur.sb);
       }
       if (classify) {
         float2 ha[HCS / 2], hb[HCS / 2];
@@ -507,11 +519,16 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
         }
       }
     }
+    __syncwarp();        // every lane has read its pairs: the slot goes to the tile NSTAGE rounds ahead (and the staged rows are visible)
+    {
+      const int64_t nt = (int64_t)tile + NSTAGE;
+      isbulk &= ~(1u << sl);
+      if (nt < t_end && fill_slot<FE, REATT_E, ATTR>(p, nt, warp * CHUNK, lane, ring + sl * SL::BYTES, wbar + sl, bulk_ok)) isbulk |= 1u << sl;
+    }
     if (!NODE || p.h_out == nullptr) continue;  // last step: the node update is dead (mpn.py:288-299); no shared state reused
 #ifdef GNNCCA_EXP_NOB
     continue;
 #endif
-    __syncwarp();
     // ------------------------------ phase B: messages of 8 edges per mma ------------------------------
     // The chunk is cut into 8-edge blocks aligned to the global numbering.  A piece (edges of one source inside the chunk) walks
     // its blocks; the accumulator tile starts as the R row of the source (C operand), ReLU and the running aggregate are applied
@@ -525,29 +542,40 @@ __global__ void __launch_bounds__(THREADS, NODE ? STEP_MIN_CTAS : STEP_MIN_CTAS 
           const float4 l4 = s_afrag[2 * i + 1][lane];
           a_c[i][0] = __float_as_uint(l4.x); a_c[i][1] = __float_as_uint(l4.y); a_c[i][2] = __float_as_uint(l4.z); a_c[i][3] = __float_as_uint(l4.w);
         }
-        unsigned long long mask = 1ull << (a - c0);      // bit i: edge c0 + i opens a piece; sorted sources: equal ends = one piece
+        // bit i of m0 (m1): edge c0 + i (c0 + 64 + i) opens a piece; sorted sources: equal ends = one piece
+        static_assert(SUB <= 2, "the piece mask is two 64-bit words");
+        unsigned long long m0 = (a - c0) < 64 ? 1ull << (a - c0) : 0ull, m1 = (a - c0) >= 64 ? 1ull << (a - c0 - 64) : 0ull;
         if (s_src[a] != s_src[b - 1]) {
-          const int ie = c0 + 2 * lane;
-          const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
-          const int prev = ie - 1 >= a ? s_src[max(ie - 1, 0)] : nb_prev;
-          const bool st_e = ie >= a && ie < b && (ie == a || my.x != prev);
-          const bool st_o = ie + 1 >= a && ie + 1 < b && (ie + 1 == a || my.y != my.x);
-          const unsigned bits = (st_e ? 1u : 0u) | (st_o ? 2u : 0u);
-          const unsigned m_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits << (2 * lane) : 0u);
-          const unsigned m_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits << (2 * lane - 32) : 0u);
-          mask = (unsigned long long)m_lo | ((unsigned long long)m_hi << 32);
+#pragma unroll
+          for (int w = 0; w < SUB; ++w) {
+            const int ie = c0 + 64 * w + 2 * lane;
+            const int2 my = *reinterpret_cast<const int2*>(&s_src[ie]);
+            const int prev = ie - 1 >= a ? s_src[max(ie - 1, 0)] : nb_prev;
+            const bool st_e = ie >= a && ie < b && (ie == a || my.x != prev);
+            const bool st_o = ie + 1 >= a && ie + 1 < b && (ie + 1 == a || my.y != my.x);
+            const unsigned bits = (st_e ? 1u : 0u) | (st_o ? 2u : 0u);
+            const unsigned m_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits << (2 * lane) : 0u);
+            const unsigned m_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits << (2 * lane - 32) : 0u);
+            const unsigned long long m = (unsigned long long)m_lo | ((unsigned long long)m_hi << 32);
+            if (w == 0) m0 = m; else m1 = m;
+          }
         }
         const bool first_cont = nb_prev == s_src[a];
         const bool last_cont = nb_next == s_src[b - 1];
-        while (mask) {
-          const int j0 = c0 + __ffsll((long long)mask) - 1;
-          mask &= mask - 1;
-          const int j1 = mask ? c0 + __ffsll((long long)mask) - 1 : b;
+        // chunk-local index of the first piece start still in the mask, -1 when none is left
+#define GNNCCA_LOWEST() (m0 ? __ffsll((long long)m0) - 1 : (m1 ? 64 + __ffsll((long long)m1) - 1 : -1))
+        int nxt = GNNCCA_LOWEST();
+        while (nxt >= 0) {
+          const int j0 = c0 + nxt;
+          if (nxt < 64) m0 &= m0 - 1; else m1 &= m1 - 1;
+          nxt = GNNCCA_LOWEST();
+          const bool more = nxt >= 0;
+          const int j1 = more ? c0 + nxt : b;
           const int s = s_src[j0];
           float r[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) r[q] = r_next[q];
-          if (mask) {   // next segment's row: in flight during this one
+          if (more) {   // next segment's row: in flight during this one
             const int sn = s_src[j1];
 #pragma unroll
             for (int q = 0; q < 4; ++q) r_next[q] = p.R[(int64_t)sn * FN + g + 8 * q];
@@ -723,7 +751,7 @@ extern "C" int64_t gnncca_mp_step_workspace_bytes(const gnncca_mp_cfg* cfg, int6
 template <int FE, int HC>
 static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
   const bool node = sp.h_out != nullptr;
-  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * (node ? STEP_MIN_CTAS : STEP_MIN_CTAS + 1));
+  const int grid = (int)min((int64_t)sp.num_tiles, (int64_t)kNumSMs * (node ? STEP_MIN_CTAS : STEP_MIN_CTAS_EDGE));
   const bool is_max = sp.agg == GNNCCA_AGG_MAX;
   const bool attr = sp.attr != nullptr;
 #define GNNCCA_STEP(R, M, A) GNNCCA_STEP_N(R, M, A, true)
