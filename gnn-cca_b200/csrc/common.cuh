@@ -20,14 +20,6 @@ inline int check_cuda(cudaError_t e) {
   return GNNCCA_OK;
 }
 
-// single-kernel forward for small frames (mpn_mega.cu); GNNCCA_ERR_UNSUPPORTED when the batch has no such path
-int mpn_mega_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* enc_W1, const float* enc_b1,
-                 const float* enc_W2, const float* enc_b2, int32_t in_dim, int32_t hidden, const float* w_enc_edge,
-                 const float* b_enc_edge, int32_t edge_in_dim, const float* x, const int64_t* edge_index,
-                 const float* edge_attr, const int64_t* graph_ptr, const int64_t* edge_ptr, int64_t n_nodes,
-                 int64_t n_edges, int64_t n_graphs, int32_t num_steps, int32_t first_class_step, int32_t cap_nodes,
-                 int32_t cap_edges, float* h_enc, float* logits, int32_t* flags, void* stream);
-
 // Set by gnncca_mpn_forward_frames around its second launch: gnncca_mp_fused_fwd then launches with programmatic
 // stream serialization, so its CTAs start (and load their weights) on SMs the encoder has already left.
 extern thread_local bool tl_launch_as_dependent;

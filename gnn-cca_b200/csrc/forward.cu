@@ -1,16 +1,7 @@
 // MOTMPNet.forward (reference models/mpn.py:250-299) for batches of small frame graphs as one C-ABI call: the host
-// side of the hot path (one persistent kernel when the frames allow it, else two launches; the entry point the drop-in module binds).
-#include <cstdlib>
+// side of the hot path (two launches: the node encoder and, as its programmatic dependent, the fused all-steps kernel; the entry point the drop-in module binds).
+// A single persistent kernel doing both (round 1's mpn_mega.cu) measured 101 us against 85 us for the two launches and was removed in round 2..
 #include "common.cuh"
-
-namespace {
-// GNNCCA_MEGA=1 selects the single persistent kernel (mpn_mega.cu).  Off by default: at cfg 2 it measures 101 us per
-// forward against 90 us for the two launches (DESIGN.md section 7 has the timeline and why).
-bool mega_enabled() {
-  const char* e = getenv("GNNCCA_MEGA");
-  return e && e[0] == '1';
-}
-}  // namespace
 
 extern "C" int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                                          const float* enc_W1, const float* enc_b1, const float* enc_W2, const float* enc_b2,
@@ -23,12 +14,6 @@ extern "C" int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_
                                          float* h_enc, float* logits, int32_t* flags, void* stream) {
   if (!cfg || !w || !x || !h_enc || !edge_index || !edge_ptr) return GNNCCA_ERR_BAD_ARG;
   if (n_nodes == 0 || n_graphs == 0) return GNNCCA_OK;
-  if (mega_enabled()) {   // one persistent kernel: encoder stream and message passing overlap on every SM
-    const int rc = gnncca::mpn_mega_fwd(cfg, w, enc_W1, enc_b1, enc_W2, enc_b2, in_dim, hidden, w_enc_edge, b_enc_edge, edge_in_dim, x,
-                                        edge_index, edge_attr, graph_ptr, edge_ptr, n_nodes, n_edges, n_graphs, num_steps,
-                                        first_class_step, cap_nodes, cap_edges, h_enc, logits, flags, stream);
-    if (rc != GNNCCA_ERR_UNSUPPORTED) return rc;
-  }
   int rc = gnncca_node_encoder(x, enc_W1, enc_b1, enc_W2, enc_b2, h_enc, n_nodes, in_dim, hidden, cfg->f_node, GNNCCA_MATH_TF32, stream);
   if (rc) return rc;
   gnncca::tl_launch_as_dependent = true;

@@ -1,5 +1,5 @@
 // All message-passing steps of MOTMPNet.forward (reference models/mpn.py:270-299) for ONE small frame graph, run
-// by a GROUP of warps (a whole CTA in mp_fused.cu, a warp group next to the encoder roles in mpn_mega.cu) that
+// by a GROUP of warps (up to 7 groups per CTA in mp_fused.cu) that
 // keeps the frame's node and edge latents in shared memory across the L steps: edge encoder (mpn.py:128-142),
 // EdgeModel (:59-69), NodeModel (:71-101) with the aggregation of :192-202, classifier (:290-293).  HBM sees the
 // encoded nodes, edge_attr, the edge list and the per-step logits, nothing of size E between steps.

@@ -1,4 +1,4 @@
-// tcgen05 / TMA / mbarrier PTX wrappers shared by the tensor-core kernels (encoder_tc.cu, mpn_mega.cu), sm_100a only.
+// tcgen05 / TMA / mbarrier PTX wrappers shared by the tensor-core kernels (encoder_tc.cu), sm_100a only.
 #pragma once
 #include <cuda.h>
 #include "common.cuh"
