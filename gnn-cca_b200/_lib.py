@@ -21,7 +21,7 @@ i64, i32, vp = C.c_int64, C.c_int32, C.c_void_p
 
 class MpCfg(C.Structure):
     _fields_ = [("f_node", i32), ("f_edge", i32), ("cls_hidden", i32), ("agg", i32), ("reattach_nodes", i32),
-                ("reattach_edges", i32), ("math", i32), ("edge_phase", i32)]
+                ("reattach_edges", i32), ("math", i32), ("edge_phase", i32), ("node_begin", i32), ("node_end", i32)]
 
 
 class MpWeights(C.Structure):

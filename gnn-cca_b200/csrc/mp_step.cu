@@ -74,6 +74,7 @@ struct StepParams {
   // projections of the NEXT step (gnncca_mp_step_fwd_next): the fold kernel, which visits every node once the step kernel is done, also
   // computes P | Q | R of the updated latents -- the stand-alone node_project launch between two steps disappears.  May alias P, Q, R.
   float* Pn; float* Qn; float* Rn; const float* h0;
+  int64_t node_lo, node_hi;      // the fold launch covers [node_lo, node_hi): all nodes, or the owned source range of an edge partition
 };
 
 
@@ -679,20 +680,20 @@ __global__ void __launch_bounds__(256) mp_step_fold_kernel(const StepParams p) {
   float* bias = fold_smem + K * OUT;
   if (PROJECT) {
     const int edge_row = p.edge_row, node_row = K + FE;
-    for (int idx = threadIdx.x; idx < K * OUT; idx += blockDim.x) {
-      const int k = idx / OUT, o = idx - k * OUT;
+    for (int idx = threadIdx.x; idx < K * OUT; idx += blockDim.x) {       // k fastest: coalesced reads of the weight rows
+      const int o = idx / K, k = idx - o * K;
       float v;
       if (o < FE) v = p.w.w_edge[o * edge_row + k];                       // source block
       else if (o < 2 * FE) v = p.w.w_edge[(o - FE) * edge_row + K + k];   // target block
       else v = p.w.w_node[(o - 2 * FE) * node_row + k];                   // node block of the node model
-      wt[idx] = v;
+      wt[k * OUT + o] = v;
     }
     for (int o = threadIdx.x; o < OUT; o += blockDim.x) bias[o] = (o < FE) ? p.w.b_edge[o] : (o < 2 * FE ? 0.f : p.w.b_node[o - 2 * FE]);
     __syncthreads();
   }
   const bool is_max = p.agg == GNNCCA_AGG_MAX;
   const int64_t wstride = (int64_t)gridDim.x * (blockDim.x >> 5);
-  for (int64_t v = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); v < p.n_nodes; v += wstride) {
+  for (int64_t v = p.node_lo + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); v < p.node_hi; v += wstride) {
     const int rs = p.rowptr[v], re = p.rowptr[v + 1];
     float out;
     bool written = false;       // does h_out[v] already hold the value (written by the step kernel)?
@@ -783,10 +784,10 @@ static int launch_step(const StepParams& sp, bool reatt_e, cudaStream_t st) {
   if (sp.Pn != nullptr) {     // fold + the next step's projections: weights staged once per block, blocks loop over the nodes
     const int K = sp.nf * FN;
     const size_t smem = sizeof(float) * (K * (2 * FE + FN) + (2 * FE + FN));
-    const unsigned blocks = (unsigned)min(ceil_div(sp.n_nodes, (int64_t)8), (int64_t)kNumSMs * 8);
+    const unsigned blocks = (unsigned)max((int64_t)1, min(ceil_div(sp.node_hi - sp.node_lo, (int64_t)8), (int64_t)kNumSMs * 8));
     mp_step_fold_kernel<true><<<blocks, 256, smem, st>>>(sp);
   } else {
-    mp_step_fold_kernel<false><<<(unsigned)ceil_div(sp.n_nodes, (int64_t)8), 256, 0, st>>>(sp);
+    mp_step_fold_kernel<false><<<(unsigned)max((int64_t)1, ceil_div(sp.node_hi - sp.node_lo, (int64_t)8)), 256, 0, st>>>(sp);
   }
   return check_launch(2);
 }
@@ -831,6 +832,11 @@ static int mp_step_impl(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
   sp.edge_row = 2 * sp.nf * FN + (cfg->reattach_edges ? 2 : 1) * cfg->f_edge;
   if (cfg->edge_phase < 0 || cfg->edge_phase >= TILE) return GNNCCA_ERR_BAD_ARG;
   sp.phase = cfg->edge_phase;
+  sp.node_lo = 0; sp.node_hi = n_nodes;
+  if (cfg->node_begin != 0 || cfg->node_end != 0) {
+    if (cfg->node_begin < 0 || cfg->node_end < cfg->node_begin || cfg->node_end > n_nodes) return GNNCCA_ERR_BAD_ARG;
+    sp.node_lo = cfg->node_begin; sp.node_hi = cfg->node_end;
+  }
   sp.num_tiles = (int)ceil_div(n_edges + sp.phase, TILE);
   char* ws = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   sp.chunk_part = (float*)ws;

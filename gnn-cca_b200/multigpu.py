@@ -164,7 +164,7 @@ def forward_edge_partitioned_host(model, x: torch.Tensor, edge_index_local: torc
 
 
 def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0,
-                           prof=None, owned: Optional[Tuple[int, int]] = None, buffers: Optional[dict] = None):
+                           prof=None, owned: Optional[Tuple[int, int]] = None, buffers: Optional[dict] = None, fold_owned_only: bool = False):
     """Generator form of the edge-partitioned forward: yields this rank's partial TARGET-PROJECTION matrix ``Q`` ([N, 8]: the
     rows of the nodes it owns are valid, all others zero) at every exchange point and expects the assembled matrix back
     through ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
@@ -179,7 +179,9 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     (6 floats, padded to 8); ``P[src]`` and ``R[src]`` are needed for the rank's own sources alone.  The fold launch of step t projects
     the freshly aggregated rows of the owned nodes (gnncca_mp_step_fwd_next), so the exchange carries N x 8 floats per step instead
     of the N x 32 node latents, and no projection launch runs between the steps.  ``owned``: this rank's node range; needed (to
-    zero the other rows of Q) only with reattach_initial_nodes, where a non-owned row projects the replicated initial latents."""
+    zero the other rows of Q) only with reattach_initial_nodes, where a non-owned row projects the replicated initial latents.
+    ``fold_owned_only``: the second launch of every step visits the owned nodes only (the rows of Q outside ``owned`` are then NOT
+    written: for exchanges that overwrite them, i.e. the all-gather of equal ranges)."""
     from . import engine
     from .plan import GraphPlan, _stream
     lib = _lib.load()
@@ -224,6 +226,8 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     h0, e0 = h, e
     sb = engine.StepBinding(model, math)
     sb.cfg.edge_phase = int(edge_base) % int(lib.gnncca_mp_step_tile())      # tile the local slice like the whole graph: bit-identical reductions
+    if fold_owned_only and owned is not None:      # the fold launch (aggregate + next projections) visits the owned sources only: the other
+        sb.cfg.node_begin, sb.cfg.node_end = int(owned[0]), int(owned[1])     # rows of Q arrive through the exchange, nobody reads their h
     k = model.num_class_steps
     first = L - k + 1
     outs: List[torch.Tensor] = []
@@ -339,7 +343,8 @@ class PartitionedForward:
         return zero
 
     def _run(self):
-        gen = edge_partitioned_steps(self.model, self.x, self.ei, self.ea, self.edge_base, owned=self.ranges[self.rank], buffers=self.buffers)
+        gen = edge_partitioned_steps(self.model, self.x, self.ei, self.ea, self.edge_base, owned=self.ranges[self.rank], buffers=self.buffers,
+                                     fold_owned_only=self.live and self.equal)
         try:
             q = next(gen)
             while True:

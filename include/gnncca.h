@@ -132,6 +132,8 @@ typedef struct {
   int32_t math;            /* GNNCCA_MATH_*: how the 6->32 message product is computed            */
   int32_t edge_phase;      /* 0, or (global id of local edge 0) % gnncca_mp_step_tile() when the edges are one rank's slice of a larger
                               source-major list: keeps the reduction tiling -- and so every bit -- of the whole graph */
+  int32_t node_begin;      /* [node_begin, node_end): the nodes whose aggregate (and next-step projections) the second launch of a step */
+  int32_t node_end;        /* produces; 0, 0 = all.  An edge partition sets its OWNED source range: the other rows come over the link */
 } gnncca_mp_cfg;
 
 /* Weights of one step, all device pointers into the caller's parameters (read at every call, so

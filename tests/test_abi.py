@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol_and_bindings_cover_them():
 
 def test_struct_layouts_match_the_header():
     lib_mod = importlib.import_module("gnn-cca_b200._lib")
-    assert ctypes.sizeof(lib_mod.MpCfg) == 32
+    assert ctypes.sizeof(lib_mod.MpCfg) == 40
     assert ctypes.sizeof(lib_mod.MpWeights) == 12 * 8 + 8
     assert ctypes.sizeof(lib_mod.FinSeg) == 2 * 8 + 8 * 4
 
