@@ -88,6 +88,7 @@ SIGNATURES = {
     "gnncca_edge_mlp": (C.c_int, [vp, vp, i64, i32, C.POINTER(i32), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32), vp]),
     "gnncca_colnorm_scratch_bytes": (i64, [i64, i32]),
     "gnncca_colnorm": (C.c_int, [vp, vp, i64, i32, vp, vp]),
+    "gnncca_colnorm_static": (C.c_int, [vp, vp, i64, i32, vp]),
     "gnncca_colnorm_norms": (C.c_int, [vp, i64, i32, vp, vp, vp]),
     "gnncca_colnorm_apply": (C.c_int, [vp, vp, i64, i32, vp, vp]),
     "gnncca_scale_columns": (C.c_int, [vp, vp, i64, i32, vp, vp]),

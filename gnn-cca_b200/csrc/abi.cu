@@ -9,6 +9,10 @@ void set_cuda_error(cudaError_t e) {
   strncpy(g_last_error, cudaGetErrorString(e), sizeof(g_last_error) - 1);
   g_last_error[sizeof(g_last_error) - 1] = 0;
 }
+void set_error_text(const char* text) {   // same slot as set_cuda_error: what gnncca_last_cuda_error() returns
+  strncpy(g_last_error, text, sizeof(g_last_error) - 1);
+  g_last_error[sizeof(g_last_error) - 1] = 0;
+}
 thread_local bool tl_launch_as_dependent = false;
 static std::atomic<long long> g_launches{0};
 void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }

@@ -7,6 +7,7 @@
 namespace gnncca {
 
 void set_cuda_error(cudaError_t e);   // thread-local last CUDA error text (abi.cu)
+void set_error_text(const char* text); // the same slot, free text (abi.cu)
 void count_launches(int n);           // process-wide count of kernels this library launched (abi.cu)
 
 inline int check_launch(int n_kernels = 1) {

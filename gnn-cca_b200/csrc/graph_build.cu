@@ -3,6 +3,8 @@
 // enumeration (cameras ascending, sources in row order, targets = every detection of another camera in
 // row order), the four edge attributes, edge labels, and the Batch.from_data_list index offsets.
 // Integer outputs are bit-exact; geometry is float64 like sklearn's paired_distances, cast to fp32 last.
+#include <stdio.h>
+#include <atomic>
 #include "common.cuh"
 
 namespace gnncca {
@@ -362,6 +364,58 @@ extern "C" int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_
   int rc = gnncca_colnorm_norms(emb, rows, cols, scratch, norm, stream);
   if (rc) return rc;
   return gnncca_colnorm_apply(emb, out, rows, cols, norm, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// gnncca_colnorm without caller scratch and without any allocation: the partial sums and the norms live in a file-scope
+// device array.  Every GPU that loads the library holds GNNCCA_COLNORM_STATIC_MAX_FLOATS * 4 bytes of it until exit.
+// In host code `g_colnorm_static` is only a handle of the symbol: the device address comes from cudaGetSymbolAddress, once
+// per device with that device current (the array exists once per device, at a different address on each).
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_colnorm_static[GNNCCA_COLNORM_STATIC_MAX_FLOATS];
+
+static int colnorm_static_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static std::atomic<float*> s_ptr[MAX_DEV];          // zero-initialised; a race between two first calls stores the same value
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) { set_error_text("gnncca_colnorm_static: no current device"); return GNNCCA_ERR_LAUNCH; }
+  float* p = s_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    void* sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_colnorm_static);
+    if (e != cudaSuccess || !sym) {
+      char msg[200];
+      snprintf(msg, sizeof(msg), "gnncca_colnorm_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      set_error_text(msg);
+      (void)cudaGetLastError();
+      return GNNCCA_ERR_LAUNCH;
+    }
+    p = static_cast<float*>(sym);
+    s_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return GNNCCA_OK;
+}
+
+extern "C" int gnncca_colnorm_static(const float* emb, float* out, int64_t rows, int32_t cols, void* stream) {
+  if (rows < 0 || cols <= 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!emb || !out) return GNNCCA_ERR_BAD_ARG;
+  const int64_t need = gnncca_colnorm_scratch_bytes(rows, cols) / (int64_t)sizeof(float);
+  if (need > (int64_t)GNNCCA_COLNORM_STATIC_MAX_FLOATS) {
+    char msg[240];
+    snprintf(msg, sizeof(msg), "gnncca_colnorm_static: [%lld, %d] needs %lld floats of scratch, the built-in array holds %lld "
+             "(use gnncca_colnorm with caller scratch)", (long long)rows, (int)cols, (long long)need,
+             (long long)GNNCCA_COLNORM_STATIC_MAX_FLOATS);
+    set_error_text(msg);
+    return GNNCCA_ERR_WORKSPACE;
+  }
+  float* scratch = nullptr;
+  const int rc = colnorm_static_ptr(&scratch);
+  if (rc) return rc;
+  // nothing in the array has to start at zero: the first launch writes every partial sum [chunk][col] the second one reads,
+  // and the second writes every norm the third reads (what the previous call left behind is never read)
+  return gnncca_colnorm(emb, out, rows, cols, scratch, stream);
 }
 
 // out[r][c] = W[r][c] / norm[c]: the column scaling of F.normalize(x, dim=0) moved onto the weights of the Linear that reads x

@@ -376,6 +376,20 @@ int gnncca_colnorm(const float* emb, float* out, int64_t rows, int32_t cols, flo
  * (emb / norm) W^T = emb (W / norm)^T, so the [rows, cols] matrix is read once for the norms and never rewritten. */
 int gnncca_colnorm_norms(const float* emb, int64_t rows, int32_t cols, float* scratch, float* norm, void* stream);
 int gnncca_colnorm_apply(const float* emb, float* out, int64_t rows, int32_t cols, const float* norm, void* stream);
+/* gnncca_colnorm for callers that cannot provide scratch and cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same launches and the same result as gnncca_colnorm, bit for bit; the partial sums and the norms live in a file-scope
+ * device array of GNNCCA_COLNORM_STATIC_MAX_FLOATS floats (4 MiB) that every GPU which loads the library holds until exit.
+ * Limit: gnncca_colnorm_scratch_bytes(rows, cols) <= 4 * GNNCCA_COLNORM_STATIC_MAX_FLOATS, i.e. (ceil(rows / 128) + 1) * cols
+ * <= 1 048 576 (e.g. 65 408 x 2048 or 523 000 x 256); beyond it GNNCCA_ERR_WORKSPACE and a message in
+ * gnncca_last_cuda_error(), nothing is launched.  Calls no cudaMalloc / cudaFree / allocating routine; the array's device
+ * address is looked up (cudaGetSymbolAddress) at the first call on each device, with the stream's device current.
+ * The array is SHARED by all calls on a device and keeps the last call's contents (nothing in it has to start at zero: every
+ * word read is written earlier in the same call): two calls that overlap on the GPU -- different streams, or graph branches
+ * without an edge between them -- race.  Calls on one stream are ordered and safe. */
+#define GNNCCA_COLNORM_STATIC_MAX_FLOATS (1 << 20)
+int gnncca_colnorm_static(const float* emb, float* out, int64_t rows, int32_t cols, void* stream);
+
 /* out[r][c] = W[r][c] / norm[c]  (W: nn.Linear weight [out_features = rows, in_features = cols]). */
 int gnncca_scale_columns(const float* W, float* out, int64_t rows, int32_t cols, const float* norm, void* stream);
 
