@@ -10,6 +10,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GNNCCA_LIB") or os.path.join(PKG, "libgnncca.so")     # GNNCCA_LIB: an experimental build (tools/variant.sh)
 
 OK, ERR_BAD_ARG, ERR_UNSUPPORTED, ERR_LAUNCH, ERR_WORKSPACE = 0, -1, -2, -3, -4
+TOTALS_MAGIC = 0x5eed5eed5eed          # GNNCCA_TOTALS_MAGIC
 AGG = {"sum": 0, "mean": 1, "max": 2}
 MATH_FP32, MATH_TF32 = 0, 1
 ATTR_MODES = {"full": 0, "only_appearance": 1, "only_dist": 2}
@@ -95,7 +96,9 @@ SIGNATURES = {
     "gnncca_graph_prepare_scratch_bytes": (i64, [i64, i64]),
     "gnncca_graph_edge_counts": (C.c_int, [vp, vp, i64, i64, vp, vp, i64, vp]),
     "gnncca_graph_tile_total_ptr": (vp, [vp, i64, i64]),
-    "gnncca_build_graphs": (C.c_int, [vp, vp, i64, i64, i64, i64, vp, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp]),
+    "gnncca_build_graphs": (C.c_int, [vp, vp, i64, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "gnncca_graph_prepare_all": (C.c_int, [vp, vp, i64, i64, vp, vp, i64, vp, i32, vp, vp, vp, i32, vp, vp, vp, vp]),
+    "gnncca_graph_join": (C.c_int, [vp]),
 }
 
 _lock = threading.Lock()

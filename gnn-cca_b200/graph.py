@@ -109,6 +109,44 @@ def column_normalize(emb: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
     return out
 
 
+_TOTALS = {}          # device index -> (pinned int64 [slots, 8], its numpy view, [next slot])
+_TOTALS_SLOTS = 8
+
+
+def _pinned_totals(dev: torch.device):
+    """Eight int64 words of pinned (device-writable) host memory: the scan kernel stores the batch totals there itself."""
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    ent = _TOTALS.get(key)
+    if ent is None:
+        t = torch.zeros((_TOTALS_SLOTS, 8), dtype=torch.int64).pin_memory()
+        ent = _TOTALS[key] = (t, t.numpy(), [0])
+    t, arr, nxt = ent
+    k = nxt[0]
+    nxt[0] = (k + 1) % _TOTALS_SLOTS
+    arr[k, 5] = 0
+    arr[k, 6] = 0
+    return t[k], arr[k]
+
+
+def _poll_totals(arr, what: str = "graph_prepare_all"):
+    """Spin until both scan blocks have set their check word (they store the values first and fence).  A kernel that never
+    gets there (a launch failure upstream) ends the wait through the stream's own error after a bounded time."""
+    import time
+    magic = _lib.TOTALS_MAGIC
+    spins, t0 = 0, None
+    while arr[5] != magic or arr[6] != magic:
+        spins += 1
+        if spins & 0x3ff == 0:
+            now = time.perf_counter()
+            t0 = now if t0 is None else t0
+            if now - t0 > 20.0:
+                torch.cuda.current_stream().synchronize()           # raises the CUDA error, if that is what happened
+                if arr[5] == magic and arr[6] == magic:
+                    break
+                raise _lib.GnnccaError("%s: the batch totals never arrived in host memory" % what)
+    return tuple(int(v) for v in arr[:5])
+
+
 def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.Tensor, xw: torch.Tensor, yw: torch.Tensor,
                       max_dist: torch.Tensor, reid_embeds: torch.Tensor, node_embeds: torch.Tensor, mode: str = "full",
                       l2norm: bool = True, lazy_x: bool = True) -> Batch:
@@ -117,7 +155,11 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     float64 (CONV_TO_M of the frame's dataset), reid_embeds [N,R] / node_embeds [N,F] float32 CNN outputs.
     ``mode``: 'full' | 'only_appearance' | 'only_dist' (train.py:335-344); ``l2norm`` = CNN_MODEL.L2norm.
     ``lazy_x``: keep ``node_embeds`` as given plus its column norms and materialise the normalised ``Batch.x`` only when it is
-    read (see ``Batch.x``); False writes it here."""
+    read (see ``Batch.x``); False writes it here.
+
+    Launch structure with ``l2norm`` (the default): ``gnncca_graph_prepare_all`` (frame tables, both scans and the ReID column norms
+    in two launches; the node-embedding norms forked onto a side stream), the batch totals polled from pinned host memory the
+    scan kernel writes itself, ``gnncca_build_graphs`` (which normalises the ReID rows while it stages them), join."""
     lib = _lib.load()
     dev = node_embeds.device
     if dev.type != "cuda":
@@ -130,29 +172,56 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     xw = xw.to(device=dev, dtype=torch.float64).contiguous()
     yw = yw.to(device=dev, dtype=torch.float64).contiguous()
     max_dist = max_dist.to(device=dev, dtype=torch.float64).contiguous()
-    x_kw = {}
-    if l2norm:
-        reid = column_normalize(reid_embeds)
-        if lazy_x:
-            raw = node_embeds.contiguous()
-            x_kw = dict(x_raw=raw, x_norm=column_norms(raw))
-        else:
-            x_kw = dict(x=column_normalize(node_embeds))
-    else:
-        reid, x_kw = reid_embeds.contiguous(), dict(x=node_embeds.contiguous())
-
+    for name, t in (("reid_embeds", reid_embeds), ("node_embeds", node_embeds)):
+        if t.dim() != 2 or t.dtype != torch.float32 or t.device != dev:
+            raise ValueError("%s must be a 2-D float32 tensor on %s" % (name, dev))
     nbytes = int(lib.gnncca_graph_prepare_scratch_bytes(B, N))
     scratch = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
     nbytes = scratch.numel() * 8
     edge_ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
-    _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
-                                            _lib.ptr(scratch), nbytes, _stream()), "graph_edge_counts")
-    # the output size is data dependent: one 32-byte read back (the reference syncs several times per FRAME)
-    if B > 0:
-        off = (lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N) - scratch.data_ptr()) // 8
-        n_tiles, E, max_n, max_e, cam_unsorted = (int(v) for v in scratch[off:off + 5].tolist())
+    stream = _stream()
+    need_reid = mode != "only_dist"
+    x_kw, reid_rnorm, join = {}, None, False
+
+    fused_ok = not need_reid or (reid_embeds.size(1) % 4 == 0 and reid_embeds.size(1) <= 1024 and reid_embeds.data_ptr() % 16 == 0)
+    if l2norm and B > 0 and N > 0 and fused_ok:
+        reid = reid_embeds.contiguous()
+        node = node_embeds.contiguous()
+        R, F = int(reid.size(1)), int(node.size(1))
+        f4 = lambda n: (n + 3) & ~3
+        n_rs = f4(int(lib.gnncca_colnorm_scratch_bytes(N, R)) // 4) if need_reid else 0
+        n_ns = f4(int(lib.gnncca_colnorm_scratch_bytes(N, F)) // 4) if lazy_x else 0
+        tmp = torch.empty(f4(R) + n_rs + n_ns, dtype=torch.float32, device=dev)      # [reid norms | reid partials | node partials]
+        if need_reid:
+            reid_rnorm = tmp[:R]
+        x_norm = torch.empty(F, dtype=torch.float32, device=dev) if lazy_x else None
+        tot_t, tot = _pinned_totals(dev)
+        _lib.check(lib.gnncca_graph_prepare_all(
+            _lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr), _lib.ptr(scratch), nbytes,
+            _lib.ptr(node) if lazy_x else None, F, _lib.ptr(x_norm), (tmp.data_ptr() + 4 * (f4(R) + n_rs)) if lazy_x else None,
+            _lib.ptr(reid) if need_reid else None, R, _lib.ptr(reid_rnorm), (tmp.data_ptr() + 4 * f4(R)) if need_reid else None,
+            tot_t.data_ptr(), stream), "graph_prepare_all")
+        join = lazy_x
+        if lazy_x:
+            x_kw = dict(x_raw=node, x_norm=x_norm)
+        else:
+            x_kw = dict(x=column_normalize(node))            # enqueued while the totals are on their way
+        n_tiles, E, max_n, max_e, cam_unsorted = _poll_totals(tot)
     else:
-        n_tiles = E = max_n = max_e = cam_unsorted = 0
+        if l2norm:
+            reid = column_normalize(reid_embeds)
+            x_kw = dict(x_raw=node_embeds.contiguous(), x_norm=column_norms(node_embeds.contiguous())) if lazy_x \
+                else dict(x=column_normalize(node_embeds))
+        else:
+            reid, x_kw = reid_embeds.contiguous(), dict(x=node_embeds.contiguous())
+        _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
+                                                _lib.ptr(scratch), nbytes, stream), "graph_edge_counts")
+        # the output size is data dependent: one 40-byte read back (the reference syncs several times per FRAME)
+        if B > 0:
+            off = (lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N) - scratch.data_ptr()) // 8
+            n_tiles, E, max_n, max_e, cam_unsorted = (int(v) for v in scratch[off:off + 5].tolist())
+        else:
+            n_tiles = E = max_n = max_e = cam_unsorted = 0
     caps = (max_n, max_e)      # exact frame maxima: sizes the fused all-steps kernel without guessing
 
     width = 4 if mode == "full" else 2
@@ -161,8 +230,10 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     edge_labels = torch.empty(E, dtype=torch.float32, device=dev)
     _lib.check(lib.gnncca_build_graphs(_lib.ptr(graph_ptr), _lib.ptr(edge_ptr), B, N, E, n_tiles, _lib.ptr(id_cam32),
                                        _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
-                                       int(reid.size(1)), attr_mode, _lib.ptr(scratch), _lib.ptr(edge_index),
-                                       _lib.ptr(edge_attr), _lib.ptr(edge_labels), _stream()), "build_graphs")
+                                       _lib.ptr(reid_rnorm), int(reid.size(1)), attr_mode, max_n, _lib.ptr(scratch), _lib.ptr(edge_index),
+                                       _lib.ptr(edge_attr), _lib.ptr(edge_labels), stream), "build_graphs")
+    if join:
+        _lib.check(lib.gnncca_graph_join(stream), "graph_join")
     # "trusted" = source-major by construction: true only when every frame's rows are in ascending camera order (the reference
     # enumerates camera by camera, train.py:292-299, so interleaved cameras give an edge_index[0] that is NOT non-decreasing);
     # otherwise the forward takes its checked path (order flags read back, stable sort + permutation)

@@ -411,12 +411,38 @@ const int64_t* gnncca_graph_tile_total_ptr(const void* scratch, int64_t n_graphs
  * column order (L2/max_dist, L1/max_dist computed in float64 then cast; ||a-b+1e-6||_2; cosine), and
  * edge_labels [E] fp32 (train.py:348-351).  Enumeration order = train.py:292-299: cameras ascending,
  * sources of the camera in row order, targets (all other cameras) in row order.  reid [N,reid_dim] is
- * the (already column-normalised) appearance embedding; ids int64, xw/yw/max_dist float64. */
+ * the appearance embedding: already column-normalised when reid_rnorm == NULL; otherwise the RAW embedding and
+ * reid_rnorm[reid_dim] = 1 / max(||column||_2, 1e-12) (gnncca_graph_prepare_all), and the normalisation of train.py:257-259
+ * happens while the rows are staged, as a multiplication (within 1 ulp of the division; an IEEE division there costs 30 % of the
+ * kernel) -- the normalised [N, reid_dim] matrix is never written.  ids int64, xw/yw/max_dist float64.
+ * max_frame_nodes: the largest frame (totals word [2] of step 1), or 0 if unknown: sizes the thread blocks for batches of
+ * small frames (a warp per 4 sources of the largest frame instead of always 8 warps); a value below the true maximum is an error
+ * of the caller (sources beyond it would be skipped). */
 int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64_t n_graphs, int64_t n_nodes,
                         int64_t n_edges, int64_t n_tiles, const int32_t* id_cam, const int64_t* ids, const double* xw,
-                        const double* yw, const double* max_dist, const float* reid, int32_t reid_dim,
-                        int32_t attr_mode, const void* scratch, int64_t* edge_index, float* edge_attr,
+                        const double* yw, const double* max_dist, const float* reid, const float* reid_rnorm, int32_t reid_dim,
+                        int32_t attr_mode, int32_t max_frame_nodes, const void* scratch, int64_t* edge_index, float* edge_attr,
                         float* edge_labels, void* stream);
+
+/* gnncca_graph_edge_counts + both column-norm reductions of train.py:257-259 in one call (n_graphs, n_nodes > 0).
+ *   on `stream`, two launches: frame tables + ReID partial sums, then the scans + the RECIPROCAL ReID column norms ->
+ *   reid_rnorm[reid_cols] (what gnncca_build_graphs takes; reid_cols % 4 == 0, <= 1024, 16-byte aligned rows);
+ *   on a library-owned side stream (forked from `stream`, one per device, created at the first call): the norms of the node
+ *   embeddings -> node_norm[node_cols]; nothing in graph construction reads them, so their HBM-bound pass runs beside
+ *   gnncca_build_graphs.  gnncca_graph_join(stream) makes `stream` wait for them: call it once after gnncca_build_graphs has
+ *   been enqueued (capturable: an event fork / join).  One host thread per device.
+ * node / reid may be NULL (that block is skipped); *_scratch: gnncca_colnorm_scratch_bytes(n_nodes, cols) each.
+ * totals_host (optional): 8 int64 words of PINNED host memory the device can write (cudaHostAlloc / torch pin_memory).  The
+ * scan blocks store the five totals of gnncca_graph_tile_total_ptr there themselves, fence, and then set the check words
+ * [5] and [6] to GNNCCA_TOTALS_MAGIC: a caller that cleared [5], [6] before the call polls them instead of synchronising the
+ * stream, and sizes step 2 while the norm passes are still running. */
+#define GNNCCA_TOTALS_MAGIC 0x5eed5eed5eedLL
+int gnncca_graph_prepare_all(const int64_t* graph_ptr, const int32_t* id_cam, int64_t n_graphs, int64_t n_nodes,
+                             int64_t* edge_ptr, void* scratch, int64_t scratch_bytes,
+                             const float* node, int32_t node_cols, float* node_norm, float* node_scratch,
+                             const float* reid, int32_t reid_cols, float* reid_rnorm, float* reid_scratch,
+                             int64_t* totals_host, void* stream);
+int gnncca_graph_join(void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Detection tables -> device tensors: libs/datasets.py:99-134, libs/utils.py:211-225.
