@@ -454,24 +454,10 @@ __global__ void __launch_bounds__(256, 3) build_graphs_kernel(const BuildParams 
         const float4 av = *reinterpret_cast<const float4*>(&s_a[k][ti0]);
         const float2 a01 = make_float2(av.x, av.y), a23 = make_float2(av.z, av.w);
         // F.pairwise_distance: ||a - b + eps||_2, eps = 1e-6 ((a - b) first, then + eps, as torch does)
-#if defined(GNNCCA_BG_SCALAR)
-        float2 df01, df23;
-        df01.x = (a01.x - b) + 1e-6f; df01.y = (a01.y - b) + 1e-6f; df23.x = (a23.x - b) + 1e-6f; df23.y = (a23.y - b) + 1e-6f;
-        d2a.x = fmaf(df01.x, df01.x, d2a.x); d2a.y = fmaf(df01.y, df01.y, d2a.y);
-        d2b.x = fmaf(df23.x, df23.x, d2b.x); d2b.y = fmaf(df23.y, df23.y, d2b.y);
-        dota.x = fmaf(a01.x, b, dota.x); dota.y = fmaf(a01.y, b, dota.y); dotb.x = fmaf(a23.x, b, dotb.x); dotb.y = fmaf(a23.y, b, dotb.y);
-#elif defined(GNNCCA_BG_FMAONLY)
-        const float2 one = pk::bc(1.f);
-        const float2 df01 = pk::ffma2(pk::ffma2(a01, one, pk::bc(-b)), one, pk::bc(1e-6f));
-        const float2 df23 = pk::ffma2(pk::ffma2(a23, one, pk::bc(-b)), one, pk::bc(1e-6f));
-        d2a = pk::ffma2(df01, df01, d2a); d2b = pk::ffma2(df23, df23, d2b);
-        dota = pk::ffma2(a01, pk::bc(b), dota); dotb = pk::ffma2(a23, pk::bc(b), dotb);
-#else
         const float2 df01 = pk::fadd2(pk::fadd2(a01, pk::bc(-b)), pk::bc(1e-6f));
         const float2 df23 = pk::fadd2(pk::fadd2(a23, pk::bc(-b)), pk::bc(1e-6f));
         d2a = pk::ffma2(df01, df01, d2a); d2b = pk::ffma2(df23, df23, d2b);
         dota = pk::ffma2(a01, pk::bc(b), dota); dotb = pk::ffma2(a23, pk::bc(b), dotb);
-#endif
       }
       __syncthreads();
     }
@@ -746,20 +732,18 @@ extern "C" int gnncca_graph_prepare_all(const int64_t* graph_ptr, const int32_t*
                                         const float* node, int32_t node_cols, float* node_norm, float* node_scratch,
                                         const float* reid, int32_t reid_cols, float* reid_rnorm, float* reid_scratch,
                                         int64_t* totals_host, void* stream) {
+  if (node && (node_cols <= 0 || !node_norm || !node_scratch)) return GNNCCA_ERR_BAD_ARG;
   if (n_graphs <= 0 || n_nodes <= 0 || n_graphs > INT32_MAX) return GNNCCA_ERR_BAD_ARG;
   if (!graph_ptr || !id_cam || !edge_ptr || !scratch) return GNNCCA_ERR_BAD_ARG;
   if (scratch_bytes < gnncca_graph_prepare_scratch_bytes(n_graphs, n_nodes)) return GNNCCA_ERR_WORKSPACE;
-  if (node && (node_cols <= 0 || !node_norm || !node_scratch)) return GNNCCA_ERR_BAD_ARG;
   if (reid && (reid_cols <= 0 || !reid_rnorm || !reid_scratch)) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   int launches = 0;
-  if (node) {                                           // fork: the node norms depend on nothing this call launches
-    SideStream* side = side_stream();
+  SideStream* side = nullptr;
+  if (node) {                                           // fork point: the node norms depend on nothing this call launches
+    side = side_stream();
     if (!side) { set_error_text("gnncca_graph_prepare_all: could not create the side stream"); return GNNCCA_ERR_LAUNCH; }
-    int rc = check_cuda(cudaEventRecord(side->fork, st));
-    if (!rc) rc = check_cuda(cudaStreamWaitEvent(side->st, side->fork, 0));
-    if (!rc) rc = gnncca_colnorm_norms(node, n_nodes, node_cols, node_scratch, node_norm, side->st);
-    if (!rc) rc = check_cuda(cudaEventRecord(side->join, side->st));
+    const int rc = check_cuda(cudaEventRecord(side->fork, st));
     if (rc) return rc;
   }
   PrepLayout L = prep_layout(scratch, n_graphs, n_nodes);
@@ -786,7 +770,15 @@ extern "C" int gnncca_graph_prepare_all(const int64_t* graph_ptr, const int32_t*
   prep_pass_kernel<<<(unsigned)(n_reid + n_graphs), 256, 0, st>>>(p);
   prep_final_kernel<<<(unsigned)(2 + (reid_fused ? ceil_div(reid_cols, 32) : 0)), 1024, 0, st>>>(p);
   launches += 2;
-  return check_launch(launches);
+  int rc = check_launch(launches);
+  if (rc || !node) return rc;
+  // The side stream's launches come second (what the host waits for, the totals, is in the two launches above) but BEFORE the
+  // edge fill is enqueued: the pass then runs while the host sizes and launches the fill.  Launched after the fill it finds
+  // every SM's registers taken by the fill's CTAs and runs behind it (measured: 152 us instead of 131 us per build at cfg 2).
+  rc = check_cuda(cudaStreamWaitEvent(side->st, side->fork, 0));
+  if (!rc) rc = gnncca_colnorm_norms(node, n_nodes, node_cols, node_scratch, node_norm, side->st);
+  if (!rc) rc = check_cuda(cudaEventRecord(side->join, side->st));
+  return rc;
 }
 
 extern "C" int gnncca_graph_join(void* stream) {
@@ -794,6 +786,7 @@ extern "C" int gnncca_graph_join(void* stream) {
   if (!side) return GNNCCA_ERR_LAUNCH;
   return check_cuda(cudaStreamWaitEvent((cudaStream_t)stream, side->join, 0));
 }
+
 
 // {n_tiles, n_edges, max nodes per frame, max edges per frame, camera-order flag} of the last gnncca_graph_edge_counts live in the
 // scratch, next to each other (5 x int64): the host reads them with ONE copy to size step 2 (and the capacity class of the fused

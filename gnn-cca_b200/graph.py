@@ -147,6 +147,23 @@ def _poll_totals(arr, what: str = "graph_prepare_all"):
     return tuple(int(v) for v in arr[:5])
 
 
+_E_GUESS = {}         # (B, N) -> E of the last batch of that shape
+
+
+def _alloc_outputs(E: int, width: int, dev):
+    return (torch.empty((2, E), dtype=torch.int64, device=dev), torch.empty((E, width), dtype=torch.float32, device=dev),
+            torch.empty(E, dtype=torch.float32, device=dev))
+
+
+_SIZES = {}           # (B, N, R, F) -> byte sizes of the parts of the work buffer
+
+
+def _as(t: torch.Tensor, dev: torch.device, dtype) -> torch.Tensor:
+    if t.dtype is dtype and t.device == dev and t.is_contiguous():
+        return t
+    return t.to(device=dev, dtype=dtype).contiguous()
+
+
 def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.Tensor, xw: torch.Tensor, yw: torch.Tensor,
                       max_dist: torch.Tensor, reid_embeds: torch.Tensor, node_embeds: torch.Tensor, mode: str = "full",
                       l2norm: bool = True, lazy_x: bool = True) -> Batch:
@@ -165,42 +182,50 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     if dev.type != "cuda":
         raise RuntimeError("gnn-cca_b200 builds graphs on CUDA tensors only (no CPU path)")
     attr_mode = _lib.ATTR_MODES[mode]
-    graph_ptr = graph_ptr.to(device=dev, dtype=torch.int64).contiguous()
+    graph_ptr = _as(graph_ptr, dev, torch.int64)
     B, N = int(graph_ptr.numel()) - 1, int(node_embeds.size(0))
-    id_cam32 = id_cam.to(device=dev, dtype=torch.int32).contiguous()
-    ids64 = ids.to(device=dev, dtype=torch.int64).contiguous()
-    xw = xw.to(device=dev, dtype=torch.float64).contiguous()
-    yw = yw.to(device=dev, dtype=torch.float64).contiguous()
-    max_dist = max_dist.to(device=dev, dtype=torch.float64).contiguous()
+    id_cam32 = _as(id_cam, dev, torch.int32)
+    ids64 = _as(ids, dev, torch.int64)
+    xw = _as(xw, dev, torch.float64)
+    yw = _as(yw, dev, torch.float64)
+    max_dist = _as(max_dist, dev, torch.float64)
     for name, t in (("reid_embeds", reid_embeds), ("node_embeds", node_embeds)):
         if t.dim() != 2 or t.dtype != torch.float32 or t.device != dev:
             raise ValueError("%s must be a 2-D float32 tensor on %s" % (name, dev))
-    nbytes = int(lib.gnncca_graph_prepare_scratch_bytes(B, N))
-    scratch = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
-    nbytes = scratch.numel() * 8
+    R, F = int(reid_embeds.size(1)), int(node_embeds.size(1))
+    # one work buffer: [frame tables | reciprocal ReID norms | ReID partial sums | node partial sums], 256-byte aligned parts
+    sizes = _SIZES.get((B, N, R, F))
+    if sizes is None:
+        up = lambda n: (int(n) + 255) & ~255
+        sizes = _SIZES[(B, N, R, F)] = (up(lib.gnncca_graph_prepare_scratch_bytes(B, N)), up(4 * R),
+                                        up(lib.gnncca_colnorm_scratch_bytes(N, R)), up(lib.gnncca_colnorm_scratch_bytes(N, F)))
+        if len(_SIZES) > 64:
+            _SIZES.clear()
+    nbytes = sizes[0]
+    work = torch.empty(sum(sizes) // 8, dtype=torch.int64, device=dev)
+    scratch_p = work.data_ptr()
     edge_ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
     stream = _stream()
     need_reid = mode != "only_dist"
-    x_kw, reid_rnorm, join = {}, None, False
+    x_kw, rnorm_p, join, pre_out, guess = {}, None, False, None, None
 
-    fused_ok = not need_reid or (reid_embeds.size(1) % 4 == 0 and reid_embeds.size(1) <= 1024 and reid_embeds.data_ptr() % 16 == 0)
+    fused_ok = not need_reid or (R % 4 == 0 and R <= 1024 and reid_embeds.data_ptr() % 16 == 0)
     if l2norm and B > 0 and N > 0 and fused_ok:
         reid = reid_embeds.contiguous()
         node = node_embeds.contiguous()
-        R, F = int(reid.size(1)), int(node.size(1))
-        f4 = lambda n: (n + 3) & ~3
-        n_rs = f4(int(lib.gnncca_colnorm_scratch_bytes(N, R)) // 4) if need_reid else 0
-        n_ns = f4(int(lib.gnncca_colnorm_scratch_bytes(N, F)) // 4) if lazy_x else 0
-        tmp = torch.empty(f4(R) + n_rs + n_ns, dtype=torch.float32, device=dev)      # [reid norms | reid partials | node partials]
-        if need_reid:
-            reid_rnorm = tmp[:R]
+        rnorm_p = scratch_p + sizes[0] if need_reid else None
         x_norm = torch.empty(F, dtype=torch.float32, device=dev) if lazy_x else None
         tot_t, tot = _pinned_totals(dev)
         _lib.check(lib.gnncca_graph_prepare_all(
-            _lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr), _lib.ptr(scratch), nbytes,
-            _lib.ptr(node) if lazy_x else None, F, _lib.ptr(x_norm), (tmp.data_ptr() + 4 * (f4(R) + n_rs)) if lazy_x else None,
-            _lib.ptr(reid) if need_reid else None, R, _lib.ptr(reid_rnorm), (tmp.data_ptr() + 4 * f4(R)) if need_reid else None,
+            graph_ptr.data_ptr(), id_cam32.data_ptr(), B, N, edge_ptr.data_ptr(), scratch_p, nbytes,
+            node.data_ptr() if lazy_x else None, F, _lib.ptr(x_norm), (scratch_p + sizes[0] + sizes[1] + sizes[2]) if lazy_x else None,
+            reid.data_ptr() if need_reid else None, R, rnorm_p, (scratch_p + sizes[0] + sizes[1]) if need_reid else None,
             tot_t.data_ptr(), stream), "graph_prepare_all")
+        # the outputs are sized by E, which is on its way from the device: allocate for the E the last batch of this shape had
+        # while waiting (a loader's batches repeat their shape); a wrong guess costs three cached allocations
+        guess = _E_GUESS.get((B, N))
+        if guess is not None:
+            pre_out = _alloc_outputs(guess, 4 if mode == "full" else 2, dev)
         join = lazy_x
         if lazy_x:
             x_kw = dict(x_raw=node, x_norm=x_norm)
@@ -215,23 +240,26 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
         else:
             reid, x_kw = reid_embeds.contiguous(), dict(x=node_embeds.contiguous())
         _lib.check(lib.gnncca_graph_edge_counts(_lib.ptr(graph_ptr), _lib.ptr(id_cam32), B, N, _lib.ptr(edge_ptr),
-                                                _lib.ptr(scratch), nbytes, stream), "graph_edge_counts")
+                                                scratch_p, nbytes, stream), "graph_edge_counts")
         # the output size is data dependent: one 40-byte read back (the reference syncs several times per FRAME)
         if B > 0:
-            off = (lib.gnncca_graph_tile_total_ptr(_lib.ptr(scratch), B, N) - scratch.data_ptr()) // 8
-            n_tiles, E, max_n, max_e, cam_unsorted = (int(v) for v in scratch[off:off + 5].tolist())
+            off = (lib.gnncca_graph_tile_total_ptr(scratch_p, B, N) - scratch_p) // 8
+            n_tiles, E, max_n, max_e, cam_unsorted = (int(v) for v in work[off:off + 5].tolist())
         else:
             n_tiles = E = max_n = max_e = cam_unsorted = 0
     caps = (max_n, max_e)      # exact frame maxima: sizes the fused all-steps kernel without guessing
 
-    width = 4 if mode == "full" else 2
-    edge_index = torch.empty((2, E), dtype=torch.int64, device=dev)
-    edge_attr = torch.empty((E, width), dtype=torch.float32, device=dev)
-    edge_labels = torch.empty(E, dtype=torch.float32, device=dev)
-    _lib.check(lib.gnncca_build_graphs(_lib.ptr(graph_ptr), _lib.ptr(edge_ptr), B, N, E, n_tiles, _lib.ptr(id_cam32),
-                                       _lib.ptr(ids64), _lib.ptr(xw), _lib.ptr(yw), _lib.ptr(max_dist), _lib.ptr(reid),
-                                       _lib.ptr(reid_rnorm), int(reid.size(1)), attr_mode, max_n, _lib.ptr(scratch), _lib.ptr(edge_index),
-                                       _lib.ptr(edge_attr), _lib.ptr(edge_labels), stream), "build_graphs")
+    if pre_out is not None and guess == E:
+        edge_index, edge_attr, edge_labels = pre_out
+    else:
+        edge_index, edge_attr, edge_labels = _alloc_outputs(E, 4 if mode == "full" else 2, dev)
+        if len(_E_GUESS) > 64:
+            _E_GUESS.clear()
+        _E_GUESS[(B, N)] = E
+    _lib.check(lib.gnncca_build_graphs(graph_ptr.data_ptr(), edge_ptr.data_ptr(), B, N, E, n_tiles, id_cam32.data_ptr(),
+                                       ids64.data_ptr(), xw.data_ptr(), yw.data_ptr(), max_dist.data_ptr(), reid.data_ptr(),
+                                       rnorm_p, R, attr_mode, max_n, scratch_p, edge_index.data_ptr(),
+                                       edge_attr.data_ptr(), edge_labels.data_ptr(), stream), "build_graphs")
     if join:
         _lib.check(lib.gnncca_graph_join(stream), "graph_join")
     # "trusted" = source-major by construction: true only when every frame's rows are in ascending camera order (the reference

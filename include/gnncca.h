@@ -428,14 +428,14 @@ int gnncca_build_graphs(const int64_t* graph_ptr, const int64_t* edge_ptr, int64
  *   on `stream`, two launches: frame tables + ReID partial sums, then the scans + the RECIPROCAL ReID column norms ->
  *   reid_rnorm[reid_cols] (what gnncca_build_graphs takes; reid_cols % 4 == 0, <= 1024, 16-byte aligned rows);
  *   on a library-owned side stream (forked from `stream`, one per device, created at the first call): the norms of the node
- *   embeddings -> node_norm[node_cols]; nothing in graph construction reads them, so their HBM-bound pass runs beside
- *   gnncca_build_graphs.  gnncca_graph_join(stream) makes `stream` wait for them: call it once after gnncca_build_graphs has
- *   been enqueued (capturable: an event fork / join).  One host thread per device.
+ *   embeddings -> node_norm[node_cols]; nothing in graph construction reads them, so their HBM-bound pass runs while the
+ *   host sizes and launches gnncca_build_graphs.  gnncca_graph_join(stream) makes `stream` wait for them: call it once after
+ *   gnncca_build_graphs has been enqueued (capturable: an event fork / join).  One host thread per device.
  * node / reid may be NULL (that block is skipped); *_scratch: gnncca_colnorm_scratch_bytes(n_nodes, cols) each.
  * totals_host (optional): 8 int64 words of PINNED host memory the device can write (cudaHostAlloc / torch pin_memory).  The
  * scan blocks store the five totals of gnncca_graph_tile_total_ptr there themselves, fence, and then set the check words
  * [5] and [6] to GNNCCA_TOTALS_MAGIC: a caller that cleared [5], [6] before the call polls them instead of synchronising the
- * stream, and sizes step 2 while the norm passes are still running. */
+ * stream, and sizes step 2 while the norm pass is still running. */
 #define GNNCCA_TOTALS_MAGIC 0x5eed5eed5eedLL
 int gnncca_graph_prepare_all(const int64_t* graph_ptr, const int32_t* id_cam, int64_t n_graphs, int64_t n_nodes,
                              int64_t* edge_ptr, void* scratch, int64_t scratch_bytes,

@@ -75,3 +75,41 @@ def test_full_size_properties_cfg2(cuda_device):
     assert torch.equal(lab, (det["ids"][src] == det["ids"][dst]).float())
     assert abs(float(lab.mean()) - 3 / 18) < 1e-6                              # C-1 positives per node
     assert bool((b.edge_attr[:, :3] >= 0).all()) and bool((b.edge_attr[:, 3].abs() <= 1 + 1e-5).all())
+
+
+@pytest.mark.parametrize("reid_dim,mode,lazy", [(256, "full", True), (64, "full", False), (6, "full", True), (20, "only_appearance", True),
+                                                (256, "only_dist", True), (1028, "full", True)])
+def test_every_launch_structure_of_build_graph_batch_matches_the_oracle(reid_dim, mode, lazy, cuda_device):
+    """The single prepare call (ReID norms fused into the frame-table launches, node norms on the side stream, totals polled from
+    pinned memory, ReID rows normalised while staged) and the separate-launch path taken for ReID widths it does not accept
+    (6: not a multiple of 4; 1028: wider than 1024) give what the CPU restatement of the reference loop gives; ragged frames of
+    up to ~60 detections so that one-tile frames, diagonal and off-diagonal tiles of larger frames and an empty camera all occur.
+    Two builds in a row: the second one finds the previous batch's size as its output-size guess (wrong on purpose)."""
+    import gnncca
+    from oracle import graph_oracle
+    rng = np.random.default_rng(reid_dim)
+    for frames_n in (7, 5):
+        frames, ptr = [], [0]
+        for _ in range(frames_n):
+            counts = rng.integers(0, 15, 5)
+            counts[rng.integers(0, 5)] += 1
+            cam = np.repeat(np.arange(5), counts).astype(np.int64)
+            n = len(cam)
+            frames.append(dict(id=rng.integers(0, 12, n).astype(np.int64), id_cam=cam, xw=rng.random(n) * 300, yw=rng.random(n) * 200))
+            ptr.append(ptr[-1] + n)
+        N = ptr[-1]
+        g = torch.Generator().manual_seed(N)
+        reid = torch.relu(torch.randn((N, reid_dim), generator=g))
+        node = torch.relu(torch.randn((N, 96), generator=g))
+        md = [50.83 + k for k in range(frames_n)]
+        ref = graph_oracle.build_batch(frames, reid, node, md, mode=mode)
+        cat = lambda k, dt: torch.from_numpy(np.concatenate([f[k] for f in frames])).to(cuda_device, dt)
+        b = gnncca.build_graph_batch(torch.tensor(ptr, device=cuda_device), cat("id_cam", torch.int32), cat("id", torch.int64),
+                                     cat("xw", torch.float64), cat("yw", torch.float64), torch.tensor(md, dtype=torch.float64, device=cuda_device),
+                                     reid.to(cuda_device), node.to(cuda_device), mode=mode, lazy_x=lazy)
+        assert (b.raw_x() is not None) == lazy
+        assert torch.equal(b.edge_index.cpu(), ref.edge_index)
+        assert torch.equal(b.edge_labels.cpu(), ref.edge_labels.float())
+        np.testing.assert_allclose(b.edge_attr.cpu().numpy(), ref.edge_attr.numpy(), rtol=1e-5, atol=2e-6)
+        np.testing.assert_allclose(b.x.cpu().numpy(), ref.x.numpy(), rtol=2e-6, atol=1e-9)
+        assert b.gnncca_caps[0] == max(len(f["id"]) for f in frames)

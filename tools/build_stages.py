@@ -55,6 +55,7 @@ def main():
     ap.add_argument("--reps", type=int, default=200)
     ap.add_argument("--flush", action="store_true", help="write 256 MB between repetitions (cold L2)")
     ap.add_argument("--profile", action="store_true", help="cProfile of 2000 build_graph_batch calls (host side)")
+    ap.add_argument("--trace", action="store_true", help="host time stamps at every C call of build_graph_batch (median over --reps)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     det = syn.make_detections(a.cams, a.dets, a.frames, seed=5, device=dev)
@@ -64,6 +65,38 @@ def main():
     print("N = %d nodes, E = %d edges, %d frames" % (b.num_nodes, b.num_edges, a.frames))
     m, lo = wall(lambda: gnncca.build_graph_batch(**det), a.reps, flush)
     print("build_graph_batch wall: median %.1f us min %.1f us" % (m, lo))
+    if a.trace:
+        lib = _lib.load()
+        marks = []
+        names = ["gnncca_graph_prepare_all", "gnncca_build_graphs", "gnncca_graph_join"]
+        orig = {n: getattr(lib, n) for n in names}
+        orig_poll = graph._poll_totals
+
+        def wrap(n, f):
+            def g(*args):
+                marks.append((n + ":enter", time.perf_counter()))
+                r = f(*args)
+                marks.append((n + ":exit", time.perf_counter()))
+                return r
+            return g
+        for n in names:
+            setattr(lib, n, wrap(n, orig[n]))
+        graph._poll_totals = wrap("poll_totals", orig_poll)
+        rows = []
+        for _ in range(a.reps):
+            torch.cuda.synchronize()
+            del marks[:]
+            t0 = time.perf_counter()
+            gnncca.build_graph_batch(**det)
+            t1 = time.perf_counter()
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            rows.append([(k, (t - t0) * 1e6) for k, t in marks] + [("return", (t1 - t0) * 1e6), ("synchronized", (t2 - t0) * 1e6)])
+        for i, (k, _) in enumerate(rows[0]):
+            print("  %-34s %7.1f us" % (k, statistics.median(r[i][1] for r in rows)))
+        for n in names:
+            setattr(lib, n, orig[n])
+        graph._poll_totals = orig_poll
     if a.profile:
         import cProfile
         import pstats
