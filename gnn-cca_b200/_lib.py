@@ -49,6 +49,7 @@ SIGNATURES = {
     "gnncca_csr_from_edge_index": (C.c_int, [vp, i64, i64, vp, vp, vp, vp, vp]),
     "gnncca_csr_from_edge_rows": (C.c_int, [vp, vp, i64, i64, i64, vp, vp, vp, vp, vp]),
     "gnncca_segment_agg": (C.c_int, [vp, vp, i64, i32, i32, vp, vp]),
+    "gnncca_csr_reverse_edges": (C.c_int, [vp, vp, vp, i64, i64, vp, vp, vp]),
     "gnncca_csr_sort_workspace_bytes": (i64, [i64, i64]),
     "gnncca_csr_sort": (C.c_int, [i64, i64, vp, vp, vp, vp, vp, i64, vp]),
     "gnncca_permute_rows": (C.c_int, [vp, vp, vp, i64, i32, i32, vp]),
@@ -81,8 +82,8 @@ SIGNATURES = {
     "gnncca_linear_bwd": (C.c_int, [vp, vp, vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, i32, vp]),
     "gnncca_finalize_grads": (C.c_int, [C.POINTER(FinSeg), i32, vp]),
     "gnncca_loss_blocks": (i32, [i64]),
-    "gnncca_bce_stats_fwd": (C.c_int, [C.POINTER(vp), i32, vp, i64, C.c_float, i32, C.c_float, C.c_float, vp, vp, vp, vp]),
-    "gnncca_bce_stats_bwd": (C.c_int, [C.POINTER(vp), C.POINTER(vp), i32, vp, i64, C.c_float, vp, vp]),
+    "gnncca_bce_stats_fwd": (C.c_int, [C.POINTER(vp), i32, vp, i64, C.c_float, i32, C.c_float, C.c_float, vp, vp, vp, vp, vp]),
+    "gnncca_bce_stats_bwd": (C.c_int, [C.POINTER(vp), C.POINTER(vp), i32, vp, i64, C.c_float, vp, vp, vp]),
     "gnncca_frame_clusters": (C.c_int, [vp, i32, vp, i64, vp, vp, i64, i64, i32, vp, vp, vp, vp, vp, vp]),
     "gnncca_foot_to_world": (C.c_int, [vp, vp, vp, vp, vp, i32, i64, vp, vp, vp, vp]),
     "gnncca_frame_valid": (C.c_int, [vp, vp, vp, vp, i64, vp, vp]),

@@ -83,6 +83,13 @@ class _MPNFunction(torch.autograd.Function):
 
         # transposed CSR (edges grouped by target) for the gQ reduction of the backward; kept with the plan, which the
         # module caches on the batch object while edge_index is unchanged
+        if getattr(plan, "tperm", None) is None and trusted and plan.perm is None:
+            # build_graph_batch output: symmetric, targets ascending inside every source segment -- the target-major permutation
+            # is the reverse-edge table (one launch, no sort), its offsets are rowptr; flags[3] reports a broken promise
+            tperm = torch.empty(E, dtype=torch.int32, device=dev)
+            _lib.check(lib.gnncca_csr_reverse_edges(P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(tperm), P(plan.flags), _stream()),
+                       "csr_reverse_edges")
+            plan.tperm, plan.colptr = tperm, plan.rowptr
         if getattr(plan, "tperm", None) is None:
             key, other = plan.dst.clone(), plan.src.clone()
             tperm = torch.empty(E, dtype=torch.int32, device=dev)
@@ -120,15 +127,23 @@ class _MPNFunction(torch.autograd.Function):
         be = _blocks(lib, E, _lib.BLOCKS_PER_EDGE)
         for step in range(1, L + 1):
             Pn, Qn, Rn = proj[step - 1, :N * 8], proj[step - 1, N * 8:N * 16], proj[step - 1, N * 16:]
-            _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), P(h0), P(hs[-1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
+            if step == 1:      # later steps: projected by the previous step's fold launch (gnncca_mp_step_fwd_next), bit-equal
+                _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), P(h0), P(hs[-1]), N, P(Pn), P(Qn), P(Rn), _stream()), "node_project")
             e_out = torch.empty_like(e0)
             h_out = torch.empty((N, sb.f_node), dtype=torch.float32, device=dev) if step < L else None
             classify = step >= first
             inline = classify and bn_mode != "train"
             logits = torch.empty((E, 1), dtype=torch.float32, device=dev) if classify else None
-            _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(Pn), P(Qn), P(Rn),
-                                              P(e0) if model.reattach_initial_edges else 0, P(es[-1]), P(e_out), P(h_out),
-                                              P(logits) if inline else 0, guard, P(wsp), ws_bytes, _stream()), "mp_step_fwd")
+            if step < L:
+                Px, Qx, Rx = proj[step, :N * 8], proj[step, N * 8:N * 16], proj[step, N * 16:]
+                _lib.check(lib.gnncca_mp_step_fwd_next(C.byref(sb.cfg), C.byref(sb.w), P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(Pn), P(Qn), P(Rn),
+                                                       0, 4, 0, 0, P(e0) if model.reattach_initial_edges else 0, P(es[-1]), P(e_out), P(h_out),
+                                                       P(logits) if inline else 0, P(h0), P(Px), P(Qx), P(Rx), guard, P(wsp), ws_bytes, _stream()),
+                           "mp_step_fwd_next")
+            else:
+                _lib.check(lib.gnncca_mp_step_fwd(C.byref(sb.cfg), C.byref(sb.w), P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(Pn), P(Qn), P(Rn),
+                                                  P(e0) if model.reattach_initial_edges else 0, P(es[-1]), P(e_out), P(h_out),
+                                                  P(logits) if inline else 0, guard, P(wsp), ws_bytes, _stream()), "mp_step_fwd")
             es.append(e_out)
             hs.append(h_out)
             if classify and bn_mode == "train":       # BatchNorm1d with batch statistics over all E edges (mlp.py:16)
@@ -281,7 +296,9 @@ class _MPNFunction(torch.autograd.Function):
         chunks = _blocks(lib, rows, _lib.BLOCKS_ROW_CHUNKS)
         for i in range(len(enc_n.layer_specs) - 1, -1, -1):
             sp, lin = enc_n.layer_specs[i], enc_n.linear(i)
-            splits = max(1, min(8, rows // 256))
+            # row splits of the weight-gradient GEMM: all its CTAs in ONE wave (3 per SM) with as few iterations each as that allows
+            tiles = ((sp.in_dim + 63) // 64) * ((sp.out_dim + 63) // 64)
+            splits = max(1, min(rows // 64, 444 // tiles))
             gz = torch.empty((rows, sp.out_dim), dtype=torch.float32, device=dev)
             gx = torch.empty((rows, sp.in_dim), dtype=torch.float32, device=dev) if i > 0 else None
             gbp = torch.empty((chunks, sp.out_dim), dtype=torch.float32, device=dev)

@@ -128,6 +128,38 @@ extern "C" int gnncca_csr_from_edge_rows(const int64_t* row, const int64_t* col,
   return check_launch();
 }
 
+// Reverse-edge table of a SYMMETRIC source-major graph whose segments list their targets in ascending order (what the
+// camera-by-camera enumeration of train.py:292-299 gives for camera-major rows): position q holds the edge (j -> i); its
+// reverse (i -> j) sits in i's segment at the lower bound of j.  That table IS the target-major permutation a stable sort by
+// dst would produce (the in-edges of j in ascending source order are the reverses of j's out-edges in order), and the
+// target-major offsets equal rowptr.  flags[3] is raised when some edge has no reverse (the table entry is then q itself).
+__global__ void __launch_bounds__(256) csr_reverse_edges_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
+                                                                const int32_t* __restrict__ dst, int64_t n_edges, int32_t* __restrict__ tperm,
+                                                                int32_t* __restrict__ flags) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_edges; q += stride) {
+    const int j = src[q], i = dst[q];
+    int lo = rowptr[i], hi = rowptr[i + 1];
+    const int end = hi;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (dst[mid] < j) lo = mid + 1; else hi = mid; }
+    if (lo < end && dst[lo] == j) {
+      tperm[q] = lo;
+    } else {
+      tperm[q] = (int32_t)q;
+      flags[3] = 1;
+    }
+  }
+}
+
+extern "C" int gnncca_csr_reverse_edges(const int32_t* rowptr, const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges,
+                                        int32_t* tperm, int32_t* flags, void* stream) {
+  if (n_nodes < 0 || n_edges < 0 || n_edges >= INT32_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (n_edges == 0) return GNNCCA_OK;
+  if (!rowptr || !src || !dst || !tperm || !flags) return GNNCCA_ERR_BAD_ARG;
+  csr_reverse_edges_kernel<<<grid_for(n_edges, 256), 256, 0, (cudaStream_t)stream>>>(rowptr, src, dst, n_edges, tperm, flags);
+  return check_launch();
+}
+
 extern "C" int64_t gnncca_csr_sort_workspace_bytes(int64_t n_nodes, int64_t n_edges) {
   if (n_edges <= 0) return 256;
   size_t temp = 0;

@@ -81,7 +81,8 @@ __global__ void __launch_bounds__(THREADS) stats_kernel(const Ptrs p, int k, con
 
 // out[5k + 4] (double): [k mean l][k mean_{y=1} pl][k mean_{y=0} pl][k mean_{y=1} sigmoid][k mean_{y=0} sigmoid],
 // then n1, n0, correct1, correct0.  Empty classes give NaN means, as torch.mean of an empty tensor does.
-__global__ void finalize_kernel(const double* __restrict__ partials, int blocks, int k, int64_t E, double* __restrict__ out) {
+__global__ void finalize_kernel(const double* __restrict__ partials, int blocks, int k, int64_t E, double* __restrict__ out,
+                                float* __restrict__ loss_sum) {
   const int width = PER * k + 4;
   __shared__ double sums[PER * MAX_STEPS + 4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -104,16 +105,22 @@ __global__ void finalize_kernel(const double* __restrict__ partials, int blocks,
       out[4 * k + s] = sums[PER * s + 4] / n0;
     }
     for (int i = 0; i < 4; ++i) out[PER * k + i] = sums[PER * k + i];
+    if (loss_sum) {                       // the summed loss of train.py:80-97 for the non-focal criteria: sum of the step means
+      double tot = 0.0;
+      for (int s = 0; s < k; ++s) tot += out[s];
+      *loss_sum = (float)tot;
+    }
   }
 }
 
 // g[s][i] = up[s] / E * d l / d x: the seed of the MPN's backward for loss = sum_s w_s mean_i l(x_s,i) (up[s] = d loss / d mean_s)
 __global__ void __launch_bounds__(THREADS) grad_kernel(const Ptrs p, int k, const float* __restrict__ labels, int64_t E, float pw,
-                                                       const double* __restrict__ up) {
+                                                       const double* __restrict__ up, const float* __restrict__ up_sum) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float scale[MAX_STEPS];
+  const double common = up_sum ? (double)*up_sum : 0.0;     // d loss / d loss_sum reaches every step mean with weight 1
 #pragma unroll
-  for (int s = 0; s < MAX_STEPS; ++s) scale[s] = s < k ? (float)(up[s] / (double)E) : 0.f;
+  for (int s = 0; s < MAX_STEPS; ++s) scale[s] = s < k ? (float)(((up ? up[s] : 0.0) + common) / (double)E) : 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < E; i += stride) {
     const float y = labels[i];
 #pragma unroll
@@ -130,25 +137,27 @@ using namespace gnncca;
 extern "C" int32_t gnncca_loss_blocks(int64_t n_edges) { return (int32_t)grid_for(n_edges, loss::THREADS, 4); }
 
 extern "C" int gnncca_bce_stats_fwd(const float* const* host_logits, int32_t n_steps, const float* labels, int64_t n_edges, float pos_weight,
-                                    int32_t focal, float focus, float balance, float* probs, double* partials, double* out, void* stream) {
+                                    int32_t focal, float focus, float balance, float* probs, double* partials, double* out, float* loss_sum,
+                                    void* stream) {
   if (n_steps < 1 || n_steps > loss::MAX_STEPS || n_edges < 1 || !host_logits || !labels || !partials || !out) return GNNCCA_ERR_BAD_ARG;
   loss::Ptrs p{};
   for (int s = 0; s < n_steps; ++s) { if (!host_logits[s]) return GNNCCA_ERR_BAD_ARG; p.logits[s] = host_logits[s]; }
   const int blocks = gnncca_loss_blocks(n_edges);
   cudaStream_t st = (cudaStream_t)stream;
   loss::stats_kernel<<<blocks, loss::THREADS, 0, st>>>(p, n_steps, labels, n_edges, pos_weight, focal, focus, balance, probs, partials);
-  loss::finalize_kernel<<<1, 256, 0, st>>>(partials, blocks, n_steps, n_edges, out);
+  loss::finalize_kernel<<<1, 256, 0, st>>>(partials, blocks, n_steps, n_edges, out, loss_sum);
   return check_launch(2);
 }
 
 extern "C" int gnncca_bce_stats_bwd(const float* const* host_logits, float* const* host_grads, int32_t n_steps, const float* labels,
-                                    int64_t n_edges, float pos_weight, const double* upstream, void* stream) {
-  if (n_steps < 1 || n_steps > loss::MAX_STEPS || n_edges < 1 || !host_logits || !host_grads || !labels || !upstream) return GNNCCA_ERR_BAD_ARG;
+                                    int64_t n_edges, float pos_weight, const double* upstream, const float* upstream_sum, void* stream) {
+  if (n_steps < 1 || n_steps > loss::MAX_STEPS || n_edges < 1 || !host_logits || !host_grads || !labels || (!upstream && !upstream_sum))
+    return GNNCCA_ERR_BAD_ARG;
   loss::Ptrs p{};
   for (int s = 0; s < n_steps; ++s) {
     if (!host_logits[s] || !host_grads[s]) return GNNCCA_ERR_BAD_ARG;
     p.logits[s] = host_logits[s]; p.out[s] = host_grads[s];
   }
-  loss::grad_kernel<<<gnncca_loss_blocks(n_edges), loss::THREADS, 0, (cudaStream_t)stream>>>(p, n_steps, labels, n_edges, pos_weight, upstream);
+  loss::grad_kernel<<<gnncca_loss_blocks(n_edges), loss::THREADS, 0, (cudaStream_t)stream>>>(p, n_steps, labels, n_edges, pos_weight, upstream, upstream_sum);
   return check_launch();
 }

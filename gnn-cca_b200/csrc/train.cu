@@ -455,7 +455,7 @@ __global__ void __launch_bounds__(TB) edge_enc_bwd_kernel(const float* edge_attr
 // G. dense layer backward (node encoder, mlp.py:14,18): gz = gy * [y > 0]; gb partials; gW = gz^T x (split over rows);
 //    gx = gz W.
 // ------------------------------------------------------------------------------------------------
-constexpr int RG_ROWS = 64;
+constexpr int RG_ROWS = 16;
 // 256 threads = (256 / out_dim) row lanes x out_dim columns: every lane sums its rows of the chunk in order, the lanes are
 // folded in lane order (fixed summation order).  out_dim > 256: one row lane, columns strided.
 __global__ void __launch_bounds__(256) relu_grad_bias_kernel(const float* __restrict__ y, const float* __restrict__ gy, int relu, int64_t rows,
@@ -486,45 +486,102 @@ __global__ void __launch_bounds__(256) relu_grad_bias_kernel(const float* __rest
   }
 }
 
-// C[m][n] = sum_r A[r][m] * B[r][n] over this split's rows; 64 x 64 tile, 16 rows per iteration
+// C[m][n] = sum_r A[r][m] * B[r][n] over this split's rows (the weight gradient gz^T x of a dense layer).  64 x 64 tile per CTA,
+// 32 rows per iteration, on the tensor cores with fp32-level accuracy: every operand is split into its tf32 prefix and the
+// (tf32-rounded) rest, and hi.hi + hi.lo + lo.hi are three mma.sync m16n8k8 into one fp32 accumulator (the dropped lo.lo term is
+// below 2^-22 of the product).  8 warps = 2 (m) x 4 (n), a warp owns 32 x 16 outputs.  Fixed summation order: bit-reproducible.
+__device__ __forceinline__ uint32_t f2tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32_u(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+constexpr int ATB_ROWS = 32, ATB_LD = 72;      // row stride 72: the fragment loads (k = lane & 3, m = lane >> 2) hit 32 banks
 __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t rows, int M, int Nn,
                                                   int64_t rows_per_split, float* __restrict__ partial /* [splits][M*Nn] */) {
-  __shared__ float as[16][64 + 4], bs[16][64 + 4];
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  __shared__ __align__(16) float as[ATB_ROWS][ATB_LD], bs[ATB_ROWS][ATB_LD];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int wm = (warp >> 2) * 32, wn = (warp & 3) * 16;
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
   const int64_t r_begin = (int64_t)blockIdx.z * rows_per_split, r_end = min(r_begin + rows_per_split, rows);
-  float2 acc[4][2] = {};                              // 4 x 4 outputs as column pairs: packed FFMA2, b pairs straight from the float4
-  const int lr = tid >> 4, lc = (tid & 15) * 4;       // 16 rows x 64 columns per load wave
-  for (int64_t r0 = r_begin; r0 < r_end; r0 += 16) {
-    const int64_t r = r0 + lr;
+  const bool vec = (M % 4 == 0) && (Nn % 4 == 0) && ((((uintptr_t)A | (uintptr_t)B) & 15) == 0);
+  float acc[2][2][4] = {};
+  // 32 rows x 64 columns of each operand per iteration: 512 float4 per operand, 2 per thread; the next iteration's tile
+  // travels in registers while this one is in the tensor cores
+  float4 va[2], vb[2];
+  auto fetch = [&](const int64_t r0) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      as[lr][lc + u] = (r < r_end && m0 + lc + u < M) ? A[r * M + m0 + lc + u] : 0.f;
-      bs[lr][lc + u] = (r < r_end && n0 + lc + u < Nn) ? B[r * Nn + n0 + lc + u] : 0.f;
+    for (int u = 0; u < 2; ++u) {
+      const int idx = tid + u * 256, lr = idx >> 4, lc = (idx & 15) * 4;
+      const int64_t r = r0 + lr;
+      va[u] = make_float4(0.f, 0.f, 0.f, 0.f); vb[u] = va[u];
+      if (r < r_end) {
+        if (vec) {
+          if (m0 + lc < M) va[u] = __ldg(reinterpret_cast<const float4*>(A + r * M + m0 + lc));
+          if (n0 + lc < Nn) vb[u] = __ldg(reinterpret_cast<const float4*>(B + r * Nn + n0 + lc));
+        } else {
+          float ta[4], tb[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            ta[q] = (m0 + lc + q < M) ? A[r * M + m0 + lc + q] : 0.f;
+            tb[q] = (n0 + lc + q < Nn) ? B[r * Nn + n0 + lc + q] : 0.f;
+          }
+          va[u] = make_float4(ta[0], ta[1], ta[2], ta[3]); vb[u] = make_float4(tb[0], tb[1], tb[2], tb[3]);
+        }
+      }
+    }
+  };
+  if (r_begin < r_end) fetch(r_begin);
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += ATB_ROWS) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int idx = tid + u * 256, lr = idx >> 4, lc = (idx & 15) * 4;
+      *reinterpret_cast<float4*>(&as[lr][lc]) = va[u];
+      *reinterpret_cast<float4*>(&bs[lr][lc]) = vb[u];
     }
     __syncthreads();
+    if (r0 + ATB_ROWS < r_end) fetch(r0 + ATB_ROWS);
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      const float4 a = *reinterpret_cast<const float4*>(&as[k][ty * 4]);
-      const float4 b = *reinterpret_cast<const float4*>(&bs[k][tx * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w};
-      const float2 b01 = make_float2(b.x, b.y), b23 = make_float2(b.z, b.w);
+    for (int k0 = 0; k0 < ATB_ROWS; k0 += 8) {
+      uint32_t ah[2][4], al[2][4], bh[2][2], bl[2][2];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        acc[i][0] = pk::ffma2(b01, pk::bc(av[i]), acc[i][0]);
-        acc[i][1] = pk::ffma2(b23, pk::bc(av[i]), acc[i][1]);
+      for (int i = 0; i < 2; ++i) {          // A fragment of C^T's row block: element (m, k) = A[k][m]
+        const float v[4] = {as[k0 + t][wm + 16 * i + g], as[k0 + t][wm + 16 * i + g + 8], as[k0 + t + 4][wm + 16 * i + g], as[k0 + t + 4][wm + 16 * i + g + 8]};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { ah[i][q] = f2tf32(v[q]); al[i][q] = f2tf32(v[q] - __uint_as_float(ah[i][q])); }
       }
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {          // B fragment: element (k, n) = B[k][n]
+        const float v[2] = {bs[k0 + t][wn + 8 * j + g], bs[k0 + t + 4][wn + 8 * j + g]};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) { bh[j][q] = f2tf32(v[q]); bl[j][q] = f2tf32(v[q] - __uint_as_float(bh[j][q])); }
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          mma_tf32_u(acc[i][j], al[i], bh[j][0], bh[j][1]);     // small terms first
+          mma_tf32_u(acc[i][j], ah[i], bl[j][0], bl[j][1]);
+          mma_tf32_u(acc[i][j], ah[i], bh[j][0], bh[j][1]);
+        }
     }
     __syncthreads();
   }
   float* out = partial + (int64_t)blockIdx.z * M * Nn;
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < 2; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
-      if (m < M && n < Nn) out[(int64_t)m * Nn + n] = (j & 1) ? acc[i][j >> 1].y : acc[i][j >> 1].x;
-    }
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int m = m0 + wm + 16 * i + g + ((q & 2) ? 8 : 0), n = n0 + wn + 8 * j + 2 * t + (q & 1);
+        if (m < M && n < Nn) out[(int64_t)m * Nn + n] = acc[i][j][q];
+      }
 }
 
 // gx[r][i] = sum_o gz[r][o] * W[o][i]
@@ -717,7 +774,7 @@ extern "C" int gnncca_linear_bwd(const float* x, const float* W, const float* y,
   if (!x || !y || !gy || !gz || !gb_partial || !gw_partial || (gx && !W)) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   tr::relu_grad_bias_kernel<<<(unsigned)ceil_div(rows, tr::RG_ROWS), 256, 0, st>>>(y, gy, relu, rows, out_dim, gz, gb_partial);
-  const int64_t rps = ceil_div(ceil_div(rows, n_splits), 16) * 16;
+  const int64_t rps = ceil_div(ceil_div(rows, n_splits), tr::ATB_ROWS) * tr::ATB_ROWS;
   dim3 grid((unsigned)ceil_div(in_dim, 64), (unsigned)ceil_div(out_dim, 64), (unsigned)n_splits);
   tr::atb_kernel<<<grid, 256, 0, st>>>(gz, x, rows, out_dim, in_dim, rps, gw_partial);
   int n = 2;
@@ -739,7 +796,7 @@ extern "C" int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_
     if (elems > max_elems) max_elems = elems;
   }
   int gy = (int)ceil_div(max_elems, 256 * 4);
-  if (gy > 64) gy = 64;
+  if (gy > 256) gy = 256;
   tr::finalize_kernel<<<dim3((unsigned)n_segs, (unsigned)gy), 256, 0, (cudaStream_t)stream>>>(t);
   return check_launch();
 }

@@ -437,7 +437,7 @@ def node_model_forward(node_model, x: torch.Tensor, edge_index: torch.Tensor, ed
 # ------------------------------------------------------------------------------------------------------------
 # frame-blocked execution of very large batches (BASELINE config 4: 4096 frames of 8 x 64 detections, 939.5 M edges)
 # ------------------------------------------------------------------------------------------------------------
-BLOCK_EDGES = int(os.environ.get("GNNCCA_BLOCK_EDGES", str(16 << 20)))     # target edges per block of frames
+BLOCK_EDGES = int(os.environ.get("GNNCCA_BLOCK_EDGES", str(32 << 20)))     # target edges per block of frames
 BLOCKED_MIN_EDGES = int(os.environ.get("GNNCCA_BLOCKED_MIN_EDGES", str(24 << 20)))   # batches above this run blocked
 
 

@@ -53,44 +53,72 @@ class _BceStats(torch.autograd.Function):
         width = PER * k + 4
         scratch = torch.empty((blocks + 1) * width, dtype=torch.float64, device=dev)
         out = scratch[blocks * width:]
+        # the summed loss of the BCE criteria comes out of the same launch as a float32 scalar, and its gradient goes straight
+        # into the backward kernel: no reduction / cast / expand kernels between the statistics and the seed of the MPN's backward
+        loss_sum = torch.empty((), dtype=torch.float32, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
         _lib.check(lib.gnncca_bce_stats_fwd(_ptr_array(flat), k, labels.data_ptr(), E, pos_weight, int(focal), focus, balance,
-                                            _lib.ptr(probs), scratch.data_ptr(), out.data_ptr(), stream), "gnncca_bce_stats_fwd")
+                                            _lib.ptr(probs), scratch.data_ptr(), out.data_ptr(), loss_sum.data_ptr(), stream), "gnncca_bce_stats_fwd")
         ctx.flat, ctx.labels, ctx.pos_weight, ctx.shapes = flat, labels, pos_weight, [x.shape for x in logits]
-        return out
+        ctx.set_materialize_grads(False)
+        return out, loss_sum
 
     @staticmethod
-    def backward(ctx, g_out):
+    def backward(ctx, g_out, g_sum):
         lib = _lib.load()
         flat, labels = ctx.flat, ctx.labels
         k, E = len(flat), flat[0].numel()
         dev = flat[0].device
-        up = g_out.detach()
-        if up.dtype != torch.float64 or not up.is_contiguous():
-            up = up.double().contiguous()
+        if g_out is None and g_sum is None:
+            return (None,) * (6 + k)
+        up = None
+        if g_out is not None:
+            up = g_out.detach()
+            if up.dtype != torch.float64 or not up.is_contiguous():
+                up = up.double().contiguous()
+        us = None
+        if g_sum is not None:
+            us = g_sum.detach()
+            if us.dtype != torch.float32:
+                us = us.float()
         grads = torch.empty((k, E), dtype=torch.float32, device=dev)
         rows = [grads[s] for s in range(k)]
         stream = torch.cuda.current_stream(dev).cuda_stream
         _lib.check(lib.gnncca_bce_stats_bwd(_ptr_array(flat), _ptr_array(rows), k, labels.data_ptr(), E, ctx.pos_weight,
-                                            up.data_ptr(), stream), "gnncca_bce_stats_bwd")
+                                            _lib.ptr(up), _lib.ptr(us), stream), "gnncca_bce_stats_bwd")
         return (None,) * 6 + tuple(rows[s].view(ctx.shapes[s]) for s in range(k))
 
 
 class LossStats:
     """Device-resident result of ``loss_stats`` (no synchronisation until a ``precision*``/``counts`` property is read)."""
 
-    def __init__(self, stats: torch.Tensor, k: int, probs: Optional[torch.Tensor], focal, focus, balance):
+    def __init__(self, stats: torch.Tensor, k: int, probs: Optional[torch.Tensor], focal, focus, balance, loss_sum=None):
         self.stats, self.k, self.probs = stats, k, probs
-        m = stats[:k]
         if focal:   # FocalLoss_binary(reduction='mean'): the focal transform of the MEAN cross entropy (utils.py:281-291)
+            m = stats[:k]
             m = balance * (1.0 - torch.exp(-m)) ** focus * m
-        self.loss = m.sum().float()
-        d = stats.detach()
-        self.loss_class1 = d[k:2 * k].sum().float()
-        self.loss_class0 = d[2 * k:3 * k].sum().float()
-        self.mean_prob_class1 = d[3 * k:4 * k]
-        self.mean_prob_class0 = d[4 * k:5 * k]
+            self.loss = m.sum().float()
+        else:
+            self.loss = loss_sum        # sum of the k step means, from the statistics launch itself
         self._host = None
+
+    # per-class losses and mean probabilities are read by compute_loss_acc / logging only: nothing is launched for them in a
+    # training step that just needs ``loss``
+    @property
+    def loss_class1(self):
+        return self.stats.detach()[self.k:2 * self.k].sum().float()
+
+    @property
+    def loss_class0(self):
+        return self.stats.detach()[2 * self.k:3 * self.k].sum().float()
+
+    @property
+    def mean_prob_class1(self):
+        return self.stats.detach()[3 * self.k:4 * self.k]
+
+    @property
+    def mean_prob_class0(self):
+        return self.stats.detach()[4 * self.k:5 * self.k]
 
     def counts(self):
         """(n1, n0, correct1, correct0) as Python ints: the one device->host copy."""
@@ -164,8 +192,8 @@ def loss_stats(logits: Sequence[torch.Tensor], labels: torch.Tensor, pos_weight:
     if E == 0:
         raise ValueError("compute_loss_acc on a batch without edges")
     probs = torch.empty((k, E), dtype=torch.float32, device=lab.device) if want_probs else None
-    stats = _BceStats.apply(lab, float(pos_weight), bool(focal), float(focus), float(balance), probs, *logits)
-    return LossStats(stats, k, probs, focal, focus, balance)
+    stats, loss_sum = _BceStats.apply(lab, float(pos_weight), bool(focal), float(focus), float(balance), probs, *logits)
+    return LossStats(stats, k, probs, focal, focus, balance, loss_sum)
 
 
 def compute_loss_acc(outputs, batch, criterion, criterion_no_reduction, mode):

@@ -66,6 +66,9 @@ class GraphPlan:
         if int(self._flags_host[1]):
             raise IndexError("edge_index has entries outside [0, num_nodes=%d) (found after a forward on a batch marked trusted: "
                              "its outputs are invalid)" % self.N)
+        if int(self._flags_host[3]):
+            raise RuntimeError("a batch marked gnncca_trusted is not symmetric (an edge without its reverse): the backward that used it "
+                               "computed wrong gradients; clear data.gnncca_trusted so that the checked path sorts by target")
         if int(self._flags_host[0]):
             raise RuntimeError("a batch marked gnncca_trusted is not source-major: the forward that used it was a no-op and its "
                                "outputs are invalid; clear data.gnncca_trusted so that the checked path sorts the edges")

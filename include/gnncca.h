@@ -55,7 +55,8 @@ int64_t gnncca_launch_count(void);
 
 /* flags[] written by gnncca_csr_from_edge_index (int32 x 4, device; the entry zeroes them first):
  *   [0] 1 if edge_index[0] is NOT non-decreasing (0 = source-major, what train.py:292-299 produces
- *         for camera-major frames);  [1] 1 if any index is outside [0, n_nodes);  [2],[3] reserved. */
+ *         for camera-major frames);  [1] 1 if any index is outside [0, n_nodes);  [2] a frame did not fit the capacity class of
+ *         gnncca_mp_fused_fwd;  [3] gnncca_csr_reverse_edges met an edge without a reverse. */
 #define GNNCCA_CSR_NFLAGS 4
 
 /* Narrow edge_index [2,E] int64 to src[E], dst[E] int32, detect ordering / range, and -- when the
@@ -77,6 +78,14 @@ int gnncca_csr_from_edge_rows(const int64_t* row, const int64_t* col, int64_t no
  * The fused step kernel does this inside its phase B; this entry is the stand-alone NodeModel.forward path. */
 int gnncca_segment_agg(const float* rows, const int32_t* rowptr, int64_t n_nodes, int32_t width, int32_t agg, float* out,
                        void* stream);
+
+/* Target-major permutation of a SYMMETRIC source-major CSR whose segments list their targets in ascending order (the
+ * enumeration of train.py:292-299 on camera-major rows; every cross-camera pair appears in both directions): tperm[q] = the
+ * position of the reverse of edge q, which equals what a stable sort of the edges by dst yields, with rowptr as its offsets.
+ * One launch instead of a radix sort (the backward's gQ reduction needs the in-edges of every node, autograd of mpn.py:68).
+ * flags[3] is raised if an edge has no reverse: the CSR was not symmetric and tperm is not a permutation of it. */
+int gnncca_csr_reverse_edges(const int32_t* rowptr, const int32_t* src, const int32_t* dst, int64_t n_nodes, int64_t n_edges,
+                             int32_t* tperm, int32_t* flags, void* stream);
 
 /* Bytes of scratch gnncca_csr_sort needs. */
 int64_t gnncca_csr_sort_workspace_bytes(int64_t n_nodes, int64_t n_edges);
@@ -339,14 +348,17 @@ int gnncca_finalize_grads(const gnncca_fin_seg* host_segs, int32_t n_segs, void*
  * step, then n1, n0 and the number of correct last-step predictions (sigmoid >= 0.5) with y = 1 / y = 0.  A class
  * without samples gives NaN means (as torch.mean of an empty tensor).  probs ([n_steps][n_edges], or NULL) receives
  * the sigmoids (train.py:100-103).  partials: [gnncca_loss_blocks(n_edges)][5 n_steps + 4] doubles of scratch.
- * Fixed-order reduction, bit-reproducible.  Two launches. */
+ * loss_sum (fp32 scalar, or NULL) receives sum_s out[s], the summed loss of train.py:80-97 for the BCE criteria, so that no
+ * further kernel runs between the statistics and the backward seed.  Fixed-order reduction, bit-reproducible.  Two launches. */
 int32_t gnncca_loss_blocks(int64_t n_edges);
 int gnncca_bce_stats_fwd(const float* const* host_logits, int32_t n_steps, const float* labels, int64_t n_edges, float pos_weight,
-                         int32_t focal, float focus, float balance, float* probs, double* partials, double* out, void* stream);
-/* host_grads[s][i] = upstream[s] / n_edges * d l / d x_s,i: gradient of sum_s upstream[s] * mean_i l(x_s,i); upstream is a
- * DEVICE array of n_steps doubles (d loss / d out[s] from gnncca_bce_stats_fwd).  One launch. */
+                         int32_t focal, float focus, float balance, float* probs, double* partials, double* out, float* loss_sum,
+                         void* stream);
+/* host_grads[s][i] = (upstream[s] + *upstream_sum) / n_edges * d l / d x_s,i: gradient of sum_s upstream[s] * mean_i l(x_s,i)
+ * plus *upstream_sum times loss_sum; upstream is a DEVICE array of n_steps doubles (d loss / d out[s] from
+ * gnncca_bce_stats_fwd), upstream_sum a DEVICE fp32 scalar (d loss / d loss_sum); either may be NULL (= 0).  One launch. */
 int gnncca_bce_stats_bwd(const float* const* host_logits, float* const* host_grads, int32_t n_steps, const float* labels,
-                         int64_t n_edges, float pos_weight, const double* upstream, void* stream);
+                         int64_t n_edges, float pos_weight, const double* upstream, const float* upstream_sum, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Edge decisions, pruning and clusters per frame graph: inference.py:286-345 with utils.py:295-317

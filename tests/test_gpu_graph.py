@@ -113,3 +113,34 @@ def test_every_launch_structure_of_build_graph_batch_matches_the_oracle(reid_dim
         np.testing.assert_allclose(b.edge_attr.cpu().numpy(), ref.edge_attr.numpy(), rtol=1e-5, atol=2e-6)
         np.testing.assert_allclose(b.x.cpu().numpy(), ref.x.numpy(), rtol=2e-6, atol=1e-9)
         assert b.gnncca_caps[0] == max(len(f["id"]) for f in frames)
+
+
+def test_reverse_edge_table_equals_the_stable_sort_by_target(cuda_device):
+    """gnncca_csr_reverse_edges on a build_graph_batch output (symmetric, source-major, targets ascending) gives the permutation
+    the radix sort by target gives, with rowptr as offsets; an edge without its reverse raises flags[3]."""
+    import importlib
+    import gnncca
+    _lib = importlib.import_module("gnn-cca_b200._lib")
+    syn = importlib.import_module("gnn-cca_b200.synthetic")
+    lib = _lib.load()
+    b = gnncca.build_graph_batch(**syn.make_detections(5, 7, 9, seed=3, device=cuda_device))
+    N, E = b.num_nodes, b.num_edges
+    plan = gnncca.GraphPlan(b.edge_index, N).resolve()
+    assert plan.perm is None
+    st = torch.cuda.current_stream().cuda_stream
+    tperm = torch.empty(E, dtype=torch.int32, device=cuda_device)
+    flags = torch.zeros(4, dtype=torch.int32, device=cuda_device)
+    _lib.check(lib.gnncca_csr_reverse_edges(_lib.ptr(plan.rowptr), _lib.ptr(plan.src), _lib.ptr(plan.dst), N, E, _lib.ptr(tperm), _lib.ptr(flags), st), "rev")
+    key, other = plan.dst.clone(), plan.src.clone()
+    want = torch.empty(E, dtype=torch.int32, device=cuda_device)
+    colptr = torch.empty(N + 1, dtype=torch.int32, device=cuda_device)
+    nbytes = int(lib.gnncca_csr_sort_workspace_bytes(N, E))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=cuda_device)
+    _lib.check(lib.gnncca_csr_sort(N, E, _lib.ptr(key), _lib.ptr(other), _lib.ptr(want), _lib.ptr(colptr), _lib.ptr(ws), nbytes, st), "sort")
+    assert torch.equal(tperm, want) and torch.equal(colptr, plan.rowptr) and int(flags.sum()) == 0
+    # drop one direction of one pair: no longer symmetric
+    ei = b.edge_index[:, 1:].contiguous()
+    plan2 = gnncca.GraphPlan(ei, N).resolve()
+    t2 = torch.empty(E - 1, dtype=torch.int32, device=cuda_device)
+    _lib.check(lib.gnncca_csr_reverse_edges(_lib.ptr(plan2.rowptr), _lib.ptr(plan2.src), _lib.ptr(plan2.dst), N, E - 1, _lib.ptr(t2), _lib.ptr(flags), st), "rev")
+    assert int(flags[3]) == 1

@@ -9,7 +9,7 @@ syn = importlib.import_module("gnn-cca_b200.synthetic")
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
 model = gnncca.MOTMPNet(copy.deepcopy(cfgmod.graph_net_params()), None, "resnet50").to(dev).train()
-opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4)
+opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, weight_decay=1e-4, fused=True)
 batches = [gnncca.build_graph_batch(**syn.make_detections(4, 10, 64, seed=7 + s, device=dev, max_dist=153.54)) for s in range(4)]
 step = gnncca.GraphedTrainStep(model)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 50
