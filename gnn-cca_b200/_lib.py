@@ -36,6 +36,12 @@ class FinSeg(C.Structure):
                 ("rows", i32), ("cols", i32), ("dst_stride", i32), ("accumulate", i32)]
 
 
+class FrameBwdStep(C.Structure):      # gnncca_frame_bwd_step
+    _fields_ = [(n, vp) for n in ("R", "e", "e_prev", "h_out", "h_prev", "g_logits", "aff", "pa_agg", "pa_edge", "pa_proj", "pa_cls", "gh_prev")]
+
+
+FRAMES_BWD_MAX_STEPS = 8
+FRAMES_BWD_SMEM_LIMIT = 190 * 1024
 MAX_FIN_SEGS = 24
 CLS_ACC = 41
 BLOCKS_PER_EDGE, BLOCKS_PER_NODE_WARP, BLOCKS_NODE_PROJECT, BLOCKS_ROW_CHUNKS = 0, 1, 2, 3
@@ -78,8 +84,10 @@ SIGNATURES = {
     "gnncca_cls_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, i32, vp, vp, vp, vp, vp]),
     "gnncca_pq_reduce": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, vp]),
     "gnncca_node_project_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, vp, i64, vp, vp, vp, vp]),
+    "gnncca_mp_frames_bwd_smem_bytes": (i64, [i32, i32]),
+    "gnncca_mp_frames_bwd": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, vp, i64, i64, i32, i32, vp, i32, vp, vp, vp, vp, vp, vp, vp]),
     "gnncca_edge_enc_bwd": (C.c_int, [vp, i32, vp, vp, i64, vp, vp]),
-    "gnncca_linear_bwd": (C.c_int, [vp, vp, vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, i32, vp]),
+    "gnncca_linear_bwd": (C.c_int, [vp, vp, vp, vp, i32, i64, i32, i32, vp, vp, vp, vp, i32, i32, vp]),
     "gnncca_finalize_grads": (C.c_int, [C.POINTER(FinSeg), i32, vp]),
     "gnncca_loss_blocks": (i32, [i64]),
     "gnncca_bce_stats_fwd": (C.c_int, [C.POINTER(vp), i32, vp, i64, C.c_float, i32, C.c_float, C.c_float, vp, vp, vp, vp, vp]),

@@ -5,6 +5,7 @@ train.py:493).  Inputs ``x`` / ``edge_attr`` get no gradient (the CNN runs under
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List
 
 import torch
@@ -13,6 +14,8 @@ from . import _lib
 from .plan import GraphPlan, _stream
 
 P = _lib.ptr
+FUSED_BWD = os.environ.get("GNNCCA_FUSED_BWD", "1") != "0"
+FUSED_BWD_MAX_EDGES = int(os.environ.get("GNNCCA_FUSED_BWD_MAX_EDGES", "3500"))     # per frame: above it the per-step chain runs
 
 
 def _blocks(lib, n, kind):
@@ -46,7 +49,7 @@ class _Seg:
 
 class _MPNFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, model, x, edge_index, edge_attr, plan, trusted, *params):
+    def forward(ctx, model, x, edge_index, edge_attr, plan, trusted, frames, *params):
         from . import engine
         lib = _lib.load()
         engine.check_supported(model)
@@ -168,6 +171,13 @@ class _MPNFunction(torch.autograd.Function):
         if guard and not plan._requested and not torch.cuda.is_current_stream_capturing():
             plan.request_flags()
         ctx.model, ctx.plan, ctx.sb = model, plan, sb
+        # one-launch backward (gnncca_mp_frames_bwd): closed frames with known offsets, every frame small enough for one CTA,
+        # the reverse-edge table in place of the sort by target, no batch statistics in the classifier
+        ctx.frames = None
+        if (frames is not None and FUSED_BWD and trusted and plan.perm is None and plan.colptr is plan.rowptr and bn_mode != "train"
+                and L <= _lib.FRAMES_BWD_MAX_STEPS and frames[2][1] <= FUSED_BWD_MAX_EDGES and int(frames[0].numel()) - 1 >= 8
+                and int(lib.gnncca_mp_frames_bwd_smem_bytes(int(frames[2][0]), int(frames[2][1]))) <= _lib.FRAMES_BWD_SMEM_LIMIT):
+            ctx.frames = (frames[0], frames[1], (int(frames[2][0]), int(frames[2][1])))
         ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, proj=proj, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
                          names=[n for n, _ in model.named_parameters_fast()])
         ctx.set_materialize_grads(False)
@@ -198,6 +208,9 @@ class _MPNFunction(torch.autograd.Function):
         cbn = cpre + "%d." % cls.layer_specs[0].bn if cls.layer_specs[0].bn is not None else None
 
         be, bnw, bp = _blocks(lib, E, _lib.BLOCKS_PER_EDGE), _blocks(lib, N, _lib.BLOCKS_PER_NODE_WARP), _blocks(lib, N, _lib.BLOCKS_NODE_PROJECT)
+        fused = ctx.frames is not None
+        if fused:          # one partial row per frame and step
+            be = bnw = bp = int(ctx.frames[0].numel()) - 1
         n_cls = L - first + 1
         shapes = [("pa_agg", (L, bnw, FN * FE)), ("pa_edge", (L, be, FE * EIN)), ("pa_proj", (L, bp, 44 * (K + 1))),
                   ("pa_cls", (n_cls, be, _lib.CLS_ACC)), ("gP", (N, 8)), ("gQ", (N, 8)),
@@ -225,7 +238,27 @@ class _MPNFunction(torch.autograd.Function):
         ge0_acc, gh0_acc, gh_prevs = zb.get("ge0_acc"), zb.get("gh0_acc"), zb["gh_prev"]
         gh, ge_next = None, None
         is_max = model.node_agg_name == "max"
-        for t in range(L, 0, -1):
+        if fused:
+            B = be
+            tmp = torch.empty(2 * E * FE, dtype=torch.float32, device=dev)
+            ge_a, ge_b = tmp[:E * FE], tmp[E * FE:]
+            steps = (_lib.FrameBwdStep * L)()
+            keep_g = []
+            for t in range(1, L + 1):
+                g = None
+                if t >= first and g_outs[t - first] is not None:
+                    g = g_outs[t - first].contiguous().view(E)
+                    keep_g.append(g)
+                aff = sv["affs"].get(t)
+                ci = t - first
+                steps[t - 1] = _lib.FrameBwdStep(proj[t - 1, N * 16:].data_ptr(), P(es[t]), P(es[t - 1]), P(hs[t]), P(hs[t - 1]), P(g), P(aff),
+                                                 P(pa_agg[t - 1]), P(pa_edge[t - 1]), P(pa_proj[t - 1]), P(pa_cls[ci]) if g is not None else 0,
+                                                 P(gh_prevs[t - 1]))
+            _lib.check(lib.gnncca_mp_frames_bwd(cfg, w, P(ctx.frames[0]), P(ctx.frames[1]), B, P(plan.rowptr), P(plan.src), P(sv["tperm"]), N, E,
+                                                ctx.frames[2][0], ctx.frames[2][1], steps, L, P(es[0]) if re else 0, P(hs[0]) if rn else 0,
+                                                P(ge_a), P(ge_b), P(ge0_acc), P(gh0_acc), _stream()), "mp_frames_bwd")
+            gh, ge_next = gh_prevs[0], ge_a.view(E, FE)
+        for t in (range(L, 0, -1) if not fused else ()):
             ge_cls = None
             if t >= first and g_outs[t - first] is not None:
                 ci = t - first
@@ -283,6 +316,7 @@ class _MPNFunction(torch.autograd.Function):
         # edge encoder
         enc_e = model.encoder.edge_mlp
         fa = int(ea.size(1))
+        be = _blocks(lib, E, _lib.BLOCKS_PER_EDGE)       # (the fused backward counted frames)
         pa_enc = torch.empty((be, FE * 8 + FE), dtype=torch.float32, device=dev)
         _lib.check(lib.gnncca_edge_enc_bwd(P(ea), fa, P(es[0]), P(ge0), E, P(pa_enc), _stream()), "edge_enc_bwd")
         epre = "encoder.edge_mlp.fc_layers.%d." % enc_e.layer_specs[0].linear
@@ -304,24 +338,25 @@ class _MPNFunction(torch.autograd.Function):
             gbp = torch.empty((chunks, sp.out_dim), dtype=torch.float32, device=dev)
             gwp = torch.empty((splits, sp.out_dim * sp.in_dim), dtype=torch.float32, device=dev)
             _lib.check(lib.gnncca_linear_bwd(P(acts[i]), P(lin.weight), P(acts[i + 1]), P(gy), int(sp.relu), rows, sp.in_dim, sp.out_dim, P(gz), P(gx),
-                                             P(gbp), P(gwp), splits, _stream()), "linear_bwd")
+                                             P(gbp), P(gwp), splits, _lib.MATH_TF32 if model.math == "tf32" else _lib.MATH_FP32, _stream()),
+                           "linear_bwd")
             npre = "encoder.node_mlp.fc_layers.%d." % sp.linear
             seg.add(gwp, splits, sp.out_dim * sp.in_dim, 0, sp.in_dim, sp.out_dim, sp.in_dim, grads[npre + "weight"], sp.in_dim)
             seg.add(gbp, chunks, sp.out_dim, 0, sp.out_dim, 1, sp.out_dim, grads[npre + "bias"], sp.out_dim)
             keep += [gz, gbp, gwp]
             gy = gx
         seg.flush()
-        out: List = [None, None, None, None, None, None]
+        out: List = [None, None, None, None, None, None, None]
         for n in sv["names"]:
             out.append(grads[n] if named[n].requires_grad else None)
         return tuple(out)
 
 
-def forward_training(model, x, edge_index, edge_attr, plan=None, trusted=False, return_plan=False):
+def forward_training(model, x, edge_index, edge_attr, plan=None, trusted=False, return_plan=False, frames=None):
     """``MOTMPNet.forward`` with an autograd graph: returns the list of per-step logits [E,1] (and, on request, the
     CSR plan it used, which carries the transposed CSR of the backward: the module caches it on the batch object)."""
     params = [p for _, p in model.named_parameters_fast()]
-    outs = list(_MPNFunction.apply(model, x, edge_index, edge_attr, plan, trusted, *params))
+    outs = list(_MPNFunction.apply(model, x, edge_index, edge_attr, plan, trusted, frames, *params))
     if return_plan:
         return outs, model.__dict__.pop("_gnncca_train_plan", None)
     return outs

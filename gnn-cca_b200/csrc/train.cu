@@ -501,6 +501,10 @@ __device__ __forceinline__ void mma_tf32_u(float (&c)[4], const uint32_t (&a)[4]
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 constexpr int ATB_ROWS = 32, ATB_LD = 72;      // row stride 72: the fragment loads (k = lane & 3, m = lane >> 2) hit 32 banks
+// PASSES = 3: the operand split described above (math = fp32).  PASSES = 1: one tf32 mma per tile, the arithmetic of the forward's
+// tcgen05 encoder (math = tf32, what torch does under allow_tf32): legacy mma.sync issues a tf32 m16n8k8 every ~16 cycles per SM
+// sub-partition, so the three-pass form is bound by exactly that pipe.
+template <int PASSES>
 __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t rows, int M, int Nn,
                                                   int64_t rows_per_split, float* __restrict__ partial /* [splits][M*Nn] */) {
   __shared__ __align__(16) float as[ATB_ROWS][ATB_LD], bs[ATB_ROWS][ATB_LD];
@@ -553,20 +557,22 @@ __global__ void __launch_bounds__(256) atb_kernel(const float* __restrict__ A, c
       for (int i = 0; i < 2; ++i) {          // A fragment of C^T's row block: element (m, k) = A[k][m]
         const float v[4] = {as[k0 + t][wm + 16 * i + g], as[k0 + t][wm + 16 * i + g + 8], as[k0 + t + 4][wm + 16 * i + g], as[k0 + t + 4][wm + 16 * i + g + 8]};
 #pragma unroll
-        for (int q = 0; q < 4; ++q) { ah[i][q] = f2tf32(v[q]); al[i][q] = f2tf32(v[q] - __uint_as_float(ah[i][q])); }
+        for (int q = 0; q < 4; ++q) { ah[i][q] = f2tf32(v[q]); al[i][q] = PASSES == 3 ? f2tf32(v[q] - __uint_as_float(ah[i][q])) : 0u; }
       }
 #pragma unroll
       for (int j = 0; j < 2; ++j) {          // B fragment: element (k, n) = B[k][n]
         const float v[2] = {bs[k0 + t][wn + 8 * j + g], bs[k0 + t + 4][wn + 8 * j + g]};
 #pragma unroll
-        for (int q = 0; q < 2; ++q) { bh[j][q] = f2tf32(v[q]); bl[j][q] = f2tf32(v[q] - __uint_as_float(bh[j][q])); }
+        for (int q = 0; q < 2; ++q) { bh[j][q] = f2tf32(v[q]); bl[j][q] = PASSES == 3 ? f2tf32(v[q] - __uint_as_float(bh[j][q])) : 0u; }
       }
 #pragma unroll
       for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          mma_tf32_u(acc[i][j], al[i], bh[j][0], bh[j][1]);     // small terms first
-          mma_tf32_u(acc[i][j], ah[i], bl[j][0], bl[j][1]);
+          if (PASSES == 3) {
+            mma_tf32_u(acc[i][j], al[i], bh[j][0], bh[j][1]);     // small terms first
+            mma_tf32_u(acc[i][j], ah[i], bl[j][0], bl[j][1]);
+          }
           mma_tf32_u(acc[i][j], ah[i], bh[j][0], bh[j][1]);
         }
     }
@@ -632,6 +638,314 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinTable t) {
     for (int b = 0; b < sg.n_blocks; ++b) acc += __ldg(src + (int64_t)b * sg.width);     // same order, 8 loads in flight
     float* d = sg.dst + (int64_t)r * sg.dst_stride + c;
     *d = sg.accumulate ? *d + acc : acc;
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// I. The whole message-passing backward of a batch of SMALL frames in ONE launch: a CTA per frame walks the steps
+//    t = L .. 1 through the phases A-E above (same arithmetic per element: the bodies below are those kernels with the
+//    frame's node / edge range in place of the grid), separated by __syncthreads() instead of kernel boundaries.  A frame is
+//    closed (no edge leaves it, Batch.from_data_list, train.py:450), so every buffer row a phase reads was written by this
+//    CTA.  For EPFL-sized frames (tens of nodes, ~10^3 edges) a kernel boundary costs more than the phase's work: 18 launches
+//    per backward become one.  Weight-gradient partials: one row per FRAME and step, folded by gnncca_finalize_grads.
+// ------------------------------------------------------------------------------------------------
+constexpr int PB_NODES = 16;
+struct FramesBwd {
+  const int64_t* graph_ptr; const int64_t* edge_ptr;
+  const int32_t* rowptr; const int32_t* src; const int32_t* tperm;
+  const float* w_edge; const float* w_node; int edge_row, node_row, K;
+  const float* w1; const float* b1; const float* w2; const float* b2;
+  const float* e0; const float* h0;
+  int n_steps, agg; int64_t n_nodes; int max_n, max_e;
+  gnncca_frame_bwd_step st[GNNCCA_FRAMES_BWD_MAX_STEPS];
+  float* ge_buf[2]; float* ge0_acc; float* gh0_acc;
+};
+
+constexpr int TBF = 512, NWF = TBF / 32;      // a frame's CTA: 16 warps (8 left each scheduler with two warps of long dependent chains)
+template <bool REATT_E, int K>
+__global__ void __launch_bounds__(TBF) frames_bwd_kernel(const FramesBwd p) {
+  constexpr int EIN = REATT_E ? 2 * FE : FE;
+  constexpr int OFF = REATT_E ? FE : 0;
+  constexpr int OUT = 2 * FE + FN;
+  __shared__ float s_wne[FE][FN];
+  __shared__ float s_wee[FE][EIN];
+  __shared__ float s_w1[HC][FE], s_b1[HC], s_w2[HC], s_aff[4 * HC];
+  __shared__ float s_red[NWF * (FE * EIN > CLS_ACC ? FE * EIN : CLS_ACC)];
+  __shared__ float s_agg[NWF][FE * FN];
+  __shared__ float s_pw[OUT * K];                    // projection weights [OUT][K]
+  __shared__ float s_ph[PB_NODES * (K + 1)];
+  // the frame's state of the current step (dynamic): every phase reads and writes it here -- through global memory each
+  // dependent access would cost an L2 round trip (stores do not allocate in L1), and a CTA per frame has nothing to hide it with
+  extern __shared__ __align__(16) float dyn[];
+  float* s_e = dyn;                                     // [max_e][FE]   e^t
+  float* s_gze = s_e + (size_t)p.max_e * FE;            // [max_e][EP]   classifier gradient, then gz_e
+  float* s_R = s_gze + (size_t)p.max_e * EP;            // [max_n][FN]
+  float* s_gh = s_R + p.max_n * FN;                     // [max_n][FN]   gradient wrt h^t (max: divided by the ties)
+  float* s_hv = s_gh + p.max_n * FN;                    // [max_n][FN]   max only: the recomputed maxima
+  float* s_gR = s_hv + p.max_n * FN;                    // [max_n][FN]
+  float* s_gP = s_gR + p.max_n * FN;                    // [max_n][EP]
+  float* s_gQ = s_gP + p.max_n * EP;                    // [max_n][EP]
+  float* s_pg = s_gQ + p.max_n * EP;                    // [max_n][OUT + 1]  phase E's left operand
+  int* s_rp = reinterpret_cast<int*>(s_pg + p.max_n * (OUT + 1));   // [max_n + 1] local row offsets
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int f = blockIdx.x;
+  const int64_t n0 = p.graph_ptr[f], eb = p.edge_ptr[f];
+  const int n = (int)(p.graph_ptr[f + 1] - n0), m = (int)(p.edge_ptr[f + 1] - eb);
+  if (n > p.max_n || m > p.max_e) return;               // the caller sized the launch from the batch maxima: cannot happen
+  for (int i = tid; i < FE * FN; i += TBF) s_wne[i / FN][i % FN] = p.w_node[(i % FN) * p.node_row + K + i / FN];
+  for (int i = tid; i < FE * EIN; i += TBF) s_wee[i / EIN][i % EIN] = p.w_edge[(i / EIN) * p.edge_row + 2 * K + i % EIN];
+  for (int i = tid; i < OUT * K; i += TBF) {
+    const int o = i / K, k = i - o * K;
+    s_pw[i] = o < FE ? p.w_edge[o * p.edge_row + k] : (o < 2 * FE ? p.w_edge[(o - FE) * p.edge_row + K + k] : p.w_node[(o - 2 * FE) * p.node_row + k]);
+  }
+  if (p.w1) {
+    for (int i = tid; i < HC * FE; i += TBF) s_w1[i / FE][i % FE] = p.w1[i];
+    for (int i = tid; i < HC; i += TBF) { s_b1[i] = p.b1[i]; s_w2[i] = p.w2[i]; }
+  }
+  for (int i = tid; i <= n; i += TBF) s_rp[i] = (int)(p.rowptr[n0 + i] - eb);
+  float wne[FE];                                        // lane = feature (phase A)
+#pragma unroll
+  for (int k = 0; k < FE; ++k) wne[k] = p.w_node[lane * p.node_row + K + k];
+  __syncthreads();
+
+  for (int t = p.n_steps; t >= 1; --t) {
+    const gnncca_frame_bwd_step& st = p.st[t - 1];
+    const float* gh = t < p.n_steps ? p.st[t].gh_prev : nullptr;       // gradient wrt h^t: what step t + 1 wrote
+    const float* ge_in = t < p.n_steps ? p.ge_buf[t & 1] : nullptr;
+    float* ge_out = p.ge_buf[(t - 1) & 1];
+    const bool has_cls = st.g_logits != nullptr;
+    // ---- stage the step: e^t, R, gh (coalesced, independent loads) ----
+    for (int i = tid; i < m * FE; i += TBF) s_e[i] = st.e[eb * FE + i];
+    if (gh != nullptr) {
+      for (int i = tid; i < n * FN; i += TBF) { s_R[i] = st.R[n0 * FN + i]; s_gh[i] = gh[n0 * FN + i]; }
+    }
+    if (has_cls && tid < HC) {
+      s_aff[tid] = st.aff ? st.aff[tid] : 1.f; s_aff[HC + tid] = st.aff ? st.aff[HC + tid] : 0.f;
+      s_aff[2 * HC + tid] = st.aff ? st.aff[2 * HC + tid] : 0.f; s_aff[3 * HC + tid] = st.aff ? st.aff[3 * HC + tid] : 1.f;
+    }
+    __syncthreads();
+
+    // ---- C. classifier backward (no BatchNorm / eval-mode BatchNorm): its gradient wrt e^t goes to s_gze ----
+    if (has_cls) {
+      float acc[CLS_ACC];
+#pragma unroll
+      for (int i = 0; i < CLS_ACC; ++i) acc[i] = 0.f;
+      for (int j = tid; j < m; j += TBF) {
+        float ev[FE], ge[FE];
+#pragma unroll
+        for (int k = 0; k < FE; ++k) { ev[k] = s_e[j * FE + k]; ge[k] = 0.f; }
+        const float g = st.g_logits[eb + j];
+        acc[HC * FE + 2 * HC] += g;
+#pragma unroll
+        for (int ff = 0; ff < HC; ++ff) {
+          float c = s_b1[ff];
+#pragma unroll
+          for (int k = 0; k < FE; ++k) c = fmaf(ev[k], s_w1[ff][k], c);
+          const float y = fmaf(c, s_aff[ff], s_aff[HC + ff]);
+          const float chat = (c - s_aff[2 * HC + ff]) * s_aff[3 * HC + ff];
+          const float gy = y > 0.f ? g * s_w2[ff] : 0.f;
+          acc[HC * FE + HC + ff] = fmaf(g, fmaxf(y, 0.f), acc[HC * FE + HC + ff]);
+          acc[HC * FE + 2 * HC + 1 + ff] = fmaf(gy, chat, acc[HC * FE + 2 * HC + 1 + ff]);
+          acc[HC * FE + 3 * HC + 1 + ff] += gy;
+          const float gc = s_aff[ff] * gy;
+          acc[HC * FE + ff] += gc;
+#pragma unroll
+          for (int k = 0; k < FE; ++k) { acc[ff * FE + k] = fmaf(gc, ev[k], acc[ff * FE + k]); ge[k] = fmaf(gc, s_w1[ff][k], ge[k]); }
+        }
+#pragma unroll
+        for (int k = 0; k < FE; ++k) s_gze[j * EP + k] = ge[k];
+      }
+      block_reduce_store<CLS_ACC>(acc, s_red, st.pa_cls + (int64_t)f * CLS_ACC);
+    }
+
+    // ---- A. node side of the node model: warp per node, lane = feature ----
+    if (gh != nullptr) {
+      float gw[FE];
+#pragma unroll
+      for (int k = 0; k < FE; ++k) gw[k] = 0.f;
+      for (int v = warp; v < n; v += NWF) {
+        const int j0 = s_rp[v], j1 = s_rp[v + 1];
+        const float r = s_R[v * FN + lane], gh_in = s_gh[v * FN + lane];
+        const float inv_deg = j1 > j0 ? 1.f / (float)(j1 - j0) : 0.f;
+        float ghv = gh_in, hval = 0.f;
+        if (p.agg == GNNCCA_AGG_MAX) {
+          int ties = 0;
+          for (int j = j0; j < j1; ++j) {
+            float z = r;
+#pragma unroll
+            for (int k = 0; k < FE; ++k) z = fmaf(s_e[j * FE + k], wne[k], z);
+            if (z > hval) { hval = z; ties = 1; }
+            else if (z > 0.f && z == hval) ++ties;
+          }
+          ghv = ties > 0 ? gh_in / (float)ties : 0.f;
+          s_gh[v * FN + lane] = ghv;                      // what the edge phase must see as gh
+          s_hv[v * FN + lane] = hval;
+        }
+        float acc = 0.f;
+        for (int j = j0; j < j1; ++j) {
+          float ev[FE];
+#pragma unroll
+          for (int k = 0; k < FE; ++k) ev[k] = s_e[j * FE + k];
+          float z = r;
+#pragma unroll
+          for (int k = 0; k < FE; ++k) z = fmaf(ev[k], wne[k], z);
+          const float g = agg_grad(p.agg, ghv, z, hval, inv_deg);
+          acc += g;
+#pragma unroll
+          for (int k = 0; k < FE; ++k) gw[k] = fmaf(g, ev[k], gw[k]);
+        }
+        s_gR[v * FN + lane] = acc;
+      }
+#pragma unroll
+      for (int k = 0; k < FE; ++k) s_agg[warp][lane * FE + k] = gw[k];
+      __syncthreads();
+      for (int i = tid; i < FE * FN; i += TBF) {
+        float v = 0.f;
+        for (int w = 0; w < NWF; ++w) v += s_agg[w][i];
+        st.pa_agg[(int64_t)f * (FE * FN) + i] = v;
+      }
+    } else {
+      for (int i = tid; i < n * FN; i += TBF) s_gR[i] = 0.f;     // the node update of the last step is dead
+    }
+    __syncthreads();
+
+    // ---- B. per-edge backward of the node model (edge side) and of the edge model ----
+    {
+      float gw[FE * EIN];
+#pragma unroll
+      for (int i = 0; i < FE * EIN; ++i) gw[i] = 0.f;
+      for (int j = tid; j < m; j += TBF) {
+        const int64_t jg = eb + j;
+        float ev[FE], ge[FE];
+#pragma unroll
+        for (int k = 0; k < FE; ++k) {
+          ev[k] = s_e[j * FE + k];
+          ge[k] = (ge_in ? ge_in[jg * FE + k] : 0.f) + (has_cls ? s_gze[j * EP + k] : 0.f);
+        }
+        if (gh != nullptr) {
+          const int s = (int)(p.src[jg] - n0);
+          const float inv_deg = 1.f / (float)max(s_rp[s + 1] - s_rp[s], 1);
+          const float4* R4 = reinterpret_cast<const float4*>(s_R + s * FN);
+          const float4* G4 = reinterpret_cast<const float4*>(s_gh + s * FN);
+          const float4* H4 = reinterpret_cast<const float4*>(s_hv + s * FN);
+#pragma unroll
+          for (int c4 = 0; c4 < FN / 4; ++c4) {
+            const float4 r = R4[c4], g = G4[c4];
+            const float4 hv = p.agg == GNNCCA_AGG_MAX ? H4[c4] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float rr[4] = {r.x, r.y, r.z, r.w}, gg[4] = {g.x, g.y, g.z, g.w}, hh[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int c = c4 * 4 + u;
+              float z = rr[u];
+#pragma unroll
+              for (int k = 0; k < FE; ++k) z = fmaf(ev[k], s_wne[k][c], z);
+              const float gz = agg_grad(p.agg, gg[u], z, hh[u], inv_deg);
+#pragma unroll
+              for (int k = 0; k < FE; ++k) ge[k] = fmaf(gz, s_wne[k][c], ge[k]);
+            }
+          }
+        }
+        float gze[FE];
+#pragma unroll
+        for (int o = 0; o < FE; ++o) gze[o] = ev[o] > 0.f ? ge[o] : 0.f;          // ReLU gate of the edge MLP
+        *reinterpret_cast<float4*>(s_gze + j * EP) = make_float4(gze[0], gze[1], gze[2], gze[3]);
+        *reinterpret_cast<float4*>(s_gze + j * EP + 4) = make_float4(gze[4], gze[5], 0.f, 0.f);
+        float ein[EIN];
+        if (REATT_E) {
+#pragma unroll
+          for (int k = 0; k < FE; ++k) ein[k] = p.e0[jg * FE + k];
+        }
+#pragma unroll
+        for (int k = 0; k < FE; ++k) ein[OFF + k] = st.e_prev[jg * FE + k];
+#pragma unroll
+        for (int k = 0; k < FE; ++k) {
+          float a = 0.f;
+#pragma unroll
+          for (int o = 0; o < FE; ++o) a = fmaf(gze[o], s_wee[o][OFF + k], a);
+          ge_out[jg * FE + k] = a;
+        }
+        if (REATT_E) {
+#pragma unroll
+          for (int k = 0; k < FE; ++k) {
+            float a = p.ge0_acc[jg * FE + k];
+#pragma unroll
+            for (int o = 0; o < FE; ++o) a = fmaf(gze[o], s_wee[o][k], a);
+            p.ge0_acc[jg * FE + k] = a;
+          }
+        }
+#pragma unroll
+        for (int o = 0; o < FE; ++o)
+#pragma unroll
+          for (int kk = 0; kk < EIN; ++kk) gw[o * EIN + kk] = fmaf(gze[o], ein[kk], gw[o * EIN + kk]);
+      }
+      block_reduce_store<FE * EIN>(gw, s_red, st.pa_edge + (int64_t)f * (FE * EIN));      // ends with __syncthreads()
+    }
+
+    // ---- D. gP / gQ: warp per node, lane = (edge slot 0..3) x (component 0..7); in-edges through the reverse-edge table ----
+    {
+      const int o = lane & 7, slot = lane >> 3;
+      for (int v = warp; v < n; v += NWF) {
+        float a = 0.f, b = 0.f;
+        for (int j = s_rp[v] + slot; j < s_rp[v + 1]; j += 4) {
+          a += s_gze[j * EP + o];
+          b += s_gze[(int)(p.tperm[eb + j] - eb) * EP + o];          // symmetric frames: colptr == rowptr
+        }
+        a += __shfl_xor_sync(0xffffffffu, a, 8); a += __shfl_xor_sync(0xffffffffu, a, 16);
+        b += __shfl_xor_sync(0xffffffffu, b, 8); b += __shfl_xor_sync(0xffffffffu, b, 16);
+        if (slot == 0) { s_gP[v * EP + o] = a; s_gQ[v * EP + o] = b; }
+      }
+    }
+    __syncthreads();
+
+    // ---- E. backward of the per-node projections, 16 nodes at a time; the weight-gradient partial of the whole frame ----
+    {
+      constexpr int PER = (OUT * (K + 1) + TBF - 1) / TBF;
+      float pacc[PER];
+#pragma unroll
+      for (int q = 0; q < PER; ++q) pacc[q] = 0.f;
+      const float* h_prev = st.h_prev;
+      for (int i = tid; i < n * OUT; i += TBF) {                // [gP | gQ | gR] of every node of the frame, row stride OUT + 1
+        const int v = i / OUT, o = i - v * OUT;
+        s_pg[v * (OUT + 1) + o] = o < FE ? s_gP[v * EP + o] : (o < 2 * FE ? s_gQ[v * EP + o - FE] : s_gR[v * FN + o - 2 * FE]);
+      }
+      for (int c0 = 0; c0 < n; c0 += PB_NODES) {
+        const int nc = min(PB_NODES, n - c0);
+        for (int i = tid; i < PB_NODES * (K + 1); i += TBF) {
+          const int v = i / (K + 1), k = i - v * (K + 1);
+          const int64_t node = n0 + c0 + v;
+          float val = 0.f;
+          if (v < nc) val = k == K ? 1.f : (K == 2 * FN ? (k < FN ? p.h0[node * FN + k] : h_prev[node * FN + k - FN]) : h_prev[node * FN + k]);
+          s_ph[i] = val;
+        }
+        __syncthreads();
+        for (int i = tid; i < nc * K; i += TBF) {
+          const int v = i / K, k = i - v * K;
+          const int64_t node = n0 + c0 + v;
+          float a = 0.f;
+          for (int o = 0; o < OUT; ++o) a = fmaf(s_pg[(c0 + v) * (OUT + 1) + o], s_pw[o * K + k], a);
+          if (K == 2 * FN && k < FN) p.gh0_acc[node * FN + k] += a;        // the reattached block is the encoder output (mpn.py:285)
+          else st.gh_prev[node * FN + (K == 2 * FN ? k - FN : k)] = a;
+        }
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+          const int i = tid + q * TBF;
+          if (i < OUT * (K + 1)) {
+            const int o = i / (K + 1), k = i - o * (K + 1);
+            float a = pacc[q];
+            for (int v = 0; v < nc; ++v) a = fmaf(s_pg[(c0 + v) * (OUT + 1) + o], s_ph[v * (K + 1) + k], a);
+            pacc[q] = a;
+          }
+        }
+        __syncthreads();
+      }
+#pragma unroll
+      for (int q = 0; q < PER; ++q) {
+        const int i = tid + q * TBF;
+        if (i < OUT * (K + 1)) st.pa_proj[(int64_t)f * (OUT * (K + 1)) + i] = pacc[q];
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -758,6 +1072,59 @@ extern "C" int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp
   return check_launch();
 }
 
+extern "C" int64_t gnncca_mp_frames_bwd_smem_bytes(int32_t max_frame_nodes, int32_t max_frame_edges) {
+  max_frame_edges = (max_frame_edges + 3) & ~3;          // keeps the arrays behind e^t 16-byte aligned
+  return 4 * ((int64_t)max_frame_edges * (tr::FE + tr::EP) + (int64_t)max_frame_nodes * (4 * tr::FN + 2 * tr::EP + 2 * tr::FE + tr::FN + 1) +
+              max_frame_nodes + 1 + 4);
+}
+
+extern "C" int gnncca_mp_frames_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int64_t* graph_ptr, const int64_t* edge_ptr,
+                                    int64_t n_graphs, const int32_t* rowptr, const int32_t* src, const int32_t* tperm, int64_t n_nodes,
+                                    int64_t n_edges, int32_t max_frame_nodes, int32_t max_frame_edges,
+                                    const gnncca_frame_bwd_step* host_steps, int32_t n_steps, const float* e0, const float* h0,
+                                    float* ge_a, float* ge_b, float* ge0_acc, float* gh0_acc, void* stream) {
+  if (!dims_ok(cfg)) return cfg ? GNNCCA_ERR_UNSUPPORTED : GNNCCA_ERR_BAD_ARG;
+  if (n_steps < 1 || n_steps > GNNCCA_FRAMES_BWD_MAX_STEPS || n_graphs < 0 || n_graphs > INT32_MAX) return GNNCCA_ERR_BAD_ARG;
+  if (n_graphs == 0 || n_edges == 0) return GNNCCA_OK;
+  if (!w || !graph_ptr || !edge_ptr || !rowptr || !src || !tperm || !host_steps || !ge_a || !ge_b) return GNNCCA_ERR_BAD_ARG;
+  if (max_frame_nodes < 1 || max_frame_edges < 1) return GNNCCA_ERR_BAD_ARG;
+  const int64_t dyn_bytes = gnncca_mp_frames_bwd_smem_bytes(max_frame_nodes, max_frame_edges);
+  if (dyn_bytes > GNNCCA_FRAMES_BWD_SMEM_LIMIT) return GNNCCA_ERR_UNSUPPORTED;         // frames too large for a CTA each: the per-step entries
+  if (cfg->reattach_edges && (!e0 || !ge0_acc)) return GNNCCA_ERR_BAD_ARG;
+  if (cfg->reattach_nodes && (!h0 || !gh0_acc)) return GNNCCA_ERR_BAD_ARG;
+  const int K = cfg->reattach_nodes ? 2 * tr::FN : tr::FN;
+  const int EIN = cfg->reattach_edges ? 2 * tr::FE : tr::FE;
+  tr::FramesBwd p{};
+  p.graph_ptr = graph_ptr; p.edge_ptr = edge_ptr; p.rowptr = rowptr; p.src = src; p.tperm = tperm;
+  p.w_edge = w->w_edge; p.w_node = w->w_node; p.edge_row = 2 * K + EIN; p.node_row = K + tr::FE; p.K = K;
+  p.w1 = w->w_c1; p.b1 = w->b_c1; p.w2 = w->w_c2; p.b2 = w->b_c2;
+  p.e0 = e0; p.h0 = h0; p.n_steps = n_steps; p.agg = cfg->agg; p.n_nodes = n_nodes;
+  bool any_cls = false;
+  for (int t = 0; t < n_steps; ++t) {
+    const gnncca_frame_bwd_step& st = host_steps[t];
+    if (!st.e || !st.e_prev || !st.h_prev || !st.pa_edge || !st.pa_proj || !st.gh_prev) return GNNCCA_ERR_BAD_ARG;
+    if (t + 1 < n_steps && (!st.R || !st.pa_agg || (cfg->agg == GNNCCA_AGG_MAX && !st.h_out))) return GNNCCA_ERR_BAD_ARG;
+    if (st.g_logits) { if (!st.pa_cls) return GNNCCA_ERR_BAD_ARG; any_cls = true; }
+    p.st[t] = st;
+  }
+  if (any_cls && (cfg->cls_hidden != tr::HC || !w->w_c1 || !w->b_c1 || !w->w_c2)) return GNNCCA_ERR_UNSUPPORTED;
+  p.ge_buf[0] = ge_a; p.ge_buf[1] = ge_b; p.ge0_acc = ge0_acc; p.gh0_acc = gh0_acc;
+  p.max_n = max_frame_nodes; p.max_e = (max_frame_edges + 3) & ~3;
+  static bool s_attr[4] = {false, false, false, false};     // opt in to > 48 KB of dynamic shared memory, once per instantiation
+  const int which = (cfg->reattach_edges ? 1 : 0) + (cfg->reattach_nodes ? 2 : 0);
+  const void* fn = which == 0 ? (const void*)tr::frames_bwd_kernel<false, tr::FN> : which == 1 ? (const void*)tr::frames_bwd_kernel<true, tr::FN>
+                 : which == 2 ? (const void*)tr::frames_bwd_kernel<false, 2 * tr::FN> : (const void*)tr::frames_bwd_kernel<true, 2 * tr::FN>;
+  if (!s_attr[which]) {
+    const cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, GNNCCA_FRAMES_BWD_SMEM_LIMIT);
+    if (e != cudaSuccess) return check_cuda(e);
+    s_attr[which] = true;
+  }
+  void* args[] = {(void*)&p};
+  const cudaError_t le = cudaLaunchKernel(fn, dim3((unsigned)n_graphs), dim3(tr::TBF), args, (size_t)dyn_bytes, (cudaStream_t)stream);
+  if (le != cudaSuccess) return check_cuda(le);
+  return check_launch();
+}
+
 extern "C" int gnncca_edge_enc_bwd(const float* edge_attr, int32_t edge_in_dim, const float* e0, const float* ge0, int64_t n_edges,
                                    float* partial, void* stream) {
   if (edge_in_dim < 1 || edge_in_dim > tr::MAX_FA) return GNNCCA_ERR_UNSUPPORTED;
@@ -769,14 +1136,15 @@ extern "C" int gnncca_edge_enc_bwd(const float* edge_attr, int32_t edge_in_dim, 
 
 extern "C" int gnncca_linear_bwd(const float* x, const float* W, const float* y, const float* gy, int32_t relu, int64_t rows, int32_t in_dim,
                                  int32_t out_dim, float* gz, float* gx, float* gb_partial, float* gw_partial, int32_t n_splits,
-                                 void* stream) {
+                                 int32_t math, void* stream) {
   if (rows <= 0 || in_dim <= 0 || out_dim <= 0 || n_splits < 1) return GNNCCA_ERR_BAD_ARG;
   if (!x || !y || !gy || !gz || !gb_partial || !gw_partial || (gx && !W)) return GNNCCA_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   tr::relu_grad_bias_kernel<<<(unsigned)ceil_div(rows, tr::RG_ROWS), 256, 0, st>>>(y, gy, relu, rows, out_dim, gz, gb_partial);
   const int64_t rps = ceil_div(ceil_div(rows, n_splits), tr::ATB_ROWS) * tr::ATB_ROWS;
   dim3 grid((unsigned)ceil_div(in_dim, 64), (unsigned)ceil_div(out_dim, 64), (unsigned)n_splits);
-  tr::atb_kernel<<<grid, 256, 0, st>>>(gz, x, rows, out_dim, in_dim, rps, gw_partial);
+  if (math == GNNCCA_MATH_TF32) tr::atb_kernel<1><<<grid, 256, 0, st>>>(gz, x, rows, out_dim, in_dim, rps, gw_partial);
+  else tr::atb_kernel<3><<<grid, 256, 0, st>>>(gz, x, rows, out_dim, in_dim, rps, gw_partial);
   int n = 2;
   if (gx) { tr::gz_times_w_kernel<<<grid_for(rows * in_dim, 256), 256, 0, st>>>(gz, W, rows, out_dim, in_dim, gx); ++n; }
   return check_launch(n);

@@ -209,7 +209,10 @@ class MOTMPNet(nn.Module):
                 self.last_plan = engine.FAST_PLAN
                 return {'classified_edges': outs}
         if train_path:
-            outs, plan = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan, trusted=trusted, return_plan=True)
+            frames = None
+            if trusted and getattr(data, "edge_ptr", None) is not None and graph_ptr is not None and caps is not None:
+                frames = (graph_ptr, data.edge_ptr, caps)      # closed frames with known offsets: the backward runs as one launch
+            outs, plan = autograd_fn.forward_training(self, x, edge_index, edge_attr, plan, trusted=trusted, return_plan=True, frames=frames)
             if engine.CACHE_PLANS and plan is not None:
                 try:                    # the CSR (and its transpose for the backward) is reused while edge_index is unchanged
                     plan.ptr_key = ptr_key

@@ -322,14 +322,46 @@ int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w
                             const float* h0, const float* h, int64_t n_nodes, float* gh_prev, float* gh0_acc, float* partial,
                             void* stream);
 
+/* The whole message-passing backward (the per-step chain gnncca_cls_bwd -> gnncca_node_agg_bwd -> gnncca_edge_bwd ->
+ * gnncca_pq_reduce -> gnncca_node_project_bwd for t = n_steps .. 1, autograd of mpn.py:279-293) of a batch of SMALL closed frames
+ * in ONE launch: a CTA per frame runs the same phases on the frame's node / edge range with __syncthreads() between them.  For
+ * EPFL-sized frames a kernel boundary costs more than a phase's work.  Needs the frame offsets (graph_ptr / edge_ptr, int64
+ * [n_graphs + 1], Batch.ptr and the edge offsets of build_graph_batch), a source-major symmetric CSR and its reverse-edge table
+ * (gnncca_csr_reverse_edges), no training-mode BatchNorm in the classifier.  host_steps[t - 1] describes step t (HOST array):
+ *   R, e = e^t, e_prev = e^{t-1}, h_out = h^t (max aggregation only), h_prev = h^{t-1}, g_logits ([E] or NULL), aff (classifier
+ *   BatchNorm affine [4][cls_hidden] or NULL), the step's partial rows pa_agg [n_graphs][f_node * f_edge], pa_edge [n_graphs][f_edge *
+ *   EIN], pa_proj [n_graphs][44 * (K + 1)], pa_cls [n_graphs][GNNCCA cls accumulators] (one row per FRAME; fold with
+ *   gnncca_finalize_grads), and gh_prev [N, f_node], which receives the gradient wrt h^{t-1}.
+ * The frame's state of a step (e^t, R, gradients per node and per edge) lives in the CTA's shared memory:
+ * gnncca_mp_frames_bwd_smem_bytes(max_frame_nodes, max_frame_edges) must not exceed GNNCCA_FRAMES_BWD_SMEM_LIMIT (GNNCCA_ERR_UNSUPPORTED otherwise:
+ * use the per-step entries), about 3500 edges per frame.  max_frame_nodes / max_frame_edges: the batch maxima (totals words [2],
+ * [3] of graph construction).  Scratch (device): ge_a / ge_b [E, f_edge] (ge_a ends up holding the gradient wrt e^0);
+ * ge0_acc / gh0_acc as in the per-step entries (zeroed by the caller). */
+#define GNNCCA_FRAMES_BWD_MAX_STEPS 8
+#define GNNCCA_FRAMES_BWD_SMEM_LIMIT (190 * 1024)
+typedef struct {
+  const float* R; const float* e; const float* e_prev; const float* h_out; const float* h_prev;
+  const float* g_logits; const float* aff;
+  float* pa_agg; float* pa_edge; float* pa_proj; float* pa_cls; float* gh_prev;
+} gnncca_frame_bwd_step;
+int64_t gnncca_mp_frames_bwd_smem_bytes(int32_t max_frame_nodes, int32_t max_frame_edges);
+int gnncca_mp_frames_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const int64_t* graph_ptr, const int64_t* edge_ptr,
+                         int64_t n_graphs, const int32_t* rowptr, const int32_t* src, const int32_t* tperm, int64_t n_nodes,
+                         int64_t n_edges, int32_t max_frame_nodes, int32_t max_frame_edges,
+                         const gnncca_frame_bwd_step* host_steps, int32_t n_steps, const float* e0, const float* h0,
+                         float* ge_a, float* ge_b, float* ge0_acc, float* gh0_acc, void* stream);
+
 /* Edge encoder Linear(edge_in_dim, f_edge)+ReLU: partial [GNNCCA_BLOCKS_PER_EDGE blocks][f_edge * 8 + f_edge] = gW[o][k] at o*8+k | gb. */
 int gnncca_edge_enc_bwd(const float* edge_attr, int32_t edge_in_dim, const float* e0, const float* ge0, int64_t n_edges,
                         float* partial, void* stream);
 
 /* Dense layer y = act(x W^T + b): gz[rows,out] = gy * [y > 0] (relu != 0), gb_partial [GNNCCA_BLOCKS_ROW_CHUNKS][out],
- * gw_partial [n_splits][out * in] (row ranges), gx[rows,in] = gz W when gx != NULL. */
+ * gw_partial [n_splits][out * in] (row ranges), gx[rows,in] = gz W when gx != NULL.  The weight gradient gz^T x runs on the
+ * tensor cores: math = GNNCCA_MATH_FP32 splits every operand (3 x tf32, fp32-level accuracy), GNNCCA_MATH_TF32 takes the
+ * operands as tf32 like the forward's tcgen05 encoder. */
 int gnncca_linear_bwd(const float* x, const float* W, const float* y, const float* gy, int32_t relu, int64_t rows, int32_t in_dim,
-                      int32_t out_dim, float* gz, float* gx, float* gb_partial, float* gw_partial, int32_t n_splits, void* stream);
+                      int32_t out_dim, float* gz, float* gx, float* gb_partial, float* gw_partial, int32_t n_splits, int32_t math,
+                      void* stream);
 
 /* dst[r * dst_stride + c] (+)= sum_{b < n_blocks} partial[b * width + src_off + r * src_stride + c]  (b ascending). */
 typedef struct {

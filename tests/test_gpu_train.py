@@ -128,3 +128,63 @@ def test_default_tf32_training_step_stays_within_tf32_tolerance_of_the_reference
         ref = torch.from_numpy(z["grad/" + name]).double()
         err = ((p.grad.cpu().double() - ref).abs() / (1 + ref.abs() + 0.01 * ref.abs().max())).max()
         assert float(err) <= TF32_GRAD_TOL, (name, float(err))
+
+
+@pytest.mark.parametrize("agg,extra", [("sum", None), ("mean", None), ("max", None),
+                                       ("sum", {"reattach_initial_nodes": True, "reattach_initial_edges": True})])
+def test_one_launch_backward_of_small_frames_matches_the_oracle_and_the_per_step_chain(agg, extra, cuda_device, monkeypatch):
+    """Batches from build_graph_batch (closed frames, offsets known) run their message-passing backward as ONE launch
+    (gnncca_mp_frames_bwd) with the reverse-edge table instead of the sort by target: loss and every gradient against torch
+    autograd through the CPU oracle, and against the per-step kernel chain on the same batch; ragged frames."""
+    import copy
+    from importlib import import_module
+    import gnncca
+    from oracle import mpn_oracle
+    afn = import_module("gnn-cca_b200.autograd_fn")
+    params = import_module("gnn-cca_b200.config").graph_net_params()
+    params["node_agg_fn"] = agg
+    if extra:
+        params.update(extra)
+    rng = np.random.default_rng(5)
+    cam, ids, ptr = [], [], [0]
+    for _ in range(19):
+        counts = rng.integers(1, 9, 4)
+        cam.append(np.repeat(np.arange(4), counts))
+        ids.append(np.concatenate([rng.permutation(8)[:c] for c in counts]))
+        ptr.append(ptr[-1] + int(counts.sum()))
+    N = ptr[-1]
+    g = torch.Generator().manual_seed(3)
+    b = gnncca.build_graph_batch(graph_ptr=torch.tensor(ptr, device=cuda_device), id_cam=torch.from_numpy(np.concatenate(cam)).to(cuda_device),
+                                 ids=torch.from_numpy(np.concatenate(ids)).to(cuda_device), xw=torch.rand(N, generator=g, dtype=torch.float64).to(cuda_device) * 300,
+                                 yw=torch.rand(N, generator=g, dtype=torch.float64).to(cuda_device) * 200,
+                                 max_dist=torch.full((19,), 50.83, dtype=torch.float64, device=cuda_device),
+                                 reid_embeds=torch.relu(torch.randn(N, 64, generator=g)).to(cuda_device),
+                                 node_embeds=torch.relu(torch.randn(N, 512, generator=g)).to(cuda_device))
+    assert b.gnncca_trusted
+    crit = torch.nn.BCEWithLogitsLoss()
+    lib = import_module("gnn-cca_b200._lib").load()
+    grads, launches = {}, {}
+    for fused in (True, False):
+        monkeypatch.setattr(afn, "FUSED_BWD", fused)
+        torch.manual_seed(0)
+        model = gnncca.MOTMPNet(copy.deepcopy(params), None, "bdnet_market", math="fp32").to(cuda_device).train()
+        if hasattr(b, "gnncca_plan"):
+            del b.gnncca_plan
+        out = model(b)["classified_edges"]
+        loss = sum(crit(o.view(-1), b.edge_labels) for o in out)
+        n0 = lib.gnncca_launch_count()
+        loss.backward()
+        launches[fused] = lib.gnncca_launch_count() - n0
+        grads[fused] = ({n: p.grad.clone() for n, p in model.named_parameters()}, float(loss.detach()))
+        sd0 = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    assert launches[True] + 12 <= launches[False]        # the one-launch path really ran (18 launches of the chain became 1)
+    spec = mpn_oracle.MPNSpec(params, "bdnet_market")
+    sdr = {k: v.clone().requires_grad_(v.is_floating_point()) for k, v in sd0.items()}
+    ref = mpn_oracle.motmpnet_forward(spec, sdr, b.x.cpu(), b.edge_index.cpu(), b.edge_attr.cpu(), training=True)["classified_edges"]
+    lref = sum(crit(r.view(-1), b.edge_labels.cpu()) for r in ref)
+    lref.backward()
+    assert abs(grads[True][1] - float(lref)) <= 1e-5 * (1 + abs(float(lref)))
+    for name in grads[True][0]:
+        a, c, r = grads[True][0][name], grads[False][0][name], sdr[name].grad
+        assert close(a, r) <= GRAD_TOL, name
+        assert close(a, c.cpu()) <= 1e-5, name            # same arithmetic per element, another grouping of the partial sums
