@@ -15,6 +15,7 @@ from .plan import GraphPlan, _stream
 
 P = _lib.ptr
 FUSED_BWD = os.environ.get("GNNCCA_FUSED_BWD", "1") != "0"
+FUSED_FWD = os.environ.get("GNNCCA_FUSED_TRAIN_FWD", "1") != "0"      # the all-steps forward of small frames in training
 FUSED_BWD_MAX_EDGES = int(os.environ.get("GNNCCA_FUSED_BWD_MAX_EDGES", "3500"))     # per frame: above it the per-step chain runs
 
 
@@ -118,6 +119,40 @@ class _MPNFunction(torch.autograd.Function):
                 acts.append(engine.linear(acts[-1], enc_n.linear(i), sp.relu, None, _lib.MATH_FP32))
         h0 = acts[-1]
         ea = plan.to_sorted(edge_attr.contiguous())
+
+        # eligibility of the one-launch paths (small closed frames with known offsets; see ctx.frames below)
+        B = int(frames[0].numel()) - 1 if frames is not None else 0
+        frames_ok = (frames is not None and FUSED_BWD and trusted and plan.perm is None and plan.colptr is plan.rowptr and bn_mode != "train"
+                     and L <= _lib.FRAMES_BWD_MAX_STEPS and frames[2][1] <= FUSED_BWD_MAX_EDGES and B >= 8
+                     and int(lib.gnncca_mp_frames_bwd_smem_bytes(int(frames[2][0]), int(frames[2][1]))) <= _lib.FRAMES_BWD_SMEM_LIMIT)
+        cap = engine.frame_capacity(model, N, E, B, frames[2]) if (frames_ok and FUSED_FWD) else None
+        if cap is not None and enc_e.layer_specs[0].relu and enc_e.layer_specs[0].bn is None:
+            # the all-steps forward of small frames (gnncca_mp_fused_fwd, a frame's latents stay in shared memory across the steps)
+            # with every step's latents written out for the backward; the projections are recomputed there
+            n_cls = L - first + 1
+            logits = torch.empty((n_cls, E), dtype=torch.float32, device=dev)
+            h_dump = torch.empty((L + 1, N, sb.f_node), dtype=torch.float32, device=dev)
+            e_dump = torch.empty((L + 1, E, sb.f_edge), dtype=torch.float32, device=dev)
+            le = enc_e.linear(0)
+            _lib.check(lib.gnncca_mp_fused_fwd(C.byref(sb.cfg), C.byref(sb.w), P(le.weight), P(le.bias), int(ea.size(1)), P(frames[0]), B, 0, 0,
+                                               P(plan.rowptr), P(plan.src), P(plan.dst), N, E, P(h0), P(ea), L, first, cap[0], cap[1],
+                                               P(logits), P(h_dump), P(e_dump), P(plan.flags), _stream()), "mp_fused_fwd")
+            hs, es = [h_dump[t] for t in range(L + 1)], [e_dump[t] for t in range(L + 1)]
+            affs = {}
+            if bn_mode == "eval":
+                invstd = torch.rsqrt(bn.running_var.detach() + bn.eps)
+                scale = bn.weight.detach() * invstd
+                aff = torch.cat([scale, bn.bias.detach() - bn.running_mean * scale, bn.running_mean.detach(), invstd]).contiguous()
+                affs = {t: aff for t in range(first, L + 1)}
+            if guard and not plan._requested and not torch.cuda.is_current_stream_capturing():
+                plan.request_flags()
+            ctx.model, ctx.plan, ctx.sb = model, plan, sb
+            ctx.frames = (frames[0], frames[1], (int(frames[2][0]), int(frames[2][1])))
+            ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, proj=None, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
+                             names=[n for n, _ in model.named_parameters_fast()])
+            ctx.set_materialize_grads(False)
+            model.__dict__["_gnncca_train_plan"] = plan
+            return tuple(logits[i].view(E, 1) for i in range(n_cls))
         e0 = engine.small_mlp_rows(enc_e, ea)
 
         hs, es, affs, outs = [h0], [e0], {}, []
@@ -173,11 +208,7 @@ class _MPNFunction(torch.autograd.Function):
         ctx.model, ctx.plan, ctx.sb = model, plan, sb
         # one-launch backward (gnncca_mp_frames_bwd): closed frames with known offsets, every frame small enough for one CTA,
         # the reverse-edge table in place of the sort by target, no batch statistics in the classifier
-        ctx.frames = None
-        if (frames is not None and FUSED_BWD and trusted and plan.perm is None and plan.colptr is plan.rowptr and bn_mode != "train"
-                and L <= _lib.FRAMES_BWD_MAX_STEPS and frames[2][1] <= FUSED_BWD_MAX_EDGES and int(frames[0].numel()) - 1 >= 8
-                and int(lib.gnncca_mp_frames_bwd_smem_bytes(int(frames[2][0]), int(frames[2][1]))) <= _lib.FRAMES_BWD_SMEM_LIMIT):
-            ctx.frames = (frames[0], frames[1], (int(frames[2][0]), int(frames[2][1])))
+        ctx.frames = (frames[0], frames[1], (int(frames[2][0]), int(frames[2][1]))) if frames_ok else None
         ctx.saved = dict(acts=acts, ea=ea, hs=hs, es=es, affs=affs, proj=proj, tperm=tperm, colptr=colptr, bn_mode=bn_mode, first=first,
                          names=[n for n, _ in model.named_parameters_fast()])
         ctx.set_materialize_grads(False)
@@ -251,7 +282,7 @@ class _MPNFunction(torch.autograd.Function):
                     keep_g.append(g)
                 aff = sv["affs"].get(t)
                 ci = t - first
-                steps[t - 1] = _lib.FrameBwdStep(proj[t - 1, N * 16:].data_ptr(), P(es[t]), P(es[t - 1]), P(hs[t]), P(hs[t - 1]), P(g), P(aff),
+                steps[t - 1] = _lib.FrameBwdStep(proj[t - 1, N * 16:].data_ptr() if proj is not None else 0, P(es[t]), P(es[t - 1]), P(hs[t]), P(hs[t - 1]), P(g), P(aff),
                                                  P(pa_agg[t - 1]), P(pa_edge[t - 1]), P(pa_proj[t - 1]), P(pa_cls[ci]) if g is not None else 0,
                                                  P(gh_prevs[t - 1]))
             _lib.check(lib.gnncca_mp_frames_bwd(cfg, w, P(ctx.frames[0]), P(ctx.frames[1]), B, P(plan.rowptr), P(plan.src), P(sv["tperm"]), N, E,

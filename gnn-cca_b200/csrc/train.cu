@@ -655,7 +655,7 @@ struct FramesBwd {
   const int64_t* graph_ptr; const int64_t* edge_ptr;
   const int32_t* rowptr; const int32_t* src; const int32_t* tperm;
   const float* w_edge; const float* w_node; int edge_row, node_row, K;
-  const float* w1; const float* b1; const float* w2; const float* b2;
+  const float* w1; const float* b1; const float* w2; const float* b2; const float* b_node;
   const float* e0; const float* h0;
   int n_steps, agg; int64_t n_nodes; int max_n, max_e;
   gnncca_frame_bwd_step st[GNNCCA_FRAMES_BWD_MAX_STEPS];
@@ -718,7 +718,24 @@ __global__ void __launch_bounds__(TBF) frames_bwd_kernel(const FramesBwd p) {
     // ---- stage the step: e^t, R, gh (coalesced, independent loads) ----
     for (int i = tid; i < m * FE; i += TBF) s_e[i] = st.e[eb * FE + i];
     if (gh != nullptr) {
-      for (int i = tid; i < n * FN; i += TBF) { s_R[i] = st.R[n0 * FN + i]; s_gh[i] = gh[n0 * FN + i]; }
+      if (st.R != nullptr) {
+        for (int i = tid; i < n * FN; i += TBF) s_R[i] = st.R[n0 * FN + i];
+      } else {
+        // the forward kept no projections (the all-steps forward of small frames): R = [h0,] h^{t-1} W_nx^T + b_n here
+        for (int i = tid; i < n * FN; i += TBF) {
+          const int v = i / FN, c = i - v * FN;
+          const float* wr = s_pw + (2 * FE + c) * K;
+          float a = p.b_node[c];
+          if (K == 2 * FN) {
+#pragma unroll 8
+            for (int k = 0; k < FN; ++k) a = fmaf(p.h0[(n0 + v) * FN + k], wr[k], a);
+          }
+#pragma unroll 8
+          for (int k = 0; k < FN; ++k) a = fmaf(st.h_prev[(n0 + v) * FN + k], wr[(K == 2 * FN ? FN : 0) + k], a);
+          s_R[i] = a;
+        }
+      }
+      for (int i = tid; i < n * FN; i += TBF) s_gh[i] = gh[n0 * FN + i];
     }
     if (has_cls && tid < HC) {
       s_aff[tid] = st.aff ? st.aff[tid] : 1.f; s_aff[HC + tid] = st.aff ? st.aff[HC + tid] : 0.f;
@@ -1097,13 +1114,13 @@ extern "C" int gnncca_mp_frames_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_we
   tr::FramesBwd p{};
   p.graph_ptr = graph_ptr; p.edge_ptr = edge_ptr; p.rowptr = rowptr; p.src = src; p.tperm = tperm;
   p.w_edge = w->w_edge; p.w_node = w->w_node; p.edge_row = 2 * K + EIN; p.node_row = K + tr::FE; p.K = K;
-  p.w1 = w->w_c1; p.b1 = w->b_c1; p.w2 = w->w_c2; p.b2 = w->b_c2;
+  p.w1 = w->w_c1; p.b1 = w->b_c1; p.w2 = w->w_c2; p.b2 = w->b_c2; p.b_node = w->b_node;
   p.e0 = e0; p.h0 = h0; p.n_steps = n_steps; p.agg = cfg->agg; p.n_nodes = n_nodes;
   bool any_cls = false;
   for (int t = 0; t < n_steps; ++t) {
     const gnncca_frame_bwd_step& st = host_steps[t];
     if (!st.e || !st.e_prev || !st.h_prev || !st.pa_edge || !st.pa_proj || !st.gh_prev) return GNNCCA_ERR_BAD_ARG;
-    if (t + 1 < n_steps && (!st.R || !st.pa_agg || (cfg->agg == GNNCCA_AGG_MAX && !st.h_out))) return GNNCCA_ERR_BAD_ARG;
+    if (t + 1 < n_steps && (!st.pa_agg || (!st.R && !w->b_node))) return GNNCCA_ERR_BAD_ARG;
     if (st.g_logits) { if (!st.pa_cls) return GNNCCA_ERR_BAD_ARG; any_cls = true; }
     p.st[t] = st;
   }

@@ -328,7 +328,8 @@ int gnncca_node_project_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w
  * EPFL-sized frames a kernel boundary costs more than a phase's work.  Needs the frame offsets (graph_ptr / edge_ptr, int64
  * [n_graphs + 1], Batch.ptr and the edge offsets of build_graph_batch), a source-major symmetric CSR and its reverse-edge table
  * (gnncca_csr_reverse_edges), no training-mode BatchNorm in the classifier.  host_steps[t - 1] describes step t (HOST array):
- *   R, e = e^t, e_prev = e^{t-1}, h_out = h^t (max aggregation only), h_prev = h^{t-1}, g_logits ([E] or NULL), aff (classifier
+ *   R (the step's projection R [N, f_node], or NULL: recomputed from h_prev), e = e^t, e_prev = e^{t-1}, h_out (unused),
+ *   h_prev = h^{t-1}, g_logits ([E] or NULL), aff (classifier
  *   BatchNorm affine [4][cls_hidden] or NULL), the step's partial rows pa_agg [n_graphs][f_node * f_edge], pa_edge [n_graphs][f_edge *
  *   EIN], pa_proj [n_graphs][44 * (K + 1)], pa_cls [n_graphs][GNNCCA cls accumulators] (one row per FRAME; fold with
  *   gnncca_finalize_grads), and gh_prev [N, f_node], which receives the gradient wrt h^{t-1}.

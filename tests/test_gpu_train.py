@@ -187,4 +187,4 @@ def test_one_launch_backward_of_small_frames_matches_the_oracle_and_the_per_step
     for name in grads[True][0]:
         a, c, r = grads[True][0][name], grads[False][0][name], sdr[name].grad
         assert close(a, r) <= GRAD_TOL, name
-        assert close(a, c.cpu()) <= 1e-5, name            # same arithmetic per element, another grouping of the partial sums
+        assert close(a, c.cpu()) <= 2e-5, name            # the same algebra, other groupings of the sums (and 3xTF32 projections)
