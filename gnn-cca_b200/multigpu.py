@@ -164,7 +164,8 @@ def forward_edge_partitioned_host(model, x: torch.Tensor, edge_index_local: torc
 
 
 def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tensor, edge_attr_local: torch.Tensor, edge_base: int = 0,
-                           prof=None, owned: Optional[Tuple[int, int]] = None, buffers: Optional[dict] = None, fold_owned_only: bool = False):
+                           prof=None, owned: Optional[Tuple[int, int]] = None, buffers: Optional[dict] = None, fold_owned_only: bool = False,
+                           shard_encoder: bool = False):
     """Generator form of the edge-partitioned forward: yields this rank's partial TARGET-PROJECTION matrix ``Q`` ([N, 8]: the
     rows of the nodes it owns are valid, all others zero) at every exchange point and expects the assembled matrix back
     through ``send``; returns the rank's logits.  (Tests drive several of these in lock step on one GPU.)
@@ -181,7 +182,10 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
     of the N x 32 node latents, and no projection launch runs between the steps.  ``owned``: this rank's node range; needed (to
     zero the other rows of Q) only with reattach_initial_nodes, where a non-owned row projects the replicated initial latents.
     ``fold_owned_only``: the second launch of every step visits the owned nodes only (the rows of Q outside ``owned`` are then NOT
-    written: for exchanges that overwrite them, i.e. the all-gather of equal ranges)."""
+    written: for exchanges that overwrite them, i.e. the all-gather of equal ranges).
+    ``shard_encoder``: the node encoder and the first projection run on the OWNED rows only (the replicated encoder is the largest
+    cost that does not shrink with the rank count) and one more exchange of ``Q`` precedes step 1; rows are independent in both
+    kernels, so the owned rows carry the same bits as in the replicated run."""
     from . import engine
     from .plan import GraphPlan, _stream
     lib = _lib.load()
@@ -212,7 +216,14 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
                 buffers[name] = t
         return t
 
-    h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math, out=get("h0", (N, 32)))
+    shard = bool(shard_encoder and owned is not None)
+    if shard:
+        na, nb = int(owned[0]), int(owned[1])
+        h = get("h0", (N, 32))                      # rows [na, nb) only
+        if nb > na:
+            engine.mlp_forward_nograd(model.encoder.node_mlp, x[na:nb], math, out=h[na:nb])
+    else:
+        h = engine.mlp_forward_nograd(model.encoder.node_mlp, x, math, out=get("h0", (N, 32)))
     if prof is not None:
         prof.mark("encoder_node")
     enc_e = model.encoder.edge_mlp
@@ -241,10 +252,24 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
         if buffers is not None:
             buffers["ws"] = ws
     h_out = get("h_out", (N, sb.f_node))
-    _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
-                                       _stream()), "node_project")
-    if prof is not None:
-        prof.mark("project1")
+    if shard:
+        if not fold_owned_only:
+            Q.zero_()                               # exchanges that SUM the partial matrices need the other rows at zero
+        if nb > na:
+            _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0[na:nb]), _lib.ptr(h[na:nb]), nb - na, _lib.ptr(P[na:nb]),
+                                               _lib.ptr(Q[na:nb]), _lib.ptr(R[na:nb]), _stream()), "node_project")
+        if prof is not None:
+            prof.mark("project1")
+        q_full = yield Q                            # the targets' projections of step 1 from their owners
+        if q_full.data_ptr() != Q.data_ptr():
+            Q.copy_(q_full)
+        if prof is not None:
+            prof.mark("exchange0")
+    else:
+        _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
+                                           _stream()), "node_project")
+        if prof is not None:
+            prof.mark("project1")
     for step in range(1, L + 1):
         last = step == L
         logits = get("logits%d" % step, (E, 1)) if step >= first else None
@@ -298,6 +323,9 @@ def check_partition_flags(model) -> None:
         raise ValueError("the local edge slice must be source-major")
 
 
+SHARD_ENCODER = os.environ.get("GNNCCA_SHARD_ENCODER", "1") != "0"
+
+
 class PartitionedForward:
     """The edge-partitioned forward of ONE rank as a replayable object: all work buffers are allocated once, the launches of one
     forward -- CSR narrowing, node encoder, L steps, and the NCCL all-gathers of the projected rows between them -- are captured
@@ -344,7 +372,7 @@ class PartitionedForward:
 
     def _run(self):
         gen = edge_partitioned_steps(self.model, self.x, self.ei, self.ea, self.edge_base, owned=self.ranges[self.rank], buffers=self.buffers,
-                                     fold_owned_only=self.live and self.equal)
+                                     fold_owned_only=self.live and self.equal, shard_encoder=self.live and self.equal and SHARD_ENCODER)
         try:
             q = next(gen)
             while True:

@@ -45,19 +45,24 @@ def test_giant_graph_matches_the_float64_oracle_end_to_end(math, tol, cuda_devic
         # the same through 4 virtual ranks in lock step on this GPU (the exchange replaced by a sum of the partial matrices)
         plan = importlib.import_module("gnn-cca_b200.plan").GraphPlan(ei, N).resolve()
         ranges = mg.balanced_source_ranges(plan.rowptr, 4)
-        gens = [mg.edge_partitioned_steps(model, x, ei[:, a * deg:b * deg].contiguous(), ea[a * deg:b * deg].contiguous(), a * deg) for a, b in ranges]
-        parts, outs = [next(gn) for gn in gens], [None] * 4
-        while any(o is None for o in outs):
-            h = torch.stack(parts).sum(0)
-            nxt = []
-            for r, gn in enumerate(gens):
-                try:
-                    nxt.append(gn.send(h))
-                except StopIteration as done:
-                    outs[r] = done.value
-            parts = nxt
-        for k in range(3):
-            assert torch.equal(torch.cat([o[k] for o in outs]), full[k])
+        for shard in (False, True):      # replicated encoder / encoder and first projection on the owned rows + one more exchange
+            gens = [mg.edge_partitioned_steps(model, x, ei[:, a * deg:b * deg].contiguous(), ea[a * deg:b * deg].contiguous(), a * deg,
+                                              owned=(a, b) if shard else None, shard_encoder=shard) for a, b in ranges]
+            parts, outs = [next(gn) for gn in gens], [None] * 4
+            rounds = 0
+            while any(o is None for o in outs):
+                h = torch.stack(parts).sum(0)
+                rounds += 1
+                nxt = []
+                for r, gn in enumerate(gens):
+                    try:
+                        nxt.append(gn.send(h))
+                    except StopIteration as done:
+                        outs[r] = done.value
+                parts = nxt
+            assert rounds == (4 if shard else 3)
+            for k in range(3):
+                assert torch.equal(torch.cat([o[k] for o in outs]), full[k])
     if "ref" not in _CACHE:            # same seed, same inputs for both math modes: one oracle evaluation (~15 s of CPU)
         spec = mpn_oracle.MPNSpec(params, "resnet50")
         sd64 = moc.cast_state_dict({k: v.detach().cpu() for k, v in model.state_dict().items()}, torch.float64)
