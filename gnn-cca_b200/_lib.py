@@ -62,6 +62,9 @@ SIGNATURES = {
     "gnncca_linear": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp, C.c_float, i32, vp]),
     "gnncca_node_encoder": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, i32, vp]),
     "gnncca_node_encoder_train": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, vp]),
+    "gnncca_node_encoder_splits": (i32, [i64, i32]),
+    "gnncca_node_encoder_scratch_bytes": (i64, [i64, i32, i32]),
+    "gnncca_node_encoder_ws": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, vp, i64, vp]),
     "gnncca_node_project": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp]),
     "gnncca_mp_step_tile": (i32, []),
     "gnncca_mp_step_workspace_bytes": (i64, [C.POINTER(MpCfg), i64, i64]),
@@ -74,7 +77,7 @@ SIGNATURES = {
     "gnncca_mp_fused_fwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i32, vp, i64, vp, vp, vp, vp, vp, i64, i64,
                                       vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp]),
     "gnncca_mpn_forward_frames": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp,
-                                            i64, i64, i64, i32, i32, i32, i32, vp, vp, vp, vp]),
+                                            i64, i64, i64, i32, i32, i32, i32, vp, vp, vp, vp, i64, vp]),
     "gnncca_train_blocks": (i32, [i64, i32]),
     "gnncca_node_agg_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gnncca_edge_bwd": (C.c_int, [C.POINTER(MpCfg), C.POINTER(MpWeights), vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),

@@ -111,8 +111,10 @@ class _MPNFunction(torch.autograd.Function):
             l1, l2 = enc_n.linear(0), enc_n.linear(1)
             h1 = torch.empty((N, l1.out_features), dtype=torch.float32, device=dev)
             h2 = torch.empty((N, l2.out_features), dtype=torch.float32, device=dev)
-            _lib.check(lib.gnncca_node_encoder_train(P(acts[0]), P(l1.weight), P(l1.bias), P(l2.weight), P(l2.bias), P(h1), P(h2), N,
-                                                     l1.in_features, l1.out_features, l2.out_features, _stream()), "node_encoder_train")
+            nb = engine.encoder_scratch_bytes(N, l1.in_features, l1.out_features)       # small batches: the split-K form
+            scr = torch.empty(nb // 4, dtype=torch.float32, device=dev) if nb else None
+            _lib.check(lib.gnncca_node_encoder_ws(P(acts[0]), P(l1.weight), P(l1.bias), P(l2.weight), P(l2.bias), P(h1), P(h2), N,
+                                                  l1.in_features, l1.out_features, l2.out_features, P(scr), nb, _stream()), "node_encoder_ws")
             acts += [h1, h2]
         else:
             for i, sp in enumerate(enc_n.layer_specs):

@@ -260,6 +260,18 @@ extern "C" int gnncca_node_encoder_train(const float* x, const float* W1, const 
   return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, h1, h, rows, in_dim, hidden, out_dim, stream);
 }
 
+int gnncca_node_encoder_tf32_ws(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
+                                int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* scratch, int64_t scratch_bytes, void* stream);
+
+extern "C" int gnncca_node_encoder_ws(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
+                                      int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* scratch, int64_t scratch_bytes,
+                                      void* stream) {
+  if (rows < 0 || in_dim <= 0 || hidden <= 0 || out_dim <= 0 || scratch_bytes < 0) return GNNCCA_ERR_BAD_ARG;
+  if (rows == 0) return GNNCCA_OK;
+  if (!x || !W1 || !b1 || !W2 || !b2 || !h) return GNNCCA_ERR_BAD_ARG;
+  return gnncca_node_encoder_tf32_ws(x, W1, b1, W2, b2, h1, h, rows, in_dim, hidden, out_dim, scratch, scratch_bytes, stream);
+}
+
 extern "C" int gnncca_node_project(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, const float* h0, const float* h,
                                    int64_t n_nodes, float* P, float* Q, float* R, void* stream) {
   if (!cfg || !w || n_nodes < 0) return GNNCCA_ERR_BAD_ARG;

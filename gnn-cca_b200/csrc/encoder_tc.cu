@@ -30,6 +30,11 @@ struct Params {
   int rows_per_cta;          // multiple of 8: CTA c owns rows [c * rows_per_cta, (c+1) * rows_per_cta)
   uint32_t a_bytes;          // bytes of a stage given to the x rows: min(rows_per_cta, 256) rows, 1024-aligned
   unsigned long long* trace; // development aid (tools/micro/enc_trace.cu): [grid][8] globaltimer stamps, normally NULL
+  // split-K form for SMALL inputs (gridDim.y = number of K splits): a CTA contracts k-blocks [blockIdx.y * kb_per_split, +kb_per_split)
+  // only and stores its raw layer-1 accumulators to partial[blockIdx.y][row][H]; encoder_finish_kernel sums the splits and applies
+  // the rest of the network.  Without it every CTA streams ALL of W1 (1 MB from L2) for its few rows: at N = 2560 that is 40-107 MB
+  // of L2 traffic for a 21 MB input and 30 us per forward.
+  float* partial; int kb_per_split;
 
 };
 
@@ -88,7 +93,8 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
   const int64_t row_end = min(row_begin + p.rows_per_cta, p.rows);
   const int my_rows = (int)(row_end - row_begin);
   const int n_super = (my_rows + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
-  const int KB = p.K / BLOCK_K;
+  const int KB = p.partial ? p.kb_per_split : p.K / BLOCK_K;
+  const int kb0 = p.partial ? (int)blockIdx.y * p.kb_per_split : 0;
 
   // producer state (warp 0, lane 0): the first ring of stages is issued BEFORE the set-up barrier, so x is already
   // streaming while the other warps allocate tensor memory and stage the small second layer
@@ -101,20 +107,20 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
       mbar_wait(empty + pr_s, pr_ph ^ 1);
       uint8_t* a = tiles + (size_t)pr_s * STAGE_BYTES;
       mbar_expect_tx(full + pr_s, (uint32_t)rows8 * (BLOCK_K * 4) + B_BYTES);
-      tma_load_2d(a + p.a_bytes, &tmap_w, full + pr_s, pr_kb * BLOCK_K, 0, HINT_EVICT_LAST);
+      tma_load_2d(a + p.a_bytes, &tmap_w, full + pr_s, (kb0 + pr_kb) * BLOCK_K, 0, HINT_EVICT_LAST);
       // sub-tile 0 at byte 0, sub-tile 1 at row 128 = byte offset A_BYTES; one box each when the row count is 128
       // or the launch's tail size (every CTA but the last), 8-row granular greedy boxes otherwise
 #pragma unroll 1
       for (int sub = 0; sub < 2; ++sub) {
         int need = min(rows8 - sub * BLOCK_M, BLOCK_M), off = sub * BLOCK_M;
         if (need <= 0) break;
-        if (need == BLOCK_M) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[4], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
-        if (need == xmaps.tail_rows) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[5], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
+        if (need == BLOCK_M) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[4], full + pr_s, (kb0 + pr_kb) * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
+        if (need == xmaps.tail_rows) { tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[5], full + pr_s, (kb0 + pr_kb) * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST); continue; }
 #pragma unroll
         for (int b = 3; b >= 0; --b) {
           const int sz = 8 << b;
           if (need >= sz) {
-            tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[b], full + pr_s, pr_kb * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST);
+            tma_load_2d(a + (size_t)off * (BLOCK_K * 4), &xmaps.m[b], full + pr_s, (kb0 + pr_kb) * BLOCK_K, (int)(r0 + off), HINT_EVICT_FIRST);
             off += sz; need -= sz;
           }
         }
@@ -208,7 +214,19 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
       if (st == n_super - 1 && threadIdx.x == 64) stamp(p, 4);
       tc_fence_after();
       const int valid = min(rem - t * BLOCK_M, BLOCK_M);               // rows of this sub-tile that exist
-      if (valid > 0) {                                                 // uniform over the sub-tile's four warps
+      if (valid > 0 && p.partial != nullptr) {                         // split-K: the raw accumulators of this K range, nothing else
+#pragma unroll 1
+        for (int c = 0; c < H / 32; ++c) {
+          float v[32];
+          tmem_ld32(lane_base + (uint32_t)(t * H + c * 32), v);
+          if (row_in_tile < valid) {
+            const int64_t row = row_begin + (int64_t)st * 2 * BLOCK_M + t * BLOCK_M + row_in_tile;
+            float4* d1 = reinterpret_cast<float4*>(p.partial + ((int64_t)blockIdx.y * p.rows + row) * H + c * 32);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) d1[j4] = make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+          }
+        }
+      } else if (valid > 0) {                                          // uniform over the sub-tile's four warps
         // hidden layer: ReLU(acc + b1) (mlp.py:14,18), rounded to tf32, written back over the accumulator
 #pragma unroll 1
         for (int c = 0; c < H / 32; ++c) {
@@ -263,6 +281,46 @@ node_encoder_tf32_kernel(const __grid_constant__ XMaps xmaps, const __grid_const
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
   }
   if (threadIdx.x == 0) stamp(p, 6);
+}
+
+
+// Second launch of the split-K form: h1 = tf32(ReLU(sum_s partial[s] + b1)) (the value layer 2 of the one-launch form consumes, and
+// what training keeps), h = ReLU(W2 h1 + b2) with W2 rounded to tf32 like there.  8 rows per 256-thread block; splits summed in order.
+template <int H>
+__global__ void __launch_bounds__(256) encoder_finish_kernel(const float* __restrict__ partial, int splits, int64_t rows,
+                                                             const float* __restrict__ b1, const float* __restrict__ W2,
+                                                             const float* __restrict__ b2, float* __restrict__ h1_out, float* __restrict__ h_out) {
+  __shared__ float s_w2[F_OUT][H + 1];
+  __shared__ float s_h1[8][H];
+  const int tid = threadIdx.x, lane = tid & 31, r = tid >> 5;
+  for (int i = tid; i < F_OUT * H; i += 256) s_w2[i / H][i % H] = tf32_rna(W2[i]);
+  const int64_t row = (int64_t)blockIdx.x * 8 + r;
+  if (row < rows) {
+    // every partial of the row's H / 32 column groups in flight at once (up to 16 splits x 4 groups of independent loads: one
+    // L2 round trip instead of one per split), then summed in split order
+    float t[H / 32][16];
+#pragma unroll
+    for (int c = 0; c < H / 32; ++c)
+#pragma unroll
+      for (int sp = 0; sp < 16; ++sp) t[c][sp] = sp < splits ? __ldg(partial + ((int64_t)sp * rows + row) * H + c * 32 + lane) : 0.f;
+#pragma unroll
+    for (int c = 0; c < H / 32; ++c) {
+      const int col = c * 32 + lane;
+      float a = 0.f;
+#pragma unroll
+      for (int sp = 0; sp < 16; ++sp) a += t[c][sp];          // the splits beyond `splits` add +0.0
+      const float v = tf32_rna(fmaxf(a + b1[col], 0.f));
+      s_h1[r][col] = v;
+      if (h1_out) h1_out[row * H + col] = v;
+    }
+  }
+  __syncthreads();
+  if (row < rows) {
+    float a = b2[lane];
+#pragma unroll 8
+    for (int k = 0; k < H; ++k) a = fmaf(s_h1[r][k], s_w2[lane][k], a);
+    h_out[row * F_OUT + lane] = fmaxf(a, 0.f);
+  }
 }
 
 }  // namespace enc
@@ -365,7 +423,57 @@ int launch_encoder(const float* x, const float* W1, const enc::Params& p0, cudaS
   return check_launch();
 }
 
+// Split-K form (see Params::partial): 128 rows per CTA x `splits` K ranges, then encoder_finish_kernel.
+template <int H>
+int launch_encoder_splitk(const float* x, const float* W1, const enc::Params& p0, int splits, float* partial, cudaStream_t st) {
+  enc::Params p = p0;
+  p.rows_per_cta = enc::BLOCK_M;
+  p.partial = partial;
+  p.kb_per_split = p.K / enc::BLOCK_K / splits;
+  const int gx = (int)ceil_div(p.rows, (int64_t)enc::BLOCK_M);
+  p.a_bytes = (uint32_t)enc::BLOCK_M * enc::BLOCK_K * 4;
+  const size_t stage = (size_t)p.a_bytes + (size_t)H * enc::BLOCK_K * 4;
+  const size_t fixed = 1024 + sizeof(float) * (H * enc::F_OUT + H + enc::F_OUT) + 8 * (2 * enc::MAX_STAGES + 4) + 32;
+  int stages = (int)((227 * 1024 - fixed) / stage);
+  if (stages > enc::MAX_STAGES) stages = enc::MAX_STAGES;
+  if (stages > p.kb_per_split) stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
+  if (stages < 2) return GNNCCA_ERR_UNSUPPORTED;
+  p.stages = stages;
+  const size_t smem = fixed + stage * stages;
+  enc::XMaps xm;
+  CUtensorMap mw;
+  for (int b = 0; b < 5; ++b)
+    if (!enc::make_map(&xm.m[b], x, p.rows, p.K, 8 << b)) return GNNCCA_ERR_LAUNCH;
+  xm.tail_rows = enc::BLOCK_M;
+  if (!enc::make_map(&xm.m[5], x, p.rows, p.K, xm.tail_rows)) return GNNCCA_ERR_LAUNCH;
+  if (!enc::make_map(&mw, W1, H, p.K, H)) return GNNCCA_ERR_LAUNCH;
+  auto kern = enc::node_encoder_tf32_kernel<H>;
+  int rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+  if (rc) return rc;
+  kern<<<dim3((unsigned)gx, (unsigned)splits), enc::NUM_THREADS, smem, st>>>(xm, mw, p);
+  // (launching this one as a programmatic dependent, with its own dependents released at once, measured SLOWER: cfg 1 59 us vs 52 us)
+  enc::encoder_finish_kernel<H><<<(unsigned)ceil_div(p.rows, (int64_t)8), 256, 0, st>>>(partial, splits, p.rows, p.b1, p.W2, p.b2, p.h1_out, p.h_out);
+  return check_launch(2);
+}
+
 }  // namespace
+
+// Number of K splits gnncca_node_encoder_ws uses for `rows` rows (1: the one-launch form).  Small inputs only: as many splits as
+// keep (row tiles x splits) within one wave of CTAs.
+extern "C" int32_t gnncca_node_encoder_splits(int64_t rows, int32_t in_dim) {
+  static const int enabled = [] { const char* e = getenv("GNNCCA_ENC_SPLITK"); return e ? atoi(e) : 1; }();
+  if (!enabled || rows <= 0 || in_dim % enc::BLOCK_K != 0) return 1;
+  const int64_t tiles = ceil_div(rows, (int64_t)enc::BLOCK_M);
+  const int kb = in_dim / enc::BLOCK_K;
+  int ks = 1;
+  while (ks < 16 && (int64_t)ks * 2 * tiles <= kNumSMs && kb % (ks * 2) == 0 && kb / (ks * 2) >= 2) ks *= 2;
+  return ks;
+}
+
+extern "C" int64_t gnncca_node_encoder_scratch_bytes(int64_t rows, int32_t in_dim, int32_t hidden) {
+  const int ks = gnncca_node_encoder_splits(rows, in_dim);
+  return ks > 1 ? (int64_t)ks * rows * hidden * (int64_t)sizeof(float) : 0;
+}
 
 // Fused two-layer node encoder on the tensor cores (see the header of this file).  Requirements: in_dim % 32 == 0,
 // hidden in {64, 128}, out_dim == 32, x and W1 16-byte aligned.
@@ -382,4 +490,20 @@ int gnncca_node_encoder_tf32(const float* x, const float* W1, const float* b1, c
     case 128: return launch_encoder<128>(x, W1, p, st);
     default: return GNNCCA_ERR_UNSUPPORTED;
   }
+}
+
+// The same with caller scratch: small inputs take the split-K form when the scratch holds its partial sums
+// (gnncca_node_encoder_scratch_bytes), everything else the one-launch form.
+int gnncca_node_encoder_tf32_ws(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
+                                int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* scratch, int64_t scratch_bytes,
+                                void* stream) {
+  const int ks = (hidden == 64 || hidden == 128) && out_dim == enc::F_OUT ? gnncca_node_encoder_splits(rows, in_dim) : 1;
+  if (ks <= 1 || !scratch || scratch_bytes < gnncca_node_encoder_scratch_bytes(rows, in_dim, hidden) || (((uintptr_t)scratch) & 15) != 0)
+    return gnncca_node_encoder_tf32(x, W1, b1, W2, b2, h1, h, rows, in_dim, hidden, out_dim, stream);
+  if (in_dim < enc::BLOCK_K) return GNNCCA_ERR_UNSUPPORTED;
+  if ((((uintptr_t)x | (uintptr_t)W1 | (uintptr_t)h | (uintptr_t)h1) & 15) != 0) return GNNCCA_ERR_BAD_ARG;
+  enc::Params p{};
+  p.b1 = b1; p.W2 = W2; p.b2 = b2; p.h_out = h; p.h1_out = h1; p.rows = rows; p.K = in_dim; p.H = hidden;
+  cudaStream_t st = (cudaStream_t)stream;
+  return hidden == 64 ? launch_encoder_splitk<64>(x, W1, p, ks, (float*)scratch, st) : launch_encoder_splitk<128>(x, W1, p, ks, (float*)scratch, st);
 }

@@ -11,10 +11,13 @@ extern "C" int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_
                                          const int64_t* graph_ptr, const int64_t* edge_ptr,
                                          int64_t n_nodes, int64_t n_edges, int64_t n_graphs,
                                          int32_t num_steps, int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges,
-                                         float* h_enc, float* logits, int32_t* flags, void* stream) {
+                                         float* h_enc, float* logits, int32_t* flags, void* enc_scratch, int64_t enc_scratch_bytes,
+                                         void* stream) {
   if (!cfg || !w || !x || !h_enc || !edge_index || !edge_ptr) return GNNCCA_ERR_BAD_ARG;
   if (n_nodes == 0 || n_graphs == 0) return GNNCCA_OK;
-  int rc = gnncca_node_encoder(x, enc_W1, enc_b1, enc_W2, enc_b2, h_enc, n_nodes, in_dim, hidden, cfg->f_node, GNNCCA_MATH_TF32, stream);
+  // small batches: the encoder's split-K form when the caller brought its scratch (gnncca_node_encoder_scratch_bytes)
+  int rc = gnncca_node_encoder_ws(x, enc_W1, enc_b1, enc_W2, enc_b2, nullptr, h_enc, n_nodes, in_dim, hidden, cfg->f_node, enc_scratch,
+                                  enc_scratch_bytes, stream);
   if (rc) return rc;
   gnncca::tl_launch_as_dependent = true;
   rc = gnncca_mp_fused_fwd(cfg, w, w_enc_edge, b_enc_edge, edge_in_dim, graph_ptr, n_graphs, edge_index, edge_ptr, nullptr, nullptr,

@@ -778,6 +778,20 @@ def node_encoder_fused_ok(mlp, inp) -> bool:
             and sp[1].out_dim == 32 and inp.data_ptr() % 16 == 0)
 
 
+_ENC_SCRATCH = {}
+
+
+def encoder_scratch_bytes(rows: int, in_dim: int, hidden: int) -> int:
+    """Bytes of scratch the node encoder's split-K form wants for ``rows`` rows (0: the one-launch form is the right one)."""
+    key = (int(rows), int(in_dim), int(hidden))
+    v = _ENC_SCRATCH.get(key)
+    if v is None:
+        if len(_ENC_SCRATCH) > 256:
+            _ENC_SCRATCH.clear()
+        v = _ENC_SCRATCH[key] = int(_lib.load().gnncca_node_encoder_scratch_bytes(*key))
+    return v
+
+
 def mlp_forward_nograd(mlp, inp, math, out=None):
     w0 = mlp.__dict__.get("_gnncca_w0")      # first-layer weight with the input's column normalisation folded in (MOTMPNet.forward)
     if math == _lib.MATH_TF32 and node_encoder_fused_ok(mlp, inp):
@@ -787,6 +801,9 @@ def mlp_forward_nograd(mlp, inp, math, out=None):
         l1, l2 = mlp.linear(0), mlp.linear(1)
         y = torch.empty((rows, l2.out_features), dtype=torch.float32, device=inp.device) if out is None else out
         assert y.is_contiguous() and y.shape == (rows, l2.out_features)
+        # (inference keeps the one-launch form at every size: for small batches the split-K form of gnncca_node_encoder_ws is 3x faster
+        # as a kernel, but the all-steps kernel that follows overlaps the one-launch encoder's tail as its programmatic dependent, and
+        # end to end the two measure the same (cfg 1: 52 us either way); the training forward, which has no such overlap, uses it)
         _lib.check(lib.gnncca_node_encoder(_lib.ptr(inp), _lib.ptr(l1.weight if w0 is None else w0), _lib.ptr(l1.bias), _lib.ptr(l2.weight), _lib.ptr(l2.bias),
                                            _lib.ptr(y), rows, l1.in_features, l1.out_features, l2.out_features, _lib.MATH_TF32,
                                            _stream()), "node_encoder")
@@ -835,7 +852,7 @@ class FastPath:
         l1, l2, le = enc_n.linear(0), enc_n.linear(1), enc_e.linear(0)
         self.prefix = (C.byref(self.sb.cfg), C.byref(self.sb.w), l1.weight.data_ptr(), l1.bias.data_ptr(), l2.weight.data_ptr(),
                        l2.bias.data_ptr(), l1.in_features, l1.out_features, le.weight.data_ptr(), le.bias.data_ptr(), self.fa)
-        self.in_dim = l1.in_features
+        self.in_dim, self.hidden = l1.in_features, l1.out_features
         self.device = l1.weight.device
         self.fn = _lib.load().gnncca_mpn_forward_frames
         # The kernel raises flags[2] when a frame breaks the trust contract (not closed / not source-major / larger than caps) and
@@ -868,10 +885,12 @@ class FastPath:
         self.verify()
         h = torch.empty((N, 32), dtype=torch.float32, device=self.device)
         logits = torch.empty((self.n_cls, E), dtype=torch.float32, device=self.device)
+        nb, scr = 0, None        # no encoder scratch: the one-launch form (see mlp_forward_nograd)
         w0 = model.encoder.node_mlp.__dict__.get("_gnncca_w0")
         prefix = self.prefix if w0 is None else self.prefix[:2] + (w0.data_ptr(),) + self.prefix[3:]
         rc = self.fn(*prefix, x.data_ptr(), edge_index.data_ptr(), edge_attr.data_ptr(), graph_ptr.data_ptr(), edge_ptr.data_ptr(),
-                     N, E, B, self.L, self.first, cap[0], cap[1], h.data_ptr(), logits.data_ptr(), self.flags.data_ptr(), _stream())
+                     N, E, B, self.L, self.first, cap[0], cap[1], h.data_ptr(), logits.data_ptr(), self.flags.data_ptr(),
+                     scr.data_ptr() if nb else None, nb, _stream())
         if rc:
             _lib.check(rc, "mpn_forward_frames")
         return [logits[i].view(E, 1) for i in range(self.n_cls)]

@@ -126,6 +126,19 @@ int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const 
 int gnncca_node_encoder_train(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1,
                               float* h, int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream);
 
+/* gnncca_node_encoder (h1 == NULL) / gnncca_node_encoder_train (h1 != NULL) with caller scratch, for SMALL inputs.  In the
+ * one-launch form every CTA streams all of W1 (in_dim x hidden floats from L2) whatever its row count: at a few thousand rows
+ * (cfg 1, cfg 3, a rank's share of cfg 5) those re-reads are most of the traffic and the launch takes ~30 us for 20 MB of x.  With
+ * scratch of gnncca_node_encoder_scratch_bytes() the contraction is split over K instead: 128-row tiles x gnncca_node_encoder_splits()
+ * K ranges in one wave of CTAs store raw partial sums, and a second launch adds them, applies bias / ReLU and layer 2 (h1 rounded to
+ * tf32 and W2 as tf32, as in the one-launch form).  scratch == NULL, too small, or an input large enough for the one-launch form
+ * (scratch_bytes() == 0): exactly gnncca_node_encoder.  The two forms sum the K products in different orders (fp32 rounding). */
+int32_t gnncca_node_encoder_splits(int64_t rows, int32_t in_dim);
+int64_t gnncca_node_encoder_scratch_bytes(int64_t rows, int32_t in_dim, int32_t hidden);
+int gnncca_node_encoder_ws(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1, float* h,
+                           int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* scratch, int64_t scratch_bytes,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * One message-passing step, models/mpn.py:32-54 (MetaLayer) = EdgeModel :67-69 + NodeModel :97-101
  * + the classifier of mpn.py:290-293, fused.
@@ -246,7 +259,8 @@ int gnncca_mp_fused_fwd(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w, co
  * (gnncca_node_encoder, tf32) + gnncca_mp_fused_fwd in its RAW form.  This is what the drop-in module calls
  * for batches whose frame structure is known (build_graph_batch): two launches, no CSR, nothing read back.
  *   enc_*: the node encoder's two Linear layers (in_dim -> hidden -> f_node); everything else as in
- *   gnncca_mp_fused_fwd.  h_enc [N][f_node] is caller-provided scratch for the encoded nodes. */
+ *   gnncca_mp_fused_fwd.  h_enc [N][f_node] is caller-provided scratch for the encoded nodes.   enc_scratch / enc_scratch_bytes: optional scratch of
+ * gnncca_node_encoder_scratch_bytes(n_nodes, in_dim, hidden) for the encoder's split-K form on small batches (NULL / 0: one-launch form). */
 int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_mp_weights* w,
                               const float* enc_W1, const float* enc_b1, const float* enc_W2, const float* enc_b2,
                               int32_t in_dim, int32_t hidden,
@@ -255,7 +269,8 @@ int gnncca_mpn_forward_frames(const gnncca_mp_cfg* cfg, const gnncca_mp_weights*
                               const int64_t* graph_ptr, const int64_t* edge_ptr,
                               int64_t n_nodes, int64_t n_edges, int64_t n_graphs,
                               int32_t num_steps, int32_t first_class_step, int32_t cap_nodes, int32_t cap_edges,
-                              float* h_enc, float* logits, int32_t* flags, void* stream);
+                              float* h_enc, float* logits, int32_t* flags, void* enc_scratch, int64_t enc_scratch_bytes,
+                              void* stream);
 
 /* Independent per-edge MLP chain (MLPGraphIndependent edge branch, mpn.py:128-142): encoder edge MLP
  * (4 -> 6 + ReLU) and, stand-alone, the classifier.  Up to 4 layers, widths <= 32.

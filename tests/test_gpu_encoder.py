@@ -90,3 +90,45 @@ def test_training_entry_also_writes_the_hidden_activations(rows, in_dim, hidden,
     with torch.no_grad():
         again = torch.relu(l2(got1))
     assert ((h.cpu() - again).abs() / (1 + again.abs())).max().item() <= TF32_TOL
+
+
+@pytest.mark.parametrize("rows,in_dim,hidden", [(2560, 2048, 128), (2304, 2048, 128), (8192, 2048, 128), (1000, 2048, 128), (130, 512, 64),
+                                                 (7, 2048, 128), (24576, 2048, 128)])
+def test_split_k_form_for_small_inputs_matches_the_reference_and_the_one_launch_form(rows, in_dim, hidden, cuda_device):
+    """gnncca_node_encoder_ws: small inputs contract K in several CTAs per row tile and finish in a second launch.  Against the torch
+    fp32 reference at the TF32 tolerance, against the one-launch form at fp32 rounding level (another summation order over K), h1
+    included; large inputs (scratch_bytes == 0) give the one-launch form's bits."""
+    lib_mod = importlib.import_module("gnn-cca_b200._lib")
+    lib = lib_mod.load()
+    g = torch.Generator().manual_seed(9)
+    x = torch.relu(torch.randn(rows, in_dim, generator=g))
+    torch.manual_seed(8)
+    l1, l2 = torch.nn.Linear(in_dim, hidden), torch.nn.Linear(hidden, 32)
+    with torch.no_grad():
+        ref1 = torch.relu(l1(x))
+        ref = torch.relu(l2(ref1))
+    dev = cuda_device
+    xd = x.to(dev)
+    W1, b1, W2, b2 = (t.detach().to(dev).contiguous() for t in (l1.weight, l1.bias, l2.weight, l2.bias))
+    st = torch.cuda.current_stream().cuda_stream
+    splits = int(lib.gnncca_node_encoder_splits(rows, in_dim))
+    nbytes = int(lib.gnncca_node_encoder_scratch_bytes(rows, in_dim, hidden))
+    assert (nbytes > 0) == (splits > 1) and (splits > 1) == (rows <= 9472)
+    scratch = torch.full((max(nbytes, 16) // 4,), float("nan"), device=dev)
+    outs = {}
+    for name, use in (("ws", True), ("one", False)):
+        h = torch.full((rows, 32), float("nan"), device=dev)
+        h1 = torch.full((rows, hidden), float("nan"), device=dev)
+        lib_mod.check(lib.gnncca_node_encoder_ws(xd.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(), h1.data_ptr(), h.data_ptr(),
+                                                 rows, in_dim, hidden, 32, scratch.data_ptr() if use else None, nbytes if use else 0, st), "node_encoder_ws")
+        torch.cuda.synchronize()
+        outs[name] = (h.cpu(), h1.cpu())
+    for h, h1 in outs.values():
+        assert torch.isfinite(h).all() and torch.isfinite(h1).all()
+        assert ((h - ref).abs() / (1 + ref.abs())).max().item() <= TF32_TOL
+        assert ((h1 - ref1).abs() / (1 + ref1.abs())).max().item() <= TF32_TOL
+    if splits > 1:      # the same products, summed in another order; h1 is rounded to tf32 (2^-11 relative) after the sum
+        assert ((outs["ws"][1] - outs["one"][1]).abs() / (1 + outs["one"][1].abs())).max().item() <= 6e-4
+        assert ((outs["ws"][0] - outs["one"][0]).abs() / (1 + outs["one"][0].abs())).max().item() <= 6e-4
+    else:
+        assert torch.equal(outs["ws"][0], outs["one"][0]) and torch.equal(outs["ws"][1], outs["one"][1])
