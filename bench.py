@@ -288,6 +288,11 @@ class Ctx:
             self.dist.destroy_process_group()
 
 
+def tail_steps(ms_per_step: float, seconds: float = 0.25) -> int:
+    """Steps that fill about ``seconds`` of device time: a COUNT derived from the rank-agreed step time, never a per-rank clock."""
+    return int(max(3, min(5000, seconds * 1e3 / max(ms_per_step, 1e-4))))
+
+
 def timed_windows(ctx: Ctx, step, steps: int, warmup: int, budget_s: float, extra_launches=lambda: 0):
     """W warm-up steps, then windows of EXACTLY ``steps`` steps, each bracketed by barrier + synchronize on both sides and timed
     with CUDA events on the launching stream; per window the MAX over ranks; the reported time is the MEDIAN window (min / max
@@ -597,11 +602,9 @@ def run_frames(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
             ctx.barrier()
             sampler.start()
         tw = timed_windows(ctx, step, steps, warmup, args.window_seconds)
-        if sampler:
-            t_end = time.perf_counter() + 0.25      # a representative amount of load for the sampler when the windows were short
-            i = 0
-            while time.perf_counter() < t_end:
-                step(i); i += 1
+        if sampler:      # a representative amount of load for the sampler when the windows were short (same count on every rank)
+            for i in range(tail_steps(tw["ms_per_step"])):
+                step(i)
             torch.cuda.synchronize()
         clocks = sampler.finish() if sampler else None
         path = getattr(model.last_plan, "last_path", None)
@@ -946,10 +949,13 @@ def run_giant(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
             sampler.start()
         tw = timed_windows(ctx, step, steps, warmup, args.window_seconds, extra_launches=(lambda: runner.launches_replayed) if runner is not None else (lambda: 0))
         if sampler:
-            t_end = time.perf_counter() + 0.25
-            while time.perf_counter() < t_end:
+            # More load for the clock sampler.  The step holds NCCL collectives: every rank must run it the SAME number of times (a
+            # loop bounded by each rank's own clock leaves the ranks that enqueued more forwards waiting in an all-gather for ever).
+            # tw is the max over ranks, identical everywhere.
+            for _ in range(tail_steps(tw["ms_per_step"])):
                 step(0)
             torch.cuda.synchronize()
+            ctx.barrier()
         clocks = sampler.finish() if sampler else None
         outs_local = [o.clone() for o in keep["out"]]
         mg.check_partition_flags(model)
@@ -1095,8 +1101,7 @@ def run_training(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
         sampler.start()
     tw = timed_windows(ctx, step, steps, warmup, args.window_seconds, extra_launches=lambda: gstep.launches_replayed)
     if sampler:
-        t_end = time.perf_counter() + 0.25
-        while time.perf_counter() < t_end:
+        for _ in range(tail_steps(tw["ms_per_step"])):
             step(0)
         torch.cuda.synchronize()
     clocks = sampler.finish() if sampler else None
