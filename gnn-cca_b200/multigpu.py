@@ -323,8 +323,9 @@ def check_partition_flags(model) -> None:
         raise ValueError("the local edge slice must be source-major")
 
 
-# Off by default: equivalent bit for bit on virtual ranks (tests/test_gpu_giant.py), but its first 8-GPU run under NCCL stalled in
-# the bench's stage-timing section (ranks waiting in different collectives) and was not debugged within the round's GPU budget.
+# Off by default: equivalent bit for bit on virtual ranks (tests/test_gpu_giant.py), not yet measured under NCCL -- its one 8-GPU run
+# ended in a stall that turned out to be the bench's own (a clock-bounded loop around steps holding all-gathers, fixed since), and the
+# round's GPU budget did not allow a second run.
 SHARD_ENCODER = os.environ.get("GNNCCA_SHARD_ENCODER", "0") == "1"
 
 
