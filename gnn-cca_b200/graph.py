@@ -211,6 +211,8 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
 
     fused_ok = not need_reid or (R % 4 == 0 and R <= 1024 and reid_embeds.data_ptr() % 16 == 0)
     if l2norm and B > 0 and N > 0 and fused_ok:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("build_graph_batch cannot be captured into a CUDA graph: the sizes of its outputs come from the device")
         reid = reid_embeds.contiguous()
         node = node_embeds.contiguous()
         rnorm_p = scratch_p + sizes[0] if need_reid else None

@@ -71,3 +71,14 @@ def test_frame_blocks_cover_the_batch():
         assert all(blocks[i][1] == blocks[i + 1][0] for i in range(len(blocks) - 1))
         assert all(b[1] > b[0] for b in blocks)
         assert all((b[2], b[3], b[4], b[5]) == (gp[b[0]], gp[b[1]], ep[b[0]], ep[b[1]]) for b in blocks)
+
+
+def test_tail_steps_is_a_count_every_rank_agrees_on():
+    """The extra load for the clock sampler is a NUMBER of steps derived from the rank-agreed step time: a loop bounded by each
+    rank's own clock around steps that hold NCCL collectives leaves some ranks waiting for peers (the 8-GPU stall of round 2)."""
+    import inspect
+    assert bench.tail_steps(0.715) == int(0.25 * 1e3 / 0.715)
+    assert bench.tail_steps(1e9) == 3 and bench.tail_steps(0.0) == 5000
+    for fn in (bench.run_giant, bench.run_frames, bench.run_training):
+        src = inspect.getsource(fn)
+        assert "while time.perf_counter()" not in src and "tail_steps(" in src
