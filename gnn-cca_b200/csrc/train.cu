@@ -1127,14 +1127,12 @@ extern "C" int gnncca_mp_frames_bwd(const gnncca_mp_cfg* cfg, const gnncca_mp_we
   if (any_cls && (cfg->cls_hidden != tr::HC || !w->w_c1 || !w->b_c1 || !w->w_c2)) return GNNCCA_ERR_UNSUPPORTED;
   p.ge_buf[0] = ge_a; p.ge_buf[1] = ge_b; p.ge0_acc = ge0_acc; p.gh0_acc = gh0_acc;
   p.max_n = max_frame_nodes; p.max_e = (max_frame_edges + 3) & ~3;
-  static bool s_attr[4] = {false, false, false, false};     // opt in to > 48 KB of dynamic shared memory, once per instantiation
   const int which = (cfg->reattach_edges ? 1 : 0) + (cfg->reattach_nodes ? 2 : 0);
   const void* fn = which == 0 ? (const void*)tr::frames_bwd_kernel<false, tr::FN> : which == 1 ? (const void*)tr::frames_bwd_kernel<true, tr::FN>
                  : which == 2 ? (const void*)tr::frames_bwd_kernel<false, 2 * tr::FN> : (const void*)tr::frames_bwd_kernel<true, 2 * tr::FN>;
-  if (!s_attr[which]) {
+  if (dyn_bytes > 48 * 1024) {       // opt in to the large dynamic shared memory (per device and function: set at every such launch)
     const cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, GNNCCA_FRAMES_BWD_SMEM_LIMIT);
     if (e != cudaSuccess) return check_cuda(e);
-    s_attr[which] = true;
   }
   void* args[] = {(void*)&p};
   const cudaError_t le = cudaLaunchKernel(fn, dim3((unsigned)n_graphs), dim3(tr::TBF), args, (size_t)dyn_bytes, (cudaStream_t)stream);
