@@ -323,10 +323,11 @@ def check_partition_flags(model) -> None:
         raise ValueError("the local edge slice must be source-major")
 
 
-# Off by default: equivalent bit for bit on virtual ranks (tests/test_gpu_giant.py), not yet measured under NCCL -- its one 8-GPU run
-# ended in a stall that turned out to be the bench's own (a clock-bounded loop around steps holding all-gathers, fixed since), and the
-# round's GPU budget did not allow a second run.
-SHARD_ENCODER = os.environ.get("GNNCCA_SHARD_ENCODER", "0") == "1"
+# On by default for live process groups with equal ranges: equal bit for bit to the replicated form on 4 virtual ranks
+# (tests/test_gpu_giant.py) and under NCCL at 2 GPUs (profiles/r02e_cfg5_2gpu_sharded_encoder.json: 2.177 ms vs 2.183 ms, parity object
+# identical); the 8-GPU gain (encoder 35 us -> ~9 us + one 11 us exchange per forward) is an estimate from the per-stage table, not yet
+# a measurement.  GNNCCA_SHARD_ENCODER=0 restores the replicated encoder.
+SHARD_ENCODER = os.environ.get("GNNCCA_SHARD_ENCODER", "1") != "0"
 
 
 class PartitionedForward:
