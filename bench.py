@@ -989,6 +989,8 @@ def run_giant(ctx: Ctx, name: str, steps: int, warmup: int, headline: bool):
     roofline = {"bound": "hbm", "kernel": dom, "peak": ctx.peak, "unit": "GB/s", "peak_source": ctx.peak_src,
                 "kernel_selection": "largest share of the step's device time", "kernels": per_kernel,
                 "stages_ms_max_over_ranks": {k: round(v, 5) for k, v in stage_max.items()},
+                "stages_note": "stage times come from eager launches of the partitioned forward with the REPLICATED encoder (multigpu.forward_edge_partitioned); "
+                               "the timed path replays one CUDA graph per rank and, for N > 1, encodes and projects the owned rows only plus one more exchange",
                 "exchange": {"ms_per_forward": exch_ms, "bytes_per_rank_per_exchange": (n1 - n0) * 32, "exchanges_per_forward": model.num_enc_steps - 1,
                              "collective": "NCCL all_gather_into_tensor (in place) of the owned rows of the target projection Q (N x 8 fp32 assembled on every rank; the node latents themselves never travel)" if ctx.world > 1 else "none (1 GPU)"},
                 "host_enqueue_ms_per_forward": statistics.median(host_s) * 1e3,

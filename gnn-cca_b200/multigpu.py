@@ -263,8 +263,6 @@ def edge_partitioned_steps(model, x: torch.Tensor, edge_index_local: torch.Tenso
         q_full = yield Q                            # the targets' projections of step 1 from their owners
         if q_full.data_ptr() != Q.data_ptr():
             Q.copy_(q_full)
-        if prof is not None:
-            prof.mark("exchange0")
     else:
         _lib.check(lib.gnncca_node_project(C.byref(sb.cfg), C.byref(sb.w), _lib.ptr(h0), _lib.ptr(h), N, _lib.ptr(P), _lib.ptr(Q), _lib.ptr(R),
                                            _stream()), "node_project")
