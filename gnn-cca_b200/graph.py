@@ -209,7 +209,8 @@ def build_graph_batch(graph_ptr: torch.Tensor, id_cam: torch.Tensor, ids: torch.
     need_reid = mode != "only_dist"
     x_kw, rnorm_p, join, pre_out, guess = {}, None, False, None, None
 
-    fused_ok = not need_reid or (R % 4 == 0 and R <= 1024 and reid_embeds.data_ptr() % 16 == 0)
+    # shapes the single prepare call takes (others: the separate launches below, same results)
+    fused_ok = N <= 65535 * 128 and (not need_reid or (R % 4 == 0 and R <= 1024 and reid_embeds.data_ptr() % 16 == 0))
     if l2norm and B > 0 and N > 0 and fused_ok:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("build_graph_batch cannot be captured into a CUDA graph: the sizes of its outputs come from the device")
