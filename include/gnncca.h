@@ -126,7 +126,8 @@ int gnncca_node_encoder(const float* x, const float* W1, const float* b1, const 
 int gnncca_node_encoder_train(const float* x, const float* W1, const float* b1, const float* W2, const float* b2, float* h1,
                               float* h, int64_t rows, int32_t in_dim, int32_t hidden, int32_t out_dim, void* stream);
 
-/* gnncca_node_encoder (h1 == NULL) / gnncca_node_encoder_train (h1 != NULL) with caller scratch, for SMALL inputs.  In the
+/* gnncca_node_encoder (h1 == NULL) / gnncca_node_encoder_train (h1 != NULL) -- the node branch of MLPGraphIndependent.forward,
+ * mpn.py:128-142 with mlp.py:12-23 -- with caller scratch, for SMALL inputs.  In the
  * one-launch form every CTA streams all of W1 (in_dim x hidden floats from L2) whatever its row count: at a few thousand rows
  * (cfg 1, cfg 3, a rank's share of cfg 5) those re-reads are most of the traffic and the launch takes ~30 us for 20 MB of x.  With
  * scratch of gnncca_node_encoder_scratch_bytes() the contraction is split over K instead: 128-row tiles x gnncca_node_encoder_splits()
